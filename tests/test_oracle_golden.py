@@ -1,0 +1,128 @@
+"""The CPU restatement (oracle/detbox_oracle.c + oracle/oracle.py) against the golden vectors
+that oracle/make_golden.py produced from the UNMODIFIED reference.  CPU only.
+
+Bars: bit-exact for IoU (f64), labels, keep indices, anchors; float32 box math and RoIAlign
+within rtol 1e-5 (+ atol 1e-6), the tolerance BASELINE.json's north_star states.
+"""
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+from util import assert_boxes_close
+
+RTOL, ATOL = 1e-5, 1e-6
+CPR = O.citypersons_retinanet_cfg()
+
+
+def test_base_anchors(golden):
+    g = golden("anchors")
+    for lvl in range(5):
+        np.testing.assert_array_equal(O.anchors(CPR.anchor_scales[lvl], CPR.anchor_ratios, 16), g["base_cpr_l%d" % lvl])
+    np.testing.assert_array_equal(O.anchors([2., 4., 8., 16., 32.], [0.5, 1, 2.0], 16), g["base_default"])
+    np.testing.assert_array_equal(O.anchors([1.5, 3], [0.5, 1, 2.0, 3.0], 15), g["base_odd15"])
+    # SURVEY KAT-1
+    np.testing.assert_allclose(g["base_cpr_l0"][1], [-20.91999984, -20.91999984, 20.91999984, 20.91999984], atol=1e-8)
+
+
+def test_anchor_pyramid(golden):
+    g = golden("anchors")
+    pyr = O.anchor_pyramid(CPR.strides, 1024, 2048, CPR.anchor_scales, CPR.anchor_ratios, 16)
+    assert tuple(g["cpr_pyramid_shape"]) == pyr.shape == (261888, 4)
+    np.testing.assert_array_equal(pyr[g["cpr_pyramid_rows_idx"]], g["cpr_pyramid_rows"])
+    np.testing.assert_array_equal(pyr.sum(0), g["cpr_pyramid_colsum"])
+    np.testing.assert_array_equal(pyr[6], [-8.5, -16.5, 24.5, 16.5])
+    small = O.anchor_pyramid([4, 8, 16], 64, 96, [[2, 3], [4, 6], [8, 12]], [0.5, 1, 2.0], 16, [[0.0, 0.0], [0.5, 0.25]])
+    np.testing.assert_array_equal(small, g["small_pyramid"])
+    np.testing.assert_array_equal(O.anchor_one_plane(5, 7, 8, [2., 4.], [0.5, 2.0], 16, [[0, 0], [0.5, 0]]), g["plane_shifted"])
+
+
+def test_iou(golden):
+    g = golden("iou")
+    np.testing.assert_array_equal(O.bbox_overlaps(g["fix_anchors"], g["fix_gt"][:, :4]), g["fix_ov"])
+    np.testing.assert_array_equal(O.bbox_overlaps(g["boxes"], g["query"]), g["ov"])
+    np.testing.assert_array_equal(O.bbox_intersections(g["boxes"], g["query"]), g["inter"])
+    np.testing.assert_array_equal(O.bbox_exclude_ignored_areas(g["boxes"], g["query"], 0.2), g["excl"])
+    np.testing.assert_array_equal(O.bbox_overlaps(g["boxes_int"], g["query_int"]), g["ov_int"])
+    # SURVEY KAT-2
+    assert abs(g["fix_ov"][0, 0] - 0.65389) < 1e-5 and abs(g["fix_ov"][5, 2] - 0.826446) < 1e-6
+
+
+def test_transform(golden):
+    g = golden("transform")
+    np.testing.assert_allclose(O.bbox_transform(g["anchors"], g["gt"]), g["enc"], rtol=RTOL, atol=ATOL)
+    assert_boxes_close(O.bbox_transform_inv(g["anchors"], g["deltas"]), g["dec"])
+    assert_boxes_close(O.bbox_transform_inv(g["anchors"], g["deltas"], im_shape=(1024, 2048)), g["dec_clip"])
+    np.testing.assert_allclose(O.bbox_transform(g["anchors"], g["gt"], "linear"), g["enc_linear"], rtol=RTOL, atol=ATOL)
+    assert_boxes_close(O.bbox_transform_inv(g["anchors"], g["deltas"], "linear"), g["dec_linear"])
+
+
+CASES = ["fixture", "small_a", "small_noclobber", "small_zero_col", "small_zero_col_noclobber", "small_nogt", "small_dup_gt"]
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_anchor_target(golden, name):
+    g = golden("anchor_target")
+    bg, fg, clob = g[name + "_cfg"]
+    cfg = O.Cfg(rpn_bg_threshold=float(bg), rpn_fg_threshold=float(fg), rpn_clobber_positives=bool(clob))
+    lab, lw, bt, bw = O.anchor_encode(g[name + "_gt"], g[name + "_anchors"], cfg)
+    np.testing.assert_array_equal(lab, g[name + "_labels"])
+    np.testing.assert_array_equal(lw, g[name + "_label_weights"])
+    np.testing.assert_array_equal(bw, g[name + "_bbox_inside_weights"])
+    np.testing.assert_allclose(bt, g[name + "_bbox_targets"], rtol=RTOL, atol=ATOL)
+
+
+def test_anchor_target_kat3(golden):
+    g = golden("anchor_target")
+    np.testing.assert_array_equal(g["fixture_labels"], [2, 0, 0, 0, 0, -1, -1, 0, 0, 0])
+    np.testing.assert_allclose(g["fixture_bbox_targets"][0], [1.190476, 1.129032, 0.667657, 0.461867], atol=1e-5)
+
+
+def test_anchor_target_cpr_image(golden):
+    g = golden("anchor_target")
+    pyr = O.anchor_pyramid(CPR.strides, 1024, 2048, CPR.anchor_scales, CPR.anchor_ratios, 16).astype(np.float32)
+    lab, lw, bt, bw = O.anchor_encode(g["cpr_gt"], pyr, CPR)
+    ref = np.zeros_like(lab)
+    ref[g["cpr_labels_nz_idx"]] = g["cpr_labels_nz_val"]
+    np.testing.assert_array_equal(lab, ref)
+    np.testing.assert_array_equal([(lab >= 1).sum(), (lab == 0).sum(), (lab < 0).sum()], g["cpr_counts"])
+    np.testing.assert_array_equal(lw[lab == 0][:1], g["cpr_bg_weight"])
+    np.testing.assert_allclose(bt[g["cpr_rows_idx"]], g["cpr_bbox_targets_rows"], rtol=RTOL, atol=ATOL)
+    np.testing.assert_array_equal(bw.sum(0), g["cpr_bbox_inside_weights_sum"])
+
+
+@pytest.mark.parametrize("name", ["rand1k", "rand3k", "clustered2k", "intgrid600"])
+@pytest.mark.parametrize("thr", [0.5, 0.3, 0.7])
+def test_nms(golden, name, thr):
+    g = golden("nms")
+    d = g[name]
+    np.testing.assert_array_equal(O.nms(d[:, :4], d[:, 4], thr, O.NMS_GE_F64), g["%s_keep_ge_%g" % (name, thr)])
+    np.testing.assert_array_equal(O.nms(d[:, :4], d[:, 4], thr, O.NMS_GT_F32), g["%s_keep_gt_%g" % (name, thr)])
+    np.testing.assert_array_equal(O.nms(d[:, :4], d[:, 4], thr, O.NMS_GE_F64), g["%s_keep_cynms_%g" % (name, thr)])
+
+
+def test_nms_comparators_differ_on_integer_grid(golden):
+    g = golden("nms")
+    assert len(g["intgrid600_keep_ge_0.5"]) != len(g["intgrid600_keep_gt_0.5"])
+
+
+def test_roialign_crop_and_resize(golden):
+    g = golden("roialign")
+    img, boxes, ind = g["image"], g["boxes"], g["box_ind"]
+    np.testing.assert_array_equal(O.crop_and_resize_fwd(img, boxes, ind, 0.0, 7, 7), g["crops7"])
+    np.testing.assert_array_equal(O.crop_and_resize_fwd(img, boxes, ind, 0.0, 3, 5), g["crops3x5"])
+    np.testing.assert_array_equal(O.crop_and_resize_fwd(img, boxes, ind, 0.0, 1, 1), g["crops1"])
+    np.testing.assert_array_equal(O.crop_and_resize_bwd(g["grad"], boxes, ind, img.shape), g["grad_image7"])
+
+
+def test_roialign_kat5(golden):
+    g = golden("roialign")
+    ramp = np.arange(16, dtype=np.float32).reshape(1, 1, 4, 4)
+    rois = np.asarray([[0, 0, 0, 3, 3]], np.float32)
+    boxes, ind = O.tf_boxes(rois, 1.0, 2, 2, 4, 4)
+    np.testing.assert_array_equal(boxes, g["kat5_box"])
+    out = O.roi_align_tf_fwd(ramp, rois, 1.0, 2, 2)
+    np.testing.assert_array_equal(out, g["kat5_fwd"])
+    np.testing.assert_allclose(out.ravel(), [1.25, 2.75, 7.25, 8.75], atol=1e-6)
+    gi = O.roi_align_tf_bwd(np.ones((1, 1, 2, 2), np.float32), rois, 1.0, ramp.shape)
+    np.testing.assert_array_equal(gi, g["kat5_bwd"])
+    np.testing.assert_allclose(gi[0, 0, 0], [.5625, .375, .5625, 0], atol=1e-6)
