@@ -1,0 +1,410 @@
+// nms.cu — greedy non-maximum suppression entirely on the device.
+// Replaces: libs/nms/gpu_nms.pyx + nms_kernel.cu:46-155 (bitmask kernel + HOST scan + per-call
+// cudaMalloc/Memcpy), libs/nms/cpu_nms.pyx:17-68, libs/layers/box.py:148-173 + layers/nms/src/*,
+// and — through segments — the per-image Python loop of libs/nets/model.py:343-355.
+//
+// Pipeline (one stream, no host round trip, no allocation):
+//   1. keys = ~ordered(score), stable radix sort (sort.cu) -> score-descending order, ties by index;
+//      with segments one more stable pass on the segment id -> segment-major order.
+//   2. gather boxes into sorted float4 rows (+ segment id).
+//   3. bitmask: 64x64 tiles of the UPPER triangle only (the reference computes the full square,
+//      nms_kernel.cu:51); column boxes and their areas staged in shared memory; one thread
+//      produces one 64-bit word.  IoU arithmetic is the reference's float32 sequence
+//      (cpu_nms.pyx:57-64 == nms_kernel.cu:24-32): (area_i + area_j) - inter, IEEE division,
+//      --fmad=false.  The division is skipped when inter == 0 and thr > 0 (the quotient is 0
+//      or NaN, neither can suppress) — most pairs in the sparse regime.
+//   4. greedy scan, one block per segment: walk the 64-row tiles in order; warp 0 resolves the
+//      diagonal word chain with shuffles (64 dependent steps of register work), then all threads
+//      OR the mask rows of the newly kept boxes into the shared-memory `removed` bitset.  Exact
+//      greedy order => exact keep indices.
+//   5. ordered compaction of the kept bits into original indices + per-segment counts.
+#include <mutex>
+#include "sort.cuh"
+
+using namespace detbox;
+typedef unsigned long long u64;
+
+namespace {
+
+struct NmsCmp { int mode; float thr_f; double thr_d; bool nonpos; };
+
+__device__ __forceinline__ bool suppresses(const NmsCmp &c, float ovr) {
+    if (c.mode == DETBOX_NMS_GE_F64) return (double)ovr >= c.thr_d;      // cpu_nms.pyx:65
+    if (c.mode == DETBOX_NMS_GE_F32) return ovr >= c.thr_f;             // nms_cpu.c:76
+    return ovr > c.thr_f;                                               // nms_kernel.cu:83
+}
+
+__global__ void __launch_bounds__(256)
+gather_kernel(const float *__restrict__ boxes, int stride, const uint32_t *__restrict__ order, long n,
+              const int32_t *__restrict__ seg_ids, float4 *__restrict__ sorted, int32_t *__restrict__ seg_sorted)
+{
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+        const uint32_t o = order ? order[i] : (uint32_t)i;
+        const float *b = boxes + (size_t)o * stride;
+        sorted[i] = make_float4(b[0], b[1], b[2], b[3]);
+        if (seg_sorted) seg_sorted[i] = seg_ids[o];
+    }
+}
+
+// segment sizes -> offsets in the (segment-major) processing order
+__global__ void __launch_bounds__(256)
+seg_count_kernel(const int32_t *__restrict__ seg_ids, long n, int n_seg, int32_t *__restrict__ seg_off)
+{
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+        const int s = seg_ids[i];
+        if (s >= 0 && s < n_seg) atomicAdd(&seg_off[s + 1], 1);
+    }
+}
+__global__ void seg_scan_kernel(int32_t *seg_off, int n_seg)
+{
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        int run = 0;
+        for (int s = 0; s <= n_seg; ++s) { run += seg_off[s]; seg_off[s] = run; }
+    }
+}
+
+constexpr int MASK_CT = 4;     // column tiles per block
+
+__global__ void __launch_bounds__(64 * MASK_CT)
+mask_kernel(const float4 *__restrict__ boxes, const int32_t *__restrict__ seg, int n, int ncol,
+            NmsCmp cmp, u64 *__restrict__ mask)
+{
+    const int rt = blockIdx.y;
+    const int cg = blockIdx.x;
+    if ((cg + 1) * MASK_CT <= rt) return;                      // strictly below the diagonal
+    __shared__ float4 cb[64 * MASK_CT];
+    __shared__ float carea[64 * MASK_CT];
+    __shared__ int cseg[64 * MASK_CT];
+    const int tid = threadIdx.x;
+    const int c0 = cg * MASK_CT * 64;
+    {
+        const int c = c0 + tid;
+        if (c < n) {
+            const float4 b = boxes[c];
+            cb[tid] = b;
+            carea[tid] = (b.z - b.x + 1) * (b.w - b.y + 1);    // cpu_nms.pyx:24
+            cseg[tid] = seg ? seg[c] : 0;
+        }
+    }
+    __syncthreads();
+    const int r = rt * 64 + (tid & 63);
+    const int ct = cg * MASK_CT + (tid >> 6);                  // this thread's column tile
+    if (r >= n || ct < rt || ct >= ncol) return;
+    if (seg) {                                                 // tiles that cannot share a segment
+        const int last_row = min(n, rt * 64 + 64) - 1;
+        if (seg[last_row] < cseg[(tid >> 6) * 64]) return;     // never read by the scan (see header)
+    }
+    const float4 a = boxes[r];
+    const float aarea = (a.z - a.x + 1) * (a.w - a.y + 1);
+    const int aseg = seg ? seg[r] : 0;
+    const int cbase = (tid >> 6) * 64;
+    const int csize = min(64, n - ct * 64);
+    const int start = (ct == rt) ? (tid & 63) + 1 : 0;         // nms_kernel.cu:76-78
+    u64 word = 0;
+    for (int i = start; i < csize; ++i) {
+        const float4 b = cb[cbase + i];
+        const float xx1 = fmaxf(a.x, b.x), yy1 = fmaxf(a.y, b.y);
+        const float xx2 = fminf(a.z, b.z), yy2 = fminf(a.w, b.w);
+        const float w = fmaxf(0.0f, xx2 - xx1 + 1), h = fmaxf(0.0f, yy2 - yy1 + 1);
+        const float inter = w * h;
+        if (inter > 0.0f || cmp.nonpos) {
+            const float ovr = inter / (aarea + carea[cbase + i] - inter);
+            if (suppresses(cmp, ovr) && aseg == cseg[cbase + i]) word |= 1ull << i;
+        }
+    }
+    mask[(size_t)r * ncol + ct] = word;
+}
+
+__device__ __forceinline__ u64 shfl64(u64 v, int src) {
+    const unsigned lo = __shfl_sync(0xffffffffu, (unsigned)v, src);
+    const unsigned hi = __shfl_sync(0xffffffffu, (unsigned)(v >> 32), src);
+    return ((u64)hi << 32) | lo;
+}
+
+__global__ void __launch_bounds__(1024)
+scan_kernel(const u64 *__restrict__ mask, int n, int ncol, const int32_t *__restrict__ seg_off, u64 *__restrict__ kept)
+{
+    extern __shared__ u64 removed[];
+    __shared__ u64 s_kept;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int s0 = seg_off ? seg_off[blockIdx.x] : 0;
+    const int s1 = seg_off ? seg_off[blockIdx.x + 1] : n;
+    if (s1 <= s0) return;
+    const int t0 = s0 >> 6, t1 = (s1 - 1) >> 6;
+    for (int i = tid; i <= t1 - t0; i += blockDim.x) removed[i] = 0;
+    __syncthreads();
+    for (int t = t0; t <= t1; ++t) {
+        const int lo = max(s0, t * 64) - t * 64, hi = min(s1, t * 64 + 64) - t * 64;   // rows [lo,hi) of the tile
+        if (tid < 32) {
+            const int ra = lane, rb = lane + 32;
+            const u64 d0 = (ra >= lo && ra < hi) ? mask[(size_t)(t * 64 + ra) * ncol + t] : 0ull;
+            const u64 d1 = (rb >= lo && rb < hi) ? mask[(size_t)(t * 64 + rb) * ncol + t] : 0ull;
+            u64 cur = removed[t - t0];
+            u64 kw = 0;
+#pragma unroll
+            for (int i = 0; i < 64; ++i) {
+                const u64 wd = shfl64(i < 32 ? d0 : d1, i & 31);
+                if (i >= lo && i < hi && !((cur >> i) & 1ull)) { kw |= 1ull << i; cur |= wd; }
+            }
+            if (lane == 0) { s_kept = kw; if (kw) atomicOr(&kept[t], kw); }
+        }
+        __syncthreads();
+        const u64 kw = s_kept;
+        if (kw) {
+            for (int j = t + 1 + tid; j <= t1; j += blockDim.x) {
+                u64 acc = 0, k = kw;
+                while (k) {
+                    const int i = __ffsll((long long)k) - 1;
+                    k &= k - 1;
+                    acc |= mask[(size_t)(t * 64 + i) * ncol + j];
+                }
+                removed[j - t0] |= acc;
+            }
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(1024)
+compact_kernel(const u64 *__restrict__ kept, int n, int ncol, const uint32_t *__restrict__ order,
+               const int32_t *__restrict__ seg_sorted, int n_seg, int64_t *__restrict__ keep, int32_t *__restrict__ n_keep)
+{
+    __shared__ int warp_sum[32];
+    __shared__ int running;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    if (tid == 0) running = 0;
+    __syncthreads();
+    for (int base = 0; base < ncol; base += 1024) {
+        const int wi = base + tid;
+        u64 word = wi < ncol ? kept[wi] : 0ull;
+        const int c = __popcll(word);
+        int incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+        if (lane == 31) warp_sum[w] = incl;
+        __syncthreads();
+        if (w == 0) {
+            const int v = warp_sum[lane]; int iv = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, iv, o); if (lane >= o) iv += t; }
+            warp_sum[lane] = iv - v;
+        }
+        __syncthreads();
+        int pos = running + warp_sum[w] + incl - c;
+        while (word) {
+            const int bit = __ffsll((long long)word) - 1;
+            word &= word - 1;
+            const int sp = wi * 64 + bit;
+            keep[pos++] = (int64_t)(order ? order[sp] : (uint32_t)sp);
+            if (n_seg > 1) atomicAdd(&n_keep[seg_sorted[sp]], 1);
+        }
+        __syncthreads();
+        if (tid == 1023) running = pos;          // last thread's end == running + block total
+        __syncthreads();
+    }
+    if (tid == 0) { n_keep[n_seg] = running; if (n_seg == 1) n_keep[0] = running; }
+}
+
+struct NmsBuffers {
+    uint32_t *ka, *kb, *va, *vb, *counts;
+    float4 *sorted; int32_t *seg_sorted, *seg_off; u64 *mask, *kept;
+    size_t total;
+};
+
+NmsBuffers carve_nms(void *ws, long n, int n_seg) {
+    Carver cv(ws);
+    NmsBuffers b;
+    const long ncol = (n + 63) / 64;
+    b.ka = cv.take<uint32_t>(n); b.kb = cv.take<uint32_t>(n);
+    b.va = cv.take<uint32_t>(n); b.vb = cv.take<uint32_t>(n);
+    b.counts = cv.take<uint32_t>(sort_counts_bytes(n) / 4);
+    b.sorted = cv.take<float4>(n);
+    b.seg_sorted = cv.take<int32_t>(n_seg > 1 ? n : 1);
+    b.seg_off = cv.take<int32_t>(n_seg + 2);
+    b.kept = cv.take<u64>(ncol);
+    b.mask = cv.take<u64>((size_t)n * ncol);
+    b.total = cv.off;
+    return b;
+}
+
+NmsCmp make_cmp(double thresh, int mode) {
+    NmsCmp c; c.mode = mode; c.thr_d = thresh; c.thr_f = (float)thresh;
+    c.nonpos = (mode == DETBOX_NMS_GE_F64) ? !(thresh > 0.0) : !(c.thr_f > 0.0f);
+    return c;
+}
+
+// mask + scan + compact over boxes that are already gathered in processing order
+int nms_sorted(const NmsBuffers &b, const uint32_t *order, long n, int n_seg,
+               NmsCmp cmp, int64_t *keep, int32_t *n_keep, cudaStream_t st)
+{
+    const int32_t *seg_off = b.seg_off;
+    const int ncol = (int)((n + 63) / 64);
+    const int32_t *seg_sorted = n_seg > 1 ? b.seg_sorted : nullptr;
+    DETBOX_CUDA_TRY(cudaMemsetAsync(b.kept, 0, (size_t)ncol * sizeof(u64), st));
+    DETBOX_CUDA_TRY(cudaMemsetAsync(n_keep, 0, (size_t)(n_seg + 1) * sizeof(int32_t), st));
+    dim3 grid((unsigned)((ncol + MASK_CT - 1) / MASK_CT), (unsigned)ncol);
+    mask_kernel<<<grid, 64 * MASK_CT, 0, st>>>(b.sorted, seg_sorted, (int)n, ncol, cmp, b.mask);
+    DETBOX_LAUNCH_CHECK();
+    const size_t smem = (size_t)ncol * sizeof(u64);
+    if (smem > 200 * 1024) return DETBOX_ERR_UNSUPPORTED;
+    if (smem > 40 * 1024)
+        DETBOX_CUDA_TRY(cudaFuncSetAttribute(scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    scan_kernel<<<n_seg, 1024, smem, st>>>(b.mask, (int)n, ncol, n_seg > 1 ? seg_off : nullptr, b.kept);
+    DETBOX_LAUNCH_CHECK();
+    compact_kernel<<<1, 1024, 0, st>>>(b.kept, (int)n, ncol, order, seg_sorted, n_seg, keep, n_keep);
+    DETBOX_LAUNCH_CHECK();
+    return DETBOX_OK;
+}
+
+}  // namespace
+
+extern "C" size_t detbox_nms_workspace_bytes(long n, int n_seg)
+{
+    if (n <= 0) return 256;
+    return carve_nms(nullptr, n, n_seg > 1 ? n_seg : 1).total;
+}
+
+extern "C" int detbox_nms(const float *boxes, int box_stride, const float *scores, long n,
+                          const int32_t *seg_ids, int n_seg, double thresh, int cmp_mode,
+                          int64_t *keep, int32_t *n_keep, void *ws, size_t ws_bytes, void *stream)
+{
+    if (n < 0 || box_stride < 4 || cmp_mode < 0 || cmp_mode > 2 || !n_keep) return DETBOX_ERR_INVALID;
+    if (!seg_ids || n_seg <= 1) { n_seg = 1; seg_ids = nullptr; }
+    cudaStream_t st = as_stream(stream);
+    if (n == 0) { DETBOX_CUDA_TRY(cudaMemsetAsync(n_keep, 0, (size_t)(n_seg + 1) * sizeof(int32_t), st)); return DETBOX_OK; }
+    if (n >= (1L << 31) - 64) return DETBOX_ERR_UNSUPPORTED;
+    if (!boxes || !scores || !keep) return DETBOX_ERR_INVALID;
+    if (!ws || ws_bytes < detbox_nms_workspace_bytes(n, n_seg)) return DETBOX_ERR_WORKSPACE;
+    NmsBuffers b = carve_nms(ws, n, n_seg);
+    int rc = make_score_keys(scores, n, b.ka, b.va, st);
+    if (rc != DETBOX_OK) return rc;
+    rc = radix_sort_pairs(b.ka, b.va, b.kb, b.vb, n, b.counts, st);
+    if (rc != DETBOX_OK) return rc;
+    uint32_t *order = b.va;
+    long gb = (n + 255) / 256; if (gb > kNumSMs * 8) gb = kNumSMs * 8;
+    if (n_seg > 1) {                              // stable grouping by segment: 1 pass per 8 bits of id
+        DETBOX_CUDA_TRY(cudaMemsetAsync(b.seg_off, 0, (size_t)(n_seg + 2) * sizeof(int32_t), st));
+        seg_count_kernel<<<(unsigned)gb, 256, 0, st>>>(seg_ids, n, n_seg, b.seg_off);
+        DETBOX_LAUNCH_CHECK();
+        seg_scan_kernel<<<1, 32, 0, st>>>(b.seg_off, n_seg);
+        DETBOX_LAUNCH_CHECK();
+        uint32_t *ki = b.ka, *vi = b.va, *ko = b.kb, *vo = b.vb;
+        for (int shift = 0; (n_seg - 1) >> shift; shift += 8) {
+            DigitSrc d{2, shift, 1u, seg_ids};
+            rc = radix_pass(ki, vi, ko, vo, n, d, b.counts, st);
+            if (rc != DETBOX_OK) return rc;
+            uint32_t *t = ki; ki = ko; ko = t; t = vi; vi = vo; vo = t;
+        }
+        order = vi;
+    }
+    gather_kernel<<<(unsigned)gb, 256, 0, st>>>(boxes, box_stride, order, n, seg_ids, b.sorted,
+                                               n_seg > 1 ? b.seg_sorted : nullptr);
+    DETBOX_LAUNCH_CHECK();
+    return nms_sorted(b, order, n, n_seg, make_cmp(thresh, cmp_mode), keep, n_keep, st);
+}
+
+// ------------------------------------------------------------------------------------------------
+// host-buffer entry points
+// ------------------------------------------------------------------------------------------------
+namespace {
+struct Scratch { void *ptr = nullptr; size_t size = 0; };
+std::mutex g_mu;
+Scratch g_scratch[64];
+
+int get_scratch(int dev, size_t bytes, void **out) {
+    if (dev < 0 || dev >= 64) return DETBOX_ERR_INVALID;
+    Scratch &s = g_scratch[dev];
+    if (s.size < bytes) {
+        if (s.ptr) cudaFree(s.ptr);
+        s.ptr = nullptr; s.size = 0;
+        const size_t want = bytes + bytes / 4;
+        DETBOX_CUDA_TRY(cudaMalloc(&s.ptr, want));
+        s.size = want;
+    }
+    *out = s.ptr;
+    return DETBOX_OK;
+}
+}  // namespace
+
+namespace detbox {
+int host_scratch(int dev, size_t bytes, void **out) { return get_scratch(dev, bytes, out); }
+std::mutex &host_mutex() { return g_mu; }
+}
+
+static int nms_host_impl(const float *dets, int n, int dim, bool presorted, double thresh, int cmp_mode,
+                         int *keep_out, int *num_out, int device_id)
+{
+    if (n < 0 || dim < 4 + (presorted ? 0 : 1) || !num_out) return DETBOX_ERR_INVALID;
+    *num_out = 0;
+    if (n == 0) return DETBOX_OK;
+    if (!dets || !keep_out) return DETBOX_ERR_INVALID;
+    std::lock_guard<std::mutex> lock(g_mu);
+    int cur = 0;
+    DETBOX_CUDA_TRY(cudaGetDevice(&cur));
+    if (cur != device_id) DETBOX_CUDA_TRY(cudaSetDevice(device_id));
+    const size_t in_bytes = align_up((size_t)n * dim * sizeof(float));
+    const size_t sc_bytes = align_up((size_t)n * sizeof(float));
+    const size_t keep_bytes = align_up((size_t)n * sizeof(int64_t));
+    const size_t ws_bytes = detbox_nms_workspace_bytes(n, 1);
+    void *base = nullptr;
+    int rc = get_scratch(device_id, in_bytes + sc_bytes + keep_bytes + 256 + ws_bytes, &base);
+    if (rc == DETBOX_OK) {
+        char *p = (char *)base;
+        float *d_in = (float *)p; p += in_bytes;
+        float *d_sc = (float *)p; p += sc_bytes;
+        int64_t *d_keep = (int64_t *)p; p += keep_bytes;
+        int32_t *d_nk = (int32_t *)p; p += 256;
+        void *ws = p;
+        cudaStream_t st = 0;
+        auto body = [&]() -> int {
+            DETBOX_CUDA_TRY(cudaMemcpyAsync(d_in, dets, (size_t)n * dim * sizeof(float), cudaMemcpyHostToDevice, st));
+            if (presorted) {
+                NmsBuffers b = carve_nms(ws, n, 1);
+                long gb = (n + 255) / 256; if (gb > kNumSMs * 8) gb = kNumSMs * 8;
+                gather_kernel<<<(unsigned)gb, 256, 0, st>>>(d_in, dim, nullptr, n, nullptr, b.sorted, nullptr);
+                DETBOX_LAUNCH_CHECK();
+                int r = nms_sorted(b, nullptr, n, 1, make_cmp(thresh, cmp_mode), d_keep, d_nk, st);
+                if (r != DETBOX_OK) return r;
+            } else {
+                DETBOX_CUDA_TRY(cudaMemcpy2DAsync(d_sc, sizeof(float), d_in + 4, (size_t)dim * sizeof(float),
+                                                  sizeof(float), n, cudaMemcpyDeviceToDevice, st));
+                int r = detbox_nms(d_in, dim, d_sc, n, nullptr, 1, thresh, cmp_mode, d_keep, d_nk, ws, ws_bytes, st);
+                if (r != DETBOX_OK) return r;
+            }
+            int32_t nk[2] = {0, 0};
+            DETBOX_CUDA_TRY(cudaMemcpyAsync(nk, d_nk, sizeof(nk), cudaMemcpyDeviceToHost, st));
+            DETBOX_CUDA_TRY(cudaStreamSynchronize(st));
+            if (nk[0] > 0) {
+                int64_t *tmp = (int64_t *)malloc((size_t)nk[0] * sizeof(int64_t));
+                if (!tmp) return DETBOX_ERR_INVALID;
+                cudaError_t e = cudaMemcpy(tmp, d_keep, (size_t)nk[0] * sizeof(int64_t), cudaMemcpyDeviceToHost);
+                if (e == cudaSuccess) for (int i = 0; i < nk[0]; ++i) keep_out[i] = (int)tmp[i];
+                free(tmp);
+                DETBOX_CUDA_TRY(e);
+            }
+            *num_out = nk[0];
+            return DETBOX_OK;
+        };
+        rc = body();
+    }
+    if (cur != device_id) cudaSetDevice(cur);
+    return rc;
+}
+
+// The reference's FFI symbol (libs/nms/gpu_nms.hpp:1-2).  Errors cannot be returned through this
+// signature; like the reference (CUDA_CHECK only prints, nms_kernel.cu:12-19) we report zero keeps,
+// and detbox_last_cuda_error() tells why.
+extern "C" void _nms(int *keep_out, int *num_out, const float *boxes_host, int boxes_num, int boxes_dim,
+                     float nms_overlap_thresh, int device_id)
+{
+    int n = 0;
+    const int rc = nms_host_impl(boxes_host, boxes_num, boxes_dim, true, (double)nms_overlap_thresh,
+                                 DETBOX_NMS_GT_F32, keep_out, &n, device_id);
+    if (num_out) *num_out = (rc == DETBOX_OK) ? n : 0;
+}
+
+extern "C" int detbox_nms_host(const float *dets, int n, double thresh, int cmp_mode,
+                               int *keep_out, int *num_out, int device_id)
+{
+    return nms_host_impl(dets, n, 5, false, thresh, cmp_mode, keep_out, num_out, device_id);
+}

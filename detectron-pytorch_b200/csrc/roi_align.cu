@@ -1,0 +1,382 @@
+// roi_align.cu — RoIAlign forward / backward over FPN levels in ONE launch.
+// Replaces
+//   bin-centre : libs/layers/roi_align_tf (roi_align_tf.py:16-42 + crop_and_resize.c:6-268 /
+//                crop_and_resize_kernel.cu:10-165)
+//   grid-point : libs/layers/roi_align (roi_align_kernel.cu:15-153; RoIAlignAvg/Max fused,
+//                modules/roi_align.py:23-46)
+//   pyramid    : pyramid_roi_align.py:30-60 (level-assigned: nonzero + gather + kernel + cat +
+//                inverse permutation per level) and :82-91 (all levels, channel concat)
+//
+// Mapping.  One block owns one RoI (x one level in all-levels mode).  Sampling is separable, so
+// the block first fills two tiny shared tables — PH row entries and PW column entries, each
+// {tap index, tap index, lerp weight, valid} — with the reference's float32 arithmetic evaluated
+// ONCE per RoI instead of once per output element; the level is picked in the same prologue
+// (pyramid_roi_align.py:33-37) and the result is written straight to the caller's RoI slot, so no
+// per-level nonzero/gather/cat/scatter passes exist.
+//   NCHW : threads run over (c, ph, pw) flattened = the output's memory order -> fully coalesced
+//          stores; the 4 taps of neighbouring pw share sectors, re-use is served by L1/L2.
+//   NHWC : threads run over (bin, c/4): every tap is one float4 load that is contiguous across
+//          the warp (channel-coalesced), the store is a float4 as well.
+// Backward scatters grad * weight into the 4 taps with red.global.add (float4-wide vector
+// reductions in NHWC, sm_90+), after an optional cudaMemsetAsync of the dense gradient maps.
+#include <type_traits>
+#include "common.cuh"
+
+using namespace detbox;
+
+namespace {
+
+constexpr int RA_THREADS = 256;
+constexpr int RA_MAXP = 33;          // max pooled size + 1 (grid-point pooled variants sample P+1)
+
+struct Tap { int i0, i1; float w; int valid; };
+
+struct RoiArgs {
+    detbox_roi_cfg cfg;
+    const float *rois; long R;
+    const int32_t *levels;
+    float *out;                // forward
+    const float *grad_out;     // backward
+};
+
+// FPN level — pyramid_roi_align.py:33-37, float32, first minimum wins
+__device__ __forceinline__ int pick_level(const detbox_roi_cfg &c, const float *roi) {
+    const float area = (roi[3] - roi[1] + 1.0f) * (roi[4] - roi[2] + 1.0f);
+    int best = 0; float bv = 0.0f;
+    for (int l = 0; l < c.n_levels; ++l) {
+        const float v = fabsf(logf(sqrtf(area / c.ref_area[l])) / 0.6931472f);
+        if (l == 0 || v < bv) { bv = v; best = l; }
+    }
+    return best;
+}
+
+// bin-centre taps along one axis: roi_align_tf.py:24-40 then crop_and_resize.c:44-72
+__device__ __forceinline__ Tap tf_tap(float lo, float hi, float scale, int P, int L, int p) {
+    const float b1 = scale * lo, b2 = scale * hi;
+    const float sp = (b2 - b1) / (float)P;
+    const float n0 = (b1 + sp / 2 - 0.5f) / (float)(L - 1);
+    const float nl = sp * (float)(P - 1) / (float)(L - 1);
+    const float n1 = n0 + nl;
+    const float step = (P > 1) ? (n1 - n0) * (L - 1) / (P - 1) : 0;
+    const float in = (P > 1) ? n0 * (L - 1) + p * step : (float)(0.5 * (double)(n0 + n1) * (L - 1));
+    Tap t;
+    t.valid = !(in < 0 || in > L - 1);
+    const int a = (int)floorf(in), b = (int)ceilf(in);
+    t.i0 = a; t.i1 = b; t.w = in - a;
+    if (!t.valid) { t.i0 = t.i1 = 0; t.w = 0.0f; }
+    return t;
+}
+
+// grid-point taps along one axis: roi_align_kernel.cu:32-56 (G = number of grid points)
+__device__ __forceinline__ Tap gp_tap(float lo, float hi, float scale, int G, int L, int p) {
+    const float s = lo * scale, e = hi * scale;
+    const float len = fmaxf(e - s + 1.0f, 0.0f);
+    const float bin = len / (float)(G - 1);
+    const float v = (float)p * bin + s;
+    Tap t;
+    t.valid = !(v < 0 || v >= L);
+    int st = (int)fminf(floorf(v), (float)(L - 2));
+    t.w = v - (float)st;
+    if (st < 0) st = 0;                 // L == 1: the reference reads out of bounds here
+    t.i0 = st; t.i1 = min(st + 1, L - 1);
+    if (!t.valid) { t.i0 = t.i1 = 0; t.w = 0.0f; }
+    return t;
+}
+
+struct Prologue { int level, b, H, W, ok; };
+
+__device__ __forceinline__ Prologue roi_prologue(const RoiArgs &a, Tap *ty, Tap *tx, int &gh, int &gw)
+{
+    __shared__ Prologue s;
+    const detbox_roi_cfg &c = a.cfg;
+    const float *roi = a.rois + (size_t)blockIdx.x * 5;
+    if (threadIdx.x == 0) {
+        int l = 0;
+        if (c.all_levels) l = blockIdx.y;
+        else if (a.levels) l = a.levels[blockIdx.x];
+        else if (c.n_levels > 1) l = pick_level(c, roi);
+        s.level = l;
+        s.b = (int)roi[0];
+        s.ok = l >= 0 && l < c.n_levels && s.b >= 0 && s.b < c.batch;
+        if (l < 0 || l >= c.n_levels) l = 0;
+        s.H = c.height[l]; s.W = c.width[l];
+    }
+    __syncthreads();
+    const int l = min(max(s.level, 0), c.n_levels - 1);
+    const int pool = (c.mode == DETBOX_ROI_GRID_POINT && c.pool != DETBOX_POOL_NONE) ? 1 : 0;
+    gh = c.pooled_h + pool; gw = c.pooled_w + pool;
+    const int t = threadIdx.x;
+    if (t < gh) ty[t] = (c.mode == DETBOX_ROI_BIN_CENTRE) ? tf_tap(roi[2], roi[4], c.spatial_scale[l], gh, s.H, t)
+                                                          : gp_tap(roi[2], roi[4], c.spatial_scale[l], gh, s.H, t);
+    else if (t >= 64 && t - 64 < gw)
+        tx[t - 64] = (c.mode == DETBOX_ROI_BIN_CENTRE) ? tf_tap(roi[1], roi[3], c.spatial_scale[l], gw, s.W, t - 64)
+                                                       : gp_tap(roi[1], roi[3], c.spatial_scale[l], gw, s.W, t - 64);
+    __syncthreads();
+    return s;
+}
+
+// one sample from its 4 taps
+template <bool GRID>
+__device__ __forceinline__ float blend(float tl, float tr, float bl, float br, float wy, float wx) {
+    if (GRID) {   // roi_align_kernel.cu:62-65 — double-promoted weights and sum
+        const double hr = wy, wr = wx;
+        return (float)((double)tl * (1. - hr) * (1. - wr) + (double)tr * (1. - hr) * wr
+                       + (double)bl * hr * (1. - wr) + (double)br * hr * wr);
+    }
+    const float top = tl + (tr - tl) * wx;        // crop_and_resize.c:101-105
+    const float bot = bl + (br - bl) * wx;
+    return top + (bot - top) * wy;
+}
+
+template <bool NHWC>
+__device__ __forceinline__ size_t feat_index(int b, int c, int y, int x, int C, int H, int W) {
+    return NHWC ? (((size_t)b * H + y) * W + x) * C + c : (((size_t)b * C + c) * H + y) * W + x;
+}
+
+template <bool GRID, bool NHWC_IN>
+__device__ __forceinline__ float sample_one(const float *f, int b, int c, const Tap &y, const Tap &x, int C, int H, int W) {
+    if (!(y.valid && x.valid)) return 0.0f;
+    const float tl = f[feat_index<NHWC_IN>(b, c, y.i0, x.i0, C, H, W)];
+    const float tr = f[feat_index<NHWC_IN>(b, c, y.i0, x.i1, C, H, W)];
+    const float bl = f[feat_index<NHWC_IN>(b, c, y.i1, x.i0, C, H, W)];
+    const float br = f[feat_index<NHWC_IN>(b, c, y.i1, x.i1, C, H, W)];
+    return blend<GRID>(tl, tr, bl, br, y.w, x.w);
+}
+
+// ---- forward ------------------------------------------------------------------------------------
+template <bool GRID, bool NHWC_IN, bool NHWC_OUT>
+__global__ void __launch_bounds__(RA_THREADS)
+roi_fwd_kernel(const RoiArgs a)
+{
+    __shared__ Tap ty[RA_MAXP], tx[RA_MAXP];
+    int gh, gw;
+    const Prologue s = roi_prologue(a, ty, tx, gh, gw);
+    const detbox_roi_cfg &c = a.cfg;
+    const int PH = c.pooled_h, PW = c.pooled_w, C = c.channels;
+    const int Ctot = c.all_levels ? C * c.n_levels : C;
+    const int coff = c.all_levels ? C * blockIdx.y : 0;
+    const int bins = PH * PW;
+    const long r = blockIdx.x;
+    const float *f = s.ok ? c.feat[s.level] : nullptr;
+    const int pool = (GRID && c.pool != DETBOX_POOL_NONE) ? c.pool : DETBOX_POOL_NONE;
+
+    if (NHWC_IN && NHWC_OUT && (C & 3) == 0 && pool == DETBOX_POOL_NONE) {
+        // channel-coalesced float4 path
+        const int C4 = C >> 2;
+        for (int idx = threadIdx.x; idx < bins * C4; idx += RA_THREADS) {
+            const int c4 = idx % C4, bin = idx / C4;
+            const int y = bin / PW, x = bin - y * PW;
+            float4 v = make_float4(0, 0, 0, 0);
+            const Tap Y = ty[y], X = tx[x];
+            if (f && Y.valid && X.valid) {
+                const float4 *p = reinterpret_cast<const float4 *>(f);
+                const size_t rowb = (size_t)s.b * s.H;
+                const float4 tl = p[(((rowb + Y.i0) * s.W + X.i0) * C >> 2) + c4];
+                const float4 tr = p[(((rowb + Y.i0) * s.W + X.i1) * C >> 2) + c4];
+                const float4 bl = p[(((rowb + Y.i1) * s.W + X.i0) * C >> 2) + c4];
+                const float4 br = p[(((rowb + Y.i1) * s.W + X.i1) * C >> 2) + c4];
+                v.x = blend<GRID>(tl.x, tr.x, bl.x, br.x, Y.w, X.w);
+                v.y = blend<GRID>(tl.y, tr.y, bl.y, br.y, Y.w, X.w);
+                v.z = blend<GRID>(tl.z, tr.z, bl.z, br.z, Y.w, X.w);
+                v.w = blend<GRID>(tl.w, tr.w, bl.w, br.w, Y.w, X.w);
+            }
+            reinterpret_cast<float4 *>(a.out)[((((size_t)r * bins + bin) * Ctot + coff) >> 2) + c4] = v;
+        }
+        return;
+    }
+    // generic path: iterate in the OUTPUT's memory order
+    for (int idx = threadIdx.x; idx < bins * C; idx += RA_THREADS) {
+        int ch, bin;
+        if (NHWC_OUT) { ch = idx % C; bin = idx / C; } else { ch = idx / bins; bin = idx - ch * bins; }
+        const int y = bin / PW, x = bin - y * PW;
+        float v = 0.0f;
+        if (f) {
+            if (pool == DETBOX_POOL_NONE) {
+                v = sample_one<GRID, NHWC_IN>(f, s.b, ch, ty[y], tx[x], C, s.H, s.W);
+            } else {   // 2x2 / stride 1 pool over the (PH+1)x(PW+1) sample grid (modules/roi_align.py:23-46)
+                const float v00 = sample_one<GRID, NHWC_IN>(f, s.b, ch, ty[y], tx[x], C, s.H, s.W);
+                const float v01 = sample_one<GRID, NHWC_IN>(f, s.b, ch, ty[y], tx[x + 1], C, s.H, s.W);
+                const float v10 = sample_one<GRID, NHWC_IN>(f, s.b, ch, ty[y + 1], tx[x], C, s.H, s.W);
+                const float v11 = sample_one<GRID, NHWC_IN>(f, s.b, ch, ty[y + 1], tx[x + 1], C, s.H, s.W);
+                v = (pool == DETBOX_POOL_AVG2) ? (((v00 + v01) + v10) + v11) * 0.25f
+                                               : fmaxf(fmaxf(v00, v01), fmaxf(v10, v11));
+            }
+        }
+        const size_t o = NHWC_OUT ? ((size_t)r * bins + bin) * Ctot + coff + ch
+                                  : ((size_t)r * Ctot + coff + ch) * bins + bin;
+        a.out[o] = v;
+    }
+}
+
+// ---- backward -----------------------------------------------------------------------------------
+__device__ __forceinline__ void red_add4(float *p, float4 v) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+template <bool GRID>
+__device__ __forceinline__ void tap_weights(float g, float wy, float wx, float &w00, float &w01, float &w10, float &w11) {
+    if (GRID) {   // roi_align_kernel.cu:147-150
+        const double hr = wy, wr = wx;
+        w00 = (float)((double)g * (1. - hr) * (1 - wr)); w01 = (float)((double)g * (1. - hr) * wr);
+        w10 = (float)((double)g * hr * (1 - wr));        w11 = (float)((double)g * hr * wr);
+    } else {      // crop_and_resize.c:258-264
+        const float dtop = (1 - wy) * g, dbot = wy * g;
+        w00 = (1 - wx) * dtop; w01 = wx * dtop; w10 = (1 - wx) * dbot; w11 = wx * dbot;
+    }
+}
+
+template <bool GRID, bool NHWC_IN, bool NHWC_OUT>
+__global__ void __launch_bounds__(RA_THREADS)
+roi_bwd_kernel(const RoiArgs a)
+{
+    __shared__ Tap ty[RA_MAXP], tx[RA_MAXP];
+    int gh, gw;
+    const Prologue s = roi_prologue(a, ty, tx, gh, gw);
+    if (!s.ok) return;
+    const detbox_roi_cfg &c = a.cfg;
+    const int PH = c.pooled_h, PW = c.pooled_w, C = c.channels;
+    const int Ctot = c.all_levels ? C * c.n_levels : C;
+    const int coff = c.all_levels ? C * blockIdx.y : 0;
+    const int bins = PH * PW;
+    const long r = blockIdx.x;
+    float *gf = c.grad_feat[s.level];
+
+    if (NHWC_IN && NHWC_OUT && (C & 3) == 0) {
+        const int C4 = C >> 2;
+        for (int idx = threadIdx.x; idx < bins * C4; idx += RA_THREADS) {
+            const int c4 = idx % C4, bin = idx / C4;
+            const int y = bin / PW, x = bin - y * PW;
+            const Tap Y = ty[y], X = tx[x];
+            if (!(Y.valid && X.valid)) continue;
+            const float4 g = reinterpret_cast<const float4 *>(a.grad_out)[((((size_t)r * bins + bin) * Ctot + coff) >> 2) + c4];
+            float4 w00, w01, w10, w11;
+            tap_weights<GRID>(g.x, Y.w, X.w, w00.x, w01.x, w10.x, w11.x);
+            tap_weights<GRID>(g.y, Y.w, X.w, w00.y, w01.y, w10.y, w11.y);
+            tap_weights<GRID>(g.z, Y.w, X.w, w00.z, w01.z, w10.z, w11.z);
+            tap_weights<GRID>(g.w, Y.w, X.w, w00.w, w01.w, w10.w, w11.w);
+            const size_t rowb = (size_t)s.b * s.H;
+            red_add4(gf + ((rowb + Y.i0) * s.W + X.i0) * C + 4 * c4, w00);
+            red_add4(gf + ((rowb + Y.i0) * s.W + X.i1) * C + 4 * c4, w01);
+            red_add4(gf + ((rowb + Y.i1) * s.W + X.i0) * C + 4 * c4, w10);
+            red_add4(gf + ((rowb + Y.i1) * s.W + X.i1) * C + 4 * c4, w11);
+        }
+        return;
+    }
+    for (int idx = threadIdx.x; idx < bins * C; idx += RA_THREADS) {
+        int ch, bin;
+        if (NHWC_OUT) { ch = idx % C; bin = idx / C; } else { ch = idx / bins; bin = idx - ch * bins; }
+        const int y = bin / PW, x = bin - y * PW;
+        const Tap Y = ty[y], X = tx[x];
+        if (!(Y.valid && X.valid)) continue;
+        const size_t o = NHWC_OUT ? ((size_t)r * bins + bin) * Ctot + coff + ch
+                                  : ((size_t)r * Ctot + coff + ch) * bins + bin;
+        const float g = a.grad_out[o];
+        float w00, w01, w10, w11;
+        tap_weights<GRID>(g, Y.w, X.w, w00, w01, w10, w11);
+        atomicAdd(gf + feat_index<NHWC_IN>(s.b, ch, Y.i0, X.i0, C, s.H, s.W), w00);
+        atomicAdd(gf + feat_index<NHWC_IN>(s.b, ch, Y.i0, X.i1, C, s.H, s.W), w01);
+        atomicAdd(gf + feat_index<NHWC_IN>(s.b, ch, Y.i1, X.i0, C, s.H, s.W), w10);
+        atomicAdd(gf + feat_index<NHWC_IN>(s.b, ch, Y.i1, X.i1, C, s.H, s.W), w11);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+assign_levels_kernel(const float *__restrict__ boxes, long R, detbox_roi_cfg c, int32_t *__restrict__ levels)
+{
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < R; i += (long)gridDim.x * blockDim.x) {
+        const float *b = boxes + i * 4;
+        const float roi[5] = {0.0f, b[0], b[1], b[2], b[3]};
+        levels[i] = pick_level(c, roi);
+    }
+}
+
+int check_cfg(const detbox_roi_cfg *c, bool backward)
+{
+    if (!c || c->n_levels < 1 || c->n_levels > DETBOX_MAX_LEVELS) return DETBOX_ERR_INVALID;
+    if (c->batch < 0 || c->channels <= 0 || c->pooled_h <= 0 || c->pooled_w <= 0) return DETBOX_ERR_INVALID;
+    if (c->mode != DETBOX_ROI_BIN_CENTRE && c->mode != DETBOX_ROI_GRID_POINT) return DETBOX_ERR_INVALID;
+    if (c->pool < 0 || c->pool > 2 || (c->pool != 0 && c->mode != DETBOX_ROI_GRID_POINT)) return DETBOX_ERR_INVALID;
+    if (backward && c->pool != DETBOX_POOL_NONE) return DETBOX_ERR_UNSUPPORTED;   // compose pool backward outside
+    if (c->pooled_h + 1 > RA_MAXP || c->pooled_w + 1 > RA_MAXP) return DETBOX_ERR_UNSUPPORTED;
+    if ((c->layout != 0 && c->layout != 1) || (c->out_layout != 0 && c->out_layout != 1)) return DETBOX_ERR_INVALID;
+    for (int l = 0; l < c->n_levels; ++l) {
+        if (c->height[l] <= 0 || c->width[l] <= 0) return DETBOX_ERR_INVALID;
+        if (backward ? !c->grad_feat[l] : !c->feat[l]) return DETBOX_ERR_INVALID;
+    }
+    return DETBOX_OK;
+}
+
+template <typename F> int dispatch(const detbox_roi_cfg &c, F &&f)
+{
+    const bool grid = c.mode == DETBOX_ROI_GRID_POINT, in = c.layout == DETBOX_LAYOUT_NHWC, out = c.out_layout == DETBOX_LAYOUT_NHWC;
+    const int k = (grid ? 4 : 0) | (in ? 2 : 0) | (out ? 1 : 0);
+    switch (k) {
+        case 0: return f(std::integral_constant<int, 0>());
+        case 1: return f(std::integral_constant<int, 1>());
+        case 2: return f(std::integral_constant<int, 2>());
+        case 3: return f(std::integral_constant<int, 3>());
+        case 4: return f(std::integral_constant<int, 4>());
+        case 5: return f(std::integral_constant<int, 5>());
+        case 6: return f(std::integral_constant<int, 6>());
+        default: return f(std::integral_constant<int, 7>());
+    }
+}
+
+}  // namespace
+
+extern "C" int detbox_roi_align_forward(const detbox_roi_cfg *cfg, const float *rois, long R,
+                                        const int32_t *levels, float *out, void *stream)
+{
+    int rc = check_cfg(cfg, false);
+    if (rc != DETBOX_OK) return rc;
+    if (R < 0) return DETBOX_ERR_INVALID;
+    if (R == 0) return DETBOX_OK;
+    if (!rois || !out) return DETBOX_ERR_INVALID;
+    RoiArgs a; a.cfg = *cfg; a.rois = rois; a.R = R; a.levels = levels; a.out = out; a.grad_out = nullptr;
+    dim3 grid((unsigned)R, cfg->all_levels ? cfg->n_levels : 1);
+    cudaStream_t st = as_stream(stream);
+    return dispatch(*cfg, [&](auto K) -> int {
+        constexpr int k = decltype(K)::value;
+        roi_fwd_kernel<(k & 4) != 0, (k & 2) != 0, (k & 1) != 0><<<grid, RA_THREADS, 0, st>>>(a);
+        DETBOX_LAUNCH_CHECK();
+        return DETBOX_OK;
+    });
+}
+
+extern "C" int detbox_roi_align_backward(const detbox_roi_cfg *cfg, const float *rois, long R,
+                                         const int32_t *levels, const float *grad_out, int zero_grad, void *stream)
+{
+    int rc = check_cfg(cfg, true);
+    if (rc != DETBOX_OK) return rc;
+    if (R < 0) return DETBOX_ERR_INVALID;
+    cudaStream_t st = as_stream(stream);
+    if (zero_grad)
+        for (int l = 0; l < cfg->n_levels; ++l)
+            DETBOX_CUDA_TRY(cudaMemsetAsync(cfg->grad_feat[l], 0,
+                                            (size_t)cfg->batch * cfg->channels * cfg->height[l] * cfg->width[l] * sizeof(float), st));
+    if (R == 0) return DETBOX_OK;
+    if (!rois || !grad_out) return DETBOX_ERR_INVALID;
+    RoiArgs a; a.cfg = *cfg; a.rois = rois; a.R = R; a.levels = levels; a.out = nullptr; a.grad_out = grad_out;
+    dim3 grid((unsigned)R, cfg->all_levels ? cfg->n_levels : 1);
+    return dispatch(*cfg, [&](auto K) -> int {
+        constexpr int k = decltype(K)::value;
+        roi_bwd_kernel<(k & 4) != 0, (k & 2) != 0, (k & 1) != 0><<<grid, RA_THREADS, 0, st>>>(a);
+        DETBOX_LAUNCH_CHECK();
+        return DETBOX_OK;
+    });
+}
+
+extern "C" int detbox_assign_levels(const float *boxes, long R, const float *ref_areas, int n_levels,
+                                    int32_t *levels, void *stream)
+{
+    if (R < 0 || n_levels < 1 || n_levels > DETBOX_MAX_LEVELS || !ref_areas) return DETBOX_ERR_INVALID;
+    if (R == 0) return DETBOX_OK;
+    if (!boxes || !levels) return DETBOX_ERR_INVALID;
+    detbox_roi_cfg c{};
+    c.n_levels = n_levels;
+    for (int l = 0; l < n_levels; ++l) c.ref_area[l] = ref_areas[l];
+    long gb = (R + 255) / 256; if (gb > kNumSMs * 8) gb = kNumSMs * 8;
+    assign_levels_kernel<<<(unsigned)gb, 256, 0, as_stream(stream)>>>(boxes, R, c, levels);
+    DETBOX_LAUNCH_CHECK();
+    return DETBOX_OK;
+}

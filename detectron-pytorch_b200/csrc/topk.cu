@@ -1,0 +1,396 @@
+// topk.cu — objectness + segmented radix top-k + gather + decode.
+// Replaces detection_model._decode_and_choose_top_n_stage1 (reference libs/nets/model.py:308-321,
+// objectness :54-61): the reference runs a full torch.sort over batch x levels x anchors to keep
+// <= 1% of the keys.  Here:
+//
+//   1. objectness  one read of the class probabilities (4*C*A bytes per image — the compulsory
+//                  traffic of this stage), score -> order-preserving descending uint32 key,
+//                  keys written once (4 B/anchor), level-0 histogram (top 11 bits) fused.
+//   2. radix select (MSB first, 11+11+10 bits): per segment find the exact key T of the k-th
+//                  best anchor, the number of strictly better keys and how many keys equal to T
+//                  are needed.  Segment = whole batch (reference behaviour, "global") or one
+//                  image ("per_image", the sharded mode).
+//   3. compaction  ORDER-PRESERVING (index order) copy of the winners: better keys + the first
+//                  `need` ties by index -> deterministic tie rule "lower flat index first".
+//   4. sort        stable radix sort of the k winners only (sort.cu); per-image mode adds one
+//                  stable pass on the image id.
+//   5. gather      deltas / probs / anchors of the winners, decode (box_math.cuh), image ids.
+//
+// Segments are equal-sized (A anchors per image), so a segment is identified by blockIdx.y.
+#include "box_math.cuh"
+#include "sort.cuh"
+
+using namespace detbox;
+
+namespace {
+
+constexpr int NB0 = 2048;            // bins of level 0 / 1 (11 bits); level 2 uses 1024 (10 bits)
+constexpr int TK_THREADS = 256;
+constexpr int TK_ROWS = 128;         // sigmoid staging tile: rows
+constexpr int TK_COLS = 64;          // sigmoid staging tile: class columns per chunk
+
+struct SegState { uint32_t prefix; uint32_t k_rem; uint32_t n_better; uint32_t pad; };
+
+// ---- 1. objectness -> keys + level-0 histogram -------------------------------------------------
+template <int ACT>
+__global__ void __launch_bounds__(TK_THREADS)
+objectness_kernel(const float *__restrict__ prob, int C, long seg_len, uint32_t *__restrict__ keys,
+                  uint32_t *__restrict__ hist /*[n_seg][NB0]*/)
+{
+    __shared__ uint32_t sh[NB0];
+    __shared__ float stage[ACT == DETBOX_ACT_SIGMOID ? TK_ROWS * (TK_COLS + 1) : 1];
+    const int tid = threadIdx.x;
+    for (int i = tid; i < NB0; i += TK_THREADS) sh[i] = 0;
+    __syncthreads();
+    const long seg0 = (long)blockIdx.y * seg_len;
+    if (ACT == DETBOX_ACT_SOFTMAX || C <= 4) {
+        for (long r = (long)blockIdx.x * TK_THREADS + tid; r < seg_len; r += (long)gridDim.x * TK_THREADS) {
+            const float *p = prob + (size_t)(seg0 + r) * C;
+            float s;
+            if (ACT == DETBOX_ACT_SOFTMAX) s = 1.0f - p[0];                    // model.py:57
+            else { s = p[0]; for (int c = 1; c < C; ++c) s = fmaxf(s, p[c]); } // model.py:59
+            const uint32_t k = ~float_to_ordered(s);
+            keys[seg0 + r] = k;
+            atomicAdd(&sh[k >> 21], 1u);
+        }
+    } else {
+        // max over C classes: stage [TK_ROWS x <=TK_COLS] through shared memory so that global reads
+        // are contiguous runs and the per-row reduction is bank-conflict free (odd row pitch)
+        for (long r0 = (long)blockIdx.x * TK_ROWS; r0 < seg_len; r0 += (long)gridDim.x * TK_ROWS) {
+            const int rn = (int)min((long)TK_ROWS, seg_len - r0);
+            float m = -__int_as_float(0x7f800000);
+            for (int c0 = 0; c0 < C; c0 += TK_COLS) {
+                const int cn = min(TK_COLS, C - c0);
+                __syncthreads();
+                for (int i = tid; i < rn * cn; i += TK_THREADS) {
+                    const int r = i / cn, c = i - r * cn;
+                    stage[r * (TK_COLS + 1) + c] = prob[(size_t)(seg0 + r0 + r) * C + c0 + c];
+                }
+                __syncthreads();
+                if (tid < rn) for (int c = 0; c < cn; ++c) m = fmaxf(m, stage[tid * (TK_COLS + 1) + c]);
+            }
+            if (tid < rn) {
+                const uint32_t k = ~float_to_ordered(m);
+                keys[seg0 + r0 + tid] = k;
+                atomicAdd(&sh[k >> 21], 1u);
+            }
+        }
+    }
+    __syncthreads();
+    uint32_t *h = hist + (size_t)blockIdx.y * NB0;
+    for (int i = tid; i < NB0; i += TK_THREADS) if (sh[i]) atomicAdd(&h[i], sh[i]);
+}
+
+// ---- 2. radix select ---------------------------------------------------------------------------
+// one block per segment: find the bin that holds the k_rem-th key (bins ascending = best first)
+__global__ void __launch_bounds__(1024)
+select_kernel(const uint32_t *__restrict__ hist, int nbins, int bits, SegState *__restrict__ state)
+{
+    __shared__ uint32_t wsum[32];
+    __shared__ uint32_t found_bin, found_before;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const uint32_t *h = hist + (size_t)blockIdx.x * NB0;
+    const int per = nbins / 1024 > 0 ? nbins / 1024 : 1;          // 2 (2048 bins) or 1
+    uint32_t c[2] = {0, 0};
+    uint32_t s = 0;
+    for (int i = 0; i < per; ++i) { const int b = tid * per + i; c[i] = b < nbins ? h[b] : 0; s += c[i]; }
+    uint32_t incl = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    if (lane == 31) wsum[w] = incl;
+    __syncthreads();
+    if (w == 0) {
+        const uint32_t v = wsum[lane]; uint32_t iv = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, iv, o); if (lane >= o) iv += t; }
+        wsum[lane] = iv - v;
+    }
+    __syncthreads();
+    const uint32_t k = state[blockIdx.x].k_rem;
+    uint32_t before = wsum[w] + incl - s;                        // keys in bins before this thread's
+    for (int i = 0; i < per; ++i) {
+        if (k > before && k <= before + c[i]) { found_bin = tid * per + i; found_before = before; }
+        before += c[i];
+    }
+    __syncthreads();
+    if (tid == 0 && k > 0) {
+        SegState st = state[blockIdx.x];
+        st.prefix = (st.prefix << bits) | found_bin;
+        st.k_rem = k - found_before;
+        st.n_better += found_before;
+        state[blockIdx.x] = st;
+    }
+}
+
+// histogram of the next digit among the keys that match the prefix found so far
+__global__ void __launch_bounds__(TK_THREADS)
+refine_kernel(const uint32_t *__restrict__ keys, long seg_len, const SegState *__restrict__ state,
+              int prefix_shift, int bin_shift, uint32_t bin_mask, uint32_t *__restrict__ hist)
+{
+    __shared__ uint32_t sh[NB0];
+    const int tid = threadIdx.x;
+    for (int i = tid; i < NB0; i += TK_THREADS) sh[i] = 0;
+    __syncthreads();
+    const uint32_t prefix = state[blockIdx.y].prefix;
+    const uint32_t *k = keys + (size_t)blockIdx.y * seg_len;
+    for (long r = (long)blockIdx.x * TK_THREADS + tid; r < seg_len; r += (long)gridDim.x * TK_THREADS) {
+        const uint32_t v = k[r];
+        if ((v >> prefix_shift) == prefix) atomicAdd(&sh[(v >> bin_shift) & bin_mask], 1u);
+    }
+    __syncthreads();
+    uint32_t *h = hist + (size_t)blockIdx.y * NB0;
+    for (int i = tid; i < NB0; i += TK_THREADS) if (sh[i]) atomicAdd(&h[i], sh[i]);
+}
+
+// ---- 3. order-preserving compaction --------------------------------------------------------------
+constexpr int CP_ITEMS = 8;
+constexpr int CP_TILE = TK_THREADS * CP_ITEMS;
+
+__global__ void __launch_bounds__(TK_THREADS)
+cand_count_kernel(const uint32_t *__restrict__ keys, long seg_len, const SegState *__restrict__ state,
+                  uint32_t *__restrict__ blk_lt, uint32_t *__restrict__ blk_eq)
+{
+    const uint32_t T = state[blockIdx.y].prefix;
+    const uint32_t *k = keys + (size_t)blockIdx.y * seg_len;
+    const long t0 = (long)blockIdx.x * CP_TILE;
+    int lt = 0, eq = 0;
+    for (int j = 0; j < CP_ITEMS; ++j) {
+        const long i = t0 + j * TK_THREADS + threadIdx.x;
+        if (i < seg_len) { const uint32_t v = k[i]; lt += v < T; eq += v == T; }
+    }
+    __shared__ int s_lt, s_eq;
+    if (threadIdx.x == 0) { s_lt = 0; s_eq = 0; }
+    __syncthreads();
+    lt = __reduce_add_sync(0xffffffffu, lt);
+    eq = __reduce_add_sync(0xffffffffu, eq);
+    if ((threadIdx.x & 31) == 0) { atomicAdd(&s_lt, lt); atomicAdd(&s_eq, eq); }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        blk_lt[(size_t)blockIdx.y * gridDim.x + blockIdx.x] = s_lt;
+        blk_eq[(size_t)blockIdx.y * gridDim.x + blockIdx.x] = s_eq;
+    }
+}
+
+// exclusive scan of the per-block counts inside every segment (one block per segment)
+__global__ void __launch_bounds__(1024)
+cand_scan_kernel(uint32_t *__restrict__ blk_lt, uint32_t *__restrict__ blk_eq, int nblk)
+{
+    __shared__ uint32_t wsum[2][32];
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    uint32_t *a = blk_lt + (size_t)blockIdx.x * nblk, *b = blk_eq + (size_t)blockIdx.x * nblk;
+    const int per = (nblk + 1023) / 1024;
+    const int begin = min(nblk, tid * per), end = min(nblk, begin + per);
+    uint32_t sa = 0, sb = 0;
+    for (int i = begin; i < end; ++i) { sa += a[i]; sb += b[i]; }
+    uint32_t ia = sa, ib = sb;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t ta = __shfl_up_sync(0xffffffffu, ia, o), tb = __shfl_up_sync(0xffffffffu, ib, o);
+        if (lane >= o) { ia += ta; ib += tb; }
+    }
+    if (lane == 31) { wsum[0][w] = ia; wsum[1][w] = ib; }
+    __syncthreads();
+    if (w < 2) {
+        const uint32_t v = wsum[w][lane]; uint32_t iv = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, iv, o); if (lane >= o) iv += t; }
+        wsum[w][lane] = iv - v;
+    }
+    __syncthreads();
+    uint32_t ra = wsum[0][w] + ia - sa, rb = wsum[1][w] + ib - sb;
+    for (int i = begin; i < end; ++i) {
+        const uint32_t ca = a[i], cb = b[i];
+        a[i] = ra; b[i] = rb; ra += ca; rb += cb;
+    }
+}
+
+__global__ void __launch_bounds__(TK_THREADS)
+cand_write_kernel(const uint32_t *__restrict__ keys, long seg_len, const SegState *__restrict__ state,
+                  const uint32_t *__restrict__ blk_lt, const uint32_t *__restrict__ blk_eq, long K,
+                  uint32_t *__restrict__ ckeys, uint32_t *__restrict__ cvals)
+{
+    __shared__ uint32_t w_lt[TK_THREADS / 32], w_eq[TK_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const SegState st = state[blockIdx.y];
+    const uint32_t T = st.prefix, need = st.k_rem;
+    const uint32_t *k = keys + (size_t)blockIdx.y * seg_len;
+    const long base = (long)blockIdx.x * CP_TILE + (long)w * 32 * CP_ITEMS;   // warp-striped: index order = (warp, step, lane)
+    uint32_t key[CP_ITEMS], m_lt[CP_ITEMS], m_eq[CP_ITEMS];
+    uint32_t tot_lt = 0, tot_eq = 0;
+#pragma unroll
+    for (int j = 0; j < CP_ITEMS; ++j) {
+        const long i = base + j * 32 + lane;
+        key[j] = i < seg_len ? k[i] : 0xffffffffu;
+        const bool ok = i < seg_len;
+        m_lt[j] = __ballot_sync(0xffffffffu, ok && key[j] < T);
+        m_eq[j] = __ballot_sync(0xffffffffu, ok && key[j] == T);
+        tot_lt += __popc(m_lt[j]); tot_eq += __popc(m_eq[j]);
+    }
+    if (lane == 0) { w_lt[w] = tot_lt; w_eq[w] = tot_eq; }
+    __syncthreads();
+    uint32_t lt_before = blk_lt[(size_t)blockIdx.y * gridDim.x + blockIdx.x];
+    uint32_t eq_before = blk_eq[(size_t)blockIdx.y * gridDim.x + blockIdx.x];
+    for (int i = 0; i < w; ++i) { lt_before += w_lt[i]; eq_before += w_eq[i]; }
+    const uint32_t below = (1u << lane) - 1u;
+    const long seg0 = (long)blockIdx.y * seg_len;
+#pragma unroll
+    for (int j = 0; j < CP_ITEMS; ++j) {
+        const long i = base + j * 32 + lane;
+        const uint32_t my_lt = lt_before + __popc(m_lt[j] & below);
+        const uint32_t my_eq = eq_before + __popc(m_eq[j] & below);
+        const bool is_lt = (m_lt[j] >> lane) & 1u, is_eq = (m_eq[j] >> lane) & 1u;
+        if (is_lt || (is_eq && my_eq < need)) {
+            const uint32_t pos = my_lt + min(my_eq, need);
+            ckeys[(size_t)blockIdx.y * K + pos] = key[j];
+            cvals[(size_t)blockIdx.y * K + pos] = (uint32_t)(seg0 + i);
+        }
+        lt_before += __popc(m_lt[j]); eq_before += __popc(m_eq[j]);
+    }
+}
+
+// ---- 5. gather + decode ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+gather_decode_kernel(const uint32_t *__restrict__ ckeys, const uint32_t *__restrict__ cvals, long n,
+                     const float *__restrict__ prob, int C, const float4 *__restrict__ deltas,
+                     const float4 *__restrict__ anchors, long A, int enc,
+                     float4 *__restrict__ boxes, float *__restrict__ probs_out, int64_t *__restrict__ img_ids,
+                     float4 *__restrict__ sel_anchors, int64_t *__restrict__ flat_idx, float *__restrict__ scores)
+{
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+        const uint32_t idx = cvals[i];
+        const long a = idx % A;                                               // model.py:316
+        const float4 anc = anchors[a];
+        boxes[i] = decode_box(anc, deltas[idx], enc);                         // model.py:318 (no clip)
+        if (img_ids) img_ids[i] = (int64_t)(idx / A);                         // model.py:319
+        if (sel_anchors) sel_anchors[i] = anc;
+        if (flat_idx) flat_idx[i] = (int64_t)idx;
+        if (scores) scores[i] = ordered_to_float(~ckeys[i]);
+        if (probs_out) for (int c = 0; c < C; ++c) probs_out[(size_t)i * C + c] = prob[(size_t)idx * C + c];
+    }
+}
+
+__global__ void init_state_kernel(SegState *state, int n_seg, uint32_t k)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_seg) { state[i].prefix = 0; state[i].k_rem = k; state[i].n_better = 0; state[i].pad = 0; }
+}
+
+struct TopkPlan {
+    int n_seg; long seg_len; long K; long n_cand; int nblk_c;
+    size_t keys_b, hist_b, state_b, blk_b, cand_b, counts_b, total;
+};
+
+TopkPlan make_plan(int batch, long A, long top_n, int per_image) {
+    TopkPlan p;
+    p.n_seg = per_image ? batch : 1;
+    p.seg_len = per_image ? A : (long)batch * A;
+    p.K = top_n < p.seg_len ? top_n : p.seg_len;
+    if (p.K < 0) p.K = 0;
+    p.n_cand = p.K * p.n_seg;
+    p.nblk_c = (int)((p.seg_len + CP_TILE - 1) / CP_TILE);
+    p.keys_b = align_up((size_t)batch * A * 4);
+    p.hist_b = align_up((size_t)3 * p.n_seg * NB0 * 4);
+    p.state_b = align_up((size_t)p.n_seg * sizeof(SegState));
+    p.blk_b = align_up((size_t)p.n_seg * p.nblk_c * 4);
+    p.cand_b = align_up((size_t)(p.n_cand > 0 ? p.n_cand : 1) * 4);
+    p.counts_b = sort_counts_bytes(p.n_cand > 0 ? p.n_cand : 1);
+    p.total = p.keys_b + p.hist_b + p.state_b + 2 * p.blk_b + 4 * p.cand_b + p.counts_b;
+    return p;
+}
+
+}  // namespace
+
+extern "C" size_t detbox_topk_decode_workspace_bytes(int batch, long A, long top_n, int per_image)
+{
+    if (batch <= 0 || A <= 0) return 256;
+    return make_plan(batch, A, top_n, per_image).total;
+}
+
+extern "C" int detbox_topk_decode(const float *prob, int C, const float *deltas, const float *anchors,
+                                  int batch, long A, int activation, long top_n, int per_image, int enc,
+                                  float *boxes, float *probs_out, int64_t *img_ids, float *sel_anchors,
+                                  int64_t *flat_idx, float *scores, void *ws, size_t ws_bytes, void *stream)
+{
+    if (batch < 0 || A < 0 || C <= 0 || top_n < 0 || enc < 0 || enc > 2) return DETBOX_ERR_INVALID;
+    if (activation != DETBOX_ACT_SOFTMAX && activation != DETBOX_ACT_SIGMOID) return DETBOX_ERR_INVALID;
+    if (batch == 0 || A == 0 || top_n == 0) return DETBOX_OK;
+    if ((double)batch * (double)A >= 2147483648.0) return DETBOX_ERR_UNSUPPORTED;
+    if (!prob || !deltas || !anchors || !boxes) return DETBOX_ERR_INVALID;
+    const TopkPlan p = make_plan(batch, A, top_n, per_image);
+    if (!ws || ws_bytes < p.total) return DETBOX_ERR_WORKSPACE;
+    if (p.n_seg > 65535) return DETBOX_ERR_UNSUPPORTED;
+    cudaStream_t st = as_stream(stream);
+    char *w = (char *)ws;
+    uint32_t *keys = (uint32_t *)w; w += p.keys_b;
+    uint32_t *hist = (uint32_t *)w; w += p.hist_b;
+    SegState *state = (SegState *)w; w += p.state_b;
+    uint32_t *blk_lt = (uint32_t *)w; w += p.blk_b;
+    uint32_t *blk_eq = (uint32_t *)w; w += p.blk_b;
+    uint32_t *cka = (uint32_t *)w; w += p.cand_b;
+    uint32_t *ckb = (uint32_t *)w; w += p.cand_b;
+    uint32_t *cva = (uint32_t *)w; w += p.cand_b;
+    uint32_t *cvb = (uint32_t *)w; w += p.cand_b;
+    uint32_t *counts = (uint32_t *)w;
+
+    DETBOX_CUDA_TRY(cudaMemsetAsync(hist, 0, p.hist_b, st));
+    init_state_kernel<<<(p.n_seg + 255) / 256, 256, 0, st>>>(state, p.n_seg, (uint32_t)p.K);
+    DETBOX_LAUNCH_CHECK();
+
+    // 1. objectness + level-0 histogram
+    {
+        const bool staged = activation == DETBOX_ACT_SIGMOID && C > 4;
+        const long rows_per_block = staged ? TK_ROWS : TK_THREADS;
+        long gx = (p.seg_len + rows_per_block - 1) / rows_per_block;
+        const long cap = (long)kNumSMs * 8 / (p.n_seg < 8 ? 1 : 1);
+        long capx = cap / p.n_seg; if (capx < 1) capx = 1; if (p.n_seg == 1) capx = cap;
+        if (gx > capx) gx = capx;
+        dim3 grid((unsigned)gx, (unsigned)p.n_seg);
+        if (activation == DETBOX_ACT_SOFTMAX) objectness_kernel<DETBOX_ACT_SOFTMAX><<<grid, TK_THREADS, 0, st>>>(prob, C, p.seg_len, keys, hist);
+        else objectness_kernel<DETBOX_ACT_SIGMOID><<<grid, TK_THREADS, 0, st>>>(prob, C, p.seg_len, keys, hist);
+        DETBOX_LAUNCH_CHECK();
+    }
+    // 2. radix select: 11 + 11 + 10 bits
+    long gx = (p.seg_len + TK_THREADS * 8 - 1) / (TK_THREADS * 8);
+    { long capx = (long)kNumSMs * 8 / p.n_seg; if (capx < 1) capx = 1; if (gx > capx) gx = capx; }
+    dim3 rgrid((unsigned)gx, (unsigned)p.n_seg);
+    uint32_t *h0 = hist, *h1 = hist + (size_t)p.n_seg * NB0, *h2 = hist + (size_t)2 * p.n_seg * NB0;
+    select_kernel<<<p.n_seg, 1024, 0, st>>>(h0, 2048, 11, state);
+    DETBOX_LAUNCH_CHECK();
+    refine_kernel<<<rgrid, TK_THREADS, 0, st>>>(keys, p.seg_len, state, 21, 10, 0x7ffu, h1);
+    DETBOX_LAUNCH_CHECK();
+    select_kernel<<<p.n_seg, 1024, 0, st>>>(h1, 2048, 11, state);
+    DETBOX_LAUNCH_CHECK();
+    refine_kernel<<<rgrid, TK_THREADS, 0, st>>>(keys, p.seg_len, state, 10, 0, 0x3ffu, h2);
+    DETBOX_LAUNCH_CHECK();
+    select_kernel<<<p.n_seg, 1024, 0, st>>>(h2, 1024, 10, state);
+    DETBOX_LAUNCH_CHECK();
+    // 3. ordered compaction
+    dim3 cgrid((unsigned)p.nblk_c, (unsigned)p.n_seg);
+    cand_count_kernel<<<cgrid, TK_THREADS, 0, st>>>(keys, p.seg_len, state, blk_lt, blk_eq);
+    DETBOX_LAUNCH_CHECK();
+    cand_scan_kernel<<<p.n_seg, 1024, 0, st>>>(blk_lt, blk_eq, p.nblk_c);
+    DETBOX_LAUNCH_CHECK();
+    cand_write_kernel<<<cgrid, TK_THREADS, 0, st>>>(keys, p.seg_len, state, blk_lt, blk_eq, p.K, cka, cva);
+    DETBOX_LAUNCH_CHECK();
+    // 4. sort the winners (stable): by key, then (per-image mode) by image id
+    int rc = radix_sort_pairs(cka, cva, ckb, cvb, p.n_cand, counts, st);
+    if (rc != DETBOX_OK) return rc;
+    uint32_t *fk = cka, *fv = cva;
+    if (p.n_seg > 1) {
+        uint32_t *ki = cka, *vi = cva, *ko = ckb, *vo = cvb;
+        for (int shift = 0; (p.n_seg - 1) >> shift; shift += 8) {
+            DigitSrc d{1, shift, (uint32_t)A, nullptr};
+            rc = radix_pass(ki, vi, ko, vo, p.n_cand, d, counts, st);
+            if (rc != DETBOX_OK) return rc;
+            uint32_t *t = ki; ki = ko; ko = t; t = vi; vi = vo; vo = t;
+        }
+        fk = ki; fv = vi;
+    }
+    // 5. gather + decode
+    long gb = (p.n_cand + 255) / 256; if (gb > kNumSMs * 8) gb = kNumSMs * 8;
+    gather_decode_kernel<<<(unsigned)gb, 256, 0, st>>>(fk, fv, p.n_cand, prob, C, (const float4 *)deltas,
+                                                      (const float4 *)anchors, A, enc, (float4 *)boxes, probs_out,
+                                                      img_ids, (float4 *)sel_anchors, flat_idx, scores);
+    DETBOX_LAUNCH_CHECK();
+    return DETBOX_OK;
+}

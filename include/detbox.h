@@ -1,0 +1,231 @@
+/* detbox.h — C ABI of libdetbox.so: the box-and-RoI hot path of CharlesShang/Detectron-PYTORCH
+ * as hand-written sm_100a CUDA kernels.
+ *
+ * Conventions (all entry points):
+ *   - extern "C", plain pointers and sizes; no torch / TH types.
+ *   - pointers named *_dev are DEVICE pointers on the current CUDA device; *_host are host
+ *     pointers.  Arrays are dense, row-major, float32 unless the name says otherwise.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).  Device
+ *     entry points only enqueue work: they never synchronise and never allocate; scratch
+ *     memory comes from the caller, sized by the matching *_workspace_bytes() query.
+ *   - return value: DETBOX_OK (0) or a negative DETBOX_ERR_* code; detbox_error_string()
+ *     describes it.  Nothing ever calls exit() (the reference's launchers do:
+ *     roi_align_kernel.cu:87-91, crop_and_resize_kernel.cu:186-191).
+ *   - "reference" file:line citations are relative to the Detectron-PYTORCH tree.
+ *
+ * The *_host entry points at the end take HOST buffers and do the copies themselves; they are
+ * what the reference's own FFI for this path binds (gpu_nms.hpp:1-2) and what bench.py's
+ * end-to-end leg times.
+ */
+#ifndef DETBOX_H
+#define DETBOX_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DETBOX_OK               0
+#define DETBOX_ERR_INVALID     -1   /* bad argument (null pointer, negative size, unknown mode) */
+#define DETBOX_ERR_WORKSPACE   -2   /* workspace missing or smaller than *_workspace_bytes()   */
+#define DETBOX_ERR_CUDA        -3   /* a CUDA runtime call or launch failed                    */
+#define DETBOX_ERR_UNSUPPORTED -4   /* size beyond a documented limit                          */
+
+/* box encodings: reference cfg.rpn_box_encoding (libs/configs/config.py:106) + 'simple' of
+ * libs/layers/box.py:102,134 */
+#define DETBOX_ENC_FASTRCNN 0
+#define DETBOX_ENC_LINEAR   1
+#define DETBOX_ENC_SIMPLE   2
+
+/* class activation: libs/nets/model.py:54-61 */
+#define DETBOX_ACT_SOFTMAX 0    /* objectness = 1 - p[:,0]   */
+#define DETBOX_ACT_SIGMOID 1    /* objectness = max_c p[:,c] */
+
+/* NMS suppression comparator */
+#define DETBOX_NMS_GE_F64 0     /* (double)iou >= thr        libs/nms/cpu_nms.pyx:65          */
+#define DETBOX_NMS_GE_F32 1     /* iou >= (float)thr         libs/layers/nms/src/nms_cpu.c:76 */
+#define DETBOX_NMS_GT_F32 2     /* iou >  (float)thr         libs/nms/nms_kernel.cu:83        */
+
+/* RoIAlign sampling convention / level mode / fused 2x2 pooling / layout */
+#define DETBOX_ROI_BIN_CENTRE 0 /* roi_align_tf (crop_and_resize.c + roi_align_tf.py:24-40)   */
+#define DETBOX_ROI_GRID_POINT 1 /* roi_align/src/cuda/roi_align_kernel.cu:15-68              */
+#define DETBOX_POOL_NONE 0
+#define DETBOX_POOL_AVG2 1      /* RoIAlignAvg roi_align/modules/roi_align.py:23-33           */
+#define DETBOX_POOL_MAX2 2      /* RoIAlignMax roi_align/modules/roi_align.py:36-46           */
+#define DETBOX_LAYOUT_NCHW 0
+#define DETBOX_LAYOUT_NHWC 1    /* torch.channels_last memory, same logical [B,C,H,W] tensor  */
+#define DETBOX_MAX_LEVELS 8
+
+const char *detbox_error_string(int code);
+int detbox_version(void);
+/* last cudaError_t seen by this library on the calling thread (0 if none) */
+int detbox_last_cuda_error(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * Anchors — replaces libs/boxes/anchor.py:101-189 (anchors / generate_anchors) and :30-70
+ * (anchor_pyramid / anchor_one_plane), and cython_anchor.anchors_plane (cython_anchor.pyx:14-48).
+ * ------------------------------------------------------------------------------------------- */
+/* HOST: base anchors at one cell, float64 [n_ratios*n_scales,4], ratio-major / scale-minor. */
+int detbox_base_anchors_host(const double *scales, int n_scales, const double *ratios, int n_ratios,
+                             long base_size, double *out_host);
+
+/* DEVICE: expand per-level cell anchors over the level grids.  cell_dev: float64
+ * [sum_l n_cell[l], 4] = base anchors (+ shift*stride), level after level.  Output rows are
+ * ordered level -> y -> x -> cell anchor; written as float32 (out_f64 == 0) or float64. */
+int detbox_anchor_pyramid(const double *cell_dev, int n_levels, const int *n_cell_host,
+                          const int *heights_host, const int *widths_host, const int *strides_host,
+                          void *out_dev, int out_f64, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * IoU matrices — replaces libs/boxes/bbox.pyx:15-55 / :57-94 / :96-135.  float64 in, float64
+ * out, identical operation order (bit-exact).
+ * ------------------------------------------------------------------------------------------- */
+int detbox_bbox_overlaps_f64(const double *boxes_dev, long n, const double *query_dev, long k,
+                             double *out_dev /*[n,k]*/, void *stream);
+int detbox_bbox_intersections_f64(const double *boxes_dev, long n, const double *query_dev, long k,
+                                  double *out_dev /*[n,k]*/, void *stream);
+int detbox_bbox_exclude_ignored_f64(const double *boxes_dev, long n, const double *ignored_dev, long k,
+                                    double threshold, int64_t *out_dev /*[n]*/, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Box encode / decode — replaces libs/boxes/bbox_transform.py:11-41,43-76,78-91,93-144 and
+ * libs/layers/box.py:72-145 (decoding_box / encoding_box).  float32.
+ * decode clips to [0,im_w-1]x[0,im_h-1] when im_h > 0 (clip_boxes), else no clip (torch path).
+ * ------------------------------------------------------------------------------------------- */
+int detbox_box_encode(const float *anchors_dev, const float *gt_dev, long n, int encoding,
+                      float *out_dev, void *stream);
+int detbox_box_decode(const float *anchors_dev, const float *deltas_dev, long n, int encoding,
+                      int im_h, int im_w, float *out_dev, void *stream);
+/* in-place clip_boxes (bbox_transform.py:78-91) on [n, 4*k] rows */
+int detbox_clip_boxes(float *boxes_dev, long n, int k, int im_h, int im_w, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Anchor-target assignment — replaces libs/layers/anchor.py:17-145 (encode, 'simple' sampling)
+ * and its batch wrapper libs/layers/data_layer.py:228-239; supersedes the disabled
+ * libs/layers/anchor_target CUDA layer.  Fused: no [A,G] overlap matrix is materialised.
+ * IoU in float64 (bit-exact labels), targets in float32.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct {
+    double bg_threshold;        /* cfg.rpn_bg_threshold */
+    double fg_threshold;        /* cfg.rpn_fg_threshold */
+    double ignore_fraction;     /* cfg.ignored_area_intersection_fraction */
+    int    clobber_positives;   /* cfg.rpn_clobber_positives */
+    int    box_encoding;        /* DETBOX_ENC_FASTRCNN | DETBOX_ENC_LINEAR */
+    float  bbweights[4];        /* cfg.bbweights */
+} detbox_target_cfg;
+
+size_t detbox_anchor_target_workspace_bytes(int batch, long total_gt);
+/* anchors_dev [A,4] shared by the batch; gt_dev [total_gt,5] = (x1,y1,x2,y2,cls), images
+ * concatenated; gt_offsets_dev int32 [batch+1].  Outputs [batch,A], [batch,A], [batch,A,4],
+ * [batch,A,4].  counts_dev (optional, may be NULL): int32 [batch,2] = (#fg, #bg). */
+int detbox_anchor_target(const float *anchors_dev, long A, const float *gt_dev,
+                         const int32_t *gt_offsets_dev, int batch, long total_gt,
+                         const detbox_target_cfg *cfg,
+                         float *labels_dev, float *label_weights_dev, float *bbox_targets_dev,
+                         float *bbox_inside_weights_dev, int32_t *counts_dev,
+                         void *workspace_dev, size_t workspace_bytes, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Objectness + top-k + gather + decode — replaces detection_model._decode_and_choose_top_n_stage1
+ * (libs/nets/model.py:308-321) incl. _objectness (:54-61).  One stable descending selection
+ * over batch x levels x anchors (per_image == 0, the reference's behaviour) or inside every
+ * image (per_image == 1, the sharded mode).  Ties: lower flat index first.
+ * Outputs are score-descending (image-major when per_image): boxes [K,4], probs [K,C],
+ * img_ids int64 [K], sel_anchors [K,4], flat_idx int64 [K], scores [K];  K = min(top_n, batch*A)
+ * (per_image: K = batch * min(top_n, A)).  Any output pointer except boxes may be NULL.
+ * ------------------------------------------------------------------------------------------- */
+size_t detbox_topk_decode_workspace_bytes(int batch, long A, long top_n, int per_image);
+int detbox_topk_decode(const float *prob_dev, int C, const float *deltas_dev, const float *anchors_dev,
+                       int batch, long A, int activation, long top_n, int per_image, int encoding,
+                       float *boxes_dev, float *probs_dev, int64_t *img_ids_dev, float *sel_anchors_dev,
+                       int64_t *flat_idx_dev, float *scores_dev,
+                       void *workspace_dev, size_t workspace_bytes, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Stable radix sort of float32 scores, descending (ties: lower index first).  Exposed because
+ * the reference's callers sort explicitly (libs/layers/box.py:160, libs/nms/gpu_nms.pyx:25).
+ * order_dev int32 [n] receives the permutation.  Segments (optional): seg_offsets_dev int32
+ * [n_seg+1] sorts every segment independently (indices stay global).
+ * ------------------------------------------------------------------------------------------- */
+size_t detbox_sort_desc_workspace_bytes(long n);
+int detbox_sort_desc(const float *scores_dev, long n, int32_t *order_dev,
+                     void *workspace_dev, size_t workspace_bytes, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * NMS — replaces libs/nms/gpu_nms.pyx + nms_kernel.cu:46-155, libs/nms/cpu_nms.pyx:17-68,
+ * libs/layers/box.py:148-173 (apply_nms) + libs/layers/nms/src/{nms_cpu.c,nms_cuda.c,
+ * nms_cuda_kernel.cu}, and the per-image loop of libs/nets/model.py:343-355
+ * (_apply_nms_in_batch) through segments.  Sorting, bitmask and the greedy scan all run on the
+ * device; nothing is copied to the host.
+ * boxes_dev [n, box_stride] (x1,y1,x2,y2 first), scores_dev [n].  seg_ids_dev: int32 [n], the
+ * segment (image id) of every row, values in [0,n_seg); rows of different segments never
+ * suppress each other (NULL or n_seg <= 1: one segment).  Rows need not be grouped.
+ * keep_dev int64 [n]: kept ORIGINAL row indices, segment-major, score-descending inside a
+ * segment.  n_keep_dev int32 [n_seg+1]: [0..n_seg) per-segment counts, [n_seg] the total
+ * (n_seg == 1: both entries hold the total).
+ * ------------------------------------------------------------------------------------------- */
+size_t detbox_nms_workspace_bytes(long n, int n_seg);
+int detbox_nms(const float *boxes_dev, int box_stride, const float *scores_dev, long n,
+               const int32_t *seg_ids_dev, int n_seg, double thresh, int cmp_mode,
+               int64_t *keep_dev, int32_t *n_keep_dev,
+               void *workspace_dev, size_t workspace_bytes, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * RoIAlign over FPN levels, forward and backward — replaces
+ *   roi_align_tf: crop_and_resize.c:6-268, crop_and_resize_kernel.cu:10-165, roi_align_tf.py:16-42
+ *   roi_align   : roi_align_kernel.cu:15-153, modules/roi_align.py:11-46 (Avg/Max fused)
+ *   pyramid     : pyramid_roi_align.py:30-60 (level-assigned) and :82-91 (all levels)
+ * One launch covers all levels: level[r] comes from levels_dev (int32 [R]) or, when NULL and
+ * n_levels > 1, is computed in-kernel from ref_areas (pyramid_roi_align.py:33-37); output is
+ * written in the caller's RoI order.  all_levels != 0: every RoI on every level, channel-
+ * concatenated ([R, n_levels*C, PH, PW]).
+ * ------------------------------------------------------------------------------------------- */
+typedef struct {
+    int n_levels;
+    const float *feat[DETBOX_MAX_LEVELS];   /* device, [B,C,H_l,W_l] in `layout`          */
+    float *grad_feat[DETBOX_MAX_LEVELS];    /* device, same shapes (backward only)         */
+    int height[DETBOX_MAX_LEVELS], width[DETBOX_MAX_LEVELS];
+    float spatial_scale[DETBOX_MAX_LEVELS];
+    float ref_area[DETBOX_MAX_LEVELS];      /* (mean(anchor_scales[l])*anchor_base)^2       */
+    int batch, channels;
+    int layout;                             /* DETBOX_LAYOUT_*  of feat / grad_feat         */
+    int out_layout;                         /* DETBOX_LAYOUT_*  of out / grad_out           */
+    int pooled_h, pooled_w;                 /* OUTPUT size (after the optional 2x2 pool)    */
+    int mode;                               /* DETBOX_ROI_*                                 */
+    int pool;                               /* DETBOX_POOL_*  (grid-point mode only)        */
+    int all_levels;
+} detbox_roi_cfg;
+
+int detbox_roi_align_forward(const detbox_roi_cfg *cfg, const float *rois_dev /*[R,5] b,x1,y1,x2,y2*/,
+                             long R, const int32_t *levels_dev, float *out_dev, void *stream);
+/* grad_feat buffers are ACCUMULATED into; zero_grad != 0 clears them first (the reference's
+ * contract: functions/roi_align.py:43, crop_and_resize_gpu.c:57). */
+int detbox_roi_align_backward(const detbox_roi_cfg *cfg, const float *rois_dev, long R,
+                              const int32_t *levels_dev, const float *grad_out_dev, int zero_grad,
+                              void *stream);
+/* level assignment alone (pyramid_roi_align.py:33-37) */
+int detbox_assign_levels(const float *boxes_dev /*[R,4]*/, long R, const float *ref_areas_host, int n_levels,
+                         int32_t *levels_dev, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * HOST-buffer entry points (copies inside; synchronous; scratch cached per device).
+ * ------------------------------------------------------------------------------------------- */
+/* Exactly the reference's FFI symbol `_nms` (libs/nms/gpu_nms.hpp:1-2, bound by gpu_nms.pyx:14):
+ * boxes_host [n, boxes_dim>=5] ALREADY SORTED by descending score; keep_out receives indices
+ * into that sorted array; comparator '>' with a float threshold. */
+void _nms(int *keep_out, int *num_out, const float *boxes_host, int boxes_num, int boxes_dim,
+          float nms_overlap_thresh, int device_id);
+/* Unsorted dets [n,5] in, kept ORIGINAL indices out (what gpu_nms.pyx / cpu_nms.pyx return). */
+int detbox_nms_host(const float *dets_host, int n, double thresh, int cmp_mode,
+                    int *keep_out_host, int *num_out_host, int device_id);
+/* libs/layers/anchor.py:17 encode() for one image with host arrays in and out. */
+int detbox_anchor_target_host(const float *anchors_host, long A, const float *gt_host, int G,
+                              const detbox_target_cfg *cfg, float *labels_host, float *label_weights_host,
+                              float *bbox_targets_host, float *bbox_inside_weights_host, int device_id);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DETBOX_H */
