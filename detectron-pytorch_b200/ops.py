@@ -1,0 +1,196 @@
+"""Device-tensor operators over the C ABI (include/detbox.h).
+
+Every function takes CUDA torch tensors (float32 unless said otherwise), launches hand-written
+sm_100a kernels from libdetbox.so on torch's CURRENT stream and returns CUDA tensors.  PyTorch is
+used for device memory and streams only — there is no eager/torch fallback: a CPU tensor raises.
+The reference-shaped wrappers (module paths, NumPy in/out, autograd Functions) live in
+``libs/`` next to this file and call these.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import check, lib
+
+ENC = {"fastrcnn": 0, "linear": 1, "simple": 2}
+ACT = {"softmax": 0, "sigmoid": 1}
+NMS_GE_F64, NMS_GE_F32, NMS_GT_F32 = 0, 1, 2
+ROI_BIN_CENTRE, ROI_GRID_POINT = 0, 1
+POOL = {None: 0, "none": 0, "avg": 1, "max": 2}
+
+_launches = 0          # kernels launched through this module (bench.py reports it)
+
+
+def launches() -> int:
+    return _launches
+
+
+def _count(n: int):
+    global _launches
+    _launches += n
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _dev(t: torch.Tensor, dtype=torch.float32, name="tensor") -> torch.Tensor:
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise _lib.DetboxError("%s must be a CUDA tensor: detbox has no CPU path" % name)
+    if t.dtype != dtype:
+        t = t.to(dtype)
+    return t.contiguous()
+
+
+def _ptr(t) -> int:
+    return 0 if t is None else t.data_ptr()
+
+
+class _Workspace:
+    """Grow-only per-(device, stream) scratch buffer handed to the *_workspace_bytes() APIs."""
+
+    def __init__(self):
+        self.bufs = {}
+
+    def get(self, nbytes: int, device) -> torch.Tensor:
+        key = (device.index, _stream())
+        buf = self.bufs.get(key)
+        if buf is None or buf.numel() < nbytes:
+            buf = torch.empty(int(nbytes * 1.25) + 1024, dtype=torch.uint8, device=device)
+            self.bufs[key] = buf
+        return buf
+
+
+_ws = _Workspace()
+
+
+# ---------------------------------------------------------------------------------- anchors ----
+def base_anchors(scales, ratios, base) -> np.ndarray:
+    """libs/boxes/anchor.py:101-103 (host, float64 [n_ratios*n_scales, 4])."""
+    s = np.ascontiguousarray(scales, np.float64).ravel()
+    r = np.ascontiguousarray(ratios, np.float64).ravel()
+    out = np.empty((r.size * s.size, 4), np.float64)
+    check(lib().detbox_base_anchors_host(s.ctypes.data_as(_lib.P_double), s.size, r.ctypes.data_as(_lib.P_double),
+                                         r.size, int(base), out.ctypes.data_as(_lib.P_double)), "base_anchors")
+    return out
+
+
+def anchor_pyramid(strides, ih, iw, anchor_scales, anchor_ratios, anchor_base, anchor_shift=((0.0, 0.0),),
+                   device="cuda", dtype=torch.float32) -> torch.Tensor:
+    """libs/boxes/anchor.py:30-44 on the device: [sum_l H_l*W_l*A, 4], level -> y -> x -> (shift, ratio, scale)."""
+    sh = np.asarray(anchor_shift, np.float64).reshape(-1, 2)
+    cells, n_cell, hs, ws = [], [], [], []
+    for i, stride in enumerate(strides):
+        sc = anchor_scales[i] if isinstance(anchor_scales[i], (list, tuple, np.ndarray)) else anchor_scales
+        base = base_anchors(sc, anchor_ratios, anchor_base)
+        shift4 = np.hstack((sh, sh)) * stride                      # anchor.py:54-55
+        cell = np.vstack([base + s for s in shift4])
+        cells.append(cell); n_cell.append(cell.shape[0])
+        hs.append(int(ih / stride)); ws.append(int(iw / stride))
+    L = len(strides)
+    cell_dev = torch.from_numpy(np.vstack(cells)).to(device)
+    total = sum(h * w * n for h, w, n in zip(hs, ws, n_cell))
+    out = torch.empty((total, 4), dtype=dtype, device=cell_dev.device)
+    arr = lambda v: (ctypes.c_int * L)(*[int(x) for x in v])
+    check(lib().detbox_anchor_pyramid(cell_dev.data_ptr(), L, arr(n_cell), arr(hs), arr(ws), arr(strides),
+                                      out.data_ptr(), 1 if dtype == torch.float64 else 0, _stream()), "anchor_pyramid")
+    _count(1)
+    return out
+
+
+# -------------------------------------------------------------------------------------- IoU ----
+def _pairwise(fn, boxes, query):
+    b, q = _dev(boxes, torch.float64, "boxes")[:, :4].contiguous(), _dev(query, torch.float64, "query_boxes")[:, :4].contiguous()
+    out = torch.empty((b.shape[0], q.shape[0]), dtype=torch.float64, device=b.device)
+    check(fn(b.data_ptr(), b.shape[0], q.data_ptr(), q.shape[0], out.data_ptr(), _stream()), "pairwise")
+    _count(1)
+    return out
+
+
+def bbox_overlaps(boxes, query_boxes):
+    """libs/boxes/bbox.pyx:15-55: float64 [N,K] IoU, +1 convention, bit-exact."""
+    return _pairwise(lib().detbox_bbox_overlaps_f64, boxes, query_boxes)
+
+
+def bbox_intersections(boxes, query_boxes):
+    """libs/boxes/bbox.pyx:57-94: inter / area(query)."""
+    return _pairwise(lib().detbox_bbox_intersections_f64, boxes, query_boxes)
+
+
+def bbox_exclude_ignored_areas(boxes, ignored, threshold):
+    """libs/boxes/bbox.pyx:96-135 -> int64 [N]."""
+    b, q = _dev(boxes, torch.float64)[:, :4].contiguous(), _dev(ignored, torch.float64)[:, :4].contiguous()
+    out = torch.empty((b.shape[0],), dtype=torch.int64, device=b.device)
+    check(lib().detbox_bbox_exclude_ignored_f64(b.data_ptr(), b.shape[0], q.data_ptr(), q.shape[0], float(threshold),
+                                                out.data_ptr(), _stream()), "bbox_exclude_ignored_areas")
+    _count(1)
+    return out
+
+
+# ---------------------------------------------------------------------------- encode/decode ----
+def box_encode(anchors, gt_boxes, box_encoding="fastrcnn"):
+    """libs/boxes/bbox_transform.py:11-41 / libs/layers/box.py:112-145."""
+    a, g = _dev(anchors).view(-1, 4), _dev(gt_boxes)[:, :4].contiguous()
+    out = torch.empty_like(a)
+    check(lib().detbox_box_encode(a.data_ptr(), g.data_ptr(), a.shape[0], ENC[box_encoding], out.data_ptr(), _stream()), "box_encode")
+    _count(1)
+    return out
+
+
+def box_decode(anchors, deltas, box_encoding="fastrcnn", im_shape=None):
+    """libs/boxes/bbox_transform.py:43-76 (+ clip :78-91 when im_shape=(ih, iw)) / libs/layers/box.py:72-109."""
+    a, d = _dev(anchors).view(-1, 4), _dev(deltas).view(-1, 4)
+    out = torch.empty_like(d)
+    ih, iw = (0, 0) if im_shape is None else (int(im_shape[0]), int(im_shape[1]))
+    check(lib().detbox_box_decode(a.data_ptr(), d.data_ptr(), d.shape[0], ENC[box_encoding], ih, iw, out.data_ptr(), _stream()), "box_decode")
+    _count(1)
+    return out
+
+
+def clip_boxes_(boxes, im_shape):
+    """libs/boxes/bbox_transform.py:78-91, in place on a contiguous [n, 4k] float32 CUDA tensor."""
+    if not (boxes.is_cuda and boxes.dtype == torch.float32 and boxes.is_contiguous()):
+        raise _lib.DetboxError("clip_boxes_ needs a contiguous float32 CUDA tensor")
+    n, k4 = boxes.shape
+    check(lib().detbox_clip_boxes(boxes.data_ptr(), n, k4 // 4, int(im_shape[0]), int(im_shape[1]), _stream()), "clip_boxes")
+    _count(1)
+    return boxes
+
+
+# ---------------------------------------------------------------------------- anchor target ----
+def make_target_cfg(bg, fg, clobber=True, ignore_fraction=0.3, bbweights=(1., 1., 1., 1.), box_encoding="fastrcnn"):
+    c = _lib.TargetCfg()
+    c.bg_threshold, c.fg_threshold, c.ignore_fraction = float(bg), float(fg), float(ignore_fraction)
+    c.clobber_positives, c.box_encoding = int(bool(clobber)), ENC[box_encoding]
+    for i in range(4):
+        c.bbweights[i] = float(bbweights[i])
+    return c
+
+
+def anchor_target(anchors, gt, gt_offsets, tcfg, return_counts=False):
+    """Batched libs/layers/anchor.py:17-145.  anchors [A,4]; gt [sumG,5] (images concatenated);
+    gt_offsets int32 [B+1] (CUDA).  Returns labels [B,A], label_weights [B,A], bbox_targets [B,A,4],
+    bbox_inside_weights [B,A,4] (+ counts int32 [B,2] = (#fg, #bg))."""
+    a = _dev(anchors).view(-1, 4)
+    g = _dev(gt).view(-1, 5)
+    off = _dev(gt_offsets, torch.int32, "gt_offsets")
+    B, A, G = off.numel() - 1, a.shape[0], g.shape[0]
+    dev = a.device
+    labels = torch.empty((B, A), dtype=torch.float32, device=dev)
+    lw = torch.empty((B, A), dtype=torch.float32, device=dev)
+    bt = torch.empty((B, A, 4), dtype=torch.float32, device=dev)
+    bw = torch.empty((B, A, 4), dtype=torch.float32, device=dev)
+    counts = torch.empty((B, 2), dtype=torch.int32, device=dev) if return_counts else None
+    nbytes = lib().detbox_anchor_target_workspace_bytes(B, G)
+    ws = _ws.get(nbytes, dev)
+    check(lib().detbox_anchor_target(a.data_ptr(), A, g.data_ptr() if G else 0, off.data_ptr(), B, G, ctypes.byref(tcfg),
+                                     labels.data_ptr(), lw.data_ptr(), bt.data_ptr(), bw.data_ptr(), _ptr(counts),
+                                     ws.data_ptr(), ws.numel(), _stream()), "anchor_target")
+    _count(3 if G else 2)
+    if return_counts:
+        return labels, lw, bt, bw, counts
+    return labels, lw, bt, bw

@@ -1,0 +1,85 @@
+"""Post-processing operators: stable sort, objectness top-k + decode, NMS (device tensors in/out).
+See ops.py for the conventions."""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from ._lib import check, lib
+from .ops import ACT, ENC, NMS_GE_F32, NMS_GE_F64, NMS_GT_F32, _count, _dev, _ptr, _stream, _ws  # noqa: F401
+
+
+def sort_desc(scores):
+    """Stable descending argsort of float32 scores (ties: lower index first) -> int32 [n].
+    The explicit sorts of libs/layers/box.py:160 and libs/nms/gpu_nms.pyx:25."""
+    s = _dev(scores).view(-1)
+    n = s.numel()
+    order = torch.empty((n,), dtype=torch.int32, device=s.device)
+    if n == 0:
+        return order
+    ws = _ws.get(lib().detbox_sort_desc_workspace_bytes(n), s.device)
+    check(lib().detbox_sort_desc(s.data_ptr(), n, order.data_ptr(), ws.data_ptr(), ws.numel(), _stream()), "sort_desc")
+    _count(13)
+    return order
+
+
+def topk_decode(rpn_box, rpn_prob, anchors, top_n, activation="softmax", box_encoding="fastrcnn",
+                per_image=False, want=("probs", "img_ids", "anchors")):
+    """detection_model._decode_and_choose_top_n_stage1 (libs/nets/model.py:308-321).
+    rpn_box [B*A,4], rpn_prob [B*A,C], anchors [A,4].  Returns a dict with 'boxes' [K,4] and, as
+    requested in `want`, 'probs' [K,C], 'img_ids' int64 [K], 'anchors' [K,4], 'flat_idx' int64 [K],
+    'scores' [K]; K = min(top_n, B*A) (per_image: B*min(top_n, A), image-major)."""
+    box, prob, anc = _dev(rpn_box).view(-1, 4), _dev(rpn_prob), _dev(anchors).view(-1, 4)
+    if prob.dim() == 1:
+        prob = prob.view(-1, 1)
+    N, C, A = box.shape[0], prob.shape[1], anc.shape[0]
+    if A == 0 or N % A or prob.shape[0] != N:
+        raise _lib.DetboxError("topk_decode: rows of rpn_box/rpn_prob (%d/%d) must be a multiple of the anchors (%d)"
+                               % (N, prob.shape[0], A))
+    B = N // A
+    K = B * min(int(top_n), A) if per_image else min(int(top_n), N)
+    dev = box.device
+    out = {"boxes": torch.empty((K, 4), dtype=torch.float32, device=dev)}
+    if "probs" in want:
+        out["probs"] = torch.empty((K, C), dtype=torch.float32, device=dev)
+    if "img_ids" in want:
+        out["img_ids"] = torch.empty((K,), dtype=torch.int64, device=dev)
+    if "anchors" in want:
+        out["anchors"] = torch.empty((K, 4), dtype=torch.float32, device=dev)
+    if "flat_idx" in want:
+        out["flat_idx"] = torch.empty((K,), dtype=torch.int64, device=dev)
+    if "scores" in want:
+        out["scores"] = torch.empty((K,), dtype=torch.float32, device=dev)
+    if K == 0:
+        return out
+    ws = _ws.get(lib().detbox_topk_decode_workspace_bytes(B, A, int(top_n), int(per_image)), dev)
+    check(lib().detbox_topk_decode(prob.data_ptr(), C, box.data_ptr(), anc.data_ptr(), B, A, ACT[activation], int(top_n),
+                                   int(per_image), ENC[box_encoding], out["boxes"].data_ptr(), _ptr(out.get("probs")),
+                                   _ptr(out.get("img_ids")), _ptr(out.get("anchors")), _ptr(out.get("flat_idx")),
+                                   _ptr(out.get("scores")), ws.data_ptr(), ws.numel(), _stream()), "topk_decode")
+    _count(24 + (3 if per_image and B > 1 else 0))
+    return out
+
+
+def nms(boxes, scores, thresh, cmp_mode=NMS_GT_F32, seg_ids=None, n_seg=1, return_counts=False):
+    """Greedy NMS on the device.  boxes [n,>=4], scores [n] -> (keep int64 [n] buffer, n_keep int32
+    [n_seg+1] on the device); no host synchronisation happens here.  keep[:n_keep[n_seg]] are the
+    kept ORIGINAL row indices, segment-major, score-descending inside a segment."""
+    b, s = _dev(boxes), _dev(scores).view(-1)
+    n = b.shape[0]
+    if s.numel() != n:
+        raise _lib.DetboxError("nms: %d boxes but %d scores" % (n, s.numel()))
+    seg = None
+    if seg_ids is not None and n_seg > 1:
+        seg = _dev(seg_ids, torch.int32, "seg_ids").view(-1)
+    else:
+        n_seg = 1
+    keep = torch.empty((n,), dtype=torch.int64, device=b.device)
+    n_keep = torch.zeros((n_seg + 1,), dtype=torch.int32, device=b.device)
+    if n == 0:
+        return keep, n_keep
+    ws = _ws.get(lib().detbox_nms_workspace_bytes(n, n_seg), b.device)
+    check(lib().detbox_nms(b.data_ptr(), b.shape[1], s.data_ptr(), n, _ptr(seg), n_seg, float(thresh), int(cmp_mode),
+                           keep.data_ptr(), n_keep.data_ptr(), ws.data_ptr(), ws.numel(), _stream()), "nms")
+    _count(13 + 4 + (5 if n_seg > 1 else 0))
+    return keep, n_keep

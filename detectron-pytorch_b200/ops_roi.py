@@ -1,0 +1,119 @@
+"""RoIAlign operators over FPN levels (device tensors in/out).  See ops.py for the conventions."""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import check, lib
+from .ops import POOL, ROI_BIN_CENTRE, ROI_GRID_POINT, _count, _dev, _ptr, _stream  # noqa: F401
+
+
+def _is_channels_last(t: torch.Tensor) -> bool:
+    return t.dim() == 4 and t.shape[1] > 1 and t.is_contiguous(memory_format=torch.channels_last) \
+        and not t.is_contiguous()
+
+
+def _make_cfg(feats, spatial_scales, ref_areas, ph, pw, mode, pool, all_levels, grads=None):
+    L = len(feats)
+    if not 1 <= L <= _lib.MAX_LEVELS:
+        raise _lib.DetboxError("1..%d pyramid levels supported" % _lib.MAX_LEVELS)
+    nhwc = all(_is_channels_last(f) for f in feats)
+    c = _lib.RoiCfg()
+    c.n_levels = L
+    keep = []
+    B, C = feats[0].shape[0], feats[0].shape[1]
+    for l, f in enumerate(feats):
+        if not f.is_cuda or f.dtype != torch.float32:
+            raise _lib.DetboxError("feature maps must be float32 CUDA tensors: detbox has no CPU path")
+        if f.shape[0] != B or f.shape[1] != C:
+            raise _lib.DetboxError("all levels must share batch and channel sizes")
+        if not nhwc:
+            f = f.contiguous()
+        keep.append(f)
+        c.feat[l] = f.data_ptr()
+        c.height[l], c.width[l] = f.shape[2], f.shape[3]
+        c.spatial_scale[l] = float(spatial_scales[l])
+        c.ref_area[l] = float(ref_areas[l]) if ref_areas is not None else 1.0
+        if grads is not None:
+            c.grad_feat[l] = grads[l].data_ptr()
+    c.batch, c.channels = B, C
+    c.layout = c.out_layout = 1 if nhwc else 0
+    c.pooled_h, c.pooled_w = int(ph), int(pw)
+    c.mode, c.pool, c.all_levels = int(mode), POOL[pool], int(bool(all_levels))
+    return c, keep, nhwc
+
+
+def _out_tensor(R, C, ph, pw, nhwc, device):
+    if nhwc:
+        return torch.empty((R, ph, pw, C), dtype=torch.float32, device=device).permute(0, 3, 1, 2)
+    return torch.empty((R, C, ph, pw), dtype=torch.float32, device=device)
+
+
+def roi_align_forward(feats, rois, spatial_scales, ph, pw, mode=ROI_BIN_CENTRE, pool=None,
+                      levels=None, ref_areas=None, all_levels=False):
+    """One launch over all pyramid levels.  feats: list of [B,C,H_l,W_l] (all NCHW-contiguous or all
+    channels_last); rois [R,5] = (batch idx, x1, y1, x2, y2) in image coordinates.  Level of a RoI:
+    `levels` (int32 [R]) if given, else computed in-kernel from ref_areas when there are several
+    levels (pyramid_roi_align.py:33-37).  Output [R, C (or L*C), ph, pw] in the input's memory format."""
+    r = _dev(rois).view(-1, 5)
+    cfg, keep, nhwc = _make_cfg(feats, spatial_scales, ref_areas, ph, pw, mode, pool, all_levels)
+    if len(feats) > 1 and not all_levels and levels is None and ref_areas is None:
+        raise _lib.DetboxError("several levels need `levels`, `ref_areas` or all_levels=True")
+    lv = _dev(levels, torch.int32, "levels").view(-1) if levels is not None else None
+    Ctot = cfg.channels * (len(feats) if all_levels else 1)
+    out = _out_tensor(r.shape[0], Ctot, ph, pw, nhwc, r.device)
+    check(lib().detbox_roi_align_forward(ctypes.byref(cfg), r.data_ptr(), r.shape[0], _ptr(lv), out.data_ptr(), _stream()),
+          "roi_align_forward")
+    _count(1)
+    return out
+
+
+def roi_align_backward(grad_out, feat_shapes, rois, spatial_scales, mode=ROI_BIN_CENTRE, levels=None,
+                       ref_areas=None, all_levels=False, channels_last=False, grads=None):
+    """Gradient w.r.t. the feature maps (dense, zero-filled here unless `grads` is given, in which
+    case it is accumulated into).  grad_out [R, C(or L*C), ph, pw] in the same memory format as the
+    features.  Returns the list of gradient maps."""
+    r = _dev(rois).view(-1, 5)
+    dev = r.device
+    g = grad_out
+    if not g.is_cuda or g.dtype != torch.float32:
+        raise _lib.DetboxError("grad_out must be a float32 CUDA tensor")
+    g = g.contiguous(memory_format=torch.channels_last) if channels_last else g.contiguous()
+    zero = grads is None
+    if grads is None:
+        grads = []
+        for (B, C, H, W) in feat_shapes:
+            t = torch.empty((B, H, W, C), dtype=torch.float32, device=dev).permute(0, 3, 1, 2) if channels_last \
+                else torch.empty((B, C, H, W), dtype=torch.float32, device=dev)
+            grads.append(t)
+    L = len(grads)
+    c = _lib.RoiCfg()
+    c.n_levels = L
+    for l, t in enumerate(grads):
+        c.grad_feat[l] = t.data_ptr()
+        c.height[l], c.width[l] = t.shape[2], t.shape[3]
+        c.spatial_scale[l] = float(spatial_scales[l])
+        c.ref_area[l] = float(ref_areas[l]) if ref_areas is not None else 1.0
+    c.batch, c.channels = grads[0].shape[0], grads[0].shape[1]
+    c.layout = c.out_layout = 1 if channels_last else 0
+    c.pooled_h, c.pooled_w = g.shape[2], g.shape[3]
+    c.mode, c.pool, c.all_levels = int(mode), 0, int(bool(all_levels))
+    lv = _dev(levels, torch.int32, "levels").view(-1) if levels is not None else None
+    check(lib().detbox_roi_align_backward(ctypes.byref(c), r.data_ptr(), r.shape[0], _ptr(lv), g.data_ptr(), int(zero), _stream()),
+          "roi_align_backward")
+    _count(1 + (L if zero else 0))
+    return grads
+
+
+def assign_levels(bboxes, ref_areas):
+    """pyramid_roi_align.py:33-37 -> int32 [R] FPN level per box."""
+    b = _dev(bboxes)[:, :4].contiguous()
+    ra = np.ascontiguousarray(ref_areas, np.float32)
+    out = torch.empty((b.shape[0],), dtype=torch.int32, device=b.device)
+    check(lib().detbox_assign_levels(b.data_ptr(), b.shape[0], ra.ctypes.data_as(_lib.P_float), int(ra.size), out.data_ptr(), _stream()),
+          "assign_levels")
+    _count(1)
+    return out

@@ -1,0 +1,67 @@
+"""CPU-only checks of the drop-in boundary: libdetbox.so loads, exports every symbol that
+include/detbox.h declares, the ctypes prototypes cover them all, and the host-side pieces
+(base anchors, argument validation that returns before any CUDA call) behave."""
+import ctypes
+import os
+import re
+
+import numpy as np
+
+import detbox
+from detbox import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def header_symbols():
+    text = open(os.path.join(ROOT, "include", "detbox.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    names = re.findall(r"^\s*(?:const\s+char\s*\*\s*|(?:int|size_t|void)\s+)([A-Za-z_]\w*)\s*\(", text, flags=re.M)
+    return sorted(set(names))
+
+
+def test_library_exports_every_declared_symbol():
+    names = header_symbols()
+    assert len(names) >= 25 and "_nms" in names and "detbox_anchor_target" in names
+    L = ctypes.CDLL(_lib.LIB_PATH)
+    missing = [n for n in names if not hasattr(L, n)]
+    assert not missing, "declared in detbox.h but not exported: %s" % missing
+
+
+def test_ctypes_prototypes_cover_the_header():
+    assert sorted(_lib.SIGNATURES) == header_symbols()
+    detbox.lib()        # attaches every prototype; raises if one cannot be resolved
+
+
+def test_struct_layouts_match_header():
+    assert ctypes.sizeof(_lib.TargetCfg) == 3 * 8 + 2 * 4 + 4 * 4
+    # n_levels(4)+pad(4) + 2*8 pointers*8 + 4*8*4 + 9*4 -> multiple of 8
+    assert ctypes.sizeof(_lib.RoiCfg) == 8 + 2 * 8 * 8 + 4 * 8 * 4 + 9 * 4 + 4
+
+
+def test_base_anchors_host(golden):
+    g = golden("anchors")
+    np.testing.assert_array_equal(detbox.base_anchors([2., 4., 8., 16., 32.], [0.5, 1, 2.0], 16), g["base_default"])
+    np.testing.assert_array_equal(detbox.base_anchors([1.5, 3], [0.5, 1, 2.0, 3.0], 15), g["base_odd15"])
+
+
+def test_argument_validation_without_gpu():
+    L = detbox.lib()
+    assert L.detbox_error_string(0) == b"ok"
+    assert L.detbox_box_encode(None, None, -1, 0, None, None) == -1          # DETBOX_ERR_INVALID
+    assert L.detbox_box_decode(None, None, 5, 9, 0, 0, None, None) == -1
+    assert L.detbox_nms_workspace_bytes(0, 1) > 0
+    n = 20000
+    need = L.detbox_nms_workspace_bytes(n, 1)
+    assert need >= n * ((n + 63) // 64) * 8                                  # the bitmask dominates
+    assert L.detbox_topk_decode_workspace_bytes(64, 261888, 900, 1) >= 64 * 261888 * 4
+    assert b"workspace" in L.detbox_error_string(-2)
+
+
+def test_ops_refuse_cpu_tensors():
+    import pytest
+    import torch
+    with pytest.raises(detbox.DetboxError):
+        detbox.nms(torch.zeros(3, 4), torch.zeros(3), 0.5)
+    with pytest.raises(detbox.DetboxError):
+        detbox.bbox_overlaps(torch.zeros(3, 4, dtype=torch.float64), torch.zeros(2, 4, dtype=torch.float64))

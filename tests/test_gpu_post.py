@@ -1,0 +1,244 @@
+"""GPU parity for the post-processing half of the path: stable sort, objectness top-k + decode,
+NMS (device and host-buffer entry points), against the CPU oracle and the golden keep lists that
+came from the reference's own cpu_nms / py_cpu_nms.  Index results are BIT-EXACT."""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+import detbox
+from oracle import oracle as O
+from util import assert_boxes_close
+
+pytestmark = pytest.mark.gpu
+
+
+def cu(a, dtype=None):
+    t = torch.from_numpy(np.ascontiguousarray(a))
+    if dtype is not None:
+        t = t.to(dtype)
+    return t.cuda()
+
+
+def keep_list(keep, n_keep):
+    nk = n_keep.cpu().numpy()
+    return keep.cpu().numpy()[:nk[-1]], nk
+
+
+# ------------------------------------------------------------------------------------- sort ----
+@pytest.mark.parametrize("n", [1, 31, 2048, 2049, 70001, 1500000])
+def test_sort_desc(n):
+    rng = np.random.RandomState(n)
+    s = rng.randn(n).astype(np.float32)
+    if n > 100:
+        s[rng.randint(0, n, n // 3)] = s[rng.randint(0, n, n // 3)]       # ties
+        s[:7] = [0.0, -0.0, np.inf, -np.inf, 1e-40, -1e-40, 3.0]
+    got = detbox.sort_desc(cu(s)).cpu().numpy()
+    srt = s[got]
+    assert (srt[:-1] >= srt[1:]).all()                                      # sortedness
+    assert np.array_equal(np.sort(got), np.arange(n))                       # a permutation
+    eq = srt[:-1] == srt[1:]
+    signs_equal = np.signbit(srt[:-1]) == np.signbit(srt[1:])
+    assert (got[:-1][eq & signs_equal] < got[1:][eq & signs_equal]).all()   # stable: ties by index
+    if n <= 70001:
+        s2 = s.copy(); s2[s2 == 0] = 0.0
+        want = O.stable_desc_order(np.where(np.signbit(s) & (s == 0), -1e-45, s).astype(np.float64))
+        # (-0.0 sorts after +0.0 in the key order: the documented total order on bit patterns)
+        np.testing.assert_array_equal(got, want)
+
+
+# ------------------------------------------------------------------------------------ top-k ----
+def make_head_outputs(rng, B, A, C, activation, ties=False):
+    deltas = rng.normal(0, 0.5, (B * A, 4)).astype(np.float32)
+    logits = rng.normal(-4.6, 1.0, (B * A, C)).astype(np.float32)
+    hot = rng.rand(B * A) < 0.01
+    logits[hot, (1 if activation == "softmax" else 0)] += 6.0
+    if activation == "softmax":
+        e = np.exp(logits - logits.max(1, keepdims=True)); p = (e / e.sum(1, keepdims=True)).astype(np.float32)
+    else:
+        p = (1.0 / (1.0 + np.exp(-logits))).astype(np.float32)
+    if ties:
+        p = np.round(p * 64).astype(np.float32) / 64       # heavy ties: the tie rule decides
+    return deltas, p
+
+
+@pytest.mark.parametrize("B,A,C,act,top_n,per_image,ties", [
+    (1, 5000, 2, "softmax", 900, False, False),
+    (3, 4097, 2, "softmax", 1000, False, True),
+    (4, 3000, 2, "softmax", 300, True, True),
+    (2, 6000, 80, "sigmoid", 900, False, False),
+    (5, 2500, 80, "sigmoid", 400, True, True),
+    (2, 3000, 3, "sigmoid", 7000, False, False),      # top_n > B*A: everything, sorted
+    (2, 300, 81, "softmax", 50, True, False),
+    (1, 261888, 2, "softmax", 900, False, False),     # CP-R size, eval setting (test.py:148)
+    (300, 64, 2, "softmax", 10, True, True),          # > 256 images: two segment passes
+])
+def test_topk_decode(B, A, C, act, top_n, per_image, ties):
+    rng = np.random.RandomState(B * 7 + A)
+    anc = rng.uniform(0, 500, (A, 4)).astype(np.float32); anc[:, 2:] += anc[:, :2]
+    deltas, p = make_head_outputs(rng, B, A, C, act, ties)
+    got = detbox.topk_decode(cu(deltas), cu(p), cu(anc), top_n, act, "fastrcnn", per_image,
+                             want=("probs", "img_ids", "anchors", "flat_idx", "scores"))
+    wb, wp, wi, wa, widx = O.decode_and_choose_top_n(deltas, p, anc, top_n, act, "fastrcnn", per_image)
+    np.testing.assert_array_equal(got["flat_idx"].cpu().numpy(), widx)       # bit-exact selection + order
+    np.testing.assert_array_equal(got["img_ids"].cpu().numpy(), wi)
+    np.testing.assert_array_equal(got["probs"].cpu().numpy(), wp)
+    np.testing.assert_array_equal(got["anchors"].cpu().numpy(), wa)
+    np.testing.assert_array_equal(got["scores"].cpu().numpy(), O.objectness(p, act)[widx])
+    assert_boxes_close(got["boxes"].cpu().numpy(), wb, extra_scale=np.abs(wa).max(1))
+
+
+def test_topk_full_batch_property():
+    """BASELINE size (64 CP-R images, 16.7M anchors): size-independent checks — the selected
+    scores are sorted, every unselected score is <= the k-th, indices are unique."""
+    B, A, k = 64, 261888, 900
+    g = torch.Generator(device="cuda"); g.manual_seed(0)
+    p0 = torch.rand((B * A,), device="cuda", generator=g)
+    prob = torch.stack([p0, 1 - p0], 1).contiguous()
+    deltas = torch.zeros((B * A, 4), device="cuda")
+    anc = torch.rand((A, 4), device="cuda") * 100
+    for per_image in (False, True):
+        out = detbox.topk_decode(deltas, prob, anc, k, "softmax", "fastrcnn", per_image, want=("flat_idx", "scores", "img_ids"))
+        idx, sc = out["flat_idx"], out["scores"]
+        obj = 1.0 - prob[:, 0]
+        assert torch.equal(sc, obj[idx])
+        assert idx.unique().numel() == idx.numel()
+        if per_image:
+            assert idx.numel() == B * k
+            assert torch.equal(out["img_ids"], torch.arange(B, device="cuda").repeat_interleave(k))
+            s2 = sc.view(B, k)
+            assert (s2[:, :-1] >= s2[:, 1:]).all()
+            kth = s2[:, -1]
+            mask = torch.ones(B * A, dtype=torch.bool, device="cuda"); mask[idx] = False
+            assert (obj.view(B, A) <= kth[:, None])[mask.view(B, A)].all()
+        else:
+            assert (sc[:-1] >= sc[1:]).all()
+            assert torch.equal(torch.sort(sc, descending=True)[0], torch.topk(obj, k)[0])
+
+
+# -------------------------------------------------------------------------------------- NMS ----
+MODES = [("ge", O.NMS_GE_F64, detbox.NMS_GE_F64), ("gt", O.NMS_GT_F32, detbox.NMS_GT_F32)]
+
+
+@pytest.mark.parametrize("name", ["rand1k", "rand3k", "clustered2k", "intgrid600"])
+@pytest.mark.parametrize("thr", [0.5, 0.3, 0.7])
+def test_nms_golden(golden, name, thr):
+    g = golden("nms")
+    d = g[name]
+    for tag, _, mode in MODES:
+        keep, nk = keep_list(*detbox.nms(cu(d[:, :4]), cu(d[:, 4]), thr, mode))
+        np.testing.assert_array_equal(keep, g["%s_keep_%s_%g" % (name, tag, thr)])
+    keep, _ = keep_list(*detbox.nms(cu(d), cu(d[:, 4]), thr, detbox.NMS_GE_F32))     # stride-5 rows
+    np.testing.assert_array_equal(keep, O.nms(d[:, :4], d[:, 4], thr, O.NMS_GE_F32))
+
+
+def sweep_boxes(rng, n):
+    h = np.exp(rng.uniform(np.log(12), np.log(264), n)); w = h / 2.44
+    cx, cy = rng.uniform(0, 2048, n), rng.uniform(0, 1024, n)
+    b = np.stack([cx - w / 2, cy - h / 2, cx + w / 2, cy + h / 2], 1)
+    b[:, 0::2] = np.clip(b[:, 0::2], 0, 2047); b[:, 1::2] = np.clip(b[:, 1::2], 0, 1023)
+    return b.astype(np.float32), rng.permutation(np.linspace(0, 1, n)).astype(np.float32)
+
+
+@pytest.mark.parametrize("n", [1, 2, 63, 64, 65, 1000, 5000, 20000])
+def test_nms_sweep_vs_oracle(n):
+    b, s = sweep_boxes(np.random.RandomState(2), n)
+    for _, omode, mode in MODES:
+        keep, nk = keep_list(*detbox.nms(cu(b), cu(s), 0.5, mode))
+        np.testing.assert_array_equal(keep, O.nms(b, s, 0.5, omode))
+        assert nk[0] == nk[1] == keep.size
+
+
+def test_nms_100k_properties():
+    """100k boxes (BASELINE sweep top end; 1.25 GB mask): greedy-NMS invariants that do not need the
+    O(n^2) CPU oracle — kept boxes are mutually below threshold, every dropped box is suppressed by
+    a higher-scored kept box, keep order is score-descending; plus idempotence."""
+    n = 100000
+    b, s = sweep_boxes(np.random.RandomState(3), n)
+    keep, nk = keep_list(*detbox.nms(cu(b), cu(s), 0.5, detbox.NMS_GT_F32))
+    assert (s[keep][:-1] > s[keep][1:]).all()
+    kb = cu(b[keep]).double()
+    iou = detbox.bbox_overlaps(kb, kb)
+    iou.fill_diagonal_(0)
+    assert float(iou.max()) <= 0.5 + 1e-6
+    dropped = np.setdiff1d(np.arange(n), keep)
+    sub = dropped[np.random.RandomState(0).choice(dropped.size, 3000, replace=False)]
+    ov = detbox.bbox_overlaps(cu(b[sub]).double(), kb).cpu().numpy()
+    higher = s[keep][None, :] > s[sub][:, None]
+    assert ((ov > 0.5 - 1e-6) & higher).any(1).all()
+    keep2, _ = keep_list(*detbox.nms(cu(b[keep]), cu(s[keep]), 0.5, detbox.NMS_GT_F32))
+    np.testing.assert_array_equal(keep2, np.arange(keep.size))            # idempotent
+
+
+def test_nms_segments_match_per_image_loop():
+    """_apply_nms_in_batch (model.py:343-355): segments == the reference's per-image Python loop."""
+    rng = np.random.RandomState(9)
+    n, B = 6000, 7
+    b, s = sweep_boxes(rng, n)
+    b = (b / 4).astype(np.float32)                      # denser -> real suppression
+    img = rng.randint(0, B, n).astype(np.int32)
+    img[img == 3] = 4                                   # an empty segment
+    keep, nk = keep_list(*detbox.nms(cu(b), cu(s), 0.5, detbox.NMS_GT_F32, seg_ids=cu(img), n_seg=B))
+    want, counts = [], []
+    for i in range(B):
+        inds = np.nonzero(img == i)[0]
+        k = O.nms(b[inds], s[inds], 0.5, O.NMS_GT_F32) if inds.size else np.zeros(0, np.int64)
+        want.append(inds[k]); counts.append(k.size)
+    np.testing.assert_array_equal(keep, np.concatenate(want))
+    np.testing.assert_array_equal(nk[:B], counts)
+    assert nk[B] == sum(counts)
+    # probs-driven variant through the oracle's composition
+    probs = np.stack([1 - s, s], 1).astype(np.float32)
+    np.testing.assert_array_equal(keep, O.apply_nms_in_batch(b, probs, img, "softmax", 0.5, O.NMS_GT_F32))
+
+
+def test_nms_many_segments():
+    rng = np.random.RandomState(11)
+    n, B = 20000, 300
+    b, s = sweep_boxes(rng, n)
+    b = (b / 8).astype(np.float32)
+    img = rng.randint(0, B, n).astype(np.int32)
+    keep, nk = keep_list(*detbox.nms(cu(b), cu(s), 0.5, detbox.NMS_GE_F64, seg_ids=cu(img), n_seg=B))
+    want = []
+    for i in range(B):
+        inds = np.nonzero(img == i)[0]
+        want.append(inds[O.nms(b[inds], s[inds], 0.5, O.NMS_GE_F64)] if inds.size else np.zeros(0, np.int64))
+    np.testing.assert_array_equal(keep, np.concatenate(want))
+
+
+def test_nms_edge_cases():
+    keep, nk = detbox.nms(torch.zeros((0, 4), device="cuda"), torch.zeros((0,), device="cuda"), 0.5)
+    assert int(nk[-1]) == 0
+    # degenerate boxes (x2 < x1): area <= 0, possibly NaN IoU -> never suppressed
+    b = np.asarray([[10, 10, 5, 5], [10, 10, 5, 5], [0, 0, -1, -1], [0, 0, -1, -1], [1, 1, 8, 8], [1, 1, 8, 8]], np.float32)
+    s = np.asarray([.9, .8, .7, .6, .5, .4], np.float32)
+    for _, omode, mode in MODES:
+        keep, _ = keep_list(*detbox.nms(cu(b), cu(s), 0.5, mode))
+        np.testing.assert_array_equal(keep, O.nms(b, s, 0.5, omode))
+    # thr <= 0 with '>=': everything after the first is suppressed
+    bb, ss = sweep_boxes(np.random.RandomState(1), 500)
+    for thr in (0.0, -1.0):
+        for _, omode, mode in MODES:
+            keep, _ = keep_list(*detbox.nms(cu(bb), cu(ss), thr, mode))
+            np.testing.assert_array_equal(keep, O.nms(bb, ss, thr, omode))
+
+
+def test_reference_ffi_symbol_nms():
+    """`_nms` with the exact signature of libs/nms/gpu_nms.hpp:1-2 (sorted host boxes in, indices
+    into the sorted array out, '>' comparator) and detbox_nms_host (unsorted dets)."""
+    b, s = sweep_boxes(np.random.RandomState(5), 3000)
+    b = (b / 3).astype(np.float32)
+    dets = np.concatenate([b, s[:, None]], 1).astype(np.float32)
+    order = O.stable_desc_order(s)
+    sorted_dets = np.ascontiguousarray(dets[order])
+    keep = np.zeros(3000, np.int32); num = ctypes.c_int(0)
+    p = lambda a: a.ctypes.data_as(ctypes.c_void_p)
+    detbox.lib()._nms(p(keep), ctypes.cast(ctypes.byref(num), ctypes.c_void_p), p(sorted_dets), 3000, 5, ctypes.c_float(0.5), 0)
+    want = O.nms(b, s, 0.5, O.NMS_GT_F32)
+    np.testing.assert_array_equal(order[keep[:num.value]], want)          # gpu_nms.pyx:31 order[keep]
+    keep2 = np.zeros(3000, np.int32); num2 = ctypes.c_int(0)
+    rc = detbox.lib().detbox_nms_host(p(dets), 3000, 0.5, detbox.NMS_GE_F64, p(keep2),
+                                      ctypes.cast(ctypes.byref(num2), ctypes.c_void_p), 0)
+    assert rc == 0
+    np.testing.assert_array_equal(keep2[:num2.value], O.nms(b, s, 0.5, O.NMS_GE_F64))
