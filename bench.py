@@ -1,0 +1,549 @@
+#!/usr/bin/env python
+"""bench.py — box-ops images/s @1024x2048 (BASELINE.json metric), one JSON line on stdout.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl detbox|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+
+A STEP is one pass of the box path over `--batch` (default 64) synthetic CityPersons-shaped
+1024x2048 images PER GPU (BASELINE.json configs[4] sharded per image, weak scaling):
+    anchor pyramid (261,888 anchors) -> anchor-target assignment -> objectness + per-image
+    top-900 + decode -> per-image NMS (IoU 0.5).
+`value`  : images/s with the inputs already resident in HBM (CUDA events, max over ranks).
+`e2e`    : the same step through detbox.pipeline.BoxOpsSession.run_host — pinned HOST buffers in,
+           HOST buffers out, the copies inside the timed region.
+Extra keys report the two other parts of BASELINE.json's metric on configs[1] / configs[2]:
+`nms_us` (1k/5k/20k/100k boxes) and `roi_align` (GB/s fwd / bwd, 4096 RoIs x 256 ch x 7x7, P2-P5).
+`roofline` is the dominant kernel of the step, timed with CUDA events around its launches
+(detbox_trace_kernel); `cpu_baseline` is the reference's own CPU code (oracle/_ref when it was
+built, else the oracle's C port) on the host cores, on a bounded sample of the same workload.
+--impl reference times only that CPU path (all host cores) and prints the same line.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+# CP-R: exper/citypersons/retinanet/train_test_resnet50_softmax.yaml:19-46
+IH, IW = 1024, 2048
+STRIDES = [8, 16, 32, 64, 128]
+SCALES = [[2, 2.520, 3.175], [4, 5.040, 6.349], [8, 10.079, 12.700], [16, 20.159, 25.398], [32, 40.317, 50.797]]
+RATIOS = [1, 2.5]
+BASE = 16
+NUM_CLASSES = 2
+BG, FG = 0.5, 0.6
+TOP_N, NMS_THR = 900, 0.5
+A_TOTAL = 261888
+GT_PER_IMAGE = 12          # real CityPersons mean ~10-12 GT per image
+METRIC, UNIT = "box_ops_images_per_s_1024x2048", "images/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--batch", type=int, default=64, help="images per GPU per step")
+    ap.add_argument("--impl", default="detbox", choices=["detbox", "reference"])
+    ap.add_argument("--no-extras", action="store_true", help="skip the NMS sweep / RoIAlign sub-benchmarks")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--breakdown", action="store_true", help="also print per-op device times to stderr")
+    ap.add_argument("--trace", type=int, default=3, help="kernel id timed for the roofline (include/detbox.h)")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------- synthetic inputs ----
+def synth_gt(rng, G):
+    """pedestrian-shaped boxes, heights log-uniform [12,264] px, aspect
+    h/w ~ U(2.0,2.8), centres uniform, 15% ignore regions (class -1)."""
+    h = np.exp(rng.uniform(np.log(12), np.log(264), G))
+    w = h / rng.uniform(2.0, 2.8, G)
+    cx, cy = rng.uniform(0, IW, G), rng.uniform(0, IH, G)
+    b = np.stack([cx - w / 2, cy - h / 2, cx + w / 2, cy + h / 2], 1)
+    b[:, 0::2] = np.clip(b[:, 0::2], 0, IW - 1)
+    b[:, 1::2] = np.clip(b[:, 1::2], 0, IH - 1)
+    cls = np.ones(G)
+    cls[rng.rand(G) < 0.15] = -1
+    return np.concatenate([b, cls[:, None]], 1).astype(np.float32)
+
+
+def synth_head(rng, n_rows, boost_rows=None):
+    """Head outputs for n_rows anchors: deltas ~ N(0, 0.5^2); 2-class softmax probabilities from a
+    background-biased foreground logit ~ N(-4.6, 1) (prior bias, libs/nets/head.py:76-79), rows in
+    boost_rows ~ N(2, 1)."""
+    deltas = rng.normal(0.0, 0.5, (n_rows, 4)).astype(np.float32)
+    logit = rng.normal(-4.6, 1.0, n_rows)
+    if boost_rows is not None and len(boost_rows):
+        logit[boost_rows] = rng.normal(2.0, 1.0, len(boost_rows))
+    p1 = (1.0 / (1.0 + np.exp(-logit))).astype(np.float32)
+    prob = np.stack([1.0 - p1, p1], 1).astype(np.float32)
+    return deltas, prob
+
+
+# --------------------------------------------------- the reference's CPU path for one image ----
+_CPU = {}
+
+
+def _cpu_setup():
+    """Per-process: load the reference's own compiled CPU code (oracle/_ref) when it was built,
+    else the oracle's C port.  Only the cpu_baseline / --impl reference legs come here."""
+    if "kind" in _CPU:
+        return _CPU
+    from oracle import ref_loader
+    if ref_loader.available():
+        r = ref_loader.load()
+        c = r.cfg
+        c.rpn_bg_threshold, c.rpn_fg_threshold, c.rpn_clobber_positives = BG, FG, True
+        c.rpn_sample_strategy, c.rpn_box_encoding = "simple", "fastrcnn"
+        c.bbweights, c.ignored_area_intersection_fraction = [1., 1., 1., 1.], 0.3
+        _CPU.update(kind="reference", r=r)
+    else:
+        from oracle import oracle as O
+        cfg = O.citypersons_retinanet_cfg()
+        _CPU.update(kind="port", O=O, cfg=cfg)
+    return _CPU
+
+
+def _cpu_inputs(seed):
+    key = "inputs"                                    # one resident synthetic image per worker process
+    if key not in _CPU:
+        rng = np.random.RandomState(seed + os.getpid() % 1000)
+        gt = synth_gt(rng, GT_PER_IMAGE)
+        deltas, prob = synth_head(rng, A_TOTAL, rng.choice(A_TOTAL, 300, replace=False))
+        _CPU[key] = (gt, deltas, prob)
+    return _CPU[key]
+
+
+def cpu_one_image(seed):
+    """anchor_pyramid + anchor.encode + objectness/top-n/decode + cpu_nms for one image, the
+    reference's per-image CPU composition.  Returns seconds (inputs untimed)."""
+    c = _cpu_setup()
+    gt, deltas, prob = _cpu_inputs(seed)
+    t0 = time.perf_counter()
+    if c["kind"] == "reference":
+        r = c["r"]
+        anchors = r.boxes_anchor.anchor_pyramid(STRIDES, IH, IW, SCALES, RATIOS, BASE, [[0.0, 0.0]]).astype(np.float32)
+        r.layers_anchor.encode(gt, anchors)                                  # libs/layers/anchor.py:17
+        obj = 1.0 - prob[:, 0]                                               # libs/nets/model.py:57
+        order = np.argsort(-obj, kind="stable")[:TOP_N]                      # model.py:311-312
+        boxes = r.bbox_transform.bbox_transform_inv(anchors[order], deltas[order])   # model.py:318
+        dets = np.hstack([boxes, obj[order, None]]).astype(np.float32)
+        r.cpu_nms.cpu_nms(dets, NMS_THR)                                     # libs/nms/cpu_nms.pyx:17
+    else:
+        O, cfg = c["O"], c["cfg"]
+        anchors = O.anchor_pyramid(STRIDES, IH, IW, SCALES, RATIOS, BASE).astype(np.float32)
+        O.anchor_encode(gt, anchors, cfg)
+        boxes, probs, _, _, _ = O.decode_and_choose_top_n(deltas, prob, anchors, TOP_N, "softmax")
+        O.nms(boxes, 1.0 - probs[:, 0], NMS_THR, O.NMS_GE_F64)
+    return time.perf_counter() - t0
+
+
+def _cpu_warm(seed):
+    _cpu_setup()
+    _cpu_inputs(seed)
+    return _CPU["kind"]
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+class CpuPool:
+    """`cores` worker processes (the reference parallelises this path over DataLoader workers,
+    one image per worker call), each with its own resident synthetic image."""
+
+    def __init__(self, cores):
+        import multiprocessing as mp
+        self.cores = cores
+        self.pool = mp.get_context("fork").Pool(cores)
+        self.kind = self.pool.map(_cpu_warm, range(1000, 1000 + cores), chunksize=1)[0]
+
+    def step(self, images):
+        """Process `images` images (round-robin over the workers); returns wall seconds."""
+        seeds = [1000 + (i % self.cores) for i in range(images)]
+        t0 = time.perf_counter()
+        self.pool.map(cpu_one_image, seeds, chunksize=1)
+        return time.perf_counter() - t0
+
+    def close(self):
+        self.pool.close()
+        self.pool.join()
+
+
+def cpu_baseline_leg(budget_s=12.0):
+    """Bounded sample for the main arm's `cpu_baseline`: all host cores, a few rounds."""
+    cores = host_cores()
+    pool = CpuPool(cores)
+    pool.step(cores)                                  # warm-up round
+    imgs, wall = 0, 0.0
+    while wall < budget_s and imgs < 16 * cores:
+        wall += pool.step(cores)
+        imgs += cores
+    pool.close()
+    return {"value": imgs / wall, "unit": UNIT, "cores": cores, "kind": pool.kind,
+            "sample": "%d synthetic 1024x2048 images (G=%d, top_n=%d) over %d worker processes, %.1f s wall: "
+                      "anchor_pyramid + anchor.encode + top-n/decode + cpu_nms per image" % (imgs, GT_PER_IMAGE, TOP_N, cores, wall)}
+
+
+# ------------------------------------------------------------------------------- GPU helpers ----
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons of one GPU, sampled every 200 ms while active."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.thread = [], None, None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        self.mark0 = self.mark1 = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
+
+    def begin(self):
+        self.mark0 = time.time()
+
+    def end(self):
+        self.mark1 = time.time()
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        rows = [r for t, r in self.rows if self.mark0 is None or (self.mark0 - 0.25 <= t <= (self.mark1 or t) + 0.25)]
+        rows = rows or [r for _, r in self.rows]
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def event_pairs(torch, n):
+    return [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n)]
+
+
+def timed_loop(torch, dist, fn, steps, warmup, before_step=None):
+    """W untimed + K timed calls of fn(); barrier + synchronize on both sides; device time by CUDA
+    events on the launching stream; returns the max over ranks in milliseconds."""
+    for i in range(warmup):
+        if before_step:
+            before_step(-1)
+        fn()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        if before_step:
+            before_step(i)
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    if dist is not None:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        dist.barrier()
+    return ms
+
+
+# --------------------------------------------------------------- extras: NMS sweep, RoIAlign ----
+def median_ms(torch, fn, iters=10, warm=3, flush=None):
+    for _ in range(warm):
+        fn()
+    ts = []
+    for _ in range(iters):
+        if flush is not None:
+            flush.add_(1.0)                          # > L2-sized write between timed iterations
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    return float(np.median(ts))
+
+
+def nms_sweep(torch, detbox):
+    """BASELINE configs[1]: n in {1k,5k,20k,100k}, IoU 0.5, SURVEY §8d config-2 boxes (seed 2)."""
+    out = {}
+    rng = np.random.RandomState(2)
+    for n in (1000, 5000, 20000, 100000):
+        h = np.exp(rng.uniform(np.log(12), np.log(264), n)); w = h / 2.44
+        cx, cy = rng.uniform(0, IW, n), rng.uniform(0, IH, n)
+        b = np.stack([np.clip(cx - w / 2, 0, IW - 1), np.clip(cy - h / 2, 0, IH - 1),
+                      np.clip(cx + w / 2, 0, IW - 1), np.clip(cy + h / 2, 0, IH - 1)], 1).astype(np.float32)
+        s = rng.permutation(np.linspace(0, 1, n)).astype(np.float32)
+        db, ds = torch.from_numpy(b).cuda(), torch.from_numpy(s).cuda()
+        ms = median_ms(torch, lambda: detbox.nms(db, ds, NMS_THR, detbox.NMS_GT_F32), iters=7 if n > 20000 else 15)
+        keep, nk = detbox.nms(db, ds, NMS_THR, detbox.NMS_GT_F32)
+        out[str(n)] = {"us": round(ms * 1e3, 1), "kept": int(nk[-1].item())}
+    return out
+
+
+def roi_align_bench(torch, detbox, hbm_peak):
+    """BASELINE configs[2]: 512 RoIs/img x 256 ch x 7x7 over P2-P5 of a 1024x2048 canvas, batch 8,
+    fp32, bin-centre sampling (the variant MaskRCNN wires in), level assigned in-kernel."""
+    B, C, P = 8, 256, 7
+    strides = [4, 8, 16, 32]
+    shapes = [(B, C, IH // s, IW // s) for s in strides]
+    ref_areas = [(float(np.mean(sc)) * BASE) ** 2 for sc in SCALES[:4]]
+    rng = np.random.RandomState(3)
+    R = 512 * B
+    g = np.concatenate([synth_gt(rng, 512)[:, :4] for _ in range(B)], 0)
+    g += rng.normal(0, 4.0, g.shape).astype(np.float32)
+    g[:, 2:] = np.maximum(g[:, 2:], g[:, :2] + 4)
+    rois = np.concatenate([np.repeat(np.arange(B), 512)[:, None].astype(np.float32), g], 1).astype(np.float32)
+    d_rois = torch.from_numpy(rois).cuda()
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    res = {}
+    lv = detbox.assign_levels(d_rois[:, 1:5], ref_areas)
+    # compulsory feature bytes: unique (level, b, y, x) positions the taps touch x C x 4 B
+    uniq = 0
+    for l, s in enumerate(strides):
+        sel = (lv == l).nonzero().flatten()
+        if sel.numel() == 0:
+            continue
+        r = d_rois[sel]; H, W = shapes[l][2], shapes[l][3]
+        sc = 1.0 / s
+        j = torch.arange(P, device="cuda", dtype=torch.float32)[None]
+        sw = (r[:, 3:4] - r[:, 1:2]) * sc / P; sh = (r[:, 4:5] - r[:, 2:3]) * sc / P
+        xs = r[:, 1:2] * sc + sw / 2 - 0.5 + j * sw; ys = r[:, 2:3] * sc + sh / 2 - 0.5 + j * sh
+        xt = torch.cat([xs.floor(), xs.ceil()], 1).clamp(0, W - 1).long(); yt = torch.cat([ys.floor(), ys.ceil()], 1).clamp(0, H - 1).long()
+        flat = (r[:, 0].long()[:, None, None] * H + yt[:, :, None]) * W + xt[:, None, :]
+        m = torch.zeros(B * H * W, dtype=torch.bool, device="cuda"); m[flat.flatten()] = True
+        uniq += int(m.sum().item())
+    out_bytes = R * C * P * P * 4
+    feat_bytes = uniq * C * 4
+    dense_bytes = sum(int(np.prod(s)) for s in shapes) * 4
+    flush = torch.empty(64 * 1024 * 1024, dtype=torch.float32, device="cuda").zero_()      # 256 MB > 126 MB L2
+    for layout in ("nchw", "nhwc"):
+        feats = [torch.randn(s, generator=gen, device="cuda", dtype=torch.float32) for s in shapes]
+        if layout == "nhwc":
+            feats = [f.contiguous(memory_format=torch.channels_last) for f in feats]
+        scales = [1.0 / s for s in strides]
+        fwd = lambda: detbox.roi_align_forward(feats, d_rois, scales, P, P, detbox.ROI_BIN_CENTRE, ref_areas=ref_areas)
+        y = fwd()
+        gout = torch.randn(y.shape, generator=gen, device="cuda", dtype=torch.float32)
+        if layout == "nhwc":
+            gout = gout.contiguous(memory_format=torch.channels_last)
+        grads = [torch.empty_like(f) for f in feats]
+        bwd_acc = lambda: detbox.roi_align_backward(gout, shapes, d_rois, scales, detbox.ROI_BIN_CENTRE, ref_areas=ref_areas,
+                                                    channels_last=(layout == "nhwc"), grads=grads)
+        bwd_full = lambda: detbox.roi_align_backward(gout, shapes, d_rois, scales, detbox.ROI_BIN_CENTRE, ref_areas=ref_areas,
+                                                     channels_last=(layout == "nhwc"))
+        t_f = median_ms(torch, fwd, flush=flush)
+        t_b = median_ms(torch, bwd_full, flush=flush)
+        t_s = median_ms(torch, bwd_acc, flush=flush)
+        fb, bb = out_bytes + feat_bytes + R * 20, out_bytes + dense_bytes + feat_bytes + R * 20
+        res[layout] = {"fwd_ms": round(t_f, 4), "fwd_gbs": round(fb / t_f / 1e6, 1), "fwd_frac_hbm": round(fb / t_f / 1e6 / hbm_peak, 3),
+                       "bwd_ms": round(t_b, 4), "bwd_gbs": round(bb / t_b / 1e6, 1), "bwd_frac_hbm": round(bb / t_b / 1e6 / hbm_peak, 3),
+                       "bwd_scatter_only_ms": round(t_s, 4)}
+        del feats, grads, gout, y
+    res["bytes"] = {"out": out_bytes, "features_touched": feat_bytes, "dense_grad_zero_fill": dense_bytes}
+    res["workload"] = "B=8, R=4096, C=256, 7x7, P2-P5 @1024x2048, bin-centre, level assigned in-kernel, fp32; L2 flushed between iterations"
+    return res
+
+
+# -------------------------------------------------------------------------------------- main ----
+def trace_bytes(kid, B, A, G_total, C):
+    """ALGORITHMIC bytes of ONE launch of the traced kernel (kernels table)."""
+    return {2: 16 * A * B + 20 * G_total,                       # colmax: anchors (re-read per image) + GT
+            3: 16 * A + B * 36 * A + 20 * G_total,              # assign: anchors once, labels+targets+inside per image
+            4: B * 8 * A,                                       # weights: labels read + label_weights written
+            5: B * A * (4 * C + 4)}.get(kid)                    # objectness: probabilities read + keys written
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU implementation of the step on all host cores.
+    Every step is a bounded sample: one image per worker process."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = host_cores()
+    pool = CpuPool(cores)
+    per_step = cores
+    for _ in range(args.warmup):
+        pool.step(per_step)
+    wall = sum(pool.step(per_step) for _ in range(args.steps))
+    pool.close()
+    v = per_step * args.steps / wall
+    line = {"impl": "reference", "metric": METRIC, "value": round(v, 3), "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * wall / args.steps, 3),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64 IoU / f32 boxes",
+            "data": "synthetic",
+            "config": {"workload": "CP-R box path @1024x2048: anchor_pyramid + anchor.encode + top-%d/decode + cpu_nms(%.1f), "
+                                   "261888 anchors/img, G=%d; bounded sample of %d images per step (1 per host core)"
+                                   % (TOP_N, NMS_THR, GT_PER_IMAGE, per_step)},
+            "cpu_baseline": {"value": round(v, 3), "unit": UNIT, "cores": cores, "kind": pool.kind,
+                             "sample": "%d images per step x %d steps, one image per worker process" % (per_step, args.steps)},
+            "e2e": {"value": round(v, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    cpu_base = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cpu_base = cpu_baseline_leg()                 # before CUDA is initialised (fork pool)
+
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: detbox has no CPU path")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    import detbox
+    from importlib import import_module
+    pipeline = import_module("detectron-pytorch_b200.pipeline")
+    L = detbox.lib()
+    hbm_peak, peak_src = measured_peaks()
+
+    B, A, C = args.batch, A_TOTAL, NUM_CLASSES
+    sess = pipeline.BoxOpsSession(STRIDES, IH, IW, SCALES, RATIOS, BASE, B, C, top_n=TOP_N, nms_thresh=NMS_THR,
+                                  bg=BG, fg=FG, max_gt_total=GT_PER_IMAGE * B)
+    assert sess.A == A
+    # synthetic inputs: images (rank*B .. rank*B+B-1), seeds 100+
+    gts = [synth_gt(np.random.RandomState(100 + rank * B + i), GT_PER_IMAGE) for i in range(B)]
+    G_total = sess.stage_gt(gts)
+    d_gt, d_off = sess.h_gt[:G_total].cuda(), sess.h_off.cuda()
+    lab = detbox.anchor_target(sess.anchors, d_gt, d_off, sess.tcfg)[0]
+    boost = (lab.flatten() != 0).nonzero().flatten().cpu().numpy()        # fg + ignored anchors score high
+    rng = np.random.RandomState(7 + rank)
+    deltas, prob = synth_head(rng, B * A, boost)
+    h_prob, h_box = torch.from_numpy(prob).pin_memory(), torch.from_numpy(deltas).pin_memory()
+    d_prob, d_box = h_prob.cuda(), h_box.cuda()
+    del lab, deltas, prob
+    torch.cuda.synchronize()
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    # ---- device-resident leg -------------------------------------------------------------------
+    pairs = event_pairs(torch, args.steps)
+    for a, b in pairs:
+        a.record(); b.record()                       # materialise the cudaEvent_t handles
+
+    def arm(i):
+        if i >= 0 and args.trace:
+            L.detbox_trace_kernel(args.trace, pairs[i][0].cuda_event, pairs[i][1].cuda_event)
+        else:
+            L.detbox_trace_kernel(0, None, None)
+
+    step_dev = lambda: sess.run_device(d_gt, d_off, d_prob, d_box)
+    n0 = detbox.launches()
+    if sampler:
+        sampler.begin()
+    ms_dev = timed_loop(torch, dist, step_dev, args.steps, args.warmup, before_step=arm)
+    launches = (detbox.launches() - n0) * args.steps // (args.steps + args.warmup)
+    L.detbox_trace_kernel(0, None, None)
+    k_ms = float(np.mean([a.elapsed_time(b) for a, b in pairs])) if args.trace else None
+    # ---- end-to-end leg: pinned host buffers in, host buffers out --------------------------------
+    step_host = lambda: sess.run_host(gts, h_prob, h_box)
+    ms_e2e = timed_loop(torch, dist, step_host, args.steps, args.warmup)
+    if sampler:
+        sampler.end()
+    clocks = sampler.stop() if sampler else None
+
+    if args.breakdown and rank == 0:
+        anc = sess.anchors
+        ops_t = {"anchor_pyramid": median_ms(torch, lambda: detbox.anchor_pyramid(STRIDES, IH, IW, SCALES, RATIOS, BASE)),
+                 "anchor_target": median_ms(torch, lambda: detbox.anchor_target(anc, d_gt, d_off, sess.tcfg)),
+                 "topk_decode": median_ms(torch, lambda: detbox.topk_decode(d_box, d_prob, anc, TOP_N, "softmax", "fastrcnn", True, want=("img_ids", "scores")))}
+        sel = detbox.topk_decode(d_box, d_prob, anc, TOP_N, "softmax", "fastrcnn", True, want=("img_ids", "scores"))
+        seg = sel["img_ids"].int()
+        ops_t["nms_segmented"] = median_ms(torch, lambda: detbox.nms(sel["boxes"], sel["scores"], NMS_THR, detbox.NMS_GT_F32, seg_ids=seg, n_seg=B))
+        for kid, name in ((2, "k_colmax"), (3, "k_assign"), (4, "k_weights"), (5, "k_objectness"), (6, "k_nms_mask"), (7, "k_nms_scan")):
+            ea, eb = event_pairs(torch, 1)[0]
+            ea.record(); eb.record()
+            L.detbox_trace_kernel(kid, ea.cuda_event, eb.cuda_event)
+            step_dev(); torch.cuda.synchronize()
+            L.detbox_trace_kernel(0, None, None)
+            ops_t[name] = ea.elapsed_time(eb)
+        print("breakdown (ms, batch %d): %s" % (B, json.dumps({k: round(v, 4) for k, v in ops_t.items()})), file=sys.stderr)
+
+    extras = {}
+    if rank == 0 and world == 1 and not args.no_extras:
+        extras["nms_us"] = nms_sweep(torch, detbox)
+        extras["roi_align"] = roi_align_bench(torch, detbox, hbm_peak)
+
+    if rank == 0:
+        total_images = B * world
+        roof = None
+        tb = trace_bytes(args.trace, B, A, G_total, C)
+        if k_ms and tb:
+            ach = tb / k_ms / 1e6
+            roof = {"bound": "hbm", "kernel_id": args.trace, "achieved": round(ach, 1), "peak": hbm_peak, "unit": "GB/s",
+                    "frac": round(ach / hbm_peak, 4), "traffic": None, "kernel_ms": round(k_ms, 4),
+                    "algorithmic_bytes_per_launch": tb, "peak_source": peak_src}
+        line = {"metric": METRIC, "value": round(total_images * args.steps / (ms_dev / 1e3), 1), "unit": UNIT,
+                "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_dev / args.steps, 4),
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64 IoU / f32 boxes",
+                "data": "synthetic",
+                "config": {"workload": "BASELINE configs[4] shard: %d CP-R images per GPU per step @1024x2048, 261888 anchors/img, "
+                                       "G=%d/img, anchor pyramid + anchor-target + per-image top-%d + decode + NMS(%.1f)"
+                                       % (B, GT_PER_IMAGE, TOP_N, NMS_THR),
+                           "images_per_gpu": B, "global_images": total_images, "parallelism": "per-image shard x%d, no collective" % world,
+                           "l2_policy": "inputs larger than L2 (%.0f MB of head outputs per step, never re-used inside a step)"
+                                        % ((d_prob.numel() + d_box.numel()) * 4 / 1e6)},
+                "e2e": {"value": round(total_images * args.steps / (ms_e2e / 1e3), 1), "unit": UNIT,
+                        "ms_per_step": round(ms_e2e / args.steps, 4),
+                        "h2d_bytes_per_step": int(sess.h2d_bytes), "d2h_bytes_per_step": int(sess.d2h_bytes)},
+                "gpu_launches": int(launches), "clocks": clocks}
+        if roof:
+            line["roofline"] = roof
+        if cpu_base:
+            line["cpu_baseline"] = cpu_base
+        line.update(extras)
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -308,15 +308,21 @@ extern "C" int detbox_anchor_target(const float *anchors, long A, const float *g
 
     dim3 grid((unsigned)((A + AT_TILE - 1) / AT_TILE), (unsigned)batch);
     if (total_gt > 0) {
+        DETBOX_TRACE_BEGIN(DETBOX_K_TARGET_COLMAX, st);
         anchor_target_kernel<1><<<grid, AT_THREADS, 0, st>>>(p);
+        DETBOX_TRACE_END(DETBOX_K_TARGET_COLMAX, st);
         DETBOX_LAUNCH_CHECK();
     }
+    DETBOX_TRACE_BEGIN(DETBOX_K_TARGET_ASSIGN, st);
     anchor_target_kernel<2><<<grid, AT_THREADS, 0, st>>>(p);
+    DETBOX_TRACE_END(DETBOX_K_TARGET_ASSIGN, st);
     DETBOX_LAUNCH_CHECK();
     long wb = (A / 4 + 255) / 256;
     if (wb < 1) wb = 1;
     if (wb > 4 * kNumSMs) wb = 4 * kNumSMs;
+    DETBOX_TRACE_BEGIN(DETBOX_K_TARGET_WEIGHTS, st);
     label_weight_kernel<<<dim3((unsigned)wb, (unsigned)batch), 256, 0, st>>>(labels, A, counts, label_weights, counts_out);
+    DETBOX_TRACE_END(DETBOX_K_TARGET_WEIGHTS, st);
     DETBOX_LAUNCH_CHECK();
     return DETBOX_OK;
 }

@@ -103,8 +103,10 @@ extern "C" int detbox_anchor_pyramid(const double *cell_dev, int n_levels, const
     long long blocks = (roff + 255) / 256;
     const long long cap = (long long)kNumSMs * 16;
     if (blocks > cap) blocks = cap;
+    DETBOX_TRACE_BEGIN(DETBOX_K_ANCHORS, as_stream(stream));
     if (out_f64) anchor_pyramid_kernel<double><<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(cell_dev, d, (double *)out_dev);
     else anchor_pyramid_kernel<float><<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(cell_dev, d, (float *)out_dev);
+    DETBOX_TRACE_END(DETBOX_K_ANCHORS, as_stream(stream));
     DETBOX_LAUNCH_CHECK();
     return DETBOX_OK;
 }

@@ -22,6 +22,12 @@ inline int cuda_fail(cudaError_t e) {
 
 #define DETBOX_LAUNCH_CHECK() DETBOX_CUDA_TRY(cudaGetLastError())
 
+// detbox_trace_kernel(): events recorded around the launches of one kernel id (bench roofline leg)
+struct KernelTrace { int id; cudaEvent_t start, stop; };
+extern thread_local KernelTrace g_trace;
+#define DETBOX_TRACE_BEGIN(kid, st) do { if (::detbox::g_trace.id == (kid)) cudaEventRecord(::detbox::g_trace.start, (st)); } while (0)
+#define DETBOX_TRACE_END(kid, st)   do { if (::detbox::g_trace.id == (kid)) cudaEventRecord(::detbox::g_trace.stop, (st)); } while (0)
+
 inline cudaStream_t as_stream(void *s) { return reinterpret_cast<cudaStream_t>(s); }
 
 inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }

@@ -243,13 +243,17 @@ int nms_sorted(const NmsBuffers &b, const uint32_t *order, long n, int n_seg,
     DETBOX_CUDA_TRY(cudaMemsetAsync(b.kept, 0, (size_t)ncol * sizeof(u64), st));
     DETBOX_CUDA_TRY(cudaMemsetAsync(n_keep, 0, (size_t)(n_seg + 1) * sizeof(int32_t), st));
     dim3 grid((unsigned)((ncol + MASK_CT - 1) / MASK_CT), (unsigned)ncol);
+    DETBOX_TRACE_BEGIN(DETBOX_K_NMS_MASK, st);
     mask_kernel<<<grid, 64 * MASK_CT, 0, st>>>(b.sorted, seg_sorted, (int)n, ncol, cmp, b.mask);
+    DETBOX_TRACE_END(DETBOX_K_NMS_MASK, st);
     DETBOX_LAUNCH_CHECK();
     const size_t smem = (size_t)ncol * sizeof(u64);
     if (smem > 200 * 1024) return DETBOX_ERR_UNSUPPORTED;
     if (smem > 40 * 1024)
         DETBOX_CUDA_TRY(cudaFuncSetAttribute(scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    DETBOX_TRACE_BEGIN(DETBOX_K_NMS_SCAN, st);
     scan_kernel<<<n_seg, 1024, smem, st>>>(b.mask, (int)n, ncol, n_seg > 1 ? seg_off : nullptr, b.kept);
+    DETBOX_TRACE_END(DETBOX_K_NMS_SCAN, st);
     DETBOX_LAUNCH_CHECK();
     compact_kernel<<<1, 1024, 0, st>>>(b.kept, (int)n, ncol, order, seg_sorted, n_seg, keep, n_keep);
     DETBOX_LAUNCH_CHECK();

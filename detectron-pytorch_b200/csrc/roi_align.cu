@@ -337,7 +337,9 @@ extern "C" int detbox_roi_align_forward(const detbox_roi_cfg *cfg, const float *
     cudaStream_t st = as_stream(stream);
     return dispatch(*cfg, [&](auto K) -> int {
         constexpr int k = decltype(K)::value;
+        DETBOX_TRACE_BEGIN(DETBOX_K_ROI_FWD, st);
         roi_fwd_kernel<(k & 4) != 0, (k & 2) != 0, (k & 1) != 0><<<grid, RA_THREADS, 0, st>>>(a);
+        DETBOX_TRACE_END(DETBOX_K_ROI_FWD, st);
         DETBOX_LAUNCH_CHECK();
         return DETBOX_OK;
     });
@@ -350,17 +352,22 @@ extern "C" int detbox_roi_align_backward(const detbox_roi_cfg *cfg, const float 
     if (rc != DETBOX_OK) return rc;
     if (R < 0) return DETBOX_ERR_INVALID;
     cudaStream_t st = as_stream(stream);
-    if (zero_grad)
+    if (zero_grad) {
+        DETBOX_TRACE_BEGIN(DETBOX_K_ROI_ZERO, st);
         for (int l = 0; l < cfg->n_levels; ++l)
             DETBOX_CUDA_TRY(cudaMemsetAsync(cfg->grad_feat[l], 0,
                                             (size_t)cfg->batch * cfg->channels * cfg->height[l] * cfg->width[l] * sizeof(float), st));
+        DETBOX_TRACE_END(DETBOX_K_ROI_ZERO, st);
+    }
     if (R == 0) return DETBOX_OK;
     if (!rois || !grad_out) return DETBOX_ERR_INVALID;
     RoiArgs a; a.cfg = *cfg; a.rois = rois; a.R = R; a.levels = levels; a.out = nullptr; a.grad_out = grad_out;
     dim3 grid((unsigned)R, cfg->all_levels ? cfg->n_levels : 1);
     return dispatch(*cfg, [&](auto K) -> int {
         constexpr int k = decltype(K)::value;
+        DETBOX_TRACE_BEGIN(DETBOX_K_ROI_BWD, st);
         roi_bwd_kernel<(k & 4) != 0, (k & 2) != 0, (k & 1) != 0><<<grid, RA_THREADS, 0, st>>>(a);
+        DETBOX_TRACE_END(DETBOX_K_ROI_BWD, st);
         DETBOX_LAUNCH_CHECK();
         return DETBOX_OK;
     });

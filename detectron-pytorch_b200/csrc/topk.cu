@@ -345,8 +345,10 @@ extern "C" int detbox_topk_decode(const float *prob, int C, const float *deltas,
         long capx = cap / p.n_seg; if (capx < 1) capx = 1; if (p.n_seg == 1) capx = cap;
         if (gx > capx) gx = capx;
         dim3 grid((unsigned)gx, (unsigned)p.n_seg);
+        DETBOX_TRACE_BEGIN(DETBOX_K_OBJECTNESS, st);
         if (activation == DETBOX_ACT_SOFTMAX) objectness_kernel<DETBOX_ACT_SOFTMAX><<<grid, TK_THREADS, 0, st>>>(prob, C, p.seg_len, keys, hist);
         else objectness_kernel<DETBOX_ACT_SIGMOID><<<grid, TK_THREADS, 0, st>>>(prob, C, p.seg_len, keys, hist);
+        DETBOX_TRACE_END(DETBOX_K_OBJECTNESS, st);
         DETBOX_LAUNCH_CHECK();
     }
     // 2. radix select: 11 + 11 + 10 bits

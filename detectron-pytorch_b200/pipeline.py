@@ -1,0 +1,123 @@
+"""Batched box path with HOST buffers in and out — the call a user of the reference makes.
+
+The reference runs this path per image on NumPy arrays:
+    anchors  = anchor_pyramid(...)                                  libs/boxes/anchor.py:30
+    targets  = compute_rpn_targets_in_batch(gt_boxes_list, anchors) libs/layers/data_layer.py:228
+    dets     = get_final_results_stage1(outputs, anchors, ...)      libs/nets/model.py:474
+             = objectness -> top_n -> decode -> per-image NMS       model.py:308-355
+`BoxOpsSession.run_host` is that composite for a whole batch: pinned host buffers are copied to
+the device, every stage runs as hand-written CUDA kernels of libdetbox.so on one stream with no
+intermediate host synchronisation, and the results are copied back into pinned host buffers.
+`run_device` is the same sequence on tensors already resident in HBM.  There is no CPU path.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import ops, ops_post
+from ._lib import DetboxError
+
+
+class BoxOpsSession:
+    """Pre-allocated staging for a fixed (batch, canvas, anchor config).
+
+    top_n is taken PER IMAGE (the sharded mode of SURVEY §8e, identical to the reference's
+    behaviour at its own eval batch size of 1, test/test.py:71).
+    """
+
+    def __init__(self, strides, ih, iw, anchor_scales, anchor_ratios, anchor_base, batch, num_classes,
+                 top_n=900, nms_thresh=0.5, nms_cmp=ops.NMS_GT_F32, activation="softmax", bg=0.5, fg=0.6,
+                 max_gt_total=None, anchor_shift=((0.0, 0.0),), device="cuda"):
+        if not torch.cuda.is_available():
+            raise DetboxError("BoxOpsSession needs a CUDA device: detbox has no CPU path")
+        self.dev = torch.device(device)
+        self.anchor_args = (list(strides), int(ih), int(iw), anchor_scales, anchor_ratios, anchor_base, anchor_shift)
+        self.B, self.C = int(batch), int(num_classes)
+        self.top_n, self.nms_thresh, self.nms_cmp, self.activation = int(top_n), float(nms_thresh), nms_cmp, activation
+        self.tcfg = ops.make_target_cfg(bg, fg)
+        self.anchors = ops.anchor_pyramid(*self.anchor_args, device=self.dev)
+        self.A = A = self.anchors.shape[0]
+        B = self.B
+        self.K = B * min(self.top_n, A)
+        G = int(max_gt_total or 128 * B)
+        pin = lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True)
+        dv = lambda shape, dt: torch.empty(shape, dtype=dt, device=self.dev)
+        # inputs: host staging + device copies
+        self.h_gt, self.d_gt = pin((G, 5), torch.float32), dv((G, 5), torch.float32)
+        self.h_off, self.d_off = pin((B + 1,), torch.int32), dv((B + 1,), torch.int32)
+        self.d_prob, self.d_box = dv((B * A, self.C), torch.float32), dv((B * A, 4), torch.float32)
+        # outputs on the host (the device tensors are allocated by the ops)
+        self.h_labels, self.h_lw = pin((B, A), torch.float32), pin((B, A), torch.float32)
+        self.h_bt, self.h_bw = pin((B, A, 4), torch.float32), pin((B, A, 4), torch.float32)
+        self.h_boxes, self.h_scores = pin((self.K, 4), torch.float32), pin((self.K,), torch.float32)
+        self.h_img = pin((self.K,), torch.int64)
+        self.h_keep, self.h_nkeep = pin((self.K,), torch.int64), pin((B + 1,), torch.int32)
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+
+    # ------------------------------------------------------------------ device-resident path --
+    def run_device(self, gt, gt_offsets, rpn_prob, rpn_box, regenerate_anchors=True):
+        """gt [sumG,5], gt_offsets int32 [B+1], rpn_prob [B*A,C], rpn_box [B*A,4] — CUDA tensors."""
+        if regenerate_anchors:      # the reference rebuilds the pyramid for every batch (data_layer.py:138)
+            self.anchors = ops.anchor_pyramid(*self.anchor_args, device=self.dev)
+        labels, lw, bt, bw = ops.anchor_target(self.anchors, gt, gt_offsets, self.tcfg)
+        sel = ops_post.topk_decode(rpn_box, rpn_prob, self.anchors, self.top_n, self.activation, "fastrcnn",
+                                   per_image=True, want=("img_ids", "scores"))
+        keep, n_keep = ops_post.nms(sel["boxes"], sel["scores"], self.nms_thresh, self.nms_cmp,
+                                    seg_ids=sel["img_ids"].to(torch.int32), n_seg=self.B)
+        return {"labels": labels, "label_weights": lw, "bbox_targets": bt, "bbox_inside_weights": bw,
+                "boxes": sel["boxes"], "scores": sel["scores"], "img_ids": sel["img_ids"],
+                "keep": keep, "n_keep": n_keep}
+
+    # ----------------------------------------------------------------------- host-buffer path --
+    def stage_gt(self, gt_boxes_list):
+        """Pack a list of [G_i,5] arrays into the pinned GT buffer; returns total G."""
+        if len(gt_boxes_list) != self.B:
+            raise DetboxError("expected %d GT arrays, got %d" % (self.B, len(gt_boxes_list)))
+        off = 0
+        self.h_off[0] = 0
+        hg = self.h_gt.numpy()
+        for i, g in enumerate(gt_boxes_list):
+            g = np.asarray(g, np.float32).reshape(-1, 5)
+            if off + g.shape[0] > hg.shape[0]:
+                raise DetboxError("more GT boxes than max_gt_total=%d" % hg.shape[0])
+            hg[off:off + g.shape[0]] = g
+            off += g.shape[0]
+            self.h_off[i + 1] = off
+        return off
+
+    def run_host(self, gt_boxes_list, rpn_prob_host, rpn_box_host):
+        """gt_boxes_list: B NumPy arrays [G_i,5]; rpn_prob_host [B*A,C] / rpn_box_host [B*A,4]:
+        float32 host tensors (pinned for asynchronous copies).  Returns pinned host tensors; the
+        call returns after the stream has drained, so they are ready to read."""
+        G = self.stage_gt(gt_boxes_list)
+        nb = True
+        self.d_gt[:G].copy_(self.h_gt[:G], non_blocking=nb)
+        self.d_off.copy_(self.h_off, non_blocking=nb)
+        self.d_prob.copy_(rpn_prob_host.view(self.B * self.A, self.C), non_blocking=nb)
+        self.d_box.copy_(rpn_box_host.view(self.B * self.A, 4), non_blocking=nb)
+        out = self.run_device(self.d_gt[:G], self.d_off, self.d_prob, self.d_box)
+        pairs = [(self.h_labels, out["labels"]), (self.h_lw, out["label_weights"]), (self.h_bt, out["bbox_targets"]),
+                 (self.h_bw, out["bbox_inside_weights"]), (self.h_boxes, out["boxes"]), (self.h_scores, out["scores"]),
+                 (self.h_img, out["img_ids"]), (self.h_keep, out["keep"]), (self.h_nkeep, out["n_keep"])]
+        for h, d in pairs:
+            h.copy_(d, non_blocking=nb)
+        torch.cuda.current_stream().synchronize()
+        self.h2d_bytes = G * 20 + self.h_off.numel() * 4 + self.d_prob.numel() * 4 + self.d_box.numel() * 4
+        self.d2h_bytes = sum(h.numel() * h.element_size() for h, _ in pairs)
+        return {"labels": self.h_labels, "label_weights": self.h_lw, "bbox_targets": self.h_bt,
+                "bbox_inside_weights": self.h_bw, "boxes": self.h_boxes, "scores": self.h_scores,
+                "img_ids": self.h_img, "keep": self.h_keep, "n_keep": self.h_nkeep}
+
+    def detections(self, host_out):
+        """Per-image [m,5] = (x1,y1,x2,y2,score) arrays from run_host()'s result (host-side views)."""
+        nk = host_out["n_keep"].numpy()
+        keep = host_out["keep"].numpy()[:int(nk[self.B])]
+        boxes, scores = host_out["boxes"].numpy(), host_out["scores"].numpy()
+        dets, o = [], 0
+        for b in range(self.B):
+            k = keep[o:o + int(nk[b])]
+            dets.append(np.concatenate([boxes[k], scores[k, None]], 1))
+            o += int(nk[b])
+        return dets

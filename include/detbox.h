@@ -63,6 +63,23 @@ int detbox_version(void);
 /* last cudaError_t seen by this library on the calling thread (0 if none) */
 int detbox_last_cuda_error(void);
 
+/* Measurement hook (bench.py's roofline leg): record the two CUDA events (cudaEvent_t passed as
+ * void*) on the launching stream immediately before and after every launch of ONE kernel,
+ * chosen by id, made from the calling thread.  kernel_id 0 switches the hook off.  Two host-side
+ * cudaEventRecord calls, nothing else; results are unaffected. */
+#define DETBOX_K_NONE            0
+#define DETBOX_K_ANCHORS         1   /* anchor_pyramid_kernel                       */
+#define DETBOX_K_TARGET_COLMAX   2   /* anchor_target_kernel<1>  per-GT column max  */
+#define DETBOX_K_TARGET_ASSIGN   3   /* anchor_target_kernel<2>  labels + targets   */
+#define DETBOX_K_TARGET_WEIGHTS  4   /* label_weight_kernel                         */
+#define DETBOX_K_OBJECTNESS      5   /* objectness_kernel (score keys + histogram)  */
+#define DETBOX_K_NMS_MASK        6   /* mask_kernel                                 */
+#define DETBOX_K_NMS_SCAN        7   /* scan_kernel                                 */
+#define DETBOX_K_ROI_FWD         8   /* roi_fwd_kernel                              */
+#define DETBOX_K_ROI_BWD         9   /* roi_bwd_kernel (without the zero fill)      */
+#define DETBOX_K_ROI_ZERO       10   /* zero fill of the dense gradient maps        */
+int detbox_trace_kernel(int kernel_id, void *start_event, void *stop_event);
+
 /* ---------------------------------------------------------------------------------------------
  * Anchors — replaces libs/boxes/anchor.py:101-189 (anchors / generate_anchors) and :30-70
  * (anchor_pyramid / anchor_one_plane), and cython_anchor.anchors_plane (cython_anchor.pyx:14-48).
