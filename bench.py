@@ -337,8 +337,10 @@ def roi_align_bench(torch, detbox, hbm_peak):
     gen = torch.Generator(device="cuda").manual_seed(3)
     res = {}
     lv = detbox.assign_levels(d_rois[:, 1:5], ref_areas)
-    # compulsory feature bytes: unique (level, b, y, x) positions the taps touch x C x 4 B
-    uniq = 0
+    # compulsory feature bytes = unique 32-byte sectors the taps touch: in NHWC a
+    # position's C floats are contiguous (uniq positions x C x 4 B); in NCHW a sector holds 8
+    # consecutive x of one (b,c,y) row (uniq (b,y,x//8) x C x 32 B)
+    uniq, uniq_sec = 0, 0
     for l, s in enumerate(strides):
         sel = (lv == l).nonzero().flatten()
         if sel.numel() == 0:
@@ -352,8 +354,9 @@ def roi_align_bench(torch, detbox, hbm_peak):
         flat = (r[:, 0].long()[:, None, None] * H + yt[:, :, None]) * W + xt[:, None, :]
         m = torch.zeros(B * H * W, dtype=torch.bool, device="cuda"); m[flat.flatten()] = True
         uniq += int(m.sum().item())
+        uniq_sec += int(m.view(B * H, W // 8, 8).any(dim=2).sum().item())
     out_bytes = R * C * P * P * 4
-    feat_bytes = uniq * C * 4
+    feat_bytes_by_layout = {"nhwc": uniq * C * 4, "nchw": uniq_sec * C * 32}
     dense_bytes = sum(int(np.prod(s)) for s in shapes) * 4
     flush = torch.empty(64 * 1024 * 1024, dtype=torch.float32, device="cuda").zero_()      # 256 MB > 126 MB L2
     for layout in ("nchw", "nhwc"):
@@ -374,12 +377,13 @@ def roi_align_bench(torch, detbox, hbm_peak):
         t_f = median_ms(torch, fwd, flush=flush)
         t_b = median_ms(torch, bwd_full, flush=flush)
         t_s = median_ms(torch, bwd_acc, flush=flush)
+        feat_bytes = feat_bytes_by_layout[layout]
         fb, bb = out_bytes + feat_bytes + R * 20, out_bytes + dense_bytes + feat_bytes + R * 20
         res[layout] = {"fwd_ms": round(t_f, 4), "fwd_gbs": round(fb / t_f / 1e6, 1), "fwd_frac_hbm": round(fb / t_f / 1e6 / hbm_peak, 3),
                        "bwd_ms": round(t_b, 4), "bwd_gbs": round(bb / t_b / 1e6, 1), "bwd_frac_hbm": round(bb / t_b / 1e6 / hbm_peak, 3),
                        "bwd_scatter_only_ms": round(t_s, 4)}
         del feats, grads, gout, y
-    res["bytes"] = {"out": out_bytes, "features_touched": feat_bytes, "dense_grad_zero_fill": dense_bytes}
+    res["bytes"] = {"out": out_bytes, "features_touched": feat_bytes_by_layout, "dense_grad_zero_fill": dense_bytes}
     res["workload"] = "B=8, R=4096, C=256, 7x7, P2-P5 @1024x2048, bin-centre, level assigned in-kernel, fp32; L2 flushed between iterations"
     return res
 
@@ -441,8 +445,7 @@ def main():
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     import detbox
-    from importlib import import_module
-    pipeline = import_module("detectron-pytorch_b200.pipeline")
+    pipeline = detbox.pipeline
     L = detbox.lib()
     hbm_peak, peak_src = measured_peaks()
 

@@ -11,7 +11,7 @@ repository root) or ``importlib.import_module("detectron-pytorch_b200")``.
 """
 from . import _lib  # noqa: F401
 from ._lib import DetboxError, lib  # noqa: F401
-from . import ops, ops_post, ops_roi  # noqa: F401
+from . import ops, ops_post, ops_roi, pipeline  # noqa: F401
 from .ops import (anchor_pyramid, anchor_target, base_anchors, bbox_exclude_ignored_areas,  # noqa: F401
                   bbox_intersections, bbox_overlaps, box_decode, box_encode, clip_boxes_, launches,
                   make_target_cfg, NMS_GE_F32, NMS_GE_F64, NMS_GT_F32, ROI_BIN_CENTRE, ROI_GRID_POINT)

@@ -35,7 +35,7 @@ __device__ __forceinline__ bool suppresses(const NmsCmp &c, float ovr) {
 }
 
 __global__ void __launch_bounds__(256)
-gather_kernel(const float *__restrict__ boxes, int stride, const uint32_t *__restrict__ order, long n,
+nms_gather_kernel(const float *__restrict__ boxes, int stride, const uint32_t *__restrict__ order, long n,
               const int32_t *__restrict__ seg_ids, float4 *__restrict__ sorted, int32_t *__restrict__ seg_sorted)
 {
     for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
@@ -48,14 +48,14 @@ gather_kernel(const float *__restrict__ boxes, int stride, const uint32_t *__res
 
 // segment sizes -> offsets in the (segment-major) processing order
 __global__ void __launch_bounds__(256)
-seg_count_kernel(const int32_t *__restrict__ seg_ids, long n, int n_seg, int32_t *__restrict__ seg_off)
+nms_seg_count_kernel(const int32_t *__restrict__ seg_ids, long n, int n_seg, int32_t *__restrict__ seg_off)
 {
     for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
         const int s = seg_ids[i];
         if (s >= 0 && s < n_seg) atomicAdd(&seg_off[s + 1], 1);
     }
 }
-__global__ void seg_scan_kernel(int32_t *seg_off, int n_seg)
+__global__ void nms_seg_scan_kernel(int32_t *seg_off, int n_seg)
 {
     if (threadIdx.x == 0 && blockIdx.x == 0) {
         int run = 0;
@@ -66,7 +66,7 @@ __global__ void seg_scan_kernel(int32_t *seg_off, int n_seg)
 constexpr int MASK_CT = 4;     // column tiles per block
 
 __global__ void __launch_bounds__(64 * MASK_CT)
-mask_kernel(const float4 *__restrict__ boxes, const int32_t *__restrict__ seg, int n, int ncol,
+nms_mask_kernel(const float4 *__restrict__ boxes, const int32_t *__restrict__ seg, int n, int ncol,
             NmsCmp cmp, u64 *__restrict__ mask)
 {
     const int rt = blockIdx.y;
@@ -122,7 +122,7 @@ __device__ __forceinline__ u64 shfl64(u64 v, int src) {
 }
 
 __global__ void __launch_bounds__(1024)
-scan_kernel(const u64 *__restrict__ mask, int n, int ncol, const int32_t *__restrict__ seg_off, u64 *__restrict__ kept)
+nms_scan_kernel(const u64 *__restrict__ mask, int n, int ncol, const int32_t *__restrict__ seg_off, u64 *__restrict__ kept)
 {
     extern __shared__ u64 removed[];
     __shared__ u64 s_kept;
@@ -166,7 +166,7 @@ scan_kernel(const u64 *__restrict__ mask, int n, int ncol, const int32_t *__rest
 }
 
 __global__ void __launch_bounds__(1024)
-compact_kernel(const u64 *__restrict__ kept, int n, int ncol, const uint32_t *__restrict__ order,
+nms_compact_kernel(const u64 *__restrict__ kept, int n, int ncol, const uint32_t *__restrict__ order,
                const int32_t *__restrict__ seg_sorted, int n_seg, int64_t *__restrict__ keep, int32_t *__restrict__ n_keep)
 {
     __shared__ int warp_sum[32];
@@ -244,18 +244,18 @@ int nms_sorted(const NmsBuffers &b, const uint32_t *order, long n, int n_seg,
     DETBOX_CUDA_TRY(cudaMemsetAsync(n_keep, 0, (size_t)(n_seg + 1) * sizeof(int32_t), st));
     dim3 grid((unsigned)((ncol + MASK_CT - 1) / MASK_CT), (unsigned)ncol);
     DETBOX_TRACE_BEGIN(DETBOX_K_NMS_MASK, st);
-    mask_kernel<<<grid, 64 * MASK_CT, 0, st>>>(b.sorted, seg_sorted, (int)n, ncol, cmp, b.mask);
+    nms_mask_kernel<<<grid, 64 * MASK_CT, 0, st>>>(b.sorted, seg_sorted, (int)n, ncol, cmp, b.mask);
     DETBOX_TRACE_END(DETBOX_K_NMS_MASK, st);
     DETBOX_LAUNCH_CHECK();
     const size_t smem = (size_t)ncol * sizeof(u64);
     if (smem > 200 * 1024) return DETBOX_ERR_UNSUPPORTED;
     if (smem > 40 * 1024)
-        DETBOX_CUDA_TRY(cudaFuncSetAttribute(scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        DETBOX_CUDA_TRY(cudaFuncSetAttribute(nms_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     DETBOX_TRACE_BEGIN(DETBOX_K_NMS_SCAN, st);
-    scan_kernel<<<n_seg, 1024, smem, st>>>(b.mask, (int)n, ncol, n_seg > 1 ? seg_off : nullptr, b.kept);
+    nms_scan_kernel<<<n_seg, 1024, smem, st>>>(b.mask, (int)n, ncol, n_seg > 1 ? seg_off : nullptr, b.kept);
     DETBOX_TRACE_END(DETBOX_K_NMS_SCAN, st);
     DETBOX_LAUNCH_CHECK();
-    compact_kernel<<<1, 1024, 0, st>>>(b.kept, (int)n, ncol, order, seg_sorted, n_seg, keep, n_keep);
+    nms_compact_kernel<<<1, 1024, 0, st>>>(b.kept, (int)n, ncol, order, seg_sorted, n_seg, keep, n_keep);
     DETBOX_LAUNCH_CHECK();
     return DETBOX_OK;
 }
@@ -288,9 +288,9 @@ extern "C" int detbox_nms(const float *boxes, int box_stride, const float *score
     long gb = (n + 255) / 256; if (gb > kNumSMs * 8) gb = kNumSMs * 8;
     if (n_seg > 1) {                              // stable grouping by segment: 1 pass per 8 bits of id
         DETBOX_CUDA_TRY(cudaMemsetAsync(b.seg_off, 0, (size_t)(n_seg + 2) * sizeof(int32_t), st));
-        seg_count_kernel<<<(unsigned)gb, 256, 0, st>>>(seg_ids, n, n_seg, b.seg_off);
+        nms_seg_count_kernel<<<(unsigned)gb, 256, 0, st>>>(seg_ids, n, n_seg, b.seg_off);
         DETBOX_LAUNCH_CHECK();
-        seg_scan_kernel<<<1, 32, 0, st>>>(b.seg_off, n_seg);
+        nms_seg_scan_kernel<<<1, 32, 0, st>>>(b.seg_off, n_seg);
         DETBOX_LAUNCH_CHECK();
         uint32_t *ki = b.ka, *vi = b.va, *ko = b.kb, *vo = b.vb;
         for (int shift = 0; (n_seg - 1) >> shift; shift += 8) {
@@ -301,7 +301,7 @@ extern "C" int detbox_nms(const float *boxes, int box_stride, const float *score
         }
         order = vi;
     }
-    gather_kernel<<<(unsigned)gb, 256, 0, st>>>(boxes, box_stride, order, n, seg_ids, b.sorted,
+    nms_gather_kernel<<<(unsigned)gb, 256, 0, st>>>(boxes, box_stride, order, n, seg_ids, b.sorted,
                                                n_seg > 1 ? b.seg_sorted : nullptr);
     DETBOX_LAUNCH_CHECK();
     return nms_sorted(b, order, n, n_seg, make_cmp(thresh, cmp_mode), keep, n_keep, st);
@@ -365,7 +365,7 @@ static int nms_host_impl(const float *dets, int n, int dim, bool presorted, doub
             if (presorted) {
                 NmsBuffers b = carve_nms(ws, n, 1);
                 long gb = (n + 255) / 256; if (gb > kNumSMs * 8) gb = kNumSMs * 8;
-                gather_kernel<<<(unsigned)gb, 256, 0, st>>>(d_in, dim, nullptr, n, nullptr, b.sorted, nullptr);
+                nms_gather_kernel<<<(unsigned)gb, 256, 0, st>>>(d_in, dim, nullptr, n, nullptr, b.sorted, nullptr);
                 DETBOX_LAUNCH_CHECK();
                 int r = nms_sorted(b, nullptr, n, 1, make_cmp(thresh, cmp_mode), d_keep, d_nk, st);
                 if (r != DETBOX_OK) return r;

@@ -53,6 +53,9 @@ class BoxOpsSession:
         self.h_boxes, self.h_scores = pin((self.K, 4), torch.float32), pin((self.K,), torch.float32)
         self.h_img = pin((self.K,), torch.int64)
         self.h_keep, self.h_nkeep = pin((self.K,), torch.int64), pin((B + 1,), torch.int32)
+        self._keep_out = pin((self.K,), torch.int64)
+        self._h_nk = None
+        self._streams = [torch.cuda.Stream(self.dev) for _ in range(3)]     # copy-in, kernels, copy-out
         self.h2d_bytes = 0
         self.d2h_bytes = 0
 
@@ -87,28 +90,79 @@ class BoxOpsSession:
             self.h_off[i + 1] = off
         return off
 
-    def run_host(self, gt_boxes_list, rpn_prob_host, rpn_box_host):
+    def run_host(self, gt_boxes_list, rpn_prob_host, rpn_box_host, chunk=8):
         """gt_boxes_list: B NumPy arrays [G_i,5]; rpn_prob_host [B*A,C] / rpn_box_host [B*A,4]:
         float32 host tensors (pinned for asynchronous copies).  Returns pinned host tensors; the
-        call returns after the stream has drained, so they are ready to read."""
+        call returns after all streams have drained, so they are ready to read.
+
+        The batch is cut into chunks of `chunk` images that flow through three streams — copy-in,
+        kernels, copy-out — so the PCIe link runs in both directions while the kernels of the
+        neighbouring chunk execute (images are independent: no result changes)."""
+        B, A, C = self.B, self.A, self.C
         G = self.stage_gt(gt_boxes_list)
-        nb = True
-        self.d_gt[:G].copy_(self.h_gt[:G], non_blocking=nb)
-        self.d_off.copy_(self.h_off, non_blocking=nb)
-        self.d_prob.copy_(rpn_prob_host.view(self.B * self.A, self.C), non_blocking=nb)
-        self.d_box.copy_(rpn_box_host.view(self.B * self.A, 4), non_blocking=nb)
-        out = self.run_device(self.d_gt[:G], self.d_off, self.d_prob, self.d_box)
-        pairs = [(self.h_labels, out["labels"]), (self.h_lw, out["label_weights"]), (self.h_bt, out["bbox_targets"]),
-                 (self.h_bw, out["bbox_inside_weights"]), (self.h_boxes, out["boxes"]), (self.h_scores, out["scores"]),
-                 (self.h_img, out["img_ids"]), (self.h_keep, out["keep"]), (self.h_nkeep, out["n_keep"])]
-        for h, d in pairs:
-            h.copy_(d, non_blocking=nb)
-        torch.cuda.current_stream().synchronize()
+        s_in, s_k, s_out = self._streams
+        cur = torch.cuda.current_stream()
+        for s in self._streams:
+            s.wait_stream(cur)
+        prob_h, box_h = rpn_prob_host.view(B * A, C), rpn_box_host.view(B * A, 4)
+        kper = min(self.top_n, A)
+        with torch.cuda.stream(s_in):
+            self.d_gt[:G].copy_(self.h_gt[:G], non_blocking=True)
+            self.d_off.copy_(self.h_off, non_blocking=True)
+        self.anchors = ops.anchor_pyramid(*self.anchor_args, device=self.dev)     # data_layer.py:138, once per batch
+        s_k.wait_stream(cur)
+        hold, d2h = [], 0
+        if self._h_nk is None or self._h_nk.shape != ((B + chunk - 1) // chunk, chunk + 1):
+            self._h_nk = torch.zeros(((B + chunk - 1) // chunk, chunk + 1), dtype=torch.int32, pin_memory=True)
+        h_nk = self._h_nk
+        for c0 in range(0, B, chunk):
+            n = min(chunk, B - c0)
+            r0, r1 = c0 * A, (c0 + n) * A
+            ev_in = torch.cuda.Event()
+            with torch.cuda.stream(s_in):
+                self.d_prob[r0:r1].copy_(prob_h[r0:r1], non_blocking=True)
+                self.d_box[r0:r1].copy_(box_h[r0:r1], non_blocking=True)
+                ev_in.record(s_in)
+            ev_k = torch.cuda.Event()
+            with torch.cuda.stream(s_k):
+                s_k.wait_event(ev_in)
+                labels, lw, bt, bw = ops.anchor_target(self.anchors, self.d_gt[:G], self.d_off[c0:c0 + n + 1], self.tcfg)
+                sel = ops_post.topk_decode(self.d_box[r0:r1], self.d_prob[r0:r1], self.anchors, self.top_n, self.activation,
+                                           "fastrcnn", per_image=True, want=("img_ids", "scores"))
+                keep, n_keep = ops_post.nms(sel["boxes"], sel["scores"], self.nms_thresh, self.nms_cmp,
+                                            seg_ids=sel["img_ids"].to(torch.int32), n_seg=n)
+                ev_k.record(s_k)
+            k0, k1 = c0 * kper, (c0 + n) * kper
+            pairs = [(self.h_labels[c0:c0 + n], labels), (self.h_lw[c0:c0 + n], lw), (self.h_bt[c0:c0 + n], bt),
+                     (self.h_bw[c0:c0 + n], bw), (self.h_boxes[k0:k1], sel["boxes"]), (self.h_scores[k0:k1], sel["scores"]),
+                     (self.h_img[k0:k1], sel["img_ids"]), (self.h_keep[k0:k1], keep), (h_nk[c0 // chunk, :n + 1], n_keep)]
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(ev_k)
+                for h, d in pairs:
+                    h.copy_(d, non_blocking=True)
+                    d2h += h.numel() * h.element_size()
+            hold.append((labels, lw, bt, bw, sel, keep, n_keep))      # keep device buffers alive until the drain
+        for s in self._streams:
+            s.synchronize()
+        # chunk-local indices -> batch-global (host side, a few thousand integers)
+        nk_all = np.zeros(B + 1, np.int32)
+        keep_np, img_np, nk_np = self.h_keep.numpy(), self.h_img.numpy(), h_nk.numpy()
+        out_keep, pos = self._keep_out.numpy(), 0
+        for ci, c0 in enumerate(range(0, B, chunk)):
+            n = min(chunk, B - c0)
+            k0 = c0 * kper
+            tot = int(nk_np[ci, n])
+            out_keep[pos:pos + tot] = keep_np[k0:k0 + tot] + k0
+            pos += tot
+            nk_all[c0:c0 + n] = nk_np[ci, :n]
+            img_np[k0:k0 + n * kper] += c0
+        nk_all[B] = pos
+        self.h_nkeep.numpy()[:] = nk_all
         self.h2d_bytes = G * 20 + self.h_off.numel() * 4 + self.d_prob.numel() * 4 + self.d_box.numel() * 4
-        self.d2h_bytes = sum(h.numel() * h.element_size() for h, _ in pairs)
+        self.d2h_bytes = d2h
         return {"labels": self.h_labels, "label_weights": self.h_lw, "bbox_targets": self.h_bt,
                 "bbox_inside_weights": self.h_bw, "boxes": self.h_boxes, "scores": self.h_scores,
-                "img_ids": self.h_img, "keep": self.h_keep, "n_keep": self.h_nkeep}
+                "img_ids": self.h_img, "keep": self._keep_out, "n_keep": self.h_nkeep}
 
     def detections(self, host_out):
         """Per-image [m,5] = (x1,y1,x2,y2,score) arrays from run_host()'s result (host-side views)."""

@@ -1,0 +1,64 @@
+"""GPU parity of the batched host-buffer entry (detbox.pipeline.BoxOpsSession) — the call bench.py's
+end-to-end leg times — against the CPU oracle, image by image: anchor labels / weights and NMS keep
+indices bit-exact, regression targets and decoded boxes within 1e-5 (util.assert_boxes_close)."""
+from importlib import import_module
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as O
+from oracle.make_golden import synth_gt
+from util import assert_boxes_close
+
+pytestmark = pytest.mark.gpu
+
+
+def make_case(B, ih, iw, seed):
+    cfg = O.citypersons_retinanet_cfg()
+    strides, scales = cfg.strides[:3], cfg.anchor_scales[:3]
+    rng = np.random.RandomState(seed)
+    anc = O.anchor_pyramid(strides, ih, iw, scales, cfg.anchor_ratios, cfg.anchor_base).astype(np.float32)
+    A = anc.shape[0]
+    gts = [synth_gt(rng, int(g), ih, iw, 0.2) if g else np.zeros((0, 5), np.float32) for g in rng.randint(0, 9, B)]
+    deltas = rng.normal(0, 0.5, (B * A, 4)).astype(np.float32)
+    p1 = rng.permutation(np.linspace(0.0, 1.0, B * A)).astype(np.float32)          # unique scores
+    prob = np.stack([1 - p1, p1], 1).astype(np.float32)
+    return cfg, strides, scales, anc, gts, deltas, prob
+
+
+@pytest.mark.parametrize("B,chunk", [(5, 2), (4, 4), (3, 8)])
+def test_run_host_matches_oracle(B, chunk):
+    pipeline = import_module("detectron-pytorch_b200.pipeline")
+    ih, iw, top_n = 256, 512, 300
+    cfg, strides, scales, anc, gts, deltas, prob = make_case(B, ih, iw, 11 + B)
+    A = anc.shape[0]
+    sess = pipeline.BoxOpsSession(strides, ih, iw, scales, cfg.anchor_ratios, cfg.anchor_base, B, 2, top_n=top_n,
+                                  nms_thresh=0.5, bg=cfg.rpn_bg_threshold, fg=cfg.rpn_fg_threshold, max_gt_total=16 * B)
+    assert sess.A == A
+    h_prob, h_box = torch.from_numpy(prob).pin_memory(), torch.from_numpy(deltas).pin_memory()
+    out = sess.run_host(gts, h_prob, h_box, chunk=chunk)
+    dev = sess.run_device(torch.from_numpy(np.concatenate(gts, 0)).cuda(), sess.h_off.cuda(), h_prob.cuda(), h_box.cuda())
+    torch.cuda.synchronize()
+    nk = out["n_keep"].numpy()
+    assert np.array_equal(nk, dev["n_keep"].cpu().numpy())                      # chunked == one-shot
+    assert np.array_equal(out["keep"].numpy()[:nk[B]], dev["keep"].cpu().numpy()[:nk[B]])
+    assert np.array_equal(out["img_ids"].numpy(), dev["img_ids"].cpu().numpy())
+    pos = 0
+    for b in range(B):
+        want = O.anchor_encode(gts[b], anc, cfg)
+        assert np.array_equal(out["labels"][b].numpy(), want[0])
+        assert np.array_equal(out["label_weights"][b].numpy(), want[1])
+        assert_boxes_close(out["bbox_targets"][b].numpy(), want[2])
+        assert np.array_equal(out["bbox_inside_weights"][b].numpy(), want[3])
+        wb, wp, _, _, widx = O.decode_and_choose_top_n(deltas[b * A:(b + 1) * A], prob[b * A:(b + 1) * A], anc, top_n, "softmax")
+        rows = slice(b * top_n, (b + 1) * top_n)
+        assert_boxes_close(out["boxes"].numpy()[rows], wb)
+        assert np.array_equal(out["scores"].numpy()[rows], 1.0 - wp[:, 0])
+        assert (out["img_ids"].numpy()[rows] == b).all()
+        wk = O.nms(out["boxes"].numpy()[rows], out["scores"].numpy()[rows], 0.5, O.NMS_GT_F32)
+        got = out["keep"].numpy()[pos:pos + nk[b]]
+        assert np.array_equal(got, wk + b * top_n)
+        pos += nk[b]
+    dets = sess.detections(out)
+    assert len(dets) == B and all(d.shape[1] == 5 for d in dets)
