@@ -35,7 +35,7 @@ class RoiCfg(ctypes.Structure):
                 ("spatial_scale", c_float * MAX_LEVELS), ("ref_area", c_float * MAX_LEVELS),
                 ("batch", c_int), ("channels", c_int), ("layout", c_int), ("out_layout", c_int),
                 ("pooled_h", c_int), ("pooled_w", c_int), ("mode", c_int), ("pool", c_int),
-                ("all_levels", c_int)]
+                ("all_levels", c_int), ("extrapolation", c_float)]
 
 
 # name -> (restype, argtypes); every symbol include/detbox.h declares

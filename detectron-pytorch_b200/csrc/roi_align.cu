@@ -27,6 +27,7 @@ using namespace detbox;
 namespace {
 
 constexpr int RA_THREADS = 256;
+constexpr int RA_UNROLL = 4;           // NHWC forward: items per thread per iteration
 constexpr int RA_MAXP = 33;          // max pooled size + 1 (grid-point pooled variants sample P+1)
 
 struct Tap { int i0, i1; float w; int valid; };
@@ -50,13 +51,8 @@ __device__ __forceinline__ int pick_level(const detbox_roi_cfg &c, const float *
     return best;
 }
 
-// bin-centre taps along one axis: roi_align_tf.py:24-40 then crop_and_resize.c:44-72
-__device__ __forceinline__ Tap tf_tap(float lo, float hi, float scale, int P, int L, int p) {
-    const float b1 = scale * lo, b2 = scale * hi;
-    const float sp = (b2 - b1) / (float)P;
-    const float n0 = (b1 + sp / 2 - 0.5f) / (float)(L - 1);
-    const float nl = sp * (float)(P - 1) / (float)(L - 1);
-    const float n1 = n0 + nl;
+// crop_and_resize taps along one axis from a NORMALISED interval [n0, n1]: crop_and_resize.c:44-72
+__device__ __forceinline__ Tap crop_tap(float n0, float n1, int P, int L, int p) {
     const float step = (P > 1) ? (n1 - n0) * (L - 1) / (P - 1) : 0;
     const float in = (P > 1) ? n0 * (L - 1) + p * step : (float)(0.5 * (double)(n0 + n1) * (L - 1));
     Tap t;
@@ -65,6 +61,15 @@ __device__ __forceinline__ Tap tf_tap(float lo, float hi, float scale, int P, in
     t.i0 = a; t.i1 = b; t.w = in - a;
     if (!t.valid) { t.i0 = t.i1 = 0; t.w = 0.0f; }
     return t;
+}
+
+// bin-centre taps along one axis: roi_align_tf.py:24-40 (normalise), then crop_tap
+__device__ __forceinline__ Tap tf_tap(float lo, float hi, float scale, int P, int L, int p) {
+    const float b1 = scale * lo, b2 = scale * hi;
+    const float sp = (b2 - b1) / (float)P;
+    const float n0 = (b1 + sp / 2 - 0.5f) / (float)(L - 1);
+    const float nl = sp * (float)(P - 1) / (float)(L - 1);
+    return crop_tap(n0, n0 + nl, P, L, p);
 }
 
 // grid-point taps along one axis: roi_align_kernel.cu:32-56 (G = number of grid points)
@@ -107,9 +112,11 @@ __device__ __forceinline__ Prologue roi_prologue(const RoiArgs &a, Tap *ty, Tap 
     gh = c.pooled_h + pool; gw = c.pooled_w + pool;
     const int t = threadIdx.x;
     if (t < gh) ty[t] = (c.mode == DETBOX_ROI_BIN_CENTRE) ? tf_tap(roi[2], roi[4], c.spatial_scale[l], gh, s.H, t)
+                      : (c.mode == DETBOX_ROI_CROP_NORM)  ? crop_tap(roi[1], roi[3], gh, s.H, t)
                                                           : gp_tap(roi[2], roi[4], c.spatial_scale[l], gh, s.H, t);
     else if (t >= 64 && t - 64 < gw)
         tx[t - 64] = (c.mode == DETBOX_ROI_BIN_CENTRE) ? tf_tap(roi[1], roi[3], c.spatial_scale[l], gw, s.W, t - 64)
+                   : (c.mode == DETBOX_ROI_CROP_NORM)  ? crop_tap(roi[2], roi[4], gw, s.W, t - 64)
                                                        : gp_tap(roi[1], roi[3], c.spatial_scale[l], gw, s.W, t - 64);
     __syncthreads();
     return s;
@@ -134,8 +141,8 @@ __device__ __forceinline__ size_t feat_index(int b, int c, int y, int x, int C, 
 }
 
 template <bool GRID, bool NHWC_IN>
-__device__ __forceinline__ float sample_one(const float *f, int b, int c, const Tap &y, const Tap &x, int C, int H, int W) {
-    if (!(y.valid && x.valid)) return 0.0f;
+__device__ __forceinline__ float sample_one(const float *f, int b, int c, const Tap &y, const Tap &x, int C, int H, int W, float ext) {
+    if (!(y.valid && x.valid)) return ext;
     const float tl = f[feat_index<NHWC_IN>(b, c, y.i0, x.i0, C, H, W)];
     const float tr = f[feat_index<NHWC_IN>(b, c, y.i0, x.i1, C, H, W)];
     const float bl = f[feat_index<NHWC_IN>(b, c, y.i1, x.i0, C, H, W)];
@@ -159,28 +166,50 @@ roi_fwd_kernel(const RoiArgs a)
     const long r = blockIdx.x;
     const float *f = s.ok ? c.feat[s.level] : nullptr;
     const int pool = (GRID && c.pool != DETBOX_POOL_NONE) ? c.pool : DETBOX_POOL_NONE;
+    const float ext = GRID ? 0.0f : c.extrapolation;
 
     if (NHWC_IN && NHWC_OUT && (C & 3) == 0 && pool == DETBOX_POOL_NONE) {
         // channel-coalesced float4 path
-        const int C4 = C >> 2;
-        for (int idx = threadIdx.x; idx < bins * C4; idx += RA_THREADS) {
-            const int c4 = idx % C4, bin = idx / C4;
-            const int y = bin / PW, x = bin - y * PW;
-            float4 v = make_float4(0, 0, 0, 0);
-            const Tap Y = ty[y], X = tx[x];
-            if (f && Y.valid && X.valid) {
-                const float4 *p = reinterpret_cast<const float4 *>(f);
-                const size_t rowb = (size_t)s.b * s.H;
-                const float4 tl = p[(((rowb + Y.i0) * s.W + X.i0) * C >> 2) + c4];
-                const float4 tr = p[(((rowb + Y.i0) * s.W + X.i1) * C >> 2) + c4];
-                const float4 bl = p[(((rowb + Y.i1) * s.W + X.i0) * C >> 2) + c4];
-                const float4 br = p[(((rowb + Y.i1) * s.W + X.i1) * C >> 2) + c4];
-                v.x = blend<GRID>(tl.x, tr.x, bl.x, br.x, Y.w, X.w);
-                v.y = blend<GRID>(tl.y, tr.y, bl.y, br.y, Y.w, X.w);
-                v.z = blend<GRID>(tl.z, tr.z, bl.z, br.z, Y.w, X.w);
-                v.w = blend<GRID>(tl.w, tr.w, bl.w, br.w, Y.w, X.w);
+        // Each thread keeps RA_UNROLL items = 4*RA_UNROLL independent 16-byte loads in flight before the
+        // first blend: the kernel is a latency-bound gather, bytes in flight are what buys bandwidth.
+        const int C4 = C >> 2, total = bins * C4;
+        const float4 *p = reinterpret_cast<const float4 *>(f);
+        const size_t rowb = (size_t)s.b * s.H;
+        float4 *outp = reinterpret_cast<float4 *>(a.out) + ((((size_t)r * bins) * Ctot + coff) >> 2);
+        const int Ctot4 = Ctot >> 2;
+        for (int base = threadIdx.x; base < total; base += RA_THREADS * RA_UNROLL) {
+            float4 tl[RA_UNROLL], tr[RA_UNROLL], bl[RA_UNROLL], br[RA_UNROLL];
+            float wy[RA_UNROLL], wx[RA_UNROLL];
+            int oidx[RA_UNROLL]; bool live[RA_UNROLL], ok[RA_UNROLL];
+#pragma unroll
+            for (int u = 0; u < RA_UNROLL; ++u) {
+                const int idx = base + u * RA_THREADS;
+                live[u] = idx < total;
+                const int bin = live[u] ? idx / C4 : 0, c4 = idx - bin * C4;
+                const int y = bin / PW, x = bin - y * PW;
+                const Tap Y = ty[y], X = tx[x];
+                ok[u] = live[u] && f && Y.valid && X.valid;
+                wy[u] = Y.w; wx[u] = X.w; oidx[u] = bin * Ctot4 + c4;
+                if (ok[u]) {
+                    const size_t r0 = (rowb + Y.i0) * s.W, r1 = (rowb + Y.i1) * s.W;
+                    tl[u] = __ldg(p + (((r0 + X.i0) * C) >> 2) + c4);
+                    tr[u] = __ldg(p + (((r0 + X.i1) * C) >> 2) + c4);
+                    bl[u] = __ldg(p + (((r1 + X.i0) * C) >> 2) + c4);
+                    br[u] = __ldg(p + (((r1 + X.i1) * C) >> 2) + c4);
+                }
             }
-            reinterpret_cast<float4 *>(a.out)[((((size_t)r * bins + bin) * Ctot + coff) >> 2) + c4] = v;
+#pragma unroll
+            for (int u = 0; u < RA_UNROLL; ++u) {
+                if (!live[u]) continue;
+                float4 v = f ? make_float4(ext, ext, ext, ext) : make_float4(0, 0, 0, 0);
+                if (ok[u]) {
+                    v.x = blend<GRID>(tl[u].x, tr[u].x, bl[u].x, br[u].x, wy[u], wx[u]);
+                    v.y = blend<GRID>(tl[u].y, tr[u].y, bl[u].y, br[u].y, wy[u], wx[u]);
+                    v.z = blend<GRID>(tl[u].z, tr[u].z, bl[u].z, br[u].z, wy[u], wx[u]);
+                    v.w = blend<GRID>(tl[u].w, tr[u].w, bl[u].w, br[u].w, wy[u], wx[u]);
+                }
+                __stcs(outp + oidx[u], v);               // streaming store: the output is not re-read here
+            }
         }
         return;
     }
@@ -192,12 +221,12 @@ roi_fwd_kernel(const RoiArgs a)
         float v = 0.0f;
         if (f) {
             if (pool == DETBOX_POOL_NONE) {
-                v = sample_one<GRID, NHWC_IN>(f, s.b, ch, ty[y], tx[x], C, s.H, s.W);
+                v = sample_one<GRID, NHWC_IN>(f, s.b, ch, ty[y], tx[x], C, s.H, s.W, ext);
             } else {   // 2x2 / stride 1 pool over the (PH+1)x(PW+1) sample grid (modules/roi_align.py:23-46)
-                const float v00 = sample_one<GRID, NHWC_IN>(f, s.b, ch, ty[y], tx[x], C, s.H, s.W);
-                const float v01 = sample_one<GRID, NHWC_IN>(f, s.b, ch, ty[y], tx[x + 1], C, s.H, s.W);
-                const float v10 = sample_one<GRID, NHWC_IN>(f, s.b, ch, ty[y + 1], tx[x], C, s.H, s.W);
-                const float v11 = sample_one<GRID, NHWC_IN>(f, s.b, ch, ty[y + 1], tx[x + 1], C, s.H, s.W);
+                const float v00 = sample_one<GRID, NHWC_IN>(f, s.b, ch, ty[y], tx[x], C, s.H, s.W, ext);
+                const float v01 = sample_one<GRID, NHWC_IN>(f, s.b, ch, ty[y], tx[x + 1], C, s.H, s.W, ext);
+                const float v10 = sample_one<GRID, NHWC_IN>(f, s.b, ch, ty[y + 1], tx[x], C, s.H, s.W, ext);
+                const float v11 = sample_one<GRID, NHWC_IN>(f, s.b, ch, ty[y + 1], tx[x + 1], C, s.H, s.W, ext);
                 v = (pool == DETBOX_POOL_AVG2) ? (((v00 + v01) + v10) + v11) * 0.25f
                                                : fmaxf(fmaxf(v00, v01), fmaxf(v10, v11));
             }
@@ -240,6 +269,43 @@ roi_bwd_kernel(const RoiArgs a)
     const int bins = PH * PW;
     const long r = blockIdx.x;
     float *gf = c.grad_feat[s.level];
+    const int pool = (GRID && c.pool != DETBOX_POOL_NONE) ? c.pool : DETBOX_POOL_NONE;
+
+    if (pool != DETBOX_POOL_NONE) {
+        // RoIAlignAvg / RoIAlignMax (modules/roi_align.py:23-46): the 2x2 / stride-1 pool over the
+        // (PH+1)x(PW+1) sample grid is differentiated here, fused with the 4-tap scatter.
+        const float *f = c.feat[s.level];
+        for (int idx = threadIdx.x; idx < bins * C; idx += RA_THREADS) {
+            int ch, bin;
+            if (NHWC_OUT) { ch = idx % C; bin = idx / C; } else { ch = idx / bins; bin = idx - ch * bins; }
+            const int y = bin / PW, x = bin - y * PW;
+            const size_t o = NHWC_OUT ? ((size_t)r * bins + bin) * Ctot + coff + ch
+                                      : ((size_t)r * Ctot + coff + ch) * bins + bin;
+            const float g = a.grad_out[o];
+            int pick = -1;
+            if (pool == DETBOX_POOL_MAX2) {          // first maximum in window order, like max_pool2d
+                float best = 0.0f;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float v = sample_one<GRID, NHWC_IN>(f, s.b, ch, ty[y + (k >> 1)], tx[x + (k & 1)], C, s.H, s.W, 0.0f);
+                    if (k == 0 || v > best) { best = v; pick = k; }
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (pick >= 0 && k != pick) continue;
+                const Tap Y = ty[y + (k >> 1)], X = tx[x + (k & 1)];
+                if (!(Y.valid && X.valid)) continue;
+                float w00, w01, w10, w11;
+                tap_weights<GRID>(pick >= 0 ? g : 0.25f * g, Y.w, X.w, w00, w01, w10, w11);
+                atomicAdd(gf + feat_index<NHWC_IN>(s.b, ch, Y.i0, X.i0, C, s.H, s.W), w00);
+                atomicAdd(gf + feat_index<NHWC_IN>(s.b, ch, Y.i0, X.i1, C, s.H, s.W), w01);
+                atomicAdd(gf + feat_index<NHWC_IN>(s.b, ch, Y.i1, X.i0, C, s.H, s.W), w10);
+                atomicAdd(gf + feat_index<NHWC_IN>(s.b, ch, Y.i1, X.i1, C, s.H, s.W), w11);
+            }
+        }
+        return;
+    }
 
     if (NHWC_IN && NHWC_OUT && (C & 3) == 0) {
         const int C4 = C >> 2;
@@ -294,14 +360,14 @@ int check_cfg(const detbox_roi_cfg *c, bool backward)
 {
     if (!c || c->n_levels < 1 || c->n_levels > DETBOX_MAX_LEVELS) return DETBOX_ERR_INVALID;
     if (c->batch < 0 || c->channels <= 0 || c->pooled_h <= 0 || c->pooled_w <= 0) return DETBOX_ERR_INVALID;
-    if (c->mode != DETBOX_ROI_BIN_CENTRE && c->mode != DETBOX_ROI_GRID_POINT) return DETBOX_ERR_INVALID;
+    if (c->mode != DETBOX_ROI_BIN_CENTRE && c->mode != DETBOX_ROI_GRID_POINT && c->mode != DETBOX_ROI_CROP_NORM) return DETBOX_ERR_INVALID;
     if (c->pool < 0 || c->pool > 2 || (c->pool != 0 && c->mode != DETBOX_ROI_GRID_POINT)) return DETBOX_ERR_INVALID;
-    if (backward && c->pool != DETBOX_POOL_NONE) return DETBOX_ERR_UNSUPPORTED;   // compose pool backward outside
     if (c->pooled_h + 1 > RA_MAXP || c->pooled_w + 1 > RA_MAXP) return DETBOX_ERR_UNSUPPORTED;
     if ((c->layout != 0 && c->layout != 1) || (c->out_layout != 0 && c->out_layout != 1)) return DETBOX_ERR_INVALID;
     for (int l = 0; l < c->n_levels; ++l) {
         if (c->height[l] <= 0 || c->width[l] <= 0) return DETBOX_ERR_INVALID;
         if (backward ? !c->grad_feat[l] : !c->feat[l]) return DETBOX_ERR_INVALID;
+        if (backward && c->pool == DETBOX_POOL_MAX2 && !c->feat[l]) return DETBOX_ERR_INVALID;   // arg-max needs the features
     }
     return DETBOX_OK;
 }

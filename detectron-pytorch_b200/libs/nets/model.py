@@ -1,0 +1,70 @@
+"""libs.nets.model — the hot-path call sites of detection_model (reference libs/nets/model.py) as
+free functions with the methods' names, arguments and return tuples.  Tensors stay on the device."""
+import torch
+
+from ... import ops, ops_post
+from ..configs import config as cfg
+
+
+def _objectness(probs, activation=None):
+    """model.py:54-61 (eager; the fused path computes it inside objectness_kernel)."""
+    activation = cfg.class_activation if activation is None else activation
+    if activation == 'softmax':
+        return 1. - probs[:, 0]
+    if activation == 'sigmoid':
+        return probs.max(dim=1)[0]
+    raise ValueError('Unknown activation funtion %s' % activation)
+
+
+def _decode_and_choose_top_n_stage1(rpn_box, rpn_prob, anchors, top_n=1000, activation=None, per_image=False):
+    """model.py:308-321: ONE descending selection over batch x levels x anchors (the multi-level
+    merge), gather, decode (no clip) -> (boxes [k,4], probs [k,C], img_ids int64 [k], anchors [k,4]).
+    Ties between equal scores: lower flat index first (upstream's torch.sort leaves them undefined).
+    per_image=True takes top_n inside every image instead (the sharded mode)."""
+    activation = cfg.class_activation if activation is None else activation
+    out = ops_post.topk_decode(rpn_box, rpn_prob, anchors, top_n, activation, cfg.rpn_box_encoding, per_image,
+                               want=("probs", "img_ids", "anchors"))
+    return out["boxes"], out["probs"], out["img_ids"], out["anchors"]
+
+
+def _decoding_and_thresholding_stage1(rpn_box, rpn_prob, anchors, score_threshold=0.3, max_dets=100, activation=None):
+    """model.py:323-340: top max_dets*3, then objectness >= threshold (fallback: the single best)."""
+    boxes, probs, img_ids, anc = _decode_and_choose_top_n_stage1(rpn_box, rpn_prob, anchors, top_n=max_dets * 3, activation=activation)
+    objness = _objectness(probs, activation)
+    inds = objness.ge(score_threshold).nonzero().view(-1)
+    if inds.numel() == 0:
+        inds = objness.sort(dim=0, descending=True, stable=True)[1][:1]
+    return boxes[inds], probs[inds], img_ids[inds], anc[inds]
+
+
+def _apply_nms_in_batch(boxes, probs, img_ids, anchors, activation, overlap_threshold=0.5):
+    """model.py:343-355: per-image NMS, kept rows image-major and score-descending inside an image.
+    Upstream loops over images in Python with a nonzero() sync per image; here the images are
+    segments of one launch sequence and the single host read is the total count."""
+    objness = _objectness(probs, activation)
+    if boxes.shape[0] == 0:
+        return boxes, probs, img_ids, anchors
+    lo = int(img_ids.min().item())
+    n_seg = int(img_ids.max().item()) - lo + 1
+    keep, n_keep = ops_post.nms(boxes[:, :4], objness, float(overlap_threshold), ops.NMS_GT_F32,
+                                seg_ids=(img_ids - lo).to(torch.int32), n_seg=n_seg)
+    all_keeps = keep[:int(n_keep[-1].item())]
+    return boxes[all_keeps], probs[all_keeps], img_ids[all_keeps], anchors[all_keeps]
+
+
+def _stage_one_results(rpn_box, rpn_prob, anchors, top_n=2000, overlap_threshold=0.7, top_n_post_nms=None, activation=None):
+    """model.py:79-90."""
+    activation = cfg.class_activation if activation is None else activation
+    boxes, probs, img_ids, anc = _decode_and_choose_top_n_stage1(rpn_box, rpn_prob, anchors, top_n=top_n, activation=activation)
+    boxes, probs, img_ids, anc = _apply_nms_in_batch(boxes, probs, img_ids, anc, activation=activation, overlap_threshold=overlap_threshold)
+    if top_n_post_nms is not None:
+        return boxes[:top_n_post_nms], probs[:top_n_post_nms], img_ids[:top_n_post_nms]
+    return boxes, probs, img_ids
+
+
+def get_final_results_stage1(rpn_box, rpn_prob, anchors, score_threshold=0.1, max_dets=100, overlap_threshold=0.5, activation=None):
+    """model.py:474-497 up to the NumPy conversion: threshold (top max_dets*9) -> per-image NMS."""
+    activation = cfg.class_activation if activation is None else activation
+    boxes, probs, img_ids, anc = _decoding_and_thresholding_stage1(rpn_box, rpn_prob, anchors, score_threshold=score_threshold,
+                                                                  max_dets=max_dets * 3, activation=activation)
+    return _apply_nms_in_batch(boxes, probs, img_ids, anc, activation=activation, overlap_threshold=overlap_threshold)

@@ -19,7 +19,7 @@ from ._lib import check, lib
 ENC = {"fastrcnn": 0, "linear": 1, "simple": 2}
 ACT = {"softmax": 0, "sigmoid": 1}
 NMS_GE_F64, NMS_GE_F32, NMS_GT_F32 = 0, 1, 2
-ROI_BIN_CENTRE, ROI_GRID_POINT = 0, 1
+ROI_BIN_CENTRE, ROI_GRID_POINT, ROI_CROP_NORM = 0, 1, 2
 POOL = {None: 0, "none": 0, "avg": 1, "max": 2}
 
 _launches = 0          # kernels launched through this module (bench.py reports it)

@@ -8,7 +8,7 @@ import torch
 
 from . import _lib
 from ._lib import check, lib
-from .ops import POOL, ROI_BIN_CENTRE, ROI_GRID_POINT, _count, _dev, _ptr, _stream  # noqa: F401
+from .ops import POOL, ROI_BIN_CENTRE, ROI_CROP_NORM, ROI_GRID_POINT, _count, _dev, _ptr, _stream  # noqa: F401
 
 
 def _is_channels_last(t: torch.Tensor) -> bool:
@@ -16,7 +16,7 @@ def _is_channels_last(t: torch.Tensor) -> bool:
         and not t.is_contiguous()
 
 
-def _make_cfg(feats, spatial_scales, ref_areas, ph, pw, mode, pool, all_levels, grads=None):
+def _make_cfg(feats, spatial_scales, ref_areas, ph, pw, mode, pool, all_levels, grads=None, extrapolation=0.0):
     L = len(feats)
     if not 1 <= L <= _lib.MAX_LEVELS:
         raise _lib.DetboxError("1..%d pyramid levels supported" % _lib.MAX_LEVELS)
@@ -43,6 +43,7 @@ def _make_cfg(feats, spatial_scales, ref_areas, ph, pw, mode, pool, all_levels, 
     c.layout = c.out_layout = 1 if nhwc else 0
     c.pooled_h, c.pooled_w = int(ph), int(pw)
     c.mode, c.pool, c.all_levels = int(mode), POOL[pool], int(bool(all_levels))
+    c.extrapolation = float(extrapolation)
     return c, keep, nhwc
 
 
@@ -53,13 +54,13 @@ def _out_tensor(R, C, ph, pw, nhwc, device):
 
 
 def roi_align_forward(feats, rois, spatial_scales, ph, pw, mode=ROI_BIN_CENTRE, pool=None,
-                      levels=None, ref_areas=None, all_levels=False):
+                      levels=None, ref_areas=None, all_levels=False, extrapolation=0.0):
     """One launch over all pyramid levels.  feats: list of [B,C,H_l,W_l] (all NCHW-contiguous or all
     channels_last); rois [R,5] = (batch idx, x1, y1, x2, y2) in image coordinates.  Level of a RoI:
     `levels` (int32 [R]) if given, else computed in-kernel from ref_areas when there are several
     levels (pyramid_roi_align.py:33-37).  Output [R, C (or L*C), ph, pw] in the input's memory format."""
     r = _dev(rois).view(-1, 5)
-    cfg, keep, nhwc = _make_cfg(feats, spatial_scales, ref_areas, ph, pw, mode, pool, all_levels)
+    cfg, keep, nhwc = _make_cfg(feats, spatial_scales, ref_areas, ph, pw, mode, pool, all_levels, extrapolation=extrapolation)
     if len(feats) > 1 and not all_levels and levels is None and ref_areas is None:
         raise _lib.DetboxError("several levels need `levels`, `ref_areas` or all_levels=True")
     lv = _dev(levels, torch.int32, "levels").view(-1) if levels is not None else None
@@ -72,10 +73,12 @@ def roi_align_forward(feats, rois, spatial_scales, ph, pw, mode=ROI_BIN_CENTRE, 
 
 
 def roi_align_backward(grad_out, feat_shapes, rois, spatial_scales, mode=ROI_BIN_CENTRE, levels=None,
-                       ref_areas=None, all_levels=False, channels_last=False, grads=None):
+                       ref_areas=None, all_levels=False, channels_last=False, grads=None, pool=None, feats=None):
     """Gradient w.r.t. the feature maps (dense, zero-filled here unless `grads` is given, in which
     case it is accumulated into).  grad_out [R, C(or L*C), ph, pw] in the same memory format as the
-    features.  Returns the list of gradient maps."""
+    features.  pool='avg'|'max' differentiates the fused 2x2 pool of RoIAlignAvg/Max as well
+    ('max' needs `feats`, the forward's feature maps, to recompute the arg-max).  Returns the list
+    of gradient maps."""
     r = _dev(rois).view(-1, 5)
     dev = r.device
     g = grad_out
@@ -100,7 +103,13 @@ def roi_align_backward(grad_out, feat_shapes, rois, spatial_scales, mode=ROI_BIN
     c.batch, c.channels = grads[0].shape[0], grads[0].shape[1]
     c.layout = c.out_layout = 1 if channels_last else 0
     c.pooled_h, c.pooled_w = g.shape[2], g.shape[3]
-    c.mode, c.pool, c.all_levels = int(mode), 0, int(bool(all_levels))
+    c.mode, c.pool, c.all_levels = int(mode), POOL[pool], int(bool(all_levels))
+    if POOL[pool] == 2:
+        if feats is None:
+            raise _lib.DetboxError("roi_align_backward(pool='max') needs the forward's feature maps")
+        feats = [f if channels_last else f.contiguous() for f in feats]
+        for l, f in enumerate(feats):
+            c.feat[l] = f.data_ptr()
     lv = _dev(levels, torch.int32, "levels").view(-1) if levels is not None else None
     check(lib().detbox_roi_align_backward(ctypes.byref(c), r.data_ptr(), r.shape[0], _ptr(lv), g.data_ptr(), int(zero), _stream()),
           "roi_align_backward")

@@ -51,6 +51,8 @@ extern "C" {
 /* RoIAlign sampling convention / level mode / fused 2x2 pooling / layout */
 #define DETBOX_ROI_BIN_CENTRE 0 /* roi_align_tf (crop_and_resize.c + roi_align_tf.py:24-40)   */
 #define DETBOX_ROI_GRID_POINT 1 /* roi_align/src/cuda/roi_align_kernel.cu:15-68              */
+#define DETBOX_ROI_CROP_NORM  2 /* raw crop_and_resize (crop_and_resize.c:6-112): rois rows are
+                                   (box_ind, y1, x1, y2, x2) with NORMALISED coordinates          */
 #define DETBOX_POOL_NONE 0
 #define DETBOX_POOL_AVG2 1      /* RoIAlignAvg roi_align/modules/roi_align.py:23-33           */
 #define DETBOX_POOL_MAX2 2      /* RoIAlignMax roi_align/modules/roi_align.py:36-46           */
@@ -213,6 +215,8 @@ typedef struct {
     int mode;                               /* DETBOX_ROI_*                                 */
     int pool;                               /* DETBOX_POOL_*  (grid-point mode only)        */
     int all_levels;
+    float extrapolation;                    /* value of samples outside the map (crop modes; the
+                                               RoIAlign wrapper passes 0, roi_align_tf.py:42)    */
 } detbox_roi_cfg;
 
 int detbox_roi_align_forward(const detbox_roi_cfg *cfg, const float *rois_dev /*[R,5] b,x1,y1,x2,y2*/,

@@ -1,0 +1,270 @@
+"""The drop-in boundary: the reference's module paths, names and call shapes, served by
+detbox.libs after install(), checked against the golden vectors the compiled reference produced
+(tests/golden/*.npz) and against the CPU oracle.  These read like the reference's own scripts:
+`import libs.boxes.cython_bbox as cython_bbox`, `from libs.layers.box import apply_nms`, ..."""
+import numpy as np
+import pytest
+import torch
+
+import detbox
+from oracle import oracle as O
+from util import assert_boxes_close
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module", autouse=True)
+def libs():
+    return detbox.libs.install()
+
+
+def cu(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+# ------------------------------------------------------------------------------- libs.boxes ----
+def test_cython_bbox_matches_golden(golden):
+    import libs.boxes.cython_bbox as cython_bbox
+    g = golden("iou")
+    assert np.array_equal(cython_bbox.bbox_overlaps(g["boxes"], g["query"]), g["ov"])
+    assert np.array_equal(cython_bbox.bbox_intersections(g["boxes"], g["query"]), g["inter"])
+    assert np.array_equal(cython_bbox.bbox_overlaps(g["boxes_int"], g["query_int"]), g["ov_int"])
+    assert np.array_equal(cython_bbox.bbox_exclude_ignored_areas(g["boxes"], g["query"], 0.2), g["excl"])
+    # the reference's own fixture (anchor_target_test.py:15-31)
+    ov = cython_bbox.bbox_overlaps(g["fix_anchors"].astype(np.float64), np.ascontiguousarray(g["fix_gt"][:, :4], np.float64))
+    assert np.array_equal(ov, g["fix_ov"])
+    with pytest.raises(ValueError):
+        cython_bbox.bbox_overlaps(g["boxes"].astype(np.float32), g["query"])
+
+
+def test_anchor_module_matches_golden(golden):
+    from libs.boxes.anchor import anchor_one_plane, anchor_pyramid, anchors, anchors_plane
+    g = golden("anchors")
+    scales = [[2, 2.520, 3.175], [4, 5.040, 6.349], [8, 10.079, 12.700], [16, 20.159, 25.398], [32, 40.317, 50.797]]
+    for l in range(5):
+        assert np.array_equal(anchors(scales[l], [1, 2.5], 16), g["base_cpr_l%d" % l])
+    pyr = anchor_pyramid([8, 16, 32, 64, 128], 1024, 2048, scales, [1, 2.5], 16, [[0.0, 0.0]])
+    assert pyr.dtype == np.float64 and tuple(pyr.shape) == tuple(g["cpr_pyramid_shape"])
+    assert np.array_equal(pyr[g["cpr_pyramid_rows_idx"]], g["cpr_pyramid_rows"])
+    assert np.array_equal(anchor_pyramid([4, 8, 16], 64, 96, [[2, 3], [4, 6], [8, 12]], [0.5, 1, 2.0], 16,
+                                         [[0.0, 0.0], [0.5, 0.25]]), g["small_pyramid"])
+    assert np.array_equal(anchor_one_plane(5, 7, 8, [2., 4.], [0.5, 2.0], 16, [[0, 0], [0.5, 0]]), g["plane_shifted"])
+    pl = anchors_plane(5, 7, 8, [2., 4.], [0.5, 2.0], 16, [[0, 0]])
+    assert pl.shape == (5, 7, 4, 4)
+    assert np.array_equal(pl.reshape(-1, 4), O.anchor_one_plane(5, 7, 8, [2., 4.], [0.5, 2.0], 16, [[0, 0]]))
+
+
+def test_bbox_transform_matches_golden(golden):
+    from libs.boxes import bbox_transform as bt
+    g = golden("transform")
+    assert_boxes_close(bt.bbox_transform(g["anchors"], g["gt"]), g["enc"])
+    assert_boxes_close(bt.bbox_transform_inv(g["anchors"], g["deltas"]), g["dec"])
+    assert_boxes_close(bt.bbox_transform_linear(g["anchors"], g["gt"]), g["enc_linear"])
+    assert_boxes_close(bt.bbox_transform_inv_linear(g["anchors"], g["deltas"]), g["dec_linear"])
+    b = g["dec"].copy()
+    r = bt.clip_boxes(b, (600, 800))
+    assert r is b                                                  # in place, same array returned
+    assert_boxes_close(b, np.stack([np.clip(g["dec"][:, 0], 0, 799), np.clip(g["dec"][:, 1], 0, 599),
+                                    np.clip(g["dec"][:, 2], 0, 799), np.clip(g["dec"][:, 3], 0, 599)], 1))
+    assert bt.bbox_transform_inv(np.zeros((0, 4), np.float32), np.zeros((0, 8), np.float32)).shape == (0, 8)
+    two = bt.bbox_transform_inv(g["anchors"], np.hstack([g["deltas"], g["deltas"]]))      # k-class layout
+    assert_boxes_close(two[:, :4], g["dec"]); assert_boxes_close(two[:, 4:], g["dec"])
+
+
+@pytest.mark.parametrize("name", ["rand1k", "rand3k", "clustered2k", "intgrid600"])
+@pytest.mark.parametrize("thr", [0.3, 0.5, 0.7])
+def test_nms_modules_match_golden(golden, name, thr):
+    from libs.boxes.nms_wrapper import nms
+    from libs.nms.cpu_nms import cpu_nms
+    from libs.nms.gpu_nms import gpu_nms
+    g = golden("nms")
+    dets = g[name]
+    assert cpu_nms(dets, thr) == list(g["%s_keep_ge_%s" % (name, thr)])          # the reference's cpu_nms
+    assert gpu_nms(dets, thr) == list(g["%s_keep_gt_%s" % (name, thr)])          # py_cpu_nms ('>')
+    assert nms(dets, thr, force_cpu=True) == list(g["%s_keep_ge_%s" % (name, thr)])
+    assert nms(dets[:0], thr) == []
+    with pytest.raises(TypeError):
+        cpu_nms(dets, 1)                                                          # thresh must be a float
+
+
+# ------------------------------------------------------------------------------ libs.layers ----
+@pytest.mark.parametrize("case", ["fixture", "small_a", "small_noclobber", "small_zero_col", "small_nogt", "small_dup_gt"])
+def test_layers_anchor_encode_matches_golden(golden, case):
+    import libs.configs.config as cfg
+    from libs.layers import anchor
+    from libs.layers.data_layer import compute_rpn_targets_in_batch
+    g = golden("anchor_target")
+    bg, fg, clobber = g[case + "_cfg"]
+    cfg.rpn_bg_threshold, cfg.rpn_fg_threshold, cfg.rpn_clobber_positives = float(bg), float(fg), bool(clobber)
+    try:
+        labels, lw, bt, bw = anchor.encode(g[case + "_gt"], g[case + "_anchors"])
+        assert np.array_equal(labels, g[case + "_labels"])
+        assert np.array_equal(lw, g[case + "_label_weights"])
+        assert_boxes_close(bt, g[case + "_bbox_targets"], extra_scale=1.0)
+        assert np.array_equal(bw, g[case + "_bbox_inside_weights"])
+        batch = compute_rpn_targets_in_batch([g[case + "_gt"], np.zeros((0, 5), np.float32)], g[case + "_anchors"])
+        assert batch[0].shape == (2, labels.shape[0]) and np.array_equal(batch[0][0], labels) and (batch[0][1] == 0).all()
+        assert np.array_equal(batch[3][0], bw)
+    finally:
+        cfg.rpn_bg_threshold, cfg.rpn_fg_threshold, cfg.rpn_clobber_positives = 0.4, 0.6, True
+
+
+def test_layers_anchor_decode_and_single_shot(golden):
+    import libs.configs.config as cfg
+    from libs.layers import anchor
+    from libs.postprocessings.single_shot import compute_detection
+    g = golden("transform")
+    rng = np.random.RandomState(3)
+    scores = rng.rand(500, 3).astype(np.float32)
+    fb, classes, sc = anchor.decode(g["deltas"], scores, g["anchors"], 600, 800, 3)
+    want = O.anchor_decode(g["deltas"], scores, g["anchors"], 600, 800, 3)
+    assert_boxes_close(fb, want[0]); assert np.array_equal(classes, want[1]) and classes.dtype == np.int32
+    # compute_detection == decode + per-class threshold + NMS + top-k, composed from the oracle's pieces
+    dets = compute_detection((None, g["deltas"], scores), g["anchors"], 600, 800, 3, score_threshold=0.5,
+                             overlap_threshold=0.5, max_det_num=50)
+    assert len(dets) == 1
+    rows = []
+    for j in (1, 2):
+        inds = np.where(scores[:, j] > 0.5)[0]
+        d = np.hstack([want[0][inds], scores[inds, j][:, None]]).astype(np.float32)
+        k = O.nms(d[:, :4], d[:, 4], 0.5, O.NMS_GT_F32)
+        rows.append(np.hstack([d[k], np.full((len(k), 1), j)]))
+    w = np.vstack(rows); w = w[np.argsort(-w[:, 4], kind="stable")][:50]
+    assert np.array_equal(dets[0][:, 4:], w[:, 4:])
+    assert_boxes_close(dets[0][:, :4], w[:, :4])
+
+
+def test_layers_box_torch_functions(golden):
+    from libs.layers.box import apply_nms, decoding_box, encoding_box
+    g, n = golden("transform"), golden("nms")
+    assert_boxes_close(decoding_box(cu(g["deltas"]), cu(g["anchors"])).cpu().numpy(), g["dec"])
+    assert_boxes_close(encoding_box(cu(g["gt"]), cu(g["anchors"])).cpu().numpy(), g["enc"])
+    dets = n["rand3k"]
+    keep = apply_nms(cu(dets[:, :4]), cu(dets[:, 4]), 0.5)
+    assert keep.dtype == torch.int64 and keep.is_cuda
+    assert keep.cpu().tolist() == list(n["rand3k_keep_gt_0.5"])
+    with pytest.raises(detbox.DetboxError):
+        apply_nms(torch.from_numpy(dets[:, :4]), torch.from_numpy(dets[:, 4]), 0.5)
+
+
+def test_anchor_target_module(golden):
+    from libs.layers.anchor_target.modules.anchor_target import AnchorTarget
+    g = golden("anchor_target")
+    labels, deltas, bbw = AnchorTarget(0.3, 0.6, ignored_threshold=0.3)(cu(g["fixture_anchors"]), g["fixture_gt"])
+    assert labels.dtype == torch.int64
+    assert np.array_equal(labels.cpu().numpy(), g["fixture_labels"].astype(np.int64))
+    assert np.array_equal(bbw.cpu().numpy(), g["fixture_bbox_inside_weights"])
+
+
+# -------------------------------------------------------------------------------- libs.nets ----
+def test_nets_model_stage_one():
+    import libs.configs.config as cfg
+    from libs.nets import model
+    rng = np.random.RandomState(5)
+    anc = O.anchor_pyramid([8, 16], 128, 256, [[2, 3], [4, 6]], [0.5, 1, 2.0], 16).astype(np.float32)
+    A, B = anc.shape[0], 3
+    deltas = rng.normal(0, 0.5, (B * A, 4)).astype(np.float32)
+    p1 = rng.permutation(np.linspace(0, 1, B * A)).astype(np.float32)
+    prob = np.stack([1 - p1, p1], 1).astype(np.float32)
+    b, p, ids, a = model._decode_and_choose_top_n_stage1(cu(deltas), cu(prob), cu(anc), top_n=500, activation="softmax")
+    wb, wp, wi, wa, _ = O.decode_and_choose_top_n(deltas, prob, anc, 500, "softmax")
+    assert_boxes_close(b.cpu().numpy(), wb)
+    assert np.array_equal(p.cpu().numpy(), wp) and np.array_equal(ids.cpu().numpy(), wi) and np.array_equal(a.cpu().numpy(), wa)
+    kb, kp, kid, ka = model._apply_nms_in_batch(b, p, ids, a, "softmax", overlap_threshold=0.5)
+    wk = O.apply_nms_in_batch(b.cpu().numpy(), wp, wi, "softmax", 0.5, O.NMS_GT_F32)
+    assert np.array_equal(kp.cpu().numpy(), wp[wk]) and np.array_equal(kid.cpu().numpy(), wi[wk])
+    sb, sp, sid = model._stage_one_results(cu(deltas), cu(prob), cu(anc), top_n=500, overlap_threshold=0.5,
+                                           top_n_post_nms=100, activation="softmax")
+    assert np.array_equal(sp.cpu().numpy(), wp[wk][:100])
+
+
+# ----------------------------------------------------------------- libs.layers.roi_align(_tf) ----
+def test_crop_and_resize_function_matches_golden(golden):
+    from libs.layers.roi_align_tf.crop_and_resize import CropAndResizeFunction
+    g = golden("roialign")
+    img = cu(g["image"]).requires_grad_(True)
+    out = CropAndResizeFunction(7, 7, 0)(img, cu(g["boxes"]), cu(g["box_ind"]))
+    assert np.array_equal(out.detach().cpu().numpy(), g["crops7"])               # bit-exact vs crop_and_resize.c
+    out.backward(cu(g["grad"]))
+    np.testing.assert_allclose(img.grad.cpu().numpy(), g["grad_image7"], rtol=1e-5, atol=1e-5)
+    assert np.array_equal(CropAndResizeFunction(3, 5, 0)(cu(g["image"]), cu(g["boxes"]), cu(g["box_ind"])).cpu().numpy(), g["crops3x5"])
+    assert np.array_equal(CropAndResizeFunction(1, 1, 0)(cu(g["image"]), cu(g["boxes"]), cu(g["box_ind"])).cpu().numpy(), g["crops1"])
+    ext = CropAndResizeFunction(7, 7, -3.5)(cu(g["image"]), cu(g["boxes"]), cu(g["box_ind"])).cpu().numpy()
+    assert np.array_equal(ext, O.crop_and_resize_fwd(g["image"], g["boxes"], g["box_ind"], -3.5, 7, 7))
+
+
+def make_pyramid(rng, B=2, C=6, ih=128, iw=256, strides=(4, 8, 16, 32)):
+    return [rng.normal(0, 1, (B, C, ih // s, iw // s)).astype(np.float32) for s in strides]
+
+
+def make_rois(rng, R, B, ih=128, iw=256):
+    wh = np.exp(rng.uniform(np.log(6), np.log(120), (R, 2)))
+    c = rng.uniform(0, 1, (R, 2)) * [iw, ih]
+    boxes = np.concatenate([c - wh / 2, c + wh / 2], 1).astype(np.float32)
+    return boxes, rng.randint(0, B, R).astype(np.int64)
+
+
+def test_roi_align_tf_modules_vs_oracle():
+    import libs.configs.config as cfg
+    from libs.layers.roi_align_tf.pyramid_roi_align import PyramidRoIAlign, PyramidRoIAlign2
+    from libs.layers.roi_align_tf.roi_align_tf import RoIAlign
+    rng = np.random.RandomState(8)
+    strides = (4, 8, 16, 32)
+    old = (cfg.strides, cfg.anchor_scales)
+    cfg.strides, cfg.anchor_scales = strides, [[2, 2.52, 3.17], [4, 5.04, 6.35], [8, 10.08, 12.70], [16, 20.16, 25.40]]
+    try:
+        feats = make_pyramid(rng)
+        boxes, bidx = make_rois(rng, 40, 2)
+        rois = np.concatenate([bidx[:, None].astype(np.float32), boxes], 1)
+        f0 = cu(feats[1]).requires_grad_(True)
+        y = RoIAlign(7, 7)(f0, cu(rois), 1.0 / 8)
+        assert np.array_equal(y.detach().cpu().numpy(), O.roi_align_tf_fwd(feats[1], rois, np.float32(1.0 / 8), 7, 7))
+        gy = rng.normal(0, 1, y.shape).astype(np.float32)
+        y.backward(cu(gy))
+        np.testing.assert_allclose(f0.grad.cpu().numpy(), O.roi_align_tf_bwd(gy, rois, np.float32(1.0 / 8), feats[1].shape), rtol=1e-4, atol=1e-5)
+        ra = (np.asarray(cfg.anchor_scales, np.float32).mean(axis=1) * cfg.anchor_base) ** 2
+        pyr = [cu(f).requires_grad_(True) for f in feats]
+        out = PyramidRoIAlign(7, 7)(pyr, cu(boxes), cu(bidx))
+        want = O.pyramid_roi_align(feats, boxes, bidx, strides, ra, 7, 7, "tf")
+        assert np.array_equal(out.detach().cpu().numpy(), want)
+        g = rng.normal(0, 1, want.shape).astype(np.float32)
+        out.backward(cu(g))
+        lv = O.assign_levels(boxes, ra)
+        for l, s in enumerate(strides):
+            sel = lv == l
+            wg = O.roi_align_tf_bwd(g[sel], rois[sel], np.float32(1.0 / s), feats[l].shape) if sel.any() else np.zeros_like(feats[l])
+            np.testing.assert_allclose(pyr[l].grad.cpu().numpy(), wg, rtol=1e-4, atol=1e-5)
+        m2 = PyramidRoIAlign2(7, 7, num_channels=6).cuda()
+        crops = m2.crop([cu(f) for f in feats], cu(boxes), cu(bidx))
+        assert np.array_equal(crops.cpu().numpy(), O.pyramid_roi_align(feats, boxes, bidx, strides, ra, 7, 7, "tf", all_levels=True))
+        assert m2([cu(f) for f in feats], cu(boxes), cu(bidx)).shape == (40, 6, 7, 7)
+    finally:
+        cfg.strides, cfg.anchor_scales = old
+
+
+@pytest.mark.parametrize("pool", [None, "avg", "max"])
+def test_roi_align_grid_modules_vs_oracle(pool):
+    import torch.nn.functional as F
+    from libs.layers.roi_align.modules.roi_align import RoIAlign, RoIAlignAvg, RoIAlignMax
+    rng = np.random.RandomState(9)
+    feat = rng.normal(0, 1, (2, 5, 24, 40)).astype(np.float32)
+    boxes, bidx = make_rois(rng, 30, 2, 96, 160)
+    rois = np.concatenate([bidx[:, None].astype(np.float32), boxes], 1)
+    mod = {None: RoIAlign, "avg": RoIAlignAvg, "max": RoIAlignMax}[pool](7, 7)
+    f = cu(feat).requires_grad_(True)
+    y = mod(f, cu(rois), 0.25)
+    P = 7 if pool is None else 8
+    grid = O.roi_align_grid_fwd(feat, rois, np.float32(0.25), P, P)
+    want = grid if pool is None else O.pool2x2(grid, pool)
+    np.testing.assert_allclose(y.detach().cpu().numpy(), want, rtol=1e-5, atol=1e-6)
+    gy = rng.normal(0, 1, y.shape).astype(np.float32)
+    y.backward(cu(gy))
+    # the reference composite: pool backward (torch autograd on the oracle's grid) then the grid-point scatter
+    if pool is None:
+        ggrid = gy
+    else:
+        t = torch.from_numpy(grid).requires_grad_(True)
+        (F.avg_pool2d(t, 2, 1) if pool == "avg" else F.max_pool2d(t, 2, 1)).backward(torch.from_numpy(gy))
+        ggrid = t.grad.numpy()
+    wg = O.roi_align_grid_bwd(ggrid, rois, np.float32(0.25), feat.shape)
+    np.testing.assert_allclose(f.grad.cpu().numpy(), wg, rtol=1e-4, atol=1e-4)
