@@ -52,7 +52,7 @@ SIGNATURES = {
     "detbox_box_encode": (c_int, [c_void, c_void, c_long, c_int, c_void, c_void]),
     "detbox_box_decode": (c_int, [c_void, c_void, c_long, c_int, c_int, c_int, c_void, c_void]),
     "detbox_clip_boxes": (c_int, [c_void, c_long, c_int, c_int, c_int, c_void]),
-    "detbox_anchor_target_workspace_bytes": (c_size, [c_int, c_long]),
+    "detbox_anchor_target_workspace_bytes": (c_size, [c_long, c_int, c_long]),
     "detbox_anchor_target": (c_int, [c_void, c_long, c_void, c_void, c_int, c_long, ctypes.POINTER(TargetCfg),
                                      c_void, c_void, c_void, c_void, c_void, c_void, c_size, c_void]),
     "detbox_topk_decode_workspace_bytes": (c_size, [c_int, c_long, c_long, c_int]),

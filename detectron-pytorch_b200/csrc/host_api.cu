@@ -23,7 +23,7 @@ extern "C" int detbox_anchor_target_host(const float *anchors, long A, const flo
     if (cur != device_id) DETBOX_CUDA_TRY(cudaSetDevice(device_id));
     const size_t b_anc = align_up((size_t)A * 16), b_gt = align_up((size_t)(G > 0 ? G : 1) * 20), b_off = 256;
     const size_t b_a1 = align_up((size_t)A * 4), b_a4 = align_up((size_t)A * 16);
-    const size_t b_ws = detbox_anchor_target_workspace_bytes(1, G);
+    const size_t b_ws = detbox_anchor_target_workspace_bytes(A, 1, G);
     void *base = nullptr;
     int rc = host_scratch(device_id, b_anc + b_gt + b_off + 2 * b_a1 + 2 * b_a4 + b_ws, &base);
     if (rc == DETBOX_OK) {

@@ -19,6 +19,7 @@
 //          the warp (channel-coalesced), the store is a float4 as well.
 // Backward scatters grad * weight into the 4 taps with red.global.add (float4-wide vector
 // reductions in NHWC, sm_90+), after an optional cudaMemsetAsync of the dense gradient maps.
+#include <stdlib.h>
 #include <type_traits>
 #include "common.cuh"
 
@@ -27,7 +28,6 @@ using namespace detbox;
 namespace {
 
 constexpr int RA_THREADS = 256;
-constexpr int RA_UNROLL = 4;           // NHWC forward: items per thread per iteration
 constexpr int RA_MAXP = 33;          // max pooled size + 1 (grid-point pooled variants sample P+1)
 
 struct Tap { int i0, i1; float w; int valid; };
@@ -151,7 +151,7 @@ __device__ __forceinline__ float sample_one(const float *f, int b, int c, const 
 }
 
 // ---- forward ------------------------------------------------------------------------------------
-template <bool GRID, bool NHWC_IN, bool NHWC_OUT>
+template <bool GRID, bool NHWC_IN, bool NHWC_OUT, int RA_UNROLL>
 __global__ void __launch_bounds__(RA_THREADS)
 roi_fwd_kernel(const RoiArgs a)
 {
@@ -404,7 +404,10 @@ extern "C" int detbox_roi_align_forward(const detbox_roi_cfg *cfg, const float *
     return dispatch(*cfg, [&](auto K) -> int {
         constexpr int k = decltype(K)::value;
         DETBOX_TRACE_BEGIN(DETBOX_K_ROI_FWD, st);
-        roi_fwd_kernel<(k & 4) != 0, (k & 2) != 0, (k & 1) != 0><<<grid, RA_THREADS, 0, st>>>(a);
+        static const int unroll = getenv("DETBOX_ROI_UNROLL") ? atoi(getenv("DETBOX_ROI_UNROLL")) : 1;
+        if ((k & 3) == 3 && unroll == 4) roi_fwd_kernel<(k & 4) != 0, (k & 2) != 0, (k & 1) != 0, 4><<<grid, RA_THREADS, 0, st>>>(a);
+        else if ((k & 3) == 3 && unroll == 2) roi_fwd_kernel<(k & 4) != 0, (k & 2) != 0, (k & 1) != 0, 2><<<grid, RA_THREADS, 0, st>>>(a);
+        else roi_fwd_kernel<(k & 4) != 0, (k & 2) != 0, (k & 1) != 0, 1><<<grid, RA_THREADS, 0, st>>>(a);
         DETBOX_TRACE_END(DETBOX_K_ROI_FWD, st);
         DETBOX_LAUNCH_CHECK();
         return DETBOX_OK;

@@ -46,3 +46,11 @@ def install(name: str = "libs"):
     for alias, sub in _ALIASES.items():          # the reference's deeper paths -> the flat mirror modules
         sys.modules["%s.%s" % (name, alias)] = sys.modules["%s.%s" % (name, sub)]
     return pkg
+
+
+def uninstall(name: str = "libs"):
+    """Remove the aliases install() created (the mirror itself stays importable as detbox.libs)."""
+    pkg = sys.modules[__name__]
+    if sys.modules.get(name) is pkg:
+        for k in [k for k in sys.modules if k == name or k.startswith(name + ".")]:
+            del sys.modules[k]

@@ -34,7 +34,7 @@ def encode(gt_boxes, all_anchors):
     check(lib().detbox_anchor_target_host(anc.ctypes.data, A, gt.ctypes.data if G else None, G, ctypes.byref(tc),
                                           labels.ctypes.data, lw.ctypes.data, bt.ctypes.data, bw.ctypes.data,
                                           torch.cuda.current_device()), "anchor.encode")
-    ops._count(3 if G else 2)
+    ops._count(4 if G else 2)
     return labels, lw, bt, bw
 
 

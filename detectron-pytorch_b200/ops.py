@@ -185,12 +185,12 @@ def anchor_target(anchors, gt, gt_offsets, tcfg, return_counts=False):
     bt = torch.empty((B, A, 4), dtype=torch.float32, device=dev)
     bw = torch.empty((B, A, 4), dtype=torch.float32, device=dev)
     counts = torch.empty((B, 2), dtype=torch.int32, device=dev) if return_counts else None
-    nbytes = lib().detbox_anchor_target_workspace_bytes(B, G)
+    nbytes = lib().detbox_anchor_target_workspace_bytes(A, B, G)
     ws = _ws.get(nbytes, dev)
     check(lib().detbox_anchor_target(a.data_ptr(), A, g.data_ptr() if G else 0, off.data_ptr(), B, G, ctypes.byref(tcfg),
                                      labels.data_ptr(), lw.data_ptr(), bt.data_ptr(), bw.data_ptr(), _ptr(counts),
                                      ws.data_ptr(), ws.numel(), _stream()), "anchor_target")
-    _count(3 if G else 2)
+    _count(4 if G else 2)
     if return_counts:
         return labels, lw, bt, bw, counts
     return labels, lw, bt, bw

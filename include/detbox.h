@@ -135,7 +135,7 @@ typedef struct {
     float  bbweights[4];        /* cfg.bbweights */
 } detbox_target_cfg;
 
-size_t detbox_anchor_target_workspace_bytes(int batch, long total_gt);
+size_t detbox_anchor_target_workspace_bytes(long A, int batch, long total_gt);
 /* anchors_dev [A,4] shared by the batch; gt_dev [total_gt,5] = (x1,y1,x2,y2,cls), images
  * concatenated; gt_offsets_dev int32 [batch+1].  Outputs [batch,A], [batch,A], [batch,A,4],
  * [batch,A,4].  counts_dev (optional, may be NULL): int32 [batch,2] = (#fg, #bg). */

@@ -15,7 +15,8 @@ pytestmark = pytest.mark.gpu
 
 @pytest.fixture(scope="module", autouse=True)
 def libs():
-    return detbox.libs.install()
+    yield detbox.libs.install()
+    detbox.libs.uninstall()          # tests/test_oracle_vs_ref.py imports the compiled reference as `libs`
 
 
 def cu(a):

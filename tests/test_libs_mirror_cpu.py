@@ -12,7 +12,8 @@ import detbox
 
 @pytest.fixture(scope="module", autouse=True)
 def libs():
-    return detbox.libs.install()
+    yield detbox.libs.install()
+    detbox.libs.uninstall()          # tests/test_oracle_vs_ref.py imports the compiled reference as `libs`
 
 
 def test_reference_module_paths_resolve():
