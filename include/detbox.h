@@ -76,7 +76,7 @@ int detbox_last_cuda_error(void);
 #define DETBOX_K_TARGET_WEIGHTS  4   /* label_weight_kernel                         */
 #define DETBOX_K_OBJECTNESS      5   /* objectness_kernel (score keys + histogram)  */
 #define DETBOX_K_NMS_MASK        6   /* mask_kernel                                 */
-#define DETBOX_K_NMS_SCAN        7   /* scan_kernel                                 */
+#define DETBOX_K_NMS_SCAN        7   /* nms_resolve_kernel (fixed-point keep set)    */
 #define DETBOX_K_ROI_FWD         8   /* roi_fwd_kernel                              */
 #define DETBOX_K_ROI_BWD         9   /* roi_bwd_kernel (without the zero fill)      */
 #define DETBOX_K_ROI_ZERO       10   /* zero fill of the dense gradient maps        */
