@@ -297,14 +297,30 @@ extern "C" int detbox_nms(const float *boxes, int box_stride, const float *score
                           const int32_t *seg_ids, int n_seg, double thresh, int cmp_mode,
                           int64_t *keep, int32_t *n_keep, void *ws, size_t ws_bytes, void *stream)
 {
+    const bool presorted = (cmp_mode & DETBOX_NMS_PRESORTED) != 0;
+    cmp_mode &= ~DETBOX_NMS_PRESORTED;
     if (n < 0 || box_stride < 4 || cmp_mode < 0 || cmp_mode > 2 || !n_keep) return DETBOX_ERR_INVALID;
+    if (presorted && (box_stride != 4 || ((uintptr_t)boxes & 15))) return DETBOX_ERR_INVALID;
     if (!seg_ids || n_seg <= 1) { n_seg = 1; seg_ids = nullptr; }
     cudaStream_t st = as_stream(stream);
     if (n == 0) { DETBOX_CUDA_TRY(cudaMemsetAsync(n_keep, 0, (size_t)(n_seg + 1) * sizeof(int32_t), st)); return DETBOX_OK; }
     if (n >= (1L << 31) - 64) return DETBOX_ERR_UNSUPPORTED;
-    if (!boxes || !scores || !keep) return DETBOX_ERR_INVALID;
+    if (!boxes || (!scores && !presorted) || !keep) return DETBOX_ERR_INVALID;
     if (!ws || ws_bytes < detbox_nms_workspace_bytes(n, n_seg)) return DETBOX_ERR_WORKSPACE;
     NmsBuffers b = carve_nms(ws, n, n_seg);
+    long gb0 = (n + 255) / 256; if (gb0 > kNumSMs * 8) gb0 = kNumSMs * 8;
+    if (presorted) {                              // rows are in processing order: no sort, no gather
+        if (n_seg > 1) {
+            DETBOX_CUDA_TRY(cudaMemsetAsync(b.seg_off, 0, (size_t)(n_seg + 2) * sizeof(int32_t), st));
+            nms_seg_count_kernel<<<(unsigned)gb0, 256, 0, st>>>(seg_ids, n, n_seg, b.seg_off);
+            DETBOX_LAUNCH_CHECK();
+            nms_seg_scan_kernel<<<1, 32, 0, st>>>(b.seg_off, n_seg);
+            DETBOX_LAUNCH_CHECK();
+        }
+        b.sorted = const_cast<float4 *>(reinterpret_cast<const float4 *>(boxes));
+        b.seg_sorted = const_cast<int32_t *>(seg_ids);
+        return nms_sorted(b, nullptr, n, n_seg, make_cmp(thresh, cmp_mode), keep, n_keep, st);
+    }
     int rc = make_score_keys(scores, n, b.ka, b.va, st);
     if (rc != DETBOX_OK) return rc;
     rc = radix_sort_pairs(b.ka, b.va, b.kb, b.vb, n, b.counts, st);

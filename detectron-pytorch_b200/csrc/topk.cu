@@ -248,6 +248,34 @@ cand_write_kernel(const uint32_t *__restrict__ keys, long seg_len, const SegStat
     }
 }
 
+// ---- 4'. sort of small segments (K <= 2048 winners each): one block per segment, bitonic network in
+// shared memory over the 64-bit composites (key << 32 | flat index) — unique, so the order is the
+// stable one (ties: lower flat index first).  Segments already sit image-major in ckeys / cvals.
+constexpr int SEG_SORT_MAX = 2048;
+
+__global__ void __launch_bounds__(SEG_SORT_MAX / 2)
+seg_sort_kernel(uint32_t *__restrict__ ckeys, uint32_t *__restrict__ cvals, int K, int N /*pow2 >= K*/)
+{
+    __shared__ unsigned long long v[SEG_SORT_MAX];
+    const int tid = threadIdx.x;
+    uint32_t *k = ckeys + (size_t)blockIdx.x * K, *x = cvals + (size_t)blockIdx.x * K;
+    for (int i = tid; i < N; i += blockDim.x)
+        v[i] = i < K ? ((unsigned long long)k[i] << 32) | x[i] : ~0ull;
+    __syncthreads();
+    for (int size = 2; size <= N; size <<= 1) {
+        for (int j = size >> 1; j > 0; j >>= 1) {
+            for (int t = tid; t < (N >> 1); t += blockDim.x) {
+                const int i = 2 * t - (t & (j - 1)), q = i + j;
+                const unsigned long long a = v[i], b = v[q];
+                const bool up = (i & size) == 0;
+                if ((a > b) == up) { v[i] = b; v[q] = a; }
+            }
+            __syncthreads();
+        }
+    }
+    for (int i = tid; i < K; i += blockDim.x) { k[i] = (uint32_t)(v[i] >> 32); x[i] = (uint32_t)v[i]; }
+}
+
 // ---- 5. gather + decode ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 gather_decode_kernel(const uint32_t *__restrict__ ckeys, const uint32_t *__restrict__ cvals, long n,
@@ -374,11 +402,20 @@ extern "C" int detbox_topk_decode(const float *prob, int C, const float *deltas,
     DETBOX_LAUNCH_CHECK();
     cand_write_kernel<<<cgrid, TK_THREADS, 0, st>>>(keys, p.seg_len, state, blk_lt, blk_eq, p.K, cka, cva);
     DETBOX_LAUNCH_CHECK();
-    // 4. sort the winners (stable): by key, then (per-image mode) by image id
-    int rc = radix_sort_pairs(cka, cva, ckb, cvb, p.n_cand, counts, st);
-    if (rc != DETBOX_OK) return rc;
+    // 4. sort the winners (stable): small segments in shared memory, else by key and then (per-image
+    //    mode) by image id with the global radix sort
+    int rc = DETBOX_OK;
     uint32_t *fk = cka, *fv = cva;
-    if (p.n_seg > 1) {
+    if (p.K <= SEG_SORT_MAX) {
+        int N = 2; while (N < p.K) N <<= 1;
+        const int threads = N / 2 < 32 ? 32 : N / 2;
+        seg_sort_kernel<<<p.n_seg, threads, 0, st>>>(cka, cva, (int)p.K, N);
+        DETBOX_LAUNCH_CHECK();
+    } else {
+        rc = radix_sort_pairs(cka, cva, ckb, cvb, p.n_cand, counts, st);
+        if (rc != DETBOX_OK) return rc;
+    }
+    if (p.K > SEG_SORT_MAX && p.n_seg > 1) {
         uint32_t *ki = cka, *vi = cva, *ko = ckb, *vo = cvb;
         for (int shift = 0; (p.n_seg - 1) >> shift; shift += 8) {
             DigitSrc d{1, shift, (uint32_t)A, nullptr};

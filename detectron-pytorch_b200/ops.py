@@ -69,6 +69,9 @@ _ws = _Workspace()
 
 
 # ---------------------------------------------------------------------------------- anchors ----
+_cell_cache = {}       # anchor configuration -> (cell anchors on the device, per-level sizes)
+
+
 def base_anchors(scales, ratios, base) -> np.ndarray:
     """libs/boxes/anchor.py:101-103 (host, float64 [n_ratios*n_scales, 4])."""
     s = np.ascontiguousarray(scales, np.float64).ravel()
@@ -82,17 +85,24 @@ def base_anchors(scales, ratios, base) -> np.ndarray:
 def anchor_pyramid(strides, ih, iw, anchor_scales, anchor_ratios, anchor_base, anchor_shift=((0.0, 0.0),),
                    device="cuda", dtype=torch.float32) -> torch.Tensor:
     """libs/boxes/anchor.py:30-44 on the device: [sum_l H_l*W_l*A, 4], level -> y -> x -> (shift, ratio, scale)."""
-    sh = np.asarray(anchor_shift, np.float64).reshape(-1, 2)
-    cells, n_cell, hs, ws = [], [], [], []
-    for i, stride in enumerate(strides):
-        sc = anchor_scales[i] if isinstance(anchor_scales[i], (list, tuple, np.ndarray)) else anchor_scales
-        base = base_anchors(sc, anchor_ratios, anchor_base)
-        shift4 = np.hstack((sh, sh)) * stride                      # anchor.py:54-55
-        cell = np.vstack([base + s for s in shift4])
-        cells.append(cell); n_cell.append(cell.shape[0])
-        hs.append(int(ih / stride)); ws.append(int(iw / stride))
+    key = (repr(list(strides)), int(ih), int(iw), repr(anchor_scales), repr(anchor_ratios), int(anchor_base),
+           repr(np.asarray(anchor_shift, np.float64).tolist()), str(device))
+    hit = _cell_cache.get(key)
+    if hit is None:
+        sh = np.asarray(anchor_shift, np.float64).reshape(-1, 2)
+        cells, n_cell, hs, ws = [], [], [], []
+        for i, stride in enumerate(strides):
+            sc = anchor_scales[i] if isinstance(anchor_scales[i], (list, tuple, np.ndarray)) else anchor_scales
+            base = base_anchors(sc, anchor_ratios, anchor_base)
+            shift4 = np.hstack((sh, sh)) * stride                      # anchor.py:54-55
+            cell = np.vstack([base + s for s in shift4])
+            cells.append(cell); n_cell.append(cell.shape[0])
+            hs.append(int(ih / stride)); ws.append(int(iw / stride))
+        if len(_cell_cache) > 64:
+            _cell_cache.clear()
+        hit = _cell_cache[key] = (torch.from_numpy(np.vstack(cells)).to(device), n_cell, hs, ws)   # <= 1 KB, uploaded once
+    cell_dev, n_cell, hs, ws = hit
     L = len(strides)
-    cell_dev = torch.from_numpy(np.vstack(cells)).to(device)
     total = sum(h * w * n for h, w, n in zip(hs, ws, n_cell))
     out = torch.empty((total, 4), dtype=dtype, device=cell_dev.device)
     arr = lambda v: (ctypes.c_int * L)(*[int(x) for x in v])

@@ -61,10 +61,13 @@ def topk_decode(rpn_box, rpn_prob, anchors, top_n, activation="softmax", box_enc
     return out
 
 
-def nms(boxes, scores, thresh, cmp_mode=NMS_GT_F32, seg_ids=None, n_seg=1, return_counts=False):
+def nms(boxes, scores, thresh, cmp_mode=NMS_GT_F32, seg_ids=None, n_seg=1, return_counts=False, presorted=False):
     """Greedy NMS on the device.  boxes [n,>=4], scores [n] -> (keep int64 [n] buffer, n_keep int32
     [n_seg+1] on the device); no host synchronisation happens here.  keep[:n_keep[n_seg]] are the
-    kept ORIGINAL row indices, segment-major, score-descending inside a segment."""
+    kept ORIGINAL row indices, segment-major, score-descending inside a segment.
+    presorted=True: the rows already are in that processing order (segment ids non-decreasing, scores
+    non-increasing inside a segment, boxes [n,4]) — e.g. topk_decode(per_image=True) output — and the
+    sort + gather are skipped."""
     b, s = _dev(boxes), _dev(scores).view(-1)
     n = b.shape[0]
     if s.numel() != n:
@@ -79,7 +82,10 @@ def nms(boxes, scores, thresh, cmp_mode=NMS_GT_F32, seg_ids=None, n_seg=1, retur
     if n == 0:
         return keep, n_keep
     ws = _ws.get(lib().detbox_nms_workspace_bytes(n, n_seg), b.device)
-    check(lib().detbox_nms(b.data_ptr(), b.shape[1], s.data_ptr(), n, _ptr(seg), n_seg, float(thresh), int(cmp_mode),
+    if presorted and b.shape[1] != 4:
+        raise _lib.DetboxError("nms(presorted=True) needs boxes of shape [n,4]")
+    check(lib().detbox_nms(b.data_ptr(), b.shape[1], s.data_ptr(), n, _ptr(seg), n_seg, float(thresh),
+                           int(cmp_mode) | (0x100 if presorted else 0),
                            keep.data_ptr(), n_keep.data_ptr(), ws.data_ptr(), ws.numel(), _stream()), "nms")
-    _count(13 + 4 + (5 if n_seg > 1 else 0))
+    _count((3 if presorted else 13 + 4) + ((2 if presorted else 5) if n_seg > 1 else 0))
     return keep, n_keep

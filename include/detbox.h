@@ -47,6 +47,10 @@ extern "C" {
 #define DETBOX_NMS_GE_F64 0     /* (double)iou >= thr        libs/nms/cpu_nms.pyx:65          */
 #define DETBOX_NMS_GE_F32 1     /* iou >= (float)thr         libs/layers/nms/src/nms_cpu.c:76 */
 #define DETBOX_NMS_GT_F32 2     /* iou >  (float)thr         libs/nms/nms_kernel.cu:83        */
+/* OR-ed into cmp_mode: the rows already are in processing order — segment ids non-decreasing and
+ * scores non-increasing inside a segment (what detbox_topk_decode(per_image=1) emits) — so the
+ * sort and the gather are skipped.  Needs box_stride == 4 and 16-byte aligned boxes. */
+#define DETBOX_NMS_PRESORTED 0x100
 
 /* RoIAlign sampling convention / level mode / fused 2x2 pooling / layout */
 #define DETBOX_ROI_BIN_CENTRE 0 /* roi_align_tf (crop_and_resize.c + roi_align_tf.py:24-40)   */
