@@ -47,6 +47,7 @@ struct TileBoxes { float4 tile; float4 warp[AT_ITEMS][AT_WARPS]; };   // (min x1
 struct GtChunk {
     double x1[GCH], y1[GCH], x2[GCH], y2[GCH], area[GCH];
     unsigned long long colmax[GCH];
+    float4 fbox[GCH];                                // the same boxes as float32, for the conservative slice test
     float cls[GCH];
 };
 
@@ -59,6 +60,13 @@ __device__ __forceinline__ bool may_touch(const float4 bb, double x1, double y1,
     const double iw = fmin((double)bb.z, x2) - fmax((double)bb.x, x1) + 1;
     const double ih = fmin((double)bb.w, y2) - fmax((double)bb.y, y1) + 1;
     return (iw > 0) && (ih > 0);
+}
+
+// Conservative float32 version for culling only: with m = min(x2), M = max(x1), iw > 0 in exact
+// arithmetic means m - M > -1, and rounding is monotone, so fl32(m - M) >= -1 can only let extra pairs
+// through (they then get the exact float64 treatment and contribute an overlap of 0).
+__device__ __forceinline__ bool may_touch32(const float4 bb, const float4 g) {
+    return (fminf(bb.z, g.z) - fmaxf(bb.x, g.x) >= -1.0f) && (fminf(bb.w, g.w) - fmaxf(bb.y, g.y) >= -1.0f);
 }
 
 struct TargetParams {
@@ -106,9 +114,9 @@ anchor_bbox_kernel(const float4 *__restrict__ anchors, long A, TileBoxes *__rest
                                              ordered_to_float(bb[2]), ordered_to_float(bb[3]));
 }
 
-// labels / flags / targets of one anchor from its row summary — anchor.py:49-62,86-87,133-138
-__device__ __forceinline__ void emit_anchor(const TargetParams &p, long o, const float4 anc, const float4 gbox,
-                                            float gcls, double mo, bool promoted, double isum, int &nfg, int &nbg)
+// label and regression flag of one anchor from its row summary — anchor.py:49-62,86-87
+__device__ __forceinline__ void label_of(const TargetParams &p, float gcls, double mo, bool promoted, double isum,
+                                         float &l_out, bool &flag_out)
 {
     float l = gcls;                                                         // anchor.py:49
     if (mo < p.bg) l = 0.0f;                                                // :50
@@ -118,9 +126,13 @@ __device__ __forceinline__ void emit_anchor(const TargetParams &p, long o, const
     if (p.clobber && mo < p.bg) l = 0.0f;                                   // :60-61
     if (l >= 1.0f) flag = true;                                             // :62
     if (isum > p.ign) { l = -1.0f; flag = false; }                          // :86-87
-    nfg += (l >= 1.0f); nbg += (l == 0.0f);
+    l_out = l; flag_out = flag;
+}
+
+__device__ __forceinline__ void store_anchor(const TargetParams &p, long o, const float4 anc, const float4 gbox, float l, bool flag)
+{
     p.labels[o] = l;
-    p.targets[o] = encode_box(anc, gbox, p.enc);                            // :133-135 every anchor
+    p.targets[o] = encode_box(anc, gbox, p.enc);                            // anchor.py:133-135 every anchor
     p.inside[o] = flag ? p.bbw : make_float4(0, 0, 0, 0);                   // :136-138
 }
 
@@ -178,11 +190,13 @@ anchor_target_kernel(const TargetParams p)
             const long a = tile0 + i * AT_THREADS + tid;
             anc[i] = a < p.A ? p.anchors[a] : make_float4(0, 0, 0, 0);
         }
+        float l0; bool f0;
+        label_of(p, gcls, 0.0, zero_any != 0, 0.0, l0, f0);     // the same for every anchor of the tile
         int nfg = 0, nbg = 0;
 #pragma unroll
         for (int i = 0; i < AT_ITEMS; ++i) {
             const long a = tile0 + i * AT_THREADS + tid;
-            if (a < p.A) emit_anchor(p, (long)b * p.A + a, anc[i], gbox, gcls, 0.0, zero_any != 0, 0.0, nfg, nbg);
+            if (a < p.A) { store_anchor(p, (long)b * p.A + a, anc[i], gbox, l0, f0); nfg += (l0 >= 1.0f); nbg += (l0 == 0.0f); }
         }
         nfg = __reduce_add_sync(0xffffffffu, nfg);
         nbg = __reduce_add_sync(0xffffffffu, nbg);
@@ -205,6 +219,7 @@ anchor_target_kernel(const TargetParams p)
             sm.x1[tid] = x1; sm.y1[tid] = y1; sm.x2[tid] = x2; sm.y2[tid] = y2;
             sm.area[tid] = (x2 - x1 + 1) * (y2 - y1 + 1);                 // bbox.pyx:34-37
             sm.cls[tid] = q[4];
+            sm.fbox[tid] = make_float4(q[0], q[1], q[2], q[3]);
             sm.colmax[tid] = (PASS == 1) ? 0ull : p.colmax[g0 + c0 + tid];
         }
         __syncthreads();
@@ -220,6 +235,8 @@ anchor_target_kernel(const TargetParams p)
     const float *q0 = p.gt + (size_t)g0 * 5;
     const float4 gbox0 = make_float4(q0[0], q0[1], q0[2], q0[3]);
     const float gcls0 = q0[4];
+    float l_zero; bool flag_zero;                    // outcome of an anchor that overlaps nothing
+    label_of(p, gcls0, 0.0, zero_any != 0, 0.0, l_zero, flag_zero);
     int nfg = 0, nbg = 0;
     // One slice at a time keeps the float64 row state (argmax, ignore sum, area) of a single anchor
     // in registers; with more than GCH GT the chunks are re-staged per slice (all warps together).
@@ -237,7 +254,7 @@ anchor_target_kernel(const TargetParams p)
             const int gn = min(GCH, G - c0);
             for (int cb = 0; cb < gn; cb += 32) {    // 32 GT at a time: one lane tests one GT against the slice's box
                 const int jl = cb + lane;
-                unsigned m = __ballot_sync(0xffffffffu, jl < gn && may_touch(wbb, sm.x1[jl], sm.y1[jl], sm.x2[jl], sm.y2[jl]));
+                unsigned m = __ballot_sync(0xffffffffu, jl < gn && may_touch32(wbb, sm.fbox[jl]));
                 if (m == 0u) continue;               // warp-uniform
                 const double ax1 = anc.x, ay1 = anc.y, ax2 = anc.z, ay2 = anc.w;
                 const double aarea = (ax2 - ax1 + 1) * (ay2 - ay1 + 1);
@@ -268,12 +285,15 @@ anchor_target_kernel(const TargetParams p)
             if (PASS == 1 && !single) flush_colmax(c0);
         }
         if (PASS == 2 && valid) {
-            if (best_g == 0) {
-                emit_anchor(p, (long)b * p.A + a, anc, gbox0, gcls0, best, promoted, isum, nfg, nbg);
-            } else {
+            float l = l_zero; bool flag = flag_zero;
+            float4 gbox = gbox0;
+            if (best > 0.0) {                        // (promotion and ignore overlap both imply best > 0)
                 const float *q = p.gt + (size_t)(g0 + best_g) * 5;
-                emit_anchor(p, (long)b * p.A + a, anc, make_float4(q[0], q[1], q[2], q[3]), q[4], best, promoted, isum, nfg, nbg);
+                gbox = make_float4(q[0], q[1], q[2], q[3]);
+                label_of(p, q[4], best, promoted, isum, l, flag);
             }
+            store_anchor(p, (long)b * p.A + a, anc, gbox, l, flag);
+            nfg += (l >= 1.0f); nbg += (l == 0.0f);
         }
     }
     if (PASS == 1) {

@@ -112,17 +112,30 @@ class BoxOpsSession:
         self.anchors = ops.anchor_pyramid(*self.anchor_args, device=self.dev)     # data_layer.py:138, once per batch
         s_k.wait_stream(cur)
         hold, d2h = [], 0
-        if self._h_nk is None or self._h_nk.shape != ((B + chunk - 1) // chunk, chunk + 1):
-            self._h_nk = torch.zeros(((B + chunk - 1) // chunk, chunk + 1), dtype=torch.int32, pin_memory=True)
+        tl = getattr(self, "timeline", None)        # optional instrumentation (profiles/timeline_probe.py)
+        if tl is not None:
+            import time as _time
+            _t0 = _time.perf_counter()
+            e = torch.cuda.Event(enable_timing=True); e.record(cur); tl.append((("start", e), None))
+        def mark(name, stream):
+            if tl is not None:
+                e = torch.cuda.Event(enable_timing=True); e.record(stream); tl.append((name, e))
+        # chunk schedule: a short first chunk starts the (bottleneck) copy-out stream early
+        starts, c0 = [], 0
+        while c0 < B:
+            n = min(max(1, chunk // 4) if c0 == 0 and chunk < B else chunk, B - c0)
+            starts.append((c0, n)); c0 += n
+        if self._h_nk is None or self._h_nk.shape != (len(starts), chunk + 1):
+            self._h_nk = torch.zeros((len(starts), chunk + 1), dtype=torch.int32, pin_memory=True)
         h_nk = self._h_nk
-        for c0 in range(0, B, chunk):
-            n = min(chunk, B - c0)
+        for ci, (c0, n) in enumerate(starts):
             r0, r1 = c0 * A, (c0 + n) * A
             ev_in = torch.cuda.Event()
             with torch.cuda.stream(s_in):
                 self.d_prob[r0:r1].copy_(prob_h[r0:r1], non_blocking=True)
                 self.d_box[r0:r1].copy_(box_h[r0:r1], non_blocking=True)
                 ev_in.record(s_in)
+                mark("h2d%d" % c0, s_in)
             ev_k = torch.cuda.Event()
             with torch.cuda.stream(s_k):
                 s_k.wait_event(ev_in)
@@ -132,24 +145,27 @@ class BoxOpsSession:
                 keep, n_keep = ops_post.nms(sel["boxes"], sel["scores"], self.nms_thresh, self.nms_cmp,
                                             seg_ids=sel["img_ids"].to(torch.int32), n_seg=n, presorted=True)
                 ev_k.record(s_k)
+                mark("krn%d" % c0, s_k)
             k0, k1 = c0 * kper, (c0 + n) * kper
             pairs = [(self.h_labels[c0:c0 + n], labels), (self.h_lw[c0:c0 + n], lw), (self.h_bt[c0:c0 + n], bt),
                      (self.h_bw[c0:c0 + n], bw), (self.h_boxes[k0:k1], sel["boxes"]), (self.h_scores[k0:k1], sel["scores"]),
-                     (self.h_img[k0:k1], sel["img_ids"]), (self.h_keep[k0:k1], keep), (h_nk[c0 // chunk, :n + 1], n_keep)]
+                     (self.h_img[k0:k1], sel["img_ids"]), (self.h_keep[k0:k1], keep), (h_nk[ci, :n + 1], n_keep)]
             with torch.cuda.stream(s_out):
                 s_out.wait_event(ev_k)
                 for h, d in pairs:
                     h.copy_(d, non_blocking=True)
                     d2h += h.numel() * h.element_size()
+                mark("d2h%d" % c0, s_out)
             hold.append((labels, lw, bt, bw, sel, keep, n_keep))      # keep device buffers alive until the drain
+        if tl is not None:
+            self.issue_ms = 1e3 * (_time.perf_counter() - _t0)
         for s in self._streams:
             s.synchronize()
         # chunk-local indices -> batch-global (host side, a few thousand integers)
         nk_all = np.zeros(B + 1, np.int32)
         keep_np, img_np, nk_np = self.h_keep.numpy(), self.h_img.numpy(), h_nk.numpy()
         out_keep, pos = self._keep_out.numpy(), 0
-        for ci, c0 in enumerate(range(0, B, chunk)):
-            n = min(chunk, B - c0)
+        for ci, (c0, n) in enumerate(starts):
             k0 = c0 * kper
             tot = int(nk_np[ci, n])
             out_keep[pos:pos + tot] = keep_np[k0:k0 + tot] + k0

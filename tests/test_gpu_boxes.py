@@ -85,6 +85,23 @@ def test_transform_golden(golden):
     assert_boxes_close(clipped, g["dec_clip"])
 
 
+def test_encode_divisions_are_ieee_exact(cpr_anchors):
+    """box_math.cuh replaces the 8 IEEE divisions of the encode by FMA-corrected reciprocals
+    (tests/tools/div_exact_check.c is the exhaustive host-side proof for the constants).  dx and dy
+    involve no transcendental, so they must equal the oracle's plain-division result BIT FOR BIT; dw
+    and dh differ only through logf (<= 1 ulp either side)."""
+    _, anc = cpr_anchors
+    a = anc.cpu().numpy()
+    rng = np.random.RandomState(17)
+    gt = synth_gt(rng, a.shape[0], 1024, 2048, 0.0)[:, :4]
+    gt[::7] = a[::7]                                   # identical boxes: zero numerators
+    gt[1::11, :2] += rng.uniform(-1e-3, 1e-3, gt[1::11, :2].shape).astype(np.float32)   # tiny numerators
+    got = detbox.box_encode(anc, cu(gt)).cpu().numpy()
+    want = O.bbox_transform(a, gt)
+    assert np.array_equal(got[:, :2].view(np.uint32), want[:, :2].view(np.uint32))
+    np.testing.assert_allclose(got[:, 2:], want[:, 2:], rtol=RTOL, atol=ATOL)
+
+
 def test_transform_full_size_roundtrip(cpr_anchors):
     """Full CP-R size: decode(encode(gt)) == gt (size-independent property) + oracle on a sample."""
     _, anc = cpr_anchors
