@@ -11,7 +11,7 @@ repository root) or ``importlib.import_module("detectron-pytorch_b200")``.
 """
 from . import _lib  # noqa: F401
 from ._lib import DetboxError, lib  # noqa: F401
-from . import ops, ops_post, ops_roi, pipeline  # noqa: F401
+from . import ops, ops_post, ops_roi, parallel, pipeline  # noqa: F401
 from . import libs  # noqa: F401  (reference-shaped mirror: detbox.libs.install() aliases it as `libs`)
 from .ops import (anchor_pyramid, anchor_target, base_anchors, bbox_exclude_ignored_areas,  # noqa: F401
                   bbox_intersections, bbox_overlaps, box_decode, box_encode, clip_boxes_, launches,

@@ -237,6 +237,7 @@ anchor_target_kernel(const TargetParams p)
     const float gcls0 = q0[4];
     float l_zero; bool flag_zero;                    // outcome of an anchor that overlaps nothing
     label_of(p, gcls0, 0.0, zero_any != 0, 0.0, l_zero, flag_zero);
+    const float4 *wbb_base = &p.tiles[blockIdx.x].warp[0][w];
     int nfg = 0, nbg = 0;
     // One slice at a time keeps the float64 row state (argmax, ignore sum, area) of a single anchor
     // in registers; with more than GCH GT the chunks are re-staged per slice (all warps together).
@@ -245,7 +246,7 @@ anchor_target_kernel(const TargetParams p)
         const long a = tile0 + i * AT_THREADS + tid;
         const bool valid = a < p.A;
         const float4 anc = valid ? p.anchors[a] : make_float4(INF, INF, -INF, -INF);
-        const float4 wbb = p.tiles[blockIdx.x].warp[i][w];
+        const float4 wbb = wbb_base[i * AT_WARPS];
         double best = 0.0, isum = 0.0;
         int best_g = 0;
         bool promoted = zero_any != 0;
