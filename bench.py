@@ -521,8 +521,15 @@ def main():
         tb = trace_bytes(args.trace, B, A, G_total, C)
         if k_ms and tb:
             ach = tb / k_ms / 1e6
+            traffic = None
+            try:                                     # per-launch DRAM bytes of the same kernel from the committed ncu capture
+                traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(str(args.trace), {}).get("bytes")
+                if B != 64:
+                    traffic = None                   # the capture is of the default batch
+            except Exception:
+                pass
             roof = {"bound": "hbm", "kernel_id": args.trace, "achieved": round(ach, 1), "peak": hbm_peak, "unit": "GB/s",
-                    "frac": round(ach / hbm_peak, 4), "traffic": None, "kernel_ms": round(k_ms, 4),
+                    "frac": round(ach / hbm_peak, 4), "traffic": traffic, "kernel_ms": round(k_ms, 4),
                     "algorithmic_bytes_per_launch": tb, "peak_source": peak_src}
         line = {"metric": METRIC, "value": round(total_images * args.steps / (ms_dev / 1e3), 1), "unit": UNIT,
                 "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_dev / args.steps, 4),
