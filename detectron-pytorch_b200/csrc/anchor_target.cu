@@ -245,7 +245,10 @@ anchor_target_kernel(const TargetParams p)
     for (int i = 0; i < AT_ITEMS; ++i) {
         const long a = tile0 + i * AT_THREADS + tid;
         const bool valid = a < p.A;
-        const float4 anc = valid ? p.anchors[a] : make_float4(INF, INF, -INF, -INF);
+        // pass 2 needs every anchor (targets are written for all of them); pass 1 only those of slices a GT may touch
+        float4 anc = make_float4(INF, INF, -INF, -INF);
+        bool have_anc = false;
+        if (PASS == 2) { if (valid) anc = p.anchors[a]; have_anc = true; }
         const float4 wbb = wbb_base[i * AT_WARPS];
         double best = 0.0, isum = 0.0;
         int best_g = 0;
@@ -257,6 +260,7 @@ anchor_target_kernel(const TargetParams p)
                 const int jl = cb + lane;
                 unsigned m = __ballot_sync(0xffffffffu, jl < gn && may_touch32(wbb, sm.fbox[jl]));
                 if (m == 0u) continue;               // warp-uniform
+                if (!have_anc) { if (valid) anc = p.anchors[a]; have_anc = true; }
                 const double ax1 = anc.x, ay1 = anc.y, ax2 = anc.z, ay2 = anc.w;
                 const double aarea = (ax2 - ax1 + 1) * (ay2 - ay1 + 1);
                 while (m) {                          // ascending GT index: first max wins (anchor.py:42)

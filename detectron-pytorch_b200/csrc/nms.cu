@@ -4,19 +4,20 @@
 // and — through segments — the per-image Python loop of libs/nets/model.py:343-355.
 //
 // Pipeline (one stream, no host round trip, no allocation):
-//   1. keys = ~ordered(score), stable radix sort (sort.cu) -> score-descending order, ties by index;
-//      with segments one more stable pass on the segment id -> segment-major order.
+//   1. keys = ~ordered(score), stable sort (sort.cu: one-block bitonic for n <= 4096, else LSD radix)
+//      -> score-descending order, ties by index; with segments one more stable pass on the segment
+//      id -> segment-major order.  DETBOX_NMS_PRESORTED skips 1 and 2 (rows already in that order).
 //   2. gather boxes into sorted float4 rows (+ segment id).
-//   3. bitmask: 64x64 tiles of the UPPER triangle only (the reference computes the full square,
-//      nms_kernel.cu:51); column boxes and their areas staged in shared memory; one thread
-//      produces one 64-bit word.  IoU arithmetic is the reference's float32 sequence
-//      (cpu_nms.pyx:57-64 == nms_kernel.cu:24-32): (area_i + area_j) - inter, IEEE division,
-//      --fmad=false.  The division is skipped when inter == 0 and thr > 0 (the quotient is 0
-//      or NaN, neither can suppress) — most pairs in the sparse regime.
-//   4. greedy scan, one block per segment: walk the 64-row tiles in order; warp 0 resolves the
-//      diagonal word chain with shuffles (64 dependent steps of register work), then all threads
-//      OR the mask rows of the newly kept boxes into the shared-memory `removed` bitset.  Exact
-//      greedy order => exact keep indices.
+//   3. suppressor bitmask, LOWER triangle only (the reference computes the full square,
+//      nms_kernel.cu:51): row i gets one 64-bit word per earlier column tile of its own segment.
+//      Broad phase: four sign-bit tests per pair against conservatively rounded column boxes reject
+//      the disjoint pairs; narrow phase: the reference's float32 IoU sequence (cpu_nms.pyx:57-64 ==
+//      nms_kernel.cu:24-32): (area_i + area_j) - inter, IEEE division, --fmad=false.  The division is
+//      only executed when an approximate quotient lands within 2^-20 of the threshold.
+//   4. resolve: greedy keep set as a monotone fixed point (kept iff no KEPT earlier suppressor),
+//      all boxes in parallel, 4-8 rounds.  Segmented input: one block per segment with the segment's
+//      mask rows and bitsets in shared memory; one segment: a cooperative grid with grid.sync
+//      between rounds.  The fixed point is unique, so the result is the exact greedy set.
 //   5. ordered compaction of the kept bits into original indices + per-segment counts.
 #include <mutex>
 #include <cooperative_groups.h>
@@ -29,12 +30,32 @@ typedef unsigned long long u64;
 
 namespace {
 
-struct NmsCmp { int mode; float thr_f; double thr_d; bool nonpos; };
+struct NmsCmp { int mode; float thr_f; double thr_d; bool nonpos; bool fast; float q_hi, q_lo; };
 
 __device__ __forceinline__ bool suppresses(const NmsCmp &c, float ovr) {
     if (c.mode == DETBOX_NMS_GE_F64) return (double)ovr >= c.thr_d;      // cpu_nms.pyx:65
     if (c.mode == DETBOX_NMS_GE_F32) return ovr >= c.thr_f;             // nms_cpu.c:76
     return ovr > c.thr_f;                                               // nms_kernel.cu:83
+}
+
+// Does the earlier box b suppress box a?  The reference's arithmetic (cpu_nms.pyx:57-64); b plays its
+// `i`, a its `j`: (area_i + area_j) - inter.  The IEEE division only runs when the approximate quotient
+// (MUFU.RCP * inter, <= 2 ulp off) is within 2^-20 of the threshold: outside that band the correctly
+// rounded quotient is on the same side (make_cmp() widens the band by one more ulp).
+__device__ __forceinline__ bool pair_suppresses(const NmsCmp &c, const float4 &a, float aarea, const float4 &b, float barea)
+{
+    const float xx1 = fmaxf(a.x, b.x), yy1 = fmaxf(a.y, b.y);
+    const float xx2 = fminf(a.z, b.z), yy2 = fminf(a.w, b.w);
+    const float w = fmaxf(0.0f, xx2 - xx1 + 1), h = fmaxf(0.0f, yy2 - yy1 + 1);
+    const float inter = w * h;
+    if (!(inter > 0.0f) && !c.nonpos) return false;        // quotient 0 or NaN: cannot suppress when thr > 0
+    const float uni = barea + aarea - inter;
+    if (c.fast && uni > 1e-30f && uni < 1e30f) {
+        const float q = __fdividef(inter, uni);
+        if (q > c.q_hi) return true;
+        if (q < c.q_lo) return false;
+    }
+    return suppresses(c, inter / uni);
 }
 
 __global__ void __launch_bounds__(256)
@@ -68,60 +89,106 @@ __global__ void nms_seg_scan_kernel(int32_t *seg_off, int n_seg)
 
 // ---- 3. suppressor mask (lower triangle) --------------------------------------------------------
 // Row i holds, for every EARLIER box j < i (processing order) of the same segment, bit j%64 of word
-// j/64 iff j would suppress i.  Blocks own (row tile, group of MASK_CG column tiles); groups right
-// of the diagonal, or left of the row tile's segment, exit at once.
+// j/64 iff j would suppress i.  A block owns MASK_RT row tiles and visits groups of `cg` column tiles:
+// blockIdx.x, + gridDim.x, ... counted from the first tile of the rows' segment; it stops at the diagonal.
+// Segments are contiguous in processing order, so "same segment" for an earlier column is just
+// "column index >= start of the row's segment".
 constexpr int MASK_CT = 4;     // column tiles staged per iteration (one per 64-thread group)
-constexpr int MASK_CG = 32;    // column tiles per block
+constexpr int MASK_RT = 2;     // row tiles per block: every staged column box is tested against 2 rows per
+                               // thread, so the shared-memory read (the limiter at 1 row) is amortised
 
 __global__ void __launch_bounds__(64 * MASK_CT)
 nms_mask_kernel(const float4 *__restrict__ boxes, const int32_t *__restrict__ seg, const int32_t *__restrict__ seg_off,
-                int n, int ncol, NmsCmp cmp, u64 *__restrict__ mask)
+                int n, int ncol, int cg, NmsCmp cmp, u64 *__restrict__ mask)
 {
-    const int rt = blockIdx.y;
-    const int ct_lo = blockIdx.x * MASK_CG;
-    if (ct_lo > rt) return;                                    // strictly right of the diagonal
-    const int row0 = rt * 64, row_last = min(n, row0 + 64) - 1;
-    int first_ct = 0;                                          // first column tile any row of this tile can see
+    const int rt0 = blockIdx.y * MASK_RT;
+    const int rt_last = min(rt0 + MASK_RT, ncol) - 1;
+    const int row0 = rt0 * 64, row_last = min(n, (rt_last + 1) * 64) - 1;
+    int first_ct = 0;                                          // first column tile any row of this block can see
     if (seg) first_ct = seg_off[seg[row0]] >> 6;
-    if (ct_lo + MASK_CG <= first_ct) return;
+    const int ct_base = first_ct & ~(MASK_CT - 1);
+    if (ct_base + (int)blockIdx.x * cg > rt_last) return;      // strictly right of the diagonal
     __shared__ float4 cb[64 * MASK_CT];
+    __shared__ float4 ccull[64 * MASK_CT];      // (x1 - 1 rounded down, y1 - 1 down, x2 + 1 up, y2 + 1 up)
     __shared__ float carea[64 * MASK_CT];
-    __shared__ int cseg[64 * MASK_CT];
     const int tid = threadIdx.x, sub = tid >> 6, rl = tid & 63;
-    const int r = row0 + rl;
-    float4 a = make_float4(0, 0, 0, 0); float aarea = 0.0f; int aseg = 0;
-    if (r < n) { a = boxes[r]; aarea = (a.z - a.x + 1) * (a.w - a.y + 1); aseg = seg ? seg[r] : 0; }
-    const int ct_hi = min(rt, ct_lo + MASK_CG - 1);
-    for (int c0 = max(ct_lo, first_ct & ~(MASK_CT - 1)); c0 <= ct_hi; c0 += MASK_CT) {
+    float4 a[MASK_RT]; float aarea[MASK_RT]; int astart[MASK_RT];
+#pragma unroll
+    for (int k = 0; k < MASK_RT; ++k) {
+        const int r = row0 + k * 64 + rl;
+        const float NaN = __int_as_float(0x7fc00000);
+        a[k] = make_float4(NaN, NaN, NaN, NaN); aarea[k] = 0.0f; astart[k] = 0;
+        if (r < n) {
+            a[k] = boxes[r]; aarea[k] = (a[k].z - a[k].x + 1) * (a[k].w - a[k].y + 1);
+            if (seg) astart[k] = seg_off[seg[r]];
+        }
+    }
+    for (int ct_lo = ct_base + (int)blockIdx.x * cg; ct_lo <= rt_last; ct_lo += (int)gridDim.x * cg) {
+    const int ct_hi = min(rt_last, ct_lo + cg - 1);
+    for (int c0 = ct_lo; c0 <= ct_hi; c0 += MASK_CT) {
         __syncthreads();
         {
             const int c = c0 * 64 + tid;
             if (c <= row_last) {
                 const float4 b = boxes[c];
                 cb[tid] = b;
+                ccull[tid] = make_float4(__fadd_rd(b.x, -1.0f), __fadd_rd(b.y, -1.0f), __fadd_ru(b.z, 1.0f), __fadd_ru(b.w, 1.0f));
                 carea[tid] = (b.z - b.x + 1) * (b.w - b.y + 1);    // cpu_nms.pyx:24
-                cseg[tid] = seg ? seg[c] : 0;
             }
         }
         __syncthreads();
         const int ct = c0 + sub;
-        if (r >= n || ct > rt || ct < ct_lo) continue;
+        if (ct > rt_last) continue;
         const int cbase = sub * 64;
-        const int cnt = (ct == rt) ? rl : 64;                      // diagonal tile: only j < i
-        u64 word = 0;
-        for (int i = 0; i < cnt; ++i) {
-            const float4 b = cb[cbase + i];
-            const float xx1 = fmaxf(a.x, b.x), yy1 = fmaxf(a.y, b.y);
-            const float xx2 = fminf(a.z, b.z), yy2 = fminf(a.w, b.w);
-            const float w = fmaxf(0.0f, xx2 - xx1 + 1), h = fmaxf(0.0f, yy2 - yy1 + 1);
-            const float inter = w * h;
-            if (inter > 0.0f || cmp.nonpos) {
-                // the earlier box j plays cpu_nms.pyx's `i`, this row its `j`: (area_i + area_j) - inter
-                const float ovr = inter / (carea[cbase + i] + aarea - inter);
-                if (suppresses(cmp, ovr) && aseg == cseg[cbase + i]) word |= 1ull << i;
+        // Broad phase (branch-free, fully unrolled): bit i of a row's candidate mask survives unless box i
+        // lies strictly beyond one side of the row's box by more than the +1 of the reference's pixel
+        // convention.  Exact by monotone rounding: a.x > up(b.x2 + 1) means min(x2) - max(x1) < -1 in real
+        // arithmetic, so the reference's fl(fl(min - max) + 1) is <= 0 and the intersection is empty.
+        unsigned lo[MASK_RT], hi[MASK_RT];
+#pragma unroll
+        for (int k = 0; k < MASK_RT; ++k) { lo[k] = 0; hi[k] = 0; }
+        // The four strict comparisons are evaluated as sign bits of float differences (FADD runs on the FMA
+        // pipe; FSETP would saturate the half-rate ALU pipe): a.x > q.z  <=>  sign(q.z - a.x).  A difference is
+        // -0 only for (-0) - (+0), which the directed roundings above exclude (q.z is never -0, q.x never +0);
+        // NaN / Inf operands may set a sign bit, but such pairs have an empty intersection (fmaxf(0, NaN) = 0).
+#pragma unroll 1
+        for (int ib = 0; ib < 32; ib += 8) {         // 8 + 8 column boxes per trip keeps the live registers bounded
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float4 q0 = ccull[cbase + ib + j], q1 = ccull[cbase + 32 + ib + j];
+#pragma unroll
+                for (int k = 0; k < MASK_RT; ++k) {
+                    const unsigned o0 = __float_as_uint(q0.z - a[k].x) | __float_as_uint(a[k].z - q0.x) |
+                                        __float_as_uint(q0.w - a[k].y) | __float_as_uint(a[k].w - q0.y);
+                    const unsigned o1 = __float_as_uint(q1.z - a[k].x) | __float_as_uint(a[k].z - q1.x) |
+                                        __float_as_uint(q1.w - a[k].y) | __float_as_uint(a[k].w - q1.y);
+                    lo[k] = (lo[k] >> 1) | (~o0 & 0x80000000u);      // bit 31 <- "not outside"; 32 shifts put box i at bit i
+                    hi[k] = (hi[k] >> 1) | (~o1 & 0x80000000u);
+                }
             }
         }
-        mask[(size_t)r * ncol + ct] = word;
+#pragma unroll
+        for (int k = 0; k < MASK_RT; ++k) {
+            const int rt = rt0 + k, r = rt * 64 + rl;
+            const int lb = astart[k] - ct * 64;                    // columns below bit lb belong to earlier segments
+            if (r >= n || ct > rt || lb >= 64) continue;
+            u64 cand = ((u64)hi[k] << 32) | lo[k];
+            if (cmp.nonpos) cand = ~0ull;                          // thr <= 0: empty intersections matter too
+            if (ct == rt) cand &= (1ull << rl) - 1ull;             // diagonal tile: only j < i
+            if (lb > 0) cand &= ~0ull << lb;
+            // narrow phase, one 32-bit half at a time (32-bit find-first-set / clear-lowest are 1/3 of the 64-bit cost)
+            unsigned wlo = 0, whi = 0;
+            for (unsigned c32 = (unsigned)cand; c32; c32 &= c32 - 1) {
+                const int i = __ffs((int)c32) - 1;
+                if (pair_suppresses(cmp, a[k], aarea[k], cb[cbase + i], carea[cbase + i])) wlo |= 1u << i;
+            }
+            for (unsigned c32 = (unsigned)(cand >> 32); c32; c32 &= c32 - 1) {
+                const int i = __ffs((int)c32) - 1;
+                if (pair_suppresses(cmp, a[k], aarea[k], cb[cbase + 32 + i], carea[cbase + 32 + i])) whi |= 1u << i;
+            }
+            mask[(size_t)r * ncol + ct] = ((u64)whi << 32) | wlo;
+        }
+    }
     }
 }
 
@@ -170,6 +237,69 @@ nms_resolve_kernel(const u64 *__restrict__ mask, int n, int ncol, const int32_t 
         grid.sync();
         if (__ldcg(&cnt[round % 3]) == 0u) break;
     }
+}
+
+// ---- 4b. resolve for segmented input: one block per segment, state in shared memory --------------
+// Same fixed point as above, but a segment (an image's top-k) is small: its mask rows (count x words
+// spanned, <= ~200 KB up to ~1200 boxes) and both bitsets live in shared memory, a round ends in a
+// __syncthreads instead of a grid.sync, and no atomics are needed — warps own aligned 32-box groups, so
+// a ballot is the group's 32-bit half-word of the bitset.  Segments too large for shared memory read
+// their rows from global memory (L2) instead.
+constexpr int RSEG_THREADS = 1024;
+
+__global__ void __launch_bounds__(RSEG_THREADS)
+nms_resolve_seg_kernel(const u64 *__restrict__ mask, int ncol, const int32_t *__restrict__ seg_off,
+                       u64 *__restrict__ kept_g, int smem_words)
+{
+    extern __shared__ u64 rsm[];
+    const int b0 = seg_off[blockIdx.x], b1 = seg_off[blockIdx.x + 1];
+    if (b1 <= b0) return;
+    const int w0 = b0 >> 6, w = ((b1 - 1) >> 6) - w0 + 1, cnt = b1 - b0;
+    const int ws = w | 1;                                  // odd row stride: 64-bit column reads hit distinct banks
+    u64 *kept = rsm, *supp = rsm + w, *rows = rsm + 2 * w;
+    const bool cached = (long)cnt * ws + 2L * w <= (long)smem_words;
+    const int tid = threadIdx.x, lane = tid & 31;
+    for (int c = tid; c < 2 * w; c += RSEG_THREADS) rsm[c] = 0ull;
+    if (cached) {
+        for (int e = tid; e < cnt * w; e += RSEG_THREADS) {
+            const int t = e / w, c = e - t * w;
+            const int i = b0 + t;
+            rows[t * ws + c] = (w0 + c <= (i >> 6)) ? __ldg(&mask[(size_t)i * ncol + w0 + c]) : 0ull;
+        }
+    }
+    const u64 *rbase = cached ? rows : mask + (size_t)b0 * ncol + w0;
+    const size_t rstride = cached ? (size_t)ws : (size_t)ncol;
+    volatile unsigned *k32 = reinterpret_cast<volatile unsigned *>(kept);
+    volatile unsigned *d32 = reinterpret_cast<volatile unsigned *>(supp);
+    volatile u64 *kv = kept, *dv = supp;
+    __syncthreads();
+    const int i_lo = b0 & ~31, i_hi = (b1 + 31) & ~31;
+    for (;;) {
+        bool undecided = false;
+        for (int i = i_lo + tid; i < i_hi; i += RSEG_THREADS) {       // warp-uniform trip count
+            const int hw = (i >> 5) - 2 * w0;                         // the warp's half-word of the bitsets
+            const bool live = i >= b0 && i < b1 && !(((k32[hw] | d32[hw]) >> (i & 31)) & 1u);
+            bool hit = false, open = false;
+            if (live) {
+                const u64 *row = rbase + (size_t)(i - b0) * rstride;
+                const int wi = (i >> 6) - w0;
+                for (int c = 0; c <= wi; ++c) {
+                    const u64 sw = row[c];
+                    if (sw) {
+                        const u64 k = kv[c], d = dv[c];
+                        hit |= (sw & k) != 0ull;
+                        open |= (sw & ~(k | d)) != 0ull;
+                    }
+                }
+            }
+            const unsigned mk = __ballot_sync(0xffffffffu, live && !hit && !open);
+            const unsigned ms = __ballot_sync(0xffffffffu, live && hit);
+            if (lane == 0) { if (mk) k32[hw] |= mk; if (ms) d32[hw] |= ms; }
+            undecided |= live && !hit && open;
+        }
+        if (!__syncthreads_or(undecided)) break;
+    }
+    for (int c = tid; c < w; c += RSEG_THREADS) if (kept[c]) atomicOr(&kept_g[w0 + c], kept[c]);
 }
 
 __global__ void __launch_bounds__(1024)
@@ -239,6 +369,15 @@ NmsBuffers carve_nms(void *ws, long n, int n_seg) {
 NmsCmp make_cmp(double thresh, int mode) {
     NmsCmp c; c.mode = mode; c.thr_d = thresh; c.thr_f = (float)thresh;
     c.nonpos = (mode == DETBOX_NMS_GE_F64) ? !(thresh > 0.0) : !(c.thr_f > 0.0f);
+    // band around the threshold outside which the approximate quotient decides (pair_suppresses)
+    const double t = (mode == DETBOX_NMS_GE_F64) ? thresh : (double)c.thr_f;
+    c.fast = t > 1e-20 && t < 1e20;
+    c.q_hi = c.q_lo = 0.0f;
+    if (c.fast) {
+        const double eps = 1.0 / (1 << 20);
+        c.q_hi = nextafterf((float)(t * (1.0 + eps)), INFINITY);
+        c.q_lo = nextafterf((float)(t * (1.0 - eps)), 0.0f);
+    }
     return c;
 }
 
@@ -251,16 +390,39 @@ int nms_sorted(const NmsBuffers &b, const uint32_t *order, long n, int n_seg,
     const int32_t *seg_sorted = n_seg > 1 ? b.seg_sorted : nullptr;
     DETBOX_CUDA_TRY(cudaMemsetAsync(b.kept, 0, (size_t)(2 * ncol + 2) * sizeof(u64), st));
     DETBOX_CUDA_TRY(cudaMemsetAsync(n_keep, 0, (size_t)(n_seg + 1) * sizeof(int32_t), st));
-    dim3 grid((unsigned)((ncol + MASK_CG - 1) / MASK_CG), (unsigned)ncol);
+    // column tiles per visit / visits in flight: whole 32-tile groups for one big triangle; single 4-tile
+    // chunks for segmented input, whose rows see only the handful of tiles of their own segment
+    const bool small_segs = seg_sorted && n / n_seg <= 4096;
+    const int cg = small_segs ? MASK_CT : 32;
+    unsigned gx = (unsigned)((ncol + cg - 1) / cg);
+    if (small_segs) { const unsigned want = 2u * (unsigned)((n / n_seg + 255) / 256) + 2u; if (gx > want) gx = want; }
+    dim3 grid(gx, (unsigned)((ncol + MASK_RT - 1) / MASK_RT));
     DETBOX_TRACE_BEGIN(DETBOX_K_NMS_MASK, st);
-    nms_mask_kernel<<<grid, 64 * MASK_CT, 0, st>>>(b.sorted, seg_sorted, seg_sorted ? seg_off : nullptr, (int)n, ncol, cmp, b.mask);
+    nms_mask_kernel<<<grid, 64 * MASK_CT, 0, st>>>(b.sorted, seg_sorted, seg_sorted ? seg_off : nullptr, (int)n, ncol, cg, cmp, b.mask);
     DETBOX_TRACE_END(DETBOX_K_NMS_MASK, st);
     DETBOX_LAUNCH_CHECK();
-    // cooperative launch: every block must be resident (grid.sync between rounds)
-    static thread_local int coop_blocks[64] = {0};
     int dev = 0;
     DETBOX_CUDA_TRY(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64) return DETBOX_ERR_UNSUPPORTED;
+    const long wmax = (n >> 6) + 2, smem_cap = 200 * 1024 / 8;      // 64-bit words
+    if (small_segs && 2 * wmax <= smem_cap) {
+        // one block per segment; shared memory sized for the largest segment n allows, capped at 200 KB
+        // (the two bitsets always fit; rows that do not are read from global memory)
+        static thread_local bool smem_set[64] = {false};
+        long words = n * (wmax | 1) + 2 * wmax;
+        if (words > smem_cap) words = smem_cap;
+        const int bytes = (int)(words * 8);
+        if (!smem_set[dev]) {
+            DETBOX_CUDA_TRY(cudaFuncSetAttribute(nms_resolve_seg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem_cap * 8)));
+            smem_set[dev] = true;
+        }
+        DETBOX_TRACE_BEGIN(DETBOX_K_NMS_SCAN, st);
+        nms_resolve_seg_kernel<<<(unsigned)n_seg, RSEG_THREADS, (size_t)bytes, st>>>(b.mask, ncol, seg_off, b.kept, (int)words);
+        DETBOX_TRACE_END(DETBOX_K_NMS_SCAN, st);
+        DETBOX_LAUNCH_CHECK();
+    } else {
+    // cooperative launch: every block must be resident (grid.sync between rounds)
+    static thread_local int coop_blocks[64] = {0};
     if (coop_blocks[dev] == 0) {
         int per_sm = 0, sms = 0, coop = 0;
         DETBOX_CUDA_TRY(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
@@ -279,6 +441,7 @@ int nms_sorted(const NmsBuffers &b, const uint32_t *order, long n, int n_seg,
         DETBOX_TRACE_BEGIN(DETBOX_K_NMS_SCAN, st);
         DETBOX_CUDA_TRY(cudaLaunchCooperativeKernel((const void *)nms_resolve_kernel, dim3(blocks), dim3(256), args, 0, st));
         DETBOX_TRACE_END(DETBOX_K_NMS_SCAN, st);
+    }
     }
     nms_compact_kernel<<<1, 1024, 0, st>>>(b.kept, (int)n, ncol, order, seg_sorted, n_seg, keep, n_keep);
     DETBOX_LAUNCH_CHECK();
@@ -321,10 +484,16 @@ extern "C" int detbox_nms(const float *boxes, int box_stride, const float *score
         b.seg_sorted = const_cast<int32_t *>(seg_ids);
         return nms_sorted(b, nullptr, n, n_seg, make_cmp(thresh, cmp_mode), keep, n_keep, st);
     }
-    int rc = make_score_keys(scores, n, b.ka, b.va, st);
-    if (rc != DETBOX_OK) return rc;
-    rc = radix_sort_pairs(b.ka, b.va, b.kb, b.vb, n, b.counts, st);
-    if (rc != DETBOX_OK) return rc;
+    int rc;
+    if (n <= SMALL_SORT_MAX && n_seg == 1) {      // one launch instead of 13
+        rc = small_sort_scores_desc(scores, n, b.va, st);
+        if (rc != DETBOX_OK) return rc;
+    } else {
+        rc = make_score_keys(scores, n, b.ka, b.va, st);
+        if (rc != DETBOX_OK) return rc;
+        rc = radix_sort_pairs(b.ka, b.va, b.kb, b.vb, n, b.counts, st);
+        if (rc != DETBOX_OK) return rc;
+    }
     uint32_t *order = b.va;
     long gb = (n + 255) / 256; if (gb > kNumSMs * 8) gb = kNumSMs * 8;
     if (n_seg > 1) {                              // stable grouping by segment: 1 pass per 8 bits of id

@@ -167,6 +167,43 @@ score_keys_kernel(const float *__restrict__ scores, long n, uint32_t *__restrict
 }
 }  // namespace
 
+namespace {
+// n <= SMALL_SORT_MAX: one block, bitonic network in shared memory over the unique 64-bit composites
+// (~ordered(score) << 32 | index) — ascending composite == descending score, ties by lower index.
+__global__ void __launch_bounds__(1024)
+small_sort_kernel(const float *__restrict__ scores, int n, int N /*pow2 >= n*/, uint32_t *__restrict__ order)
+{
+    __shared__ unsigned long long v[SMALL_SORT_MAX];
+    const int tid = threadIdx.x;
+    for (int i = tid; i < N; i += blockDim.x)
+        v[i] = i < n ? ((unsigned long long)(~float_to_ordered(scores[i])) << 32) | (unsigned)i : ~0ull;
+    __syncthreads();
+    for (int size = 2; size <= N; size <<= 1) {
+        for (int j = size >> 1; j > 0; j >>= 1) {
+            for (int t = tid; t < (N >> 1); t += blockDim.x) {
+                const int i = 2 * t - (t & (j - 1)), q = i + j;
+                const unsigned long long a = v[i], b = v[q];
+                const bool up = (i & size) == 0;
+                if ((a > b) == up) { v[i] = b; v[q] = a; }
+            }
+            __syncthreads();
+        }
+    }
+    for (int i = tid; i < n; i += blockDim.x) order[i] = (uint32_t)v[i];
+}
+}  // namespace
+
+int small_sort_scores_desc(const float *scores, long n, uint32_t *order, cudaStream_t st)
+{
+    if (n <= 0) return DETBOX_OK;
+    if (n > SMALL_SORT_MAX) return DETBOX_ERR_UNSUPPORTED;
+    int N = 2; while (N < n) N <<= 1;
+    const int threads = N / 2 < 32 ? 32 : (N / 2 > 1024 ? 1024 : N / 2);
+    small_sort_kernel<<<1, threads, 0, st>>>(scores, (int)n, N, order);
+    DETBOX_LAUNCH_CHECK();
+    return DETBOX_OK;
+}
+
 int make_score_keys(const float *scores, long n, uint32_t *keys, uint32_t *vals, cudaStream_t st)
 {
     if (n <= 0) return DETBOX_OK;
@@ -197,6 +234,7 @@ extern "C" int detbox_sort_desc(const float *scores, long n, int32_t *order, voi
     uint32_t *ka = cv.take<uint32_t>(n), *kb = cv.take<uint32_t>(n), *vb = cv.take<uint32_t>(n);
     uint32_t *counts = cv.take<uint32_t>(sort_counts_bytes(n) / 4);
     cudaStream_t st = as_stream(stream);
+    if (n <= SMALL_SORT_MAX) return small_sort_scores_desc(scores, n, (uint32_t *)order, st);
     int rc = make_score_keys(scores, n, ka, (uint32_t *)order, st);
     if (rc != DETBOX_OK) return rc;
     return radix_sort_pairs(ka, (uint32_t *)order, kb, vb, n, counts, st);

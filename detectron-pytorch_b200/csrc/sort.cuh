@@ -50,6 +50,10 @@ int radix_pass(const uint32_t *keys_in, const uint32_t *vals_in, uint32_t *keys_
 int radix_sort_pairs(uint32_t *keys_a, uint32_t *vals_a, uint32_t *keys_b, uint32_t *vals_b,
                      long n, uint32_t *counts, cudaStream_t st);
 
+// Descending, stable argsort of n <= SMALL_SORT_MAX scores in ONE launch (single block, shared memory).
+constexpr int SMALL_SORT_MAX = 4096;
+int small_sort_scores_desc(const float *scores, long n, uint32_t *order, cudaStream_t st);
+
 // keys[i] = ~ordered(scores[i]) (ascending key == descending score), vals[i] = i
 int make_score_keys(const float *scores, long n, uint32_t *keys, uint32_t *vals, cudaStream_t st);
 

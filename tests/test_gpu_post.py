@@ -73,6 +73,10 @@ def make_head_outputs(rng, B, A, C, activation, ties=False):
     (2, 300, 81, "softmax", 50, True, False),
     (1, 261888, 2, "softmax", 900, False, False),     # CP-R size, eval setting (test.py:148)
     (300, 64, 2, "softmax", 10, True, True),          # > 256 images: two segment passes
+    (3, 9000, 2, "softmax", 3000, True, True),        # per-image K > 2048: global radix sort + image pass
+    (2, 20000, 2, "softmax", 6000, True, False),      # MaskRCNN test-time budget per image (maskrcnn.py:97)
+    (16, 132450, 80, "sigmoid", 14400, False, False), # BASELINE configs[3]: COCO-R batch 16, global 900*B
+    (16, 132450, 80, "sigmoid", 1000, True, False),   # ... and 1000 per image
 ])
 def test_topk_decode(B, A, C, act, top_n, per_image, ties):
     rng = np.random.RandomState(B * 7 + A)
@@ -205,6 +209,44 @@ def test_nms_many_segments():
         inds = np.nonzero(img == i)[0]
         want.append(inds[O.nms(b[inds], s[inds], 0.5, O.NMS_GE_F64)] if inds.size else np.zeros(0, np.int64))
     np.testing.assert_array_equal(keep, np.concatenate(want))
+
+
+def test_nms_unbalanced_segments():
+    """Segment sizes from 0 to 5000: the per-segment resolve with rows in shared memory (<= ~1200 boxes),
+    rows read from global memory (larger), and empty segments, in one call."""
+    rng = np.random.RandomState(21)
+    sizes = [5000, 0, 1000, 37, 1, 1900, 64, 0]
+    n, B = sum(sizes), len(sizes)
+    b, s = sweep_boxes(rng, n)
+    b = (b / 4).astype(np.float32)
+    img = rng.permutation(np.repeat(np.arange(B), sizes)).astype(np.int32)
+    for _, omode, mode in MODES:
+        keep, nk = keep_list(*detbox.nms(cu(b), cu(s), 0.4, mode, seg_ids=cu(img), n_seg=B))
+        want = []
+        for i in range(B):
+            inds = np.nonzero(img == i)[0]
+            want.append(inds[O.nms(b[inds], s[inds], 0.4, omode)] if inds.size else np.zeros(0, np.int64))
+        np.testing.assert_array_equal(keep, np.concatenate(want))
+        np.testing.assert_array_equal(nk[:B], [w.size for w in want])
+
+
+@pytest.mark.parametrize("thr", [0.5, 1.0 / 3.0, 0.25, 0.2, 0.6, 1.0])
+def test_nms_quotients_on_the_threshold(thr):
+    """Small integer boxes: thousands of pairs whose IoU is exactly thr (or one ulp off after float32
+    rounding) — the approximate-quotient shortcut must hand every one of them to the IEEE division."""
+    rng = np.random.RandomState(4)
+    n = 3000
+    x1 = rng.randint(0, 24, n); y1 = rng.randint(0, 24, n)
+    b = np.stack([x1, y1, x1 + rng.randint(0, 8, n), y1 + rng.randint(0, 8, n)], 1).astype(np.float32)
+    s = rng.permutation(n).astype(np.float32)
+    for omode, mode in ((O.NMS_GE_F64, detbox.NMS_GE_F64), (O.NMS_GE_F32, detbox.NMS_GE_F32), (O.NMS_GT_F32, detbox.NMS_GT_F32)):
+        keep, _ = keep_list(*detbox.nms(cu(b), cu(s), thr, mode))
+        np.testing.assert_array_equal(keep, O.nms(b, s, thr, omode))
+        img = (np.arange(n) % 5).astype(np.int32)
+        keep, _ = keep_list(*detbox.nms(cu(b), cu(s), thr, mode, seg_ids=cu(img), n_seg=5))
+        want = [np.nonzero(img == i)[0] for i in range(5)]
+        want = np.concatenate([w[O.nms(b[w], s[w], thr, omode)] for w in want])
+        np.testing.assert_array_equal(keep, want)
 
 
 def test_nms_edge_cases():
