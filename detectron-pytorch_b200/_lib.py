@@ -38,6 +38,11 @@ class RoiCfg(ctypes.Structure):
                 ("all_levels", c_int), ("extrapolation", c_float)]
 
 
+class MatchCfg(ctypes.Structure):
+    """detbox_match_cfg (include/detbox.h)."""
+    _fields_ = [("bg_thresh", c_double), ("fg_thresh", c_double), ("ignore_thresh", c_double), ("min_size", c_float)]
+
+
 # name -> (restype, argtypes); every symbol include/detbox.h declares
 SIGNATURES = {
     "detbox_error_string": (ctypes.c_char_p, [c_int]),
@@ -66,6 +71,14 @@ SIGNATURES = {
     "detbox_roi_align_forward": (c_int, [ctypes.POINTER(RoiCfg), c_void, c_long, c_void, c_void, c_void]),
     "detbox_roi_align_backward": (c_int, [ctypes.POINTER(RoiCfg), c_void, c_long, c_void, c_void, c_int, c_void]),
     "detbox_assign_levels": (c_int, [c_void, c_long, P_float, c_int, c_void, c_void]),
+    "detbox_match_boxes": (c_int, [c_void, c_int, c_void, c_long, c_void, c_void, c_int, ctypes.POINTER(MatchCfg),
+                                   c_void, c_void, c_void, c_void]),
+    "detbox_roi_target": (c_int, [c_void, c_int, c_void, c_long, c_void, c_void, c_long, c_float, c_float,
+                                  c_void, c_void, c_void, c_void]),
+    "detbox_sample_compact": (c_int, [c_void, c_int, c_void, c_void, c_long, c_void, c_void, c_void, c_int,
+                                      c_void, c_void, c_void, c_void, c_void, c_void, c_void]),
+    "detbox_sample_gather": (c_int, [c_void, c_void, c_void, c_void, c_void, c_void, c_int, c_void, c_int,
+                                     c_void, c_void, c_void, c_void]),
     "_nms": (None, [c_void, c_void, c_void, c_int, c_int, c_float, c_int]),
     "detbox_nms_host": (c_int, [c_void, c_int, c_double, c_int, c_void, c_void, c_int]),
     "detbox_anchor_target_host": (c_int, [c_void, c_long, c_void, c_int, ctypes.POINTER(TargetCfg),

@@ -17,13 +17,15 @@ _SUBMODULES = [
     "configs.config", "boxes.cython_bbox", "boxes.cython_anchor", "boxes.anchor", "boxes.bbox_transform",
     "boxes.cython_nms", "boxes.nms_wrapper", "nms.cpu_nms", "nms.gpu_nms", "nms.py_cpu_nms",
     "layers.anchor", "layers.box", "layers.data_layer", "layers.anchor_target", "layers.nms_layer",
-    "layers.roi_align_tf", "layers.roi_align", "nets.model", "postprocessings.single_shot",
+    "layers.roi_align_tf", "layers.roi_align", "layers.roi_target", "nets.model", "postprocessings.single_shot",
 ]
 
 
 _ALIASES = {
     "layers.anchor_target.modules.anchor_target": "layers.anchor_target",
     "layers.nms.nms_layer": "layers.nms_layer",
+    "layers.roi_target.modules.roi_target": "layers.roi_target",
+    "layers.roi_target.functions.roi_target": "layers.roi_target",
     "layers.roi_align_tf.roi_align_tf": "layers.roi_align_tf",
     "layers.roi_align_tf.crop_and_resize": "layers.roi_align_tf",
     "layers.roi_align_tf.pyramid_roi_align": "layers.roi_align_tf",

@@ -235,6 +235,55 @@ int detbox_assign_levels(const float *boxes_dev /*[R,4]*/, long R, const float *
                          int32_t *levels_dev, void *stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * RoI -> ground-truth matching, RoI targets, RoI sampling (the MaskRCNN training
+ * step right after NMS).  All pointers are device pointers; nothing round-trips through the host.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct {
+    double bg_thresh;      /* match index = -1 below this max overlap   libs/layers/box.py:44        */
+    double fg_thresh;      /* label = 0 below this max overlap          libs/layers/box.py:51, 210   */
+    double ignore_thresh;  /* < 0: off.  Else rows with inter/area(row) > thresh against a GT of
+                              class <= 0 get label -1                   libs/layers/box.py:213-221   */
+    float  min_size;       /* 0: off.  Else rows with w or h (+1) below it get label -2
+                              (filter_boxes)                            libs/layers/box.py:310-315   */
+} detbox_match_cfg;
+
+/* libs/layers/box.py:12-69 matching_box and the labelling half of sample_rois (:193-221), batched:
+ * boxes [R, box_stride>=4] f32, image_inds [R] i64, gt [sum G, 5] f32 (x1,y1,x2,y2,cls) concatenated
+ * image-major with gt_offsets [B+1] i32.  IoU in float64 with bbox.pyx:15-55's arithmetic, first
+ * maximum wins.  Outputs in INPUT order (any may be NULL): labels [R] i64, match_inds [R] i32 (index
+ * inside the image's GT list, -1 = unmatched), match_boxes [R,4] f32 (16-byte aligned).  Rows whose
+ * image index is outside [0,B) get label -2 / match -1 (the reference drops them). */
+int detbox_match_boxes(const float *boxes_dev, int box_stride, const int64_t *image_inds_dev, long R,
+                       const float *gt_dev, const int32_t *gt_offsets_dev, int B, const detbox_match_cfg *cfg,
+                       int64_t *labels_dev, int32_t *match_inds_dev, float *match_boxes_dev, void *stream);
+
+/* The reference's FFI `roi_target_forward_cuda` (libs/layers/roi_target/src/roi_target_cuda.h,
+ * kernel roi_target_kernel.cu:49-90) with raw pointers: float32 IoU (inter/area(roi) for GT of class
+ * <= 0), last maximum wins, labels i64, deltas / bbwght [R,4] zero-filled here then written for
+ * matched rows.  bg_overlap is accepted and unused, as upstream. */
+int detbox_roi_target(const float *rois_dev, int roi_stride, const int64_t *roi_batch_inds_dev, long R,
+                      const float *gt_dev /*[G,5]*/, const int64_t *gt_batch_inds_dev, long G,
+                      float bg_overlap, float fg_overlap,
+                      int64_t *labels_dev, float *deltas_dev, float *bbwght_dev, void *stream);
+
+/* sample_rois, ordered compaction (libs/layers/box.py:236-254): per image the proposals with
+ * label >= 0 (rows must be image-major) followed by that image's extra rows (the jittered GT boxes,
+ * extra_offsets [B+1]); then the ascending positions of foreground (label > 0) and background
+ * (label == 0) rows.  Outputs sized R + E; counts = (rows, n_fg, n_bg).  B <= 2048. */
+int detbox_sample_compact(const float *boxes_dev, int box_stride, const int64_t *image_inds_dev,
+                          const int64_t *labels_dev, long R,
+                          const float *extra_boxes_dev, const int64_t *extra_labels_dev,
+                          const int32_t *extra_offsets_dev, int B,
+                          float *out_boxes_dev, int64_t *out_labels_dev, int64_t *out_image_inds_dev,
+                          int32_t *fg_pos_dev, int32_t *bg_pos_dev, int32_t *counts_dev, void *stream);
+/* sample_rois, final gather (libs/layers/box.py:271-280): rows fg_pos[fg_choice[..]] then
+ * bg_pos[bg_choice[..]]; the choices are the caller's random draws (np.random.choice positions). */
+int detbox_sample_gather(const float *boxes_dev, const int64_t *labels_dev, const int64_t *image_inds_dev,
+                         const int32_t *fg_pos_dev, const int32_t *bg_pos_dev,
+                         const int64_t *fg_choice_dev, int n_fg, const int64_t *bg_choice_dev, int n_bg,
+                         float *out_boxes_dev, int64_t *out_labels_dev, int64_t *out_image_inds_dev, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
  * HOST-buffer entry points (copies inside; synchronous; scratch cached per device).
  * ------------------------------------------------------------------------------------------- */
 /* Exactly the reference's FFI symbol `_nms` (libs/nms/gpu_nms.hpp:1-2, bound by gpu_nms.pyx:14):

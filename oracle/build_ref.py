@@ -24,7 +24,8 @@ written, all of them below ``oracle/_ref/`` which is git-ignored but travels to 
   12-line ``oracle/th_stub/TH/TH.h`` (a struct + five accessors) into ``libcrop_and_resize_ref.so``.
 * with ``--cuda``: the reference's CUDA kernels (``libs/nms/nms_kernel.cu``,
   ``libs/layers/roi_align/src/cuda/roi_align_kernel.cu``,
-  ``libs/layers/roi_align_tf/src/cuda/crop_and_resize_kernel.cu``) are compiled unmodified by
+  ``libs/layers/roi_align_tf/src/cuda/crop_and_resize_kernel.cu``,
+  ``libs/layers/roi_target/src/cuda/roi_target_kernel.cu``) are compiled unmodified by
   nvcc for sm_100a into ``libref_cuda_*.so`` — a same-box GPU cross-check for the ``>``
   comparator NMS and for grid-point RoIAlign, which has no CPU code upstream.
 
@@ -57,6 +58,8 @@ PY = [
     ("libs/boxes/bbox_transform.py", "libs/boxes", "bbox_transform"),
     ("libs/boxes/nms.py", "libs/boxes", "nms"),
     ("libs/layers/anchor.py", "libs/layers", "anchor"),
+    ("libs/layers/box.py", "libs/layers", "box"),
+    ("libs/layers/roi.py", "libs/layers", "roi"),
     ("libs/configs/config.py", "libs/configs", "config"),
     ("libs/nms/py_cpu_nms.py", "libs/nms", "py_cpu_nms"),
 ]
@@ -133,6 +136,11 @@ def build_cython(ref):
     with open(os.path.join(OUT, "libs/logs/log.py"), "w") as f:
         f.write("# shim written by oracle/build_ref.py (not reference code)\n"
                 "def LOG(mssg, onscreen=True):\n    print(mssg)\n")
+    # libs/layers/box.py imports its torch.utils.ffi extension at module level (`from .nms._ext import nms`);
+    # that API no longer exists.  Only box.py's NumPy functions (matching_box, sample_rois, ...) are used.
+    ensure_pkg(os.path.join(OUT, "libs/layers/nms/_ext"))
+    with open(os.path.join(OUT, "libs/layers/nms/_ext/__init__.py"), "w") as f:
+        f.write("# shim written by oracle/build_ref.py (not reference code)\nnms = None\n")
 
 
 def build_crop_and_resize(ref):
@@ -154,6 +162,9 @@ def build_cuda(ref):
     d = os.path.join(ref, "libs/layers/roi_align_tf/src/cuda")
     run(common + ["-I", d, os.path.join(d, "crop_and_resize_kernel.cu"),
                   "-o", os.path.join(OUT, "libref_cuda_crop_and_resize.so")])
+    d = os.path.join(ref, "libs/layers/roi_target/src/cuda")
+    run(common + ["-I", d, os.path.join(d, "roi_target_kernel.cu"),
+                  "-o", os.path.join(OUT, "libref_cuda_roi_target.so")])
 
 
 def main():

@@ -54,9 +54,63 @@ def set_cfg(cfg, bg, fg, clobber=True, enc="fastrcnn"):
     cfg.ignored_area_intersection_fraction = 0.3
 
 
+def synth_rois(seed, n=None, B=None, sorted_ids=True):
+    """Proposals + per-image GT lists for matching_box / sample_rois: log-uniform sizes (some below
+    filter_boxes' 8 px), GT classes in {-1, 0, 1, 2, 3} (<= 0 are ignore regions), a few proposals planted
+    on top of GT boxes so that foregrounds exist, one image possibly without GT."""
+    rng = np.random.RandomState(seed)
+    n = rng.randint(1, 400) if n is None else n
+    B = rng.randint(1, 5) if B is None else B
+    wh = np.exp(rng.uniform(np.log(3), np.log(200), (n, 2)))
+    c = rng.uniform(0, 300, (n, 2))
+    b = np.concatenate([c - wh / 2, c + wh / 2], 1).astype(np.float32)
+    ids = rng.randint(0, B, n)
+    if sorted_ids:
+        ids = np.sort(ids)
+    gts = []
+    for i in range(B):
+        G = rng.randint(0, 6)
+        gwh = np.exp(rng.uniform(np.log(10), np.log(200), (G, 2)))
+        gc = rng.uniform(0, 300, (G, 2))
+        cls = rng.choice([-1, 0, 1, 2, 3], G).astype(np.float32)
+        gts.append(np.concatenate([gc - gwh / 2, gc + gwh / 2, cls[:, None]], 1).astype(np.float32))
+    for i in range(B):
+        for g in gts[i]:
+            for _ in range(3):
+                k = rng.randint(0, n)
+                b[k] = g[:4] + rng.uniform(-3, 3, 4).astype(np.float32)
+                ids[k] = i
+    if sorted_ids:
+        o = np.argsort(ids, kind="stable"); b, ids = b[o], ids[o]
+    return b, ids.astype(np.int64), gts
+
+
+def roi_sampling_golden(r):
+    """matching_box / sample_rois of the reference's libs/layers/box.py (CPU torch tensors in and out;
+    np.random seeded per case, which fixes the jitter and both np.random.choice draws)."""
+    import torch
+    out = {}
+    for case, (seed, sorted_ids) in enumerate([(0, True), (1, True), (2, False), (3, True), (4, False), (5, True)]):
+        b, ids, gts = synth_rois(seed, sorted_ids=sorted_ids)
+        out["c%d_boxes" % case] = b; out["c%d_ids" % case] = ids
+        out["c%d_ngt" % case] = np.asarray([g.shape[0] for g in gts], np.int32)
+        out["c%d_gt" % case] = np.concatenate(gts, 0) if sum(g.shape[0] for g in gts) else np.zeros((0, 5), np.float32)
+        lab, match, mbox = r.layers_box.matching_box(torch.from_numpy(b), torch.from_numpy(ids), gts, 0.4, 0.6)
+        out["c%d_match_labels" % case] = lab.numpy(); out["c%d_match_inds" % case] = match.numpy()
+        out["c%d_match_boxes" % case] = mbox.numpy()
+        np.random.seed(100 + case)
+        sb, sl, si = r.layers_box.sample_rois(torch.from_numpy(b), torch.from_numpy(ids), gts, 0.5, 16, 0.25, 0.2)
+        out["c%d_sample_boxes" % case] = sb.numpy(); out["c%d_sample_labels" % case] = sl.numpy()
+        out["c%d_sample_ids" % case] = si.numpy()
+    np.savez_compressed(os.path.join(GOLD, "roi_sampling.npz"), **out)
+
+
 def main():
     r = ref_loader.load()
     os.makedirs(GOLD, exist_ok=True)
+    if "--only-roi-sampling" in sys.argv:
+        roi_sampling_golden(r)
+        return
     A = r.boxes_anchor
 
     # ---- anchors -------------------------------------------------------------------------
@@ -195,6 +249,8 @@ def main():
     out["kat5_fwd"] = r.crop_and_resize_forward(ramp, kb, np.zeros(1, np.int32), 0.0, 2, 2)
     out["kat5_bwd"] = r.crop_and_resize_backward(np.ones((1, 1, 2, 2), np.float32), kb, np.zeros(1, np.int32), ramp.shape)
     np.savez_compressed(os.path.join(GOLD, "roialign.npz"), **out)
+
+    roi_sampling_golden(r)
 
     sz = sum(os.path.getsize(os.path.join(GOLD, f)) for f in os.listdir(GOLD))
     print("golden vectors written to", GOLD, "(%d KiB)" % (sz // 1024))

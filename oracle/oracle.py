@@ -387,3 +387,138 @@ def pyramid_roi_align(pyramids, bboxes, batch_inds, strides, ref_areas, ph, pw, 
         if sel.size:
             out[sel] = fwd(p, rois[sel], np.float32(1.0 / s), ph, pw)
     return out
+
+
+# ------------------------------------------------------------------------------------------------
+# RoI -> GT matching, RoI sampling, RoI targets
+# ------------------------------------------------------------------------------------------------
+def matching_box(boxes, image_inds, gt_boxes_list, bg_overlap_threshold=0.5, fg_overlap_threshold=0.6):
+    """libs/layers/box.py:12-69 on NumPy arrays: per image (rows `image_inds == i`, in image order) the
+    float64 IoU argmax -> (labels int64, match int32, match_box f32), concatenated."""
+    boxes = np.asarray(boxes, np.float32); image_inds = np.asarray(image_inds)
+    labels_all, match_all, box_all = [], [], []
+    for i, gt in enumerate(gt_boxes_list):
+        gt = np.asarray(gt, np.float32).reshape(-1, 5)
+        b = boxes[image_inds == i]
+        match = np.zeros((b.shape[0],), np.int32) - 1                       # :33
+        labels = np.zeros((b.shape[0],), np.int64)
+        mbox = np.zeros((b.shape[0], 4), np.float32)
+        if gt.size > 0 and b.size > 0:                                      # :36
+            ov = bbox_overlaps(b[:, :4].astype(np.float64), gt[:, :4].astype(np.float64))
+            arg = ov.argmax(axis=1)                                         # :42 (first maximum)
+            mx = ov[np.arange(b.shape[0]), arg]
+            match[:] = arg
+            match[mx < bg_overlap_threshold] = -1                           # :45
+            mbox[:, :4] = gt[arg, :4]
+            labels[:] = gt[arg, 4]                                          # :48 (float -> int64 truncation)
+            labels[mx < fg_overlap_threshold] = 0                           # :52
+        labels_all.append(labels); match_all.append(match); box_all.append(mbox)
+    return np.concatenate(labels_all), np.concatenate(match_all), np.concatenate(box_all)
+
+
+def jitter_boxes(boxes, rng):
+    """libs/layers/box.py:295-307 (in place; rand(num) drawn for x1, y1, then x2, y2)."""
+    num = boxes.shape[0]
+    ws = boxes[:, 2] - boxes[:, 0] + 1.0
+    hs = boxes[:, 3] - boxes[:, 1] + 1.0
+    dws = (rng.rand(num) - 0.5) * 0.2 * ws
+    dhs = (rng.rand(num) - 0.5) * 0.2 * hs
+    boxes[:, 0] = boxes[:, 0] + dws
+    boxes[:, 1] = boxes[:, 1] + dhs
+    dws = (rng.rand(num) - 0.5) * 0.2 * ws
+    dhs = (rng.rand(num) - 0.5) * 0.2 * hs
+    boxes[:, 2] = boxes[:, 2] + dws
+    boxes[:, 3] = boxes[:, 3] + dhs
+    return boxes
+
+
+def sample_rois(boxes, image_inds, gt_boxes_list, fg_overlap_threshold=0.5, rois_per_image=512, fg_fraction=0.25,
+                ignore_threshold=0.2, rng=np.random):
+    """libs/layers/box.py:175-292 on NumPy arrays with an injectable RandomState (upstream uses the global
+    np.random): filter small boxes (:310-315), label by float64 IoU argmax, ignore regions (class <= 0,
+    inter/area(box) > ignore_threshold), append jittered valid GT, keep label >= 0, then the
+    'faster rcnn sampling' branch (:264-276)."""
+    boxes = np.asarray(boxes, np.float32); image_inds = np.asarray(image_inds)
+    batch_size = len(gt_boxes_list)
+    s_boxes, s_labels, s_inds = [], [], []
+    for i, gt in enumerate(gt_boxes_list):
+        gt = np.asarray(gt, np.float32).reshape(-1, 5)
+        b = boxes[image_inds == i]
+        ii = image_inds[image_inds == i]
+        ws = b[:, 2] - b[:, 0] + 1.0; hs = b[:, 3] - b[:, 1] + 1.0           # filter_boxes, float32
+        keep = np.where(np.logical_and(ws >= 8, hs >= 8))[0]
+        b = b[keep]; ii = ii[keep]
+        labels = np.zeros((b.shape[0],), np.int64)
+        if gt.size > 0:
+            ov = bbox_overlaps(b[:, :4].astype(np.float64), gt[:, :4].astype(np.float64))
+            arg = ov.argmax(axis=1)
+            mx = ov[np.arange(b.shape[0]), arg]
+            labels[:] = gt[arg, 4]
+            labels[mx < fg_overlap_threshold] = 0
+            ign = gt[:, 4] <= 0                                               # :213
+            if np.any(ign):
+                flag = bbox_exclude_ignored_areas(b[:, :4].astype(np.float64), gt[ign][:, :4].astype(np.float64), ignore_threshold)
+                labels[flag == 1] = -1
+            valid = np.where(gt[:, 4] > 0)[0]                                 # :224-236
+            gb = jitter_boxes(gt[valid][:, :4].astype(np.float32), rng)
+            b = np.concatenate((b[:, :4], gb), axis=0)
+            labels = np.concatenate((labels, gt[valid][:, 4].astype(np.int64)), axis=0)
+            ii = np.concatenate((ii, np.zeros((gb.shape[0],), ii.dtype) + i), axis=0)
+        s_boxes.append(b[labels >= 0][:, :4]); s_labels.append(labels[labels >= 0]); s_inds.append(ii[labels >= 0])
+    s_boxes = np.concatenate(s_boxes, 0); s_labels = np.concatenate(s_labels, 0).astype(np.int64)
+    s_inds = np.concatenate(s_inds, 0).astype(np.int64)
+    bg_inds = np.where(s_labels == 0)[0]
+    fg_inds = np.where(s_labels > 0)[0]
+    num_fg = min(fg_inds.size, int(fg_fraction * rois_per_image * batch_size))
+    if num_fg > 0:
+        fg_inds = rng.choice(fg_inds, num_fg, replace=False)
+    num_bg = min(rois_per_image * batch_size - num_fg, bg_inds.size)
+    if bg_inds.size > 0:
+        bg_inds = rng.choice(bg_inds, num_bg, replace=False)
+    keep_inds = np.append(fg_inds, bg_inds).astype(np.int64)
+    s_labels, s_boxes, s_inds = s_labels[keep_inds], s_boxes[keep_inds], s_inds[keep_inds]
+    if s_labels.size == 0:                                                    # :282-286
+        return boxes[:1, :4], np.array([-1], np.int64), image_inds[:1].astype(np.int64)
+    return s_boxes, s_labels, s_inds
+
+
+def roi_target(rois, roi_batch_inds, gt_boxes, gt_batch_inds, fg_overlap):
+    """libs/layers/roi_target/src/cuda/roi_target_kernel.cu:16-90 restated (CUDA-only upstream; parity
+    pinned on the GPU box against the kernel compiled unmodified, tests/test_gpu_ref_cuda.py).  float32
+    arithmetic with the kernel's double-literal promotions; `<=` keeps the LAST maximum."""
+    f = np.float32
+    rois = np.asarray(rois, f).reshape(-1, 4); gt = np.asarray(gt_boxes, f).reshape(-1, 5)
+    R = rois.shape[0]
+    labels = np.zeros(R, np.int64); deltas = np.zeros((R, 4), f); bbw = np.zeros((R, 4), f)
+    one = f(1.0)
+    for r in range(R):
+        a = rois[r]
+        best, best_ind, match_cls = f(0.0), -1, -1
+        for j in range(gt.shape[0]):
+            if int(gt_batch_inds[j]) != int(roi_batch_inds[r]):
+                continue
+            b = gt[j]; cls = int(b[4])
+            left, right = max(a[0], b[0]), min(a[2], b[2])
+            top, bottom = max(a[1], b[1]), min(a[3], b[3])
+            width = max(f(f(right - left) + one), f(0)); height = max(f(f(bottom - top) + one), f(0))
+            inter = f(width * height)
+            sa = f(f(f(a[2] - a[0]) + one) * f(f(a[3] - a[1]) + one))
+            sb = f(f(f(b[2] - b[0]) + one) * f(f(b[3] - b[1]) + one))
+            with np.errstate(all="ignore"):
+                iou = f(inter / sa) if cls <= 0 else f(inter / f(f(sa + sb) - inter))
+            if best <= iou:
+                best, best_ind, match_cls = iou, j, cls
+        labels[r] = (match_cls if match_cls > 0 else -1) if best >= f(fg_overlap) else 0
+        if best >= min(f(0.5), f(fg_overlap)) and match_cls > 0 and best_ind >= 0:
+            b = gt[best_ind]
+            bw = f(np.float64(f(b[2] - b[0])) + 1.0); bh = f(np.float64(f(b[3] - b[1])) + 1.0)
+            bx = f(np.float64(b[0]) + np.float64(bw) * 0.5); by = f(np.float64(b[1]) + np.float64(bh) * 0.5)
+            aw = f(np.float64(f(a[2] - a[0])) + 1.0); ah = f(np.float64(f(a[3] - a[1])) + 1.0)
+            ax = f(np.float64(a[0]) + np.float64(aw) * 0.5); ay = f(np.float64(a[1]) + np.float64(ah) * 0.5)
+            with np.errstate(all="ignore"):
+                deltas[r, 0] = f(np.float64(f(f(bx - ax) / aw)) / 0.1)
+                deltas[r, 1] = f(np.float64(f(f(by - ay) / ah)) / 0.1)
+                deltas[r, 2] = f(np.float64(np.log(f(bw / aw))) / 0.2)     # logf: float32 in, float32 out
+                deltas[r, 3] = f(np.float64(np.log(f(bh / ah))) / 0.2)
+            bbw[r] = 1.0
+    return labels, deltas, bbw

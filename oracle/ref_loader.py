@@ -10,6 +10,8 @@
   boxes_anchor     libs/boxes/anchor.py           anchor_pyramid / anchors / ...
   bbox_transform   libs/boxes/bbox_transform.py   bbox_transform(_inv) / clip_boxes / *_linear
   layers_anchor    libs/layers/anchor.py          encode / decode
+  layers_box       libs/layers/box.py             matching_box / sample_rois (CPU torch tensors in and out)
+  layers_roi       libs/layers/roi.py             encode / decode (RoI targets, NumPy)
   cfg              libs/configs/config.py         the module-global config the above read
   crop_and_resize_forward / crop_and_resize_backward
                    libs/layers/roi_align_tf/src/crop_and_resize.c through the TH stub
@@ -93,11 +95,16 @@ def load():
     import libs.nms.cpu_nms as cpu_nms
     import libs.nms.py_cpu_nms as py_cpu_nms
     import libs.layers.anchor as layers_anchor
+    try:                                    # needs torch (CPU tensors) — matching_box / sample_rois / roi.encode
+        import libs.layers.box as layers_box
+        import libs.layers.roi as layers_roi
+    except ImportError:
+        layers_box = layers_roi = None
 
     ns = types.SimpleNamespace(
         cfg=cfg, cython_bbox=cython_bbox, cython_nms=cython_nms, boxes_anchor=boxes_anchor,
         bbox_transform=bbox_transform, cpu_nms=cpu_nms, py_cpu_nms=py_cpu_nms,
-        layers_anchor=layers_anchor)
+        layers_anchor=layers_anchor, layers_box=layers_box, layers_roi=layers_roi)
 
     lib = ctypes.CDLL(os.path.join(REF, "libcrop_and_resize_ref.so"))
     lib.crop_and_resize_forward.argtypes = [

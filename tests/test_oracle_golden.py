@@ -126,3 +126,24 @@ def test_roialign_kat5(golden):
     gi = O.roi_align_tf_bwd(np.ones((1, 1, 2, 2), np.float32), rois, 1.0, ramp.shape)
     np.testing.assert_array_equal(gi, g["kat5_bwd"])
     np.testing.assert_allclose(gi[0, 0, 0], [.5625, .375, .5625, 0], atol=1e-6)
+
+
+def _roi_case(g, c):
+    ngt = g["c%d_ngt" % c]
+    gts = np.split(g["c%d_gt" % c], np.cumsum(ngt)[:-1]) if ngt.size else []
+    return g["c%d_boxes" % c], g["c%d_ids" % c], [x.reshape(-1, 5) for x in gts]
+
+
+@pytest.mark.parametrize("case", range(6))
+def test_roi_matching_and_sampling(golden, case):
+    """libs/layers/box.py matching_box / sample_rois outputs recorded from the reference (make_golden.py)."""
+    g = golden("roi_sampling")
+    b, ids, gts = _roi_case(g, case)
+    lab, match, mbox = O.matching_box(b, ids, gts, 0.4, 0.6)
+    np.testing.assert_array_equal(lab, g["c%d_match_labels" % case])
+    np.testing.assert_array_equal(match, g["c%d_match_inds" % case])
+    np.testing.assert_array_equal(mbox, g["c%d_match_boxes" % case])
+    sb, sl, si = O.sample_rois(b, ids, gts, 0.5, 16, 0.25, 0.2, rng=np.random.RandomState(100 + case))
+    np.testing.assert_array_equal(sb, g["c%d_sample_boxes" % case])
+    np.testing.assert_array_equal(sl, g["c%d_sample_labels" % case])
+    np.testing.assert_array_equal(si, g["c%d_sample_ids" % case])

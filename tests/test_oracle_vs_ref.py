@@ -120,3 +120,23 @@ def test_tf_boxes_matches_torch_wrapper_arithmetic():
     want = torch.cat((ny0, nx0, ny0 + nh, nx0 + nw), 1).numpy()
     got, _ = O.tf_boxes(rois, s, ch, cw, H, W)
     np.testing.assert_array_equal(got, want)
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_matching_box_and_sample_rois_random(ref, seed):
+    """oracle.matching_box / sample_rois == the reference's libs/layers/box.py:12-69, 175-292 (its own code on
+    CPU torch tensors; np.random seeded identically on both sides)."""
+    torch = pytest.importorskip("torch")
+    from oracle.make_golden import synth_rois
+    if ref.layers_box is None:
+        pytest.skip("reference box.py not importable")
+    b, ids, gts = synth_rois(50 + seed, sorted_ids=seed % 2 == 0)
+    want = ref.layers_box.matching_box(torch.from_numpy(b), torch.from_numpy(ids), gts, 0.4, 0.6)
+    got = O.matching_box(b, ids, gts, 0.4, 0.6)
+    for w, g in zip(want, got):
+        np.testing.assert_array_equal(w.numpy(), g)
+    np.random.seed(seed)
+    want = ref.layers_box.sample_rois(torch.from_numpy(b), torch.from_numpy(ids), gts, 0.5, 16, 0.25, 0.2)
+    got = O.sample_rois(b, ids, gts, 0.5, 16, 0.25, 0.2, rng=np.random.RandomState(seed))
+    for w, g in zip(want, got):
+        np.testing.assert_array_equal(w.numpy(), g)
