@@ -30,7 +30,7 @@ typedef unsigned long long u64;
 
 namespace {
 
-struct NmsCmp { int mode; float thr_f; double thr_d; bool nonpos; bool fast; float q_hi, q_lo; };
+struct NmsCmp { int mode; float thr_f; double thr_d; bool nonpos; bool fast; float q_hi, q_lo; int variant; };
 
 __device__ __forceinline__ bool suppresses(const NmsCmp &c, float ovr) {
     if (c.mode == DETBOX_NMS_GE_F64) return (double)ovr >= c.thr_d;      // cpu_nms.pyx:65
@@ -42,14 +42,29 @@ __device__ __forceinline__ bool suppresses(const NmsCmp &c, float ovr) {
 // `i`, a its `j`: (area_i + area_j) - inter.  The IEEE division only runs when the approximate quotient
 // (MUFU.RCP * inter, <= 2 ulp off) is within 2^-20 of the threshold: outside that band the correctly
 // rounded quotient is on the same side (make_cmp() widens the band by one more ulp).
+template <int VARIANT>
 __device__ __forceinline__ bool pair_suppresses(const NmsCmp &c, const float4 &a, float aarea, const float4 &b, float barea)
 {
     const float xx1 = fmaxf(a.x, b.x), yy1 = fmaxf(a.y, b.y);
     const float xx2 = fminf(a.z, b.z), yy2 = fminf(a.w, b.w);
     const float w = fmaxf(0.0f, xx2 - xx1 + 1), h = fmaxf(0.0f, yy2 - yy1 + 1);
     const float inter = w * h;
+    if (VARIANT == DETBOX_NMS_VARIANT_MULTIANCHOR) {
+        // libs/boxes/nms.pyx:125-195.  `+ 0.1` promotes to double, the quotient is stored in a float32;
+        // then the centre rule: sqrt(d2) <= 0.2 * min(w, h) with Python-float (double) centres.  b is `i`, a is `j`.
+        const double od = ((double)inter + 0.1) / ((double)(barea + aarea - inter) + 0.1);
+        if (suppresses(c, (float)od)) return true;
+        const double icx = 0.5 * (double)(b.x + b.z), icy = 0.5 * (double)(b.y + b.w);
+        const double jcx = 0.5 * (double)(a.x + a.z), jcy = 0.5 * (double)(a.y + a.w);
+        const double dist = (jcx - icx) * (jcx - icx) + (jcy - icy) * (jcy - icy);
+        return sqrt(dist) <= 0.2 * (double)fminf(w, h);
+    }
     if (!(inter > 0.0f) && !c.nonpos) return false;        // quotient 0 or NaN: cannot suppress when thr > 0
     const float uni = barea + aarea - inter;
+    if (VARIANT == DETBOX_NMS_VARIANT_NEW) {
+        // libs/boxes/nms.pyx:70-123: also containment, inter/area_i > 0.95 or inter/area_j > 0.95 (compared as doubles)
+        return suppresses(c, inter / uni) || (double)(inter / barea) > 0.95 || (double)(inter / aarea) > 0.95;
+    }
     if (c.fast && uni > 1e-30f && uni < 1e30f) {
         const float q = __fdividef(inter, uni);
         if (q > c.q_hi) return true;
@@ -97,6 +112,7 @@ constexpr int MASK_CT = 4;     // column tiles staged per iteration (one per 64-
 constexpr int MASK_RT = 2;     // row tiles per block: every staged column box is tested against 2 rows per
                                // thread, so the shared-memory read (the limiter at 1 row) is amortised
 
+template <int VARIANT>
 __global__ void __launch_bounds__(64 * MASK_CT)
 nms_mask_kernel(const float4 *__restrict__ boxes, const int32_t *__restrict__ seg, const int32_t *__restrict__ seg_off,
                 int n, int ncol, int cg, NmsCmp cmp, u64 *__restrict__ mask)
@@ -173,18 +189,18 @@ nms_mask_kernel(const float4 *__restrict__ boxes, const int32_t *__restrict__ se
             const int lb = astart[k] - ct * 64;                    // columns below bit lb belong to earlier segments
             if (r >= n || ct > rt || lb >= 64) continue;
             u64 cand = ((u64)hi[k] << 32) | lo[k];
-            if (cmp.nonpos) cand = ~0ull;                          // thr <= 0: empty intersections matter too
+            if (cmp.nonpos || VARIANT == DETBOX_NMS_VARIANT_MULTIANCHOR) cand = ~0ull;   // empty intersections matter too
             if (ct == rt) cand &= (1ull << rl) - 1ull;             // diagonal tile: only j < i
             if (lb > 0) cand &= ~0ull << lb;
             // narrow phase, one 32-bit half at a time (32-bit find-first-set / clear-lowest are 1/3 of the 64-bit cost)
             unsigned wlo = 0, whi = 0;
             for (unsigned c32 = (unsigned)cand; c32; c32 &= c32 - 1) {
                 const int i = __ffs((int)c32) - 1;
-                if (pair_suppresses(cmp, a[k], aarea[k], cb[cbase + i], carea[cbase + i])) wlo |= 1u << i;
+                if (pair_suppresses<VARIANT>(cmp, a[k], aarea[k], cb[cbase + i], carea[cbase + i])) wlo |= 1u << i;
             }
             for (unsigned c32 = (unsigned)(cand >> 32); c32; c32 &= c32 - 1) {
                 const int i = __ffs((int)c32) - 1;
-                if (pair_suppresses(cmp, a[k], aarea[k], cb[cbase + 32 + i], carea[cbase + 32 + i])) whi |= 1u << i;
+                if (pair_suppresses<VARIANT>(cmp, a[k], aarea[k], cb[cbase + 32 + i], carea[cbase + 32 + i])) whi |= 1u << i;
             }
             mask[(size_t)r * ncol + ct] = ((u64)whi << 32) | wlo;
         }
@@ -302,6 +318,28 @@ nms_resolve_seg_kernel(const u64 *__restrict__ mask, int ncol, const int32_t *__
     for (int c = tid; c < w; c += RSEG_THREADS) if (kept[c]) atomicOr(&kept_g[w0 + c], kept[c]);
 }
 
+// nms_multianchor's `clusters` (nms.pyx:150, 177, 184): a kept box is its own cluster, a suppressed box
+// belongs to the kept box that suppressed it in the greedy order = its FIRST kept suppressor.
+__global__ void __launch_bounds__(256)
+nms_cluster_kernel(const u64 *__restrict__ mask, const u64 *__restrict__ kept, int n, int ncol,
+                   const uint32_t *__restrict__ order, const int32_t *__restrict__ seg, const int32_t *__restrict__ seg_off,
+                   int64_t *__restrict__ clusters)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int64_t self = order ? order[i] : (uint32_t)i;
+    int64_t cl = self;
+    const int wi = i >> 6;
+    if (!((kept[wi] >> (i & 63)) & 1ull)) {
+        const u64 *row = mask + (size_t)i * ncol;
+        for (int c = seg ? (seg_off[seg[i]] >> 6) : 0; c <= wi; ++c) {
+            const u64 hit = row[c] & kept[c];
+            if (hit) { const int p = c * 64 + __ffsll((long long)hit) - 1; cl = order ? order[p] : (uint32_t)p; break; }
+        }
+    }
+    clusters[self] = cl;
+}
+
 __global__ void __launch_bounds__(1024)
 nms_compact_kernel(const u64 *__restrict__ kept, int n, int ncol, const uint32_t *__restrict__ order,
                const int32_t *__restrict__ seg_sorted, int n_seg, int64_t *__restrict__ keep, int32_t *__restrict__ n_keep)
@@ -366,12 +404,12 @@ NmsBuffers carve_nms(void *ws, long n, int n_seg) {
     return b;
 }
 
-NmsCmp make_cmp(double thresh, int mode) {
-    NmsCmp c; c.mode = mode; c.thr_d = thresh; c.thr_f = (float)thresh;
+NmsCmp make_cmp(double thresh, int mode, int variant = 0) {
+    NmsCmp c; c.mode = mode; c.variant = variant; c.thr_d = thresh; c.thr_f = (float)thresh;
     c.nonpos = (mode == DETBOX_NMS_GE_F64) ? !(thresh > 0.0) : !(c.thr_f > 0.0f);
     // band around the threshold outside which the approximate quotient decides (pair_suppresses)
     const double t = (mode == DETBOX_NMS_GE_F64) ? thresh : (double)c.thr_f;
-    c.fast = t > 1e-20 && t < 1e20;
+    c.fast = variant == 0 && t > 1e-20 && t < 1e20;
     c.q_hi = c.q_lo = 0.0f;
     if (c.fast) {
         const double eps = 1.0 / (1 << 20);
@@ -383,7 +421,7 @@ NmsCmp make_cmp(double thresh, int mode) {
 
 // mask + scan + compact over boxes that are already gathered in processing order
 int nms_sorted(const NmsBuffers &b, const uint32_t *order, long n, int n_seg,
-               NmsCmp cmp, int64_t *keep, int32_t *n_keep, cudaStream_t st)
+               NmsCmp cmp, int64_t *keep, int32_t *n_keep, cudaStream_t st, int64_t *clusters = nullptr)
 {
     const int32_t *seg_off = b.seg_off;
     const int ncol = (int)((n + 63) / 64);
@@ -398,7 +436,12 @@ int nms_sorted(const NmsBuffers &b, const uint32_t *order, long n, int n_seg,
     if (small_segs) { const unsigned want = 2u * (unsigned)((n / n_seg + 255) / 256) + 2u; if (gx > want) gx = want; }
     dim3 grid(gx, (unsigned)((ncol + MASK_RT - 1) / MASK_RT));
     DETBOX_TRACE_BEGIN(DETBOX_K_NMS_MASK, st);
-    nms_mask_kernel<<<grid, 64 * MASK_CT, 0, st>>>(b.sorted, seg_sorted, seg_sorted ? seg_off : nullptr, (int)n, ncol, cg, cmp, b.mask);
+    if (cmp.variant == DETBOX_NMS_VARIANT_PLAIN)
+        nms_mask_kernel<0><<<grid, 64 * MASK_CT, 0, st>>>(b.sorted, seg_sorted, seg_sorted ? seg_off : nullptr, (int)n, ncol, cg, cmp, b.mask);
+    else if (cmp.variant == DETBOX_NMS_VARIANT_NEW)
+        nms_mask_kernel<1><<<grid, 64 * MASK_CT, 0, st>>>(b.sorted, seg_sorted, seg_sorted ? seg_off : nullptr, (int)n, ncol, cg, cmp, b.mask);
+    else
+        nms_mask_kernel<2><<<grid, 64 * MASK_CT, 0, st>>>(b.sorted, seg_sorted, seg_sorted ? seg_off : nullptr, (int)n, ncol, cg, cmp, b.mask);
     DETBOX_TRACE_END(DETBOX_K_NMS_MASK, st);
     DETBOX_LAUNCH_CHECK();
     int dev = 0;
@@ -445,6 +488,11 @@ int nms_sorted(const NmsBuffers &b, const uint32_t *order, long n, int n_seg,
     }
     nms_compact_kernel<<<1, 1024, 0, st>>>(b.kept, (int)n, ncol, order, seg_sorted, n_seg, keep, n_keep);
     DETBOX_LAUNCH_CHECK();
+    if (clusters) {
+        nms_cluster_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(b.mask, b.kept, (int)n, ncol, order, seg_sorted,
+                                                                        seg_sorted ? seg_off : nullptr, clusters);
+        DETBOX_LAUNCH_CHECK();
+    }
     return DETBOX_OK;
 }
 
@@ -456,10 +504,11 @@ extern "C" size_t detbox_nms_workspace_bytes(long n, int n_seg)
     return carve_nms(nullptr, n, n_seg > 1 ? n_seg : 1).total;
 }
 
-extern "C" int detbox_nms(const float *boxes, int box_stride, const float *scores, long n,
-                          const int32_t *seg_ids, int n_seg, double thresh, int cmp_mode,
-                          int64_t *keep, int32_t *n_keep, void *ws, size_t ws_bytes, void *stream)
+static int nms_impl(const float *boxes, int box_stride, const float *scores, long n,
+                    const int32_t *seg_ids, int n_seg, double thresh, int cmp_mode, int variant,
+                    int64_t *keep, int32_t *n_keep, int64_t *clusters, void *ws, size_t ws_bytes, void *stream)
 {
+    if (variant < 0 || variant > 2) return DETBOX_ERR_INVALID;
     const bool presorted = (cmp_mode & DETBOX_NMS_PRESORTED) != 0;
     cmp_mode &= ~DETBOX_NMS_PRESORTED;
     if (n < 0 || box_stride < 4 || cmp_mode < 0 || cmp_mode > 2 || !n_keep) return DETBOX_ERR_INVALID;
@@ -482,7 +531,7 @@ extern "C" int detbox_nms(const float *boxes, int box_stride, const float *score
         }
         b.sorted = const_cast<float4 *>(reinterpret_cast<const float4 *>(boxes));
         b.seg_sorted = const_cast<int32_t *>(seg_ids);
-        return nms_sorted(b, nullptr, n, n_seg, make_cmp(thresh, cmp_mode), keep, n_keep, st);
+        return nms_sorted(b, nullptr, n, n_seg, make_cmp(thresh, cmp_mode, variant), keep, n_keep, st, clusters);
     }
     int rc;
     if (n <= SMALL_SORT_MAX && n_seg == 1) {      // one launch instead of 13
@@ -514,7 +563,24 @@ extern "C" int detbox_nms(const float *boxes, int box_stride, const float *score
     nms_gather_kernel<<<(unsigned)gb, 256, 0, st>>>(boxes, box_stride, order, n, seg_ids, b.sorted,
                                                n_seg > 1 ? b.seg_sorted : nullptr);
     DETBOX_LAUNCH_CHECK();
-    return nms_sorted(b, order, n, n_seg, make_cmp(thresh, cmp_mode), keep, n_keep, st);
+    return nms_sorted(b, order, n, n_seg, make_cmp(thresh, cmp_mode, variant), keep, n_keep, st, clusters);
+}
+
+extern "C" int detbox_nms(const float *boxes, int box_stride, const float *scores, long n,
+                          const int32_t *seg_ids, int n_seg, double thresh, int cmp_mode,
+                          int64_t *keep, int32_t *n_keep, void *ws, size_t ws_bytes, void *stream)
+{
+    return nms_impl(boxes, box_stride, scores, n, seg_ids, n_seg, thresh, cmp_mode, DETBOX_NMS_VARIANT_PLAIN,
+                    keep, n_keep, nullptr, ws, ws_bytes, stream);
+}
+
+extern "C" int detbox_nms_variant(const float *boxes, int box_stride, const float *scores, long n,
+                                  const int32_t *seg_ids, int n_seg, double thresh, int cmp_mode, int variant,
+                                  int64_t *keep, int32_t *n_keep, int64_t *clusters,
+                                  void *ws, size_t ws_bytes, void *stream)
+{
+    return nms_impl(boxes, box_stride, scores, n, seg_ids, n_seg, thresh, cmp_mode, variant,
+                    keep, n_keep, clusters, ws, ws_bytes, stream);
 }
 
 // ------------------------------------------------------------------------------------------------

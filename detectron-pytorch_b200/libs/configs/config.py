@@ -26,6 +26,9 @@ roi_bg_threshold = 0.3
 max_det_num = 100
 score_threshold = 0.5
 overlap_threshold = 0.5
+overlap_threshold_noncrowd = 0.4                  # config.py:151
+noncrowd_classes = [5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 16] + list(range(25, 34)) + list(range(36, 56)) + list(range(57, 81))  # config.py:154-158
+batch_size = 6                                    # config.py:78
 ignored_area_intersection_fraction = 0.3
 
 

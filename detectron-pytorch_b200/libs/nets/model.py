@@ -37,6 +37,15 @@ def _decoding_and_thresholding_stage1(rpn_box, rpn_prob, anchors, score_threshol
     return boxes[inds], probs[inds], img_ids[inds], anc[inds]
 
 
+def _thresholding(boxes, probs, batch_ids, score_threshold=0.1, activation=None):
+    """model.py:92-104: objectness >= threshold, or the ten best when nothing passes."""
+    objness = _objectness(probs, activation)
+    inds = objness.ge(score_threshold).nonzero().view(-1)
+    if inds.numel() == 0:
+        inds = objness.sort(dim=0, descending=True, stable=True)[1][:10]
+    return boxes[inds], probs[inds], batch_ids[inds]
+
+
 def _apply_nms_in_batch(boxes, probs, img_ids, anchors, activation, overlap_threshold=0.5):
     """model.py:343-355: per-image NMS, kept rows image-major and score-descending inside an image.
     Upstream loops over images in Python with a nonzero() sync per image; here the images are

@@ -61,13 +61,19 @@ def topk_decode(rpn_box, rpn_prob, anchors, top_n, activation="softmax", box_enc
     return out
 
 
-def nms(boxes, scores, thresh, cmp_mode=NMS_GT_F32, seg_ids=None, n_seg=1, return_counts=False, presorted=False):
+NMS_VARIANTS = {None: 0, "plain": 0, "new": 1, "multianchor": 2}
+
+
+def nms(boxes, scores, thresh, cmp_mode=NMS_GT_F32, seg_ids=None, n_seg=1, return_counts=False, presorted=False,
+        variant=None, want_clusters=False):
     """Greedy NMS on the device.  boxes [n,>=4], scores [n] -> (keep int64 [n] buffer, n_keep int32
     [n_seg+1] on the device); no host synchronisation happens here.  keep[:n_keep[n_seg]] are the
     kept ORIGINAL row indices, segment-major, score-descending inside a segment.
     presorted=True: the rows already are in that processing order (segment ids non-decreasing, scores
     non-increasing inside a segment, boxes [n,4]) — e.g. topk_decode(per_image=True) output — and the
-    sort + gather are skipped."""
+    sort + gather are skipped.
+    variant='new' | 'multianchor': the pair rules of libs/boxes/nms.pyx:70-195; want_clusters=True adds
+    nms_multianchor's cluster ids (int64 [n], original indices) as a third result."""
     b, s = _dev(boxes), _dev(scores).view(-1)
     n = b.shape[0]
     if s.numel() != n:
@@ -79,13 +85,21 @@ def nms(boxes, scores, thresh, cmp_mode=NMS_GT_F32, seg_ids=None, n_seg=1, retur
         n_seg = 1
     keep = torch.empty((n,), dtype=torch.int64, device=b.device)
     n_keep = torch.zeros((n_seg + 1,), dtype=torch.int32, device=b.device)
+    clusters = torch.empty((n,), dtype=torch.int64, device=b.device) if want_clusters else None
     if n == 0:
-        return keep, n_keep
+        return (keep, n_keep, clusters) if want_clusters else (keep, n_keep)
     ws = _ws.get(lib().detbox_nms_workspace_bytes(n, n_seg), b.device)
     if presorted and b.shape[1] != 4:
         raise _lib.DetboxError("nms(presorted=True) needs boxes of shape [n,4]")
-    check(lib().detbox_nms(b.data_ptr(), b.shape[1], s.data_ptr(), n, _ptr(seg), n_seg, float(thresh),
-                           int(cmp_mode) | (0x100 if presorted else 0),
-                           keep.data_ptr(), n_keep.data_ptr(), ws.data_ptr(), ws.numel(), _stream()), "nms")
-    _count((3 if presorted else 13 + 4) + ((2 if presorted else 5) if n_seg > 1 else 0))
-    return keep, n_keep
+    mode = int(cmp_mode) | (0x100 if presorted else 0)
+    if NMS_VARIANTS[variant] or want_clusters:
+        check(lib().detbox_nms_variant(b.data_ptr(), b.shape[1], s.data_ptr(), n, _ptr(seg), n_seg, float(thresh), mode,
+                                       NMS_VARIANTS[variant], keep.data_ptr(), n_keep.data_ptr(), _ptr(clusters),
+                                       ws.data_ptr(), ws.numel(), _stream()), "nms_variant")
+    else:
+        check(lib().detbox_nms(b.data_ptr(), b.shape[1], s.data_ptr(), n, _ptr(seg), n_seg, float(thresh), mode,
+                               keep.data_ptr(), n_keep.data_ptr(), ws.data_ptr(), ws.numel(), _stream()), "nms")
+    # launches: sort (1 for n <= 4096, else 13) + gather unless presorted; segment count/scan (+ id passes); mask, resolve, compact
+    _count((0 if presorted else (2 if n <= 4096 and n_seg == 1 else 14)) + 3 + ((2 if presorted else 5) if n_seg > 1 else 0)
+           + (1 if want_clusters else 0))
+    return (keep, n_keep, clusters) if want_clusters else (keep, n_keep)

@@ -51,6 +51,10 @@ extern "C" {
  * scores non-increasing inside a segment (what detbox_topk_decode(per_image=1) emits) — so the
  * sort and the gather are skipped.  Needs box_stride == 4 and 16-byte aligned boxes. */
 #define DETBOX_NMS_PRESORTED 0x100
+/* suppression rule variants of libs/boxes/nms.pyx (detbox_nms_variant) */
+#define DETBOX_NMS_VARIANT_PLAIN       0   /* nms             nms.pyx:17-68   IoU only                                    */
+#define DETBOX_NMS_VARIANT_NEW         1   /* nms_new         nms.pyx:70-123  + inter/area_i > 0.95 or inter/area_j > 0.95 */
+#define DETBOX_NMS_VARIANT_MULTIANCHOR 2   /* nms_multianchor nms.pyx:125-195 (inter+0.1)/(union+0.1), centre-distance rule */
 
 /* RoIAlign sampling convention / level mode / fused 2x2 pooling / layout */
 #define DETBOX_ROI_BIN_CENTRE 0 /* roi_align_tf (crop_and_resize.c + roi_align_tf.py:24-40)   */
@@ -194,6 +198,15 @@ int detbox_nms(const float *boxes_dev, int box_stride, const float *scores_dev, 
                const int32_t *seg_ids_dev, int n_seg, double thresh, int cmp_mode,
                int64_t *keep_dev, int32_t *n_keep_dev,
                void *workspace_dev, size_t workspace_bytes, void *stream);
+/* The NMS variants of libs/boxes/nms.pyx:70-195 (`nms_new`, `nms_multianchor`; used by
+ * single_shot.nms_advanced / nms_stitch) on the same mask + resolve pipeline: `variant` selects the
+ * pair rule (DETBOX_NMS_VARIANT_*), cmp_mode the IoU comparison (upstream: DETBOX_NMS_GE_F64).
+ * clusters_dev (optional, int64 [n]): nms_multianchor's second result — a kept box's own index, a
+ * suppressed box's first kept suppressor (original indices). */
+int detbox_nms_variant(const float *boxes_dev, int box_stride, const float *scores_dev, long n,
+                       const int32_t *seg_ids_dev, int n_seg, double thresh, int cmp_mode, int variant,
+                       int64_t *keep_dev, int32_t *n_keep_dev, int64_t *clusters_dev,
+                       void *workspace_dev, size_t workspace_bytes, void *stream);
 
 /* ---------------------------------------------------------------------------------------------
  * RoIAlign over FPN levels, forward and backward — replaces

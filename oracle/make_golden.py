@@ -105,11 +105,40 @@ def roi_sampling_golden(r):
     np.savez_compressed(os.path.join(GOLD, "roi_sampling.npz"), **out)
 
 
+def variant_dets(seed):
+    rng = np.random.RandomState(seed)
+    n = [200, 500, 40, 700][seed % 4]
+    wh = np.exp(rng.uniform(np.log(4), np.log(80), (n, 2)))
+    c = rng.uniform(0, 250, (n, 2))
+    b = np.concatenate([c - wh / 2, c + wh / 2], 1)
+    if seed % 2:
+        b = np.round(b)                     # integer boxes: quotients exactly on thresholds, coincident centres
+    s = rng.permutation(n) / float(n)
+    return np.concatenate([b, s[:, None]], 1).astype(np.float32)
+
+
+def nms_variants_golden(r):
+    """nms_new / nms_multianchor of the reference's libs/boxes/nms.pyx (compiled as cython_nms)."""
+    out = {}
+    for seed in range(4):
+        d = variant_dets(seed)
+        out["d%d" % seed] = d
+        for thr in (0.3, 0.5):
+            out["d%d_new_%g" % (seed, thr)] = np.asarray(r.cython_nms.nms_new(d, thr), np.int64)
+            keep, clusters = r.cython_nms.nms_multianchor(d, thr)
+            out["d%d_multi_keep_%g" % (seed, thr)] = np.asarray(keep, np.int64)
+            out["d%d_multi_clusters_%g" % (seed, thr)] = np.asarray(clusters, np.int64)
+    np.savez_compressed(os.path.join(GOLD, "nms_variants.npz"), **out)
+
+
 def main():
     r = ref_loader.load()
     os.makedirs(GOLD, exist_ok=True)
     if "--only-roi-sampling" in sys.argv:
         roi_sampling_golden(r)
+        return
+    if "--only-nms-variants" in sys.argv:
+        nms_variants_golden(r)
         return
     A = r.boxes_anchor
 
@@ -251,6 +280,7 @@ def main():
     np.savez_compressed(os.path.join(GOLD, "roialign.npz"), **out)
 
     roi_sampling_golden(r)
+    nms_variants_golden(r)
 
     sz = sum(os.path.getsize(os.path.join(GOLD, f)) for f in os.listdir(GOLD))
     print("golden vectors written to", GOLD, "(%d KiB)" % (sz // 1024))

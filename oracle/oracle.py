@@ -522,3 +522,59 @@ def roi_target(rois, roi_batch_inds, gt_boxes, gt_batch_inds, fg_overlap):
                 deltas[r, 3] = f(np.float64(np.log(f(bh / ah))) / 0.2)
             bbw[r] = 1.0
     return labels, deltas, bbw
+
+
+# ------------------------------------------------------------------------------------------------
+# NMS variants
+# ------------------------------------------------------------------------------------------------
+def _nms_variant(dets, thresh, variant):
+    """libs/boxes/nms.pyx:70-123 (nms_new) / :125-195 (nms_multianchor) restated with the typed arithmetic the
+    generated C has: float32 for every `cdef np.float32_t`, double where an untyped Python float or a double
+    literal enters.  Ties: ascending index (upstream's argsort()[::-1] is unstable)."""
+    f = np.float32
+    dets = np.asarray(dets, f)
+    x1, y1, x2, y2, sc = (dets[:, k] for k in range(5))
+    areas = (x2 - x1 + f(1)) * (y2 - y1 + f(1))
+    order = stable_desc_order(sc)
+    n = dets.shape[0]
+    suppressed = np.zeros(n, np.int64)
+    clusters = np.arange(n)
+    keep = []
+    thresh = float(thresh)
+    with np.errstate(all="ignore"):
+        for _i in range(n):
+            i = order[_i]
+            if suppressed[i]:
+                continue
+            keep.append(int(i))
+            icx = 0.5 * float(f(x1[i] + x2[i])); icy = 0.5 * float(f(y1[i] + y2[i]))
+            for _j in range(_i + 1, n):
+                j = order[_j]
+                if suppressed[j]:
+                    continue
+                xx1 = max(x1[i], x1[j]); yy1 = max(y1[i], y1[j]); xx2 = min(x2[i], x2[j]); yy2 = min(y2[i], y2[j])
+                w = f(max(0.0, float(f(f(xx2 - xx1) + f(1))))); h = f(max(0.0, float(f(f(yy2 - yy1) + f(1)))))
+                inter = f(w * h)
+                if variant == "new":
+                    ovr = f(inter / f(f(areas[i] + areas[j]) - inter))
+                    ovr1 = f(inter / areas[i]); ovr2 = f(inter / areas[j])
+                    if float(ovr) >= thresh or float(ovr1) > 0.95 or float(ovr2) > 0.95:
+                        suppressed[j] = 1
+                else:
+                    ovr = f((float(inter) + 0.1) / (float(f(f(areas[i] + areas[j]) - inter)) + 0.1))
+                    if float(ovr) >= thresh:
+                        suppressed[j] = 1; clusters[j] = i
+                        continue
+                    jcx = 0.5 * float(f(x1[j] + x2[j])); jcy = 0.5 * float(f(y1[j] + y2[j]))
+                    dist = (jcx - icx) * (jcx - icx) + (jcy - icy) * (jcy - icy)
+                    if np.sqrt(dist) <= 0.2 * float(min(w, h)):
+                        suppressed[j] = 1; clusters[j] = i
+    return keep, clusters
+
+
+def nms_new(dets, thresh):
+    return _nms_variant(dets, thresh, "new")[0]
+
+
+def nms_multianchor(dets, thresh):
+    return _nms_variant(dets, thresh, "multianchor")

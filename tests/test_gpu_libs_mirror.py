@@ -269,3 +269,52 @@ def test_roi_align_grid_modules_vs_oracle(pool):
         ggrid = t.grad.numpy()
     wg = O.roi_align_grid_bwd(ggrid, rois, np.float32(0.25), feat.shape)
     np.testing.assert_allclose(f.grad.cpu().numpy(), wg, rtol=1e-4, atol=1e-4)
+
+
+def test_single_shot_new_advanced_stitch(golden):
+    """compute_detection_new / nms_advanced / nms_stitch (single_shot.py:62-177) against the same compositions
+    over the oracle's pieces."""
+    import libs.configs.config as cfg
+    from libs.postprocessings.single_shot import compute_detection_new, nms_advanced, nms_stitch
+    g = golden("transform")
+    rng = np.random.RandomState(5)
+    n = g["deltas"].shape[0]
+    probs = rng.dirichlet([1.0, 0.6, 0.6], n).astype(np.float32)
+    img = np.sort(rng.randint(0, 2, n))
+    dets = compute_detection_new(g["deltas"], probs, g["anchors"], img, 600, 800, 3, score_threshold=0.3,
+                                 overlap_threshold=0.5, max_dets=40, batch_size=2)
+    assert len(dets) == 2
+    for i in range(2):
+        inds = np.where(img == i)[0]
+        fb = O.anchor_decode(g["deltas"][inds], probs[inds], g["anchors"][inds], 600, 800, 3)[0]
+        obj = 1 - probs[inds][:, 0]
+        od = np.hstack([fb, obj[:, None]]).astype(np.float32)
+        keep = np.asarray(O.nms(od[:, :4], od[:, 4], 0.5, O.NMS_GT_F32))
+        od = od[keep]
+        keep = keep[:40]
+        po = probs[inds][keep][:, 1:]
+        d0, d1 = np.where(po > 0.3)
+        w = np.zeros((d0.size, 6)); w[:, :4] = od[d0, :4]; w[:, 4] = po[d0, d1]; w[:, 5] = d1 + 1
+        w = w[np.argsort(-w[:, 4], kind="stable")]
+        assert np.array_equal(dets[i][:, 4:], w[:, 4:])
+        assert_boxes_close(dets[i][:, :4], w[:, :4])
+    # nms_advanced: per class nms_multianchor with the crowd / non-crowd thresholds
+    D = []
+    for s in (0, 1):
+        b = np.round(rng.uniform(0, 120, (300, 2))); wh = np.round(np.exp(rng.uniform(np.log(6), np.log(60), (300, 2))))
+        D.append(np.hstack([b, b + wh, rng.rand(300, 1), rng.choice([1, 2, 5], 300)[:, None]]))
+    got = nms_advanced(D)
+    for dets_i, got_i in zip(D, got):
+        rows = []
+        cls = dets_i[:, 5].astype(np.int32)
+        for c in np.unique(cls):
+            thr = cfg.overlap_threshold_noncrowd if c in cfg.noncrowd_classes else cfg.overlap_threshold
+            dt = dets_i[cls == c]
+            rows.append(dt[O.nms_multianchor(dt[:, :5].astype(np.float32), thr)[0]])
+        assert np.array_equal(got_i, np.vstack(rows))
+    got = nms_stitch(D)
+    for dets_i, got_i in zip(D, got):
+        p = dets_i[:, 4].astype(np.float32)
+        inds = np.where((p > 0.1) & (p <= 0.5))[0]
+        keep = O.nms_multianchor(dets_i[:, :5].astype(np.float32), 0.95)[0]
+        assert np.array_equal(got_i, dets_i[np.setdiff1d(np.arange(p.size), np.setdiff1d(inds, keep))])

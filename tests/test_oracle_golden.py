@@ -147,3 +147,14 @@ def test_roi_matching_and_sampling(golden, case):
     np.testing.assert_array_equal(sb, g["c%d_sample_boxes" % case])
     np.testing.assert_array_equal(sl, g["c%d_sample_labels" % case])
     np.testing.assert_array_equal(si, g["c%d_sample_ids" % case])
+
+
+@pytest.mark.parametrize("seed", range(4))
+@pytest.mark.parametrize("thr", [0.3, 0.5])
+def test_nms_variants(golden, seed, thr):
+    g = golden("nms_variants")
+    d = g["d%d" % seed]
+    np.testing.assert_array_equal(O.nms_new(d, thr), g["d%d_new_%g" % (seed, thr)])
+    keep, clusters = O.nms_multianchor(d, thr)
+    np.testing.assert_array_equal(keep, g["d%d_multi_keep_%g" % (seed, thr)])
+    np.testing.assert_array_equal(clusters, g["d%d_multi_clusters_%g" % (seed, thr)])

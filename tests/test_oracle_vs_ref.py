@@ -140,3 +140,16 @@ def test_matching_box_and_sample_rois_random(ref, seed):
     got = O.sample_rois(b, ids, gts, 0.5, 16, 0.25, 0.2, rng=np.random.RandomState(seed))
     for w, g in zip(want, got):
         np.testing.assert_array_equal(w.numpy(), g)
+
+
+@pytest.mark.parametrize("seed", range(4, 8))
+def test_nms_variants_random(ref, seed):
+    """oracle.nms_new / nms_multianchor == the reference's compiled libs/boxes/nms.pyx:70-195."""
+    from oracle.make_golden import variant_dets
+    d = variant_dets(seed)
+    for thr in (0.3, 0.6):
+        assert [int(i) for i in ref.cython_nms.nms_new(d, thr)] == O.nms_new(d, thr)
+        keep, clusters = ref.cython_nms.nms_multianchor(d, thr)
+        k2, c2 = O.nms_multianchor(d, thr)
+        assert [int(i) for i in keep] == k2
+        np.testing.assert_array_equal(np.asarray(clusters), c2)
