@@ -64,14 +64,18 @@ def test_argument_validation_and_no_cpu_fallback():
         cython_bbox.bbox_overlaps([[0, 0, 1, 1]], b)
     with pytest.raises(TypeError):
         cpu_nms(np.zeros((2, 5), np.float32), 1)                    # thresh must be a Python float
-    with pytest.raises(NotImplementedError):
-        nms_new(np.zeros((2, 5), np.float32), 0.5)
+    with pytest.raises(TypeError):
+        nms_new(np.zeros((2, 5), np.float32), 1)
+    with pytest.raises(ValueError):
+        nms_new(np.zeros((2, 5), np.float64), 0.5)
     assert cython_bbox.bbox_overlaps(np.zeros((0, 4)), b).shape == (0, 3)
     if not torch.cuda.is_available():
         with pytest.raises(detbox.DetboxError):
             cython_bbox.bbox_overlaps(b, b)                          # no CPU path: fails loudly
         with pytest.raises(detbox.DetboxError):
             cpu_nms(np.zeros((2, 5), np.float32), 0.5)
+        with pytest.raises(detbox.DetboxError):
+            nms_new(np.zeros((2, 5), np.float32), 0.5)
 
 
 def test_config_defaults_are_the_references():
