@@ -13,7 +13,8 @@ A STEP is one pass of the box path over `--batch` (default 64) synthetic CityPer
 `e2e`    : the same step through detbox.pipeline.BoxOpsSession.run_host — pinned HOST buffers in,
            HOST buffers out, the copies inside the timed region.
 Extra keys report the two other parts of BASELINE.json's metric on configs[1] / configs[2]:
-`nms_us` (1k/5k/20k/100k boxes) and `roi_align` (GB/s fwd / bwd, 4096 RoIs x 256 ch x 7x7, P2-P5).
+`nms_us` (1k/5k/20k/100k boxes), `roi_align` (GB/s fwd / bwd, 4096 RoIs x 256 ch x 7x7, P2-P5) and
+`single_image` (batch-1 latency of the whole path, eager and CUDA-graph replay).
 `roofline` is the dominant kernel of the step, timed with CUDA events around its launches
 (detbox_trace_kernel); `cpu_baseline` is the reference's own CPU code (oracle/_ref when it was
 built, else the oracle's C port) on the host cores, on a bounded sample of the same workload.
@@ -389,6 +390,39 @@ def roi_align_bench(torch, detbox, hbm_peak):
 
 
 # -------------------------------------------------------------------------------------- main ----
+def single_image_latency(torch, detbox, gt1, h_prob, h_box, A):
+    """one CP-R image per call (the launch-latency regime) — the whole device-resident path
+    eagerly launched, and the same launch sequence captured once in a CUDA graph and replayed."""
+    sess1 = detbox.pipeline.BoxOpsSession(STRIDES, IH, IW, SCALES, RATIOS, BASE, 1, NUM_CLASSES, top_n=TOP_N, nms_thresh=NMS_THR,
+                                          bg=BG, fg=FG, max_gt_total=GT_PER_IMAGE)
+    G = sess1.stage_gt([gt1])
+    d_gt, d_off = sess1.h_gt[:G].cuda(), sess1.h_off.cuda()
+    d_prob, d_box = h_prob[:A].cuda(), h_box[:A].cuda()
+    fn = lambda: sess1.run_device(d_gt, d_off, d_prob, d_box)
+    n0 = detbox.launches(); ref = fn(); per_call = detbox.launches() - n0
+    out = {"launches_per_image": int(per_call), "eager_us": round(median_ms(torch, fn, iters=40, warm=5) * 1e3, 1)}
+    try:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                fn()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            got = fn()
+        graph.replay(); torch.cuda.synchronize()
+        same = all(torch.equal(got[k], ref[k]) for k in ("labels", "bbox_targets", "n_keep")) and \
+            torch.equal(got["keep"][:int(got["n_keep"][-1])], ref["keep"][:int(ref["n_keep"][-1])])
+        out["graph_us"] = round(median_ms(torch, graph.replay, iters=40, warm=5) * 1e3, 1)
+        out["graph_matches_eager"] = bool(same)
+        out["images_per_s_graph"] = round(1e6 / out["graph_us"], 1)
+    except Exception as e:                             # keep the bench line; say why there is no graph number
+        out["graph_error"] = str(e).splitlines()[0][:160]
+    return out
+
+
 def trace_bytes(kid, B, A, G_total, C):
     """ALGORITHMIC bytes of ONE launch of the traced kernel (kernels table)."""
     return {2: 16 * A * B + 20 * G_total,                       # colmax: anchors (re-read per image) + GT
@@ -514,6 +548,7 @@ def main():
     if rank == 0 and world == 1 and not args.no_extras:
         extras["nms_us"] = nms_sweep(torch, detbox)
         extras["roi_align"] = roi_align_bench(torch, detbox, hbm_peak)
+        extras["single_image"] = single_image_latency(torch, detbox, gts[0], h_prob, h_box, A)
 
     if rank == 0:
         total_images = B * world

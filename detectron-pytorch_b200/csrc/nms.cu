@@ -85,13 +85,18 @@ nms_gather_kernel(const float *__restrict__ boxes, int stride, const uint32_t *_
     }
 }
 
-// segment sizes -> offsets in the (segment-major) processing order
+// segment sizes -> offsets in the (segment-major) processing order.  One atomic per distinct id per warp
+// (__match_any): ids arrive sorted or in long runs, so a warp usually issues one or two.
 __global__ void __launch_bounds__(256)
 nms_seg_count_kernel(const int32_t *__restrict__ seg_ids, long n, int n_seg, int32_t *__restrict__ seg_off)
 {
-    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
-        const int s = seg_ids[i];
-        if (s >= 0 && s < n_seg) atomicAdd(&seg_off[s + 1], 1);
+    const int lane = threadIdx.x & 31;
+    for (long base = (long)blockIdx.x * blockDim.x; base < n; base += (long)gridDim.x * blockDim.x) {   // block-uniform trip count
+        const long i = base + threadIdx.x;
+        int s = i < n ? seg_ids[i] : -1;
+        if (s < 0 || s >= n_seg) s = -1;
+        const unsigned peers = __match_any_sync(0xffffffffu, s);
+        if (s >= 0 && lane == __ffs(peers) - 1) atomicAdd(&seg_off[s + 1], __popc(peers));
     }
 }
 __global__ void nms_seg_scan_kernel(int32_t *seg_off, int n_seg)
@@ -342,7 +347,8 @@ nms_cluster_kernel(const u64 *__restrict__ mask, const u64 *__restrict__ kept, i
 
 __global__ void __launch_bounds__(1024)
 nms_compact_kernel(const u64 *__restrict__ kept, int n, int ncol, const uint32_t *__restrict__ order,
-               const int32_t *__restrict__ seg_sorted, int n_seg, int64_t *__restrict__ keep, int32_t *__restrict__ n_keep)
+                   const int32_t *__restrict__ seg_off, int n_seg, uint32_t *__restrict__ wrank /*[ncol + 1]*/,
+                   int64_t *__restrict__ keep, int32_t *__restrict__ n_keep)
 {
     __shared__ int warp_sum[32];
     __shared__ int running;
@@ -366,23 +372,36 @@ nms_compact_kernel(const u64 *__restrict__ kept, int n, int ncol, const uint32_t
         }
         __syncthreads();
         int pos = running + warp_sum[w] + incl - c;
+        if (wi < ncol) wrank[wi] = (uint32_t)pos;            // kept boxes before this word
         while (word) {
             const int bit = __ffsll((long long)word) - 1;
             word &= word - 1;
             const int sp = wi * 64 + bit;
             keep[pos++] = (int64_t)(order ? order[sp] : (uint32_t)sp);
-            if (n_seg > 1) atomicAdd(&n_keep[seg_sorted[sp]], 1);
         }
         __syncthreads();
         if (tid == 1023) running = pos;          // last thread's end == running + block total
         __syncthreads();
     }
-    if (tid == 0) { n_keep[n_seg] = running; if (n_seg == 1) n_keep[0] = running; }
+    if (tid == 0) { wrank[ncol] = (uint32_t)running; n_keep[n_seg] = running; if (n_seg == 1) n_keep[0] = running; }
+    if (n_seg > 1) {
+        // kept boxes of a segment = rank(end) - rank(begin); rank(p) = kept boxes at positions < p
+        __syncthreads();
+        for (int s = tid; s < n_seg; s += 1024) {
+            int r[2];
+            for (int e = 0; e < 2; ++e) {
+                const int p = seg_off[s + e];
+                const int wi = p >> 6;
+                r[e] = wi >= ncol ? running : (int)wrank[wi] + __popcll(kept[wi] & ((1ull << (p & 63)) - 1ull));
+            }
+            n_keep[s] = r[1] - r[0];
+        }
+    }
 }
 
 struct NmsBuffers {
     uint32_t *ka, *kb, *va, *vb, *counts;
-    float4 *sorted; int32_t *seg_sorted, *seg_off; u64 *mask, *kept, *supp; unsigned *cnt;
+    float4 *sorted; int32_t *seg_sorted, *seg_off; u64 *mask, *kept, *supp; unsigned *cnt; uint32_t *wrank;
     size_t total;
 };
 
@@ -399,6 +418,7 @@ NmsBuffers carve_nms(void *ws, long n, int n_seg) {
     b.kept = cv.take<u64>(2 * ncol + 2);           // kept | supp | round counters, cleared together
     b.supp = b.kept + ncol;
     b.cnt = reinterpret_cast<unsigned *>(b.supp + ncol);
+    b.wrank = cv.take<uint32_t>(ncol + 1);
     b.mask = cv.take<u64>((size_t)n * ncol);
     b.total = cv.off;
     return b;
@@ -486,7 +506,7 @@ int nms_sorted(const NmsBuffers &b, const uint32_t *order, long n, int n_seg,
         DETBOX_TRACE_END(DETBOX_K_NMS_SCAN, st);
     }
     }
-    nms_compact_kernel<<<1, 1024, 0, st>>>(b.kept, (int)n, ncol, order, seg_sorted, n_seg, keep, n_keep);
+    nms_compact_kernel<<<1, 1024, 0, st>>>(b.kept, (int)n, ncol, order, seg_sorted ? seg_off : nullptr, n_seg, b.wrank, keep, n_keep);
     DETBOX_LAUNCH_CHECK();
     if (clusters) {
         nms_cluster_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(b.mask, b.kept, (int)n, ncol, order, seg_sorted,

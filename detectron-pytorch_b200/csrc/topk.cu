@@ -248,6 +248,141 @@ cand_write_kernel(const uint32_t *__restrict__ keys, long seg_len, const SegStat
     }
 }
 
+// ---- 3'. partition + candidate select (K <= SEG_SORT_MAX) -----------------------------------------
+// When the winners are sorted by (key, index) afterwards (seg_sort_kernel), their order of arrival does not
+// matter, so ONE more pass over the keys is enough after the level-0 select: keys in better bins than the
+// threshold bin are winners outright, keys inside it become candidates (appended to per-segment lists with
+// warp-aggregated atomics); a block per segment then finds the k_rem best candidates by radix select over
+// the 53-bit composite (low 21 key bits, flat index) — unique values, so the tie rule "lower flat index
+// first" is part of the order.  This replaces two refine passes and the count / scan / write compaction
+// (four reads of the key array) by one.
+constexpr int PT_ITEMS = 4;
+
+__global__ void __launch_bounds__(TK_THREADS)
+partition_kernel(const uint32_t *__restrict__ keys, long seg_len, const SegState *__restrict__ state, long K,
+                 uint32_t *__restrict__ ckeys, uint32_t *__restrict__ cvals,
+                 uint32_t *__restrict__ cand_keys, uint32_t *__restrict__ cand_idx, uint32_t *__restrict__ cnt /*[n_seg][2]*/)
+{
+    const int tid = threadIdx.x, lane = tid & 31;
+    const uint32_t b0 = state[blockIdx.y].prefix;
+    const long seg0 = (long)blockIdx.y * seg_len;
+    const uint32_t *k = keys + seg0;
+    uint32_t *win_cnt = cnt + 2 * blockIdx.y, *cand_cnt = win_cnt + 1;
+    const uint32_t below = (1u << lane) - 1u;
+    for (long r0 = (long)blockIdx.x * TK_THREADS * PT_ITEMS; r0 < seg_len; r0 += (long)gridDim.x * TK_THREADS * PT_ITEMS) {
+        uint32_t v[PT_ITEMS];
+#pragma unroll
+        for (int j = 0; j < PT_ITEMS; ++j) {
+            const long r = r0 + j * TK_THREADS + tid;
+            v[j] = r < seg_len ? k[r] : 0xffffffffu;
+        }
+#pragma unroll
+        for (int j = 0; j < PT_ITEMS; ++j) {
+            const long r = r0 + j * TK_THREADS + tid;
+            const bool ok = r < seg_len;
+            const uint32_t bin = v[j] >> 21;
+            const bool better = ok && bin < b0, cand = ok && bin == b0;
+            const unsigned mb = __ballot_sync(0xffffffffu, better), mc = __ballot_sync(0xffffffffu, cand);
+            if (mb) {
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(win_cnt, (uint32_t)__popc(mb));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (better) {
+                    const size_t pos = (size_t)blockIdx.y * K + base + __popc(mb & below);
+                    ckeys[pos] = v[j]; cvals[pos] = (uint32_t)(seg0 + r);
+                }
+            }
+            if (mc) {
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(cand_cnt, (uint32_t)__popc(mc));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (cand) {
+                    const size_t pos = (size_t)seg0 + base + __popc(mc & below);
+                    cand_keys[pos] = v[j]; cand_idx[pos] = (uint32_t)(seg0 + r);
+                }
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(1024)
+cand_select_kernel(const uint32_t *__restrict__ cand_keys, const uint32_t *__restrict__ cand_idx, long seg_len,
+                   const SegState *__restrict__ state, const uint32_t *__restrict__ cnt, long K,
+                   uint32_t *__restrict__ ckeys, uint32_t *__restrict__ cvals)
+{
+    typedef unsigned long long u64;
+    __shared__ uint32_t hist[NB0];
+    __shared__ uint32_t wsum[32];
+    __shared__ uint32_t s_bin, s_before, s_out;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const SegState st = state[blockIdx.x];
+    const uint32_t c0 = cnt[2 * blockIdx.x + 1];
+    const uint32_t *ck = cand_keys + (size_t)blockIdx.x * seg_len, *ci = cand_idx + (size_t)blockIdx.x * seg_len;
+    uint32_t need = st.k_rem;                    // 1 <= need <= c0
+    // composite = (key & 0x1fffff) << 32 | idx, 53 bits, digits MSB first: 11, 10 (key), 11, 11, 10 (index)
+    const int shifts[5] = {42, 32, 21, 10, 0};
+    const int bits[5] = {11, 10, 11, 11, 10};
+    u64 prefix = 0;                              // value of the digits fixed so far, already shifted into place
+    int fixed_shift = 53;                        // composites with (comp >> fixed_shift) == (prefix >> fixed_shift) still compete
+    u64 T = ~0ull;
+    uint32_t remaining = c0;                     // competitors under the current prefix
+    for (int lv = 0; lv < 5; ++lv) {
+        if (need == remaining) { T = prefix | ((1ull << fixed_shift) - 1ull); break; }   // everything left wins
+        const int sh = shifts[lv], nb = 1 << bits[lv];
+        for (int i = tid; i < nb; i += 1024) hist[i] = 0;
+        __syncthreads();
+        for (uint32_t i = tid; i < c0; i += 1024) {
+            const u64 comp = ((u64)(ck[i] & 0x1fffffu) << 32) | ci[i];
+            if (fixed_shift == 53 || (comp >> fixed_shift) == (prefix >> fixed_shift)) atomicAdd(&hist[(comp >> sh) & (nb - 1)], 1u);
+        }
+        __syncthreads();
+        // block scan over the bins (2 per thread for 2048 bins): find the bin holding the need-th competitor
+        const int per = nb > 1024 ? 2 : 1;
+        uint32_t c[2] = {0, 0}, sum = 0;
+        for (int j = 0; j < per; ++j) { const int b = tid * per + j; c[j] = b < nb ? hist[b] : 0; sum += c[j]; }
+        uint32_t incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+        if (lane == 31) wsum[w] = incl;
+        __syncthreads();
+        if (w == 0) {
+            const uint32_t x = wsum[lane]; uint32_t ix = x;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, ix, o); if (lane >= o) ix += t; }
+            wsum[lane] = ix - x;
+        }
+        __syncthreads();
+        uint32_t before = wsum[w] + incl - sum;
+        for (int j = 0; j < per; ++j) {
+            if (need > before && need <= before + c[j]) { s_bin = tid * per + j; s_before = before; }
+            before += c[j];
+        }
+        __syncthreads();
+        prefix |= (u64)s_bin << sh;
+        need -= s_before;
+        remaining = hist[s_bin];
+        fixed_shift = sh;
+        __syncthreads();
+        if (lv == 4) T = prefix;                 // all 53 bits fixed: the need-th (== only) competitor itself
+    }
+    // emit: every candidate with composite <= T (exactly k_rem of them), after the segment's outright winners
+    if (tid == 0) s_out = 0;
+    __syncthreads();
+    const size_t out0 = (size_t)blockIdx.x * K + st.n_better;
+    for (uint32_t i0 = 0; i0 < c0; i0 += 1024) {
+        const uint32_t i = i0 + tid;
+        bool take = false; uint32_t key = 0, idx = 0;
+        if (i < c0) { key = ck[i]; idx = ci[i]; take = (((u64)(key & 0x1fffffu) << 32) | idx) <= T; }
+        const unsigned m = __ballot_sync(0xffffffffu, take);
+        if (m) {
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(&s_out, (uint32_t)__popc(m));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (take) { const size_t pos = out0 + base + __popc(m & ((1u << lane) - 1u)); ckeys[pos] = key; cvals[pos] = idx; }
+        }
+    }
+}
+
 // ---- 4'. sort of small segments (K <= 2048 winners each): one block per segment, bitonic network in
 // shared memory over the 64-bit composites (key << 32 | flat index) — unique, so the order is the
 // stable one (ties: lower flat index first).  Segments already sit image-major in ckeys / cvals.
@@ -305,7 +440,7 @@ __global__ void init_state_kernel(SegState *state, int n_seg, uint32_t k)
 
 struct TopkPlan {
     int n_seg; long seg_len; long K; long n_cand; int nblk_c;
-    size_t keys_b, hist_b, state_b, blk_b, cand_b, counts_b, total;
+    size_t keys_b, hist_b, state_b, blk_b, cand_b, counts_b, part_b, cnt_b, total;
 };
 
 TopkPlan make_plan(int batch, long A, long top_n, int per_image) {
@@ -322,7 +457,9 @@ TopkPlan make_plan(int batch, long A, long top_n, int per_image) {
     p.blk_b = align_up((size_t)p.n_seg * p.nblk_c * 4);
     p.cand_b = align_up((size_t)(p.n_cand > 0 ? p.n_cand : 1) * 4);
     p.counts_b = sort_counts_bytes(p.n_cand > 0 ? p.n_cand : 1);
-    p.total = p.keys_b + p.hist_b + p.state_b + 2 * p.blk_b + 4 * p.cand_b + p.counts_b;
+    p.part_b = p.K <= SEG_SORT_MAX ? align_up((size_t)batch * A * 4) : 0;       // candidate lists of the partition path
+    p.cnt_b = align_up((size_t)p.n_seg * 2 * 4);
+    p.total = p.keys_b + p.hist_b + p.cnt_b + p.state_b + 2 * p.blk_b + 4 * p.cand_b + p.counts_b + 2 * p.part_b;
     return p;
 }
 
@@ -351,6 +488,7 @@ extern "C" int detbox_topk_decode(const float *prob, int C, const float *deltas,
     char *w = (char *)ws;
     uint32_t *keys = (uint32_t *)w; w += p.keys_b;
     uint32_t *hist = (uint32_t *)w; w += p.hist_b;
+    uint32_t *part_cnt = (uint32_t *)w; w += p.cnt_b;            // right after hist: cleared by the same memset
     SegState *state = (SegState *)w; w += p.state_b;
     uint32_t *blk_lt = (uint32_t *)w; w += p.blk_b;
     uint32_t *blk_eq = (uint32_t *)w; w += p.blk_b;
@@ -358,9 +496,11 @@ extern "C" int detbox_topk_decode(const float *prob, int C, const float *deltas,
     uint32_t *ckb = (uint32_t *)w; w += p.cand_b;
     uint32_t *cva = (uint32_t *)w; w += p.cand_b;
     uint32_t *cvb = (uint32_t *)w; w += p.cand_b;
-    uint32_t *counts = (uint32_t *)w;
+    uint32_t *counts = (uint32_t *)w; w += p.counts_b;
+    uint32_t *cand_keys = (uint32_t *)w; w += p.part_b;
+    uint32_t *cand_idx = (uint32_t *)w;
 
-    DETBOX_CUDA_TRY(cudaMemsetAsync(hist, 0, p.hist_b, st));
+    DETBOX_CUDA_TRY(cudaMemsetAsync(hist, 0, p.hist_b + p.cnt_b, st));
     init_state_kernel<<<(p.n_seg + 255) / 256, 256, 0, st>>>(state, p.n_seg, (uint32_t)p.K);
     DETBOX_LAUNCH_CHECK();
 
@@ -386,22 +526,33 @@ extern "C" int detbox_topk_decode(const float *prob, int C, const float *deltas,
     uint32_t *h0 = hist, *h1 = hist + (size_t)p.n_seg * NB0, *h2 = hist + (size_t)2 * p.n_seg * NB0;
     select_kernel<<<p.n_seg, 1024, 0, st>>>(h0, 2048, 11, state);
     DETBOX_LAUNCH_CHECK();
+    if (p.K <= SEG_SORT_MAX) {
+        // 3'. one pass: outright winners + candidates of the threshold bin; then select among the candidates
+        long px = (p.seg_len + TK_THREADS * PT_ITEMS - 1) / (TK_THREADS * PT_ITEMS);
+        { long capx = (long)kNumSMs * 8 / p.n_seg; if (capx < 1) capx = 1; if (px > capx) px = capx; }
+        partition_kernel<<<dim3((unsigned)px, (unsigned)p.n_seg), TK_THREADS, 0, st>>>(keys, p.seg_len, state, p.K, cka, cva,
+                                                                                     cand_keys, cand_idx, part_cnt);
+        DETBOX_LAUNCH_CHECK();
+        cand_select_kernel<<<p.n_seg, 1024, 0, st>>>(cand_keys, cand_idx, p.seg_len, state, part_cnt, p.K, cka, cva);
+        DETBOX_LAUNCH_CHECK();
+    } else {
     refine_kernel<<<rgrid, TK_THREADS, 0, st>>>(keys, p.seg_len, state, 21, 10, 0x7ffu, h1);
-    DETBOX_LAUNCH_CHECK();
-    select_kernel<<<p.n_seg, 1024, 0, st>>>(h1, 2048, 11, state);
-    DETBOX_LAUNCH_CHECK();
-    refine_kernel<<<rgrid, TK_THREADS, 0, st>>>(keys, p.seg_len, state, 10, 0, 0x3ffu, h2);
-    DETBOX_LAUNCH_CHECK();
-    select_kernel<<<p.n_seg, 1024, 0, st>>>(h2, 1024, 10, state);
-    DETBOX_LAUNCH_CHECK();
-    // 3. ordered compaction
-    dim3 cgrid((unsigned)p.nblk_c, (unsigned)p.n_seg);
-    cand_count_kernel<<<cgrid, TK_THREADS, 0, st>>>(keys, p.seg_len, state, blk_lt, blk_eq);
-    DETBOX_LAUNCH_CHECK();
-    cand_scan_kernel<<<p.n_seg, 1024, 0, st>>>(blk_lt, blk_eq, p.nblk_c);
-    DETBOX_LAUNCH_CHECK();
-    cand_write_kernel<<<cgrid, TK_THREADS, 0, st>>>(keys, p.seg_len, state, blk_lt, blk_eq, p.K, cka, cva);
-    DETBOX_LAUNCH_CHECK();
+        DETBOX_LAUNCH_CHECK();
+        select_kernel<<<p.n_seg, 1024, 0, st>>>(h1, 2048, 11, state);
+        DETBOX_LAUNCH_CHECK();
+        refine_kernel<<<rgrid, TK_THREADS, 0, st>>>(keys, p.seg_len, state, 10, 0, 0x3ffu, h2);
+        DETBOX_LAUNCH_CHECK();
+        select_kernel<<<p.n_seg, 1024, 0, st>>>(h2, 1024, 10, state);
+        DETBOX_LAUNCH_CHECK();
+        // 3. ordered compaction
+        dim3 cgrid((unsigned)p.nblk_c, (unsigned)p.n_seg);
+        cand_count_kernel<<<cgrid, TK_THREADS, 0, st>>>(keys, p.seg_len, state, blk_lt, blk_eq);
+        DETBOX_LAUNCH_CHECK();
+        cand_scan_kernel<<<p.n_seg, 1024, 0, st>>>(blk_lt, blk_eq, p.nblk_c);
+        DETBOX_LAUNCH_CHECK();
+        cand_write_kernel<<<cgrid, TK_THREADS, 0, st>>>(keys, p.seg_len, state, blk_lt, blk_eq, p.K, cka, cva);
+        DETBOX_LAUNCH_CHECK();
+    }
     // 4. sort the winners (stable): small segments in shared memory, else by key and then (per-image
     //    mode) by image id with the global radix sort
     int rc = DETBOX_OK;

@@ -19,7 +19,7 @@ def sort_desc(scores):
         return order
     ws = _ws.get(lib().detbox_sort_desc_workspace_bytes(n), s.device)
     check(lib().detbox_sort_desc(s.data_ptr(), n, order.data_ptr(), ws.data_ptr(), ws.numel(), _stream()), "sort_desc")
-    _count(13)
+    _count(1 if n <= 4096 else 13)           # one-block bitonic sort, else keys + 4 x (count, scan, scatter)
     return order
 
 
@@ -57,7 +57,11 @@ def topk_decode(rpn_box, rpn_prob, anchors, top_n, activation="softmax", box_enc
                                    int(per_image), ENC[box_encoding], out["boxes"].data_ptr(), _ptr(out.get("probs")),
                                    _ptr(out.get("img_ids")), _ptr(out.get("anchors")), _ptr(out.get("flat_idx")),
                                    _ptr(out.get("scores")), ws.data_ptr(), ws.numel(), _stream()), "topk_decode")
-    _count(24 + (3 if per_image and B > 1 else 0))
+    # kernels launched (memsets not counted): init, objectness, select, then
+    #   k <= 2048: partition, candidate select, per-segment sort                              -> 7 with the gather
+    #   else     : 2 x (refine, select), count / scan / write, 13-launch radix sort (+3 per image-id pass)
+    k_seg = min(int(top_n), A if per_image else B * A)
+    _count(7 if k_seg <= 2048 else 24 + (3 if per_image and B > 1 else 0))
     return out
 
 
