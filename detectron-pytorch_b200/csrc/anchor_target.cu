@@ -36,8 +36,13 @@ using namespace detbox;
 
 namespace {
 
-constexpr int AT_THREADS = 256;
-constexpr int AT_ITEMS = 4;                         // anchors per thread
+// 288 = 9 warps: a multiple of 6, 9, 12, 18, 36 — the anchors-per-cell counts of the reference's configs
+// (3 scales x 2 ratios, 3 x 3, x2 shifts).  A thread's anchors are AT_THREADS apart, so with the standard
+// cell-major anchor layout they all have the same shape, and the per-shape part of the box encoding
+// (two reciprocals, and the two log terms when the matched GT is the same) is computed once per thread
+// instead of once per anchor (EncMemo; a pure memoisation keyed on the operand bits, so any layout is exact).
+constexpr int AT_THREADS = 288;
+constexpr int AT_ITEMS = 8;                         // anchors per thread
 constexpr int AT_TILE = AT_THREADS * AT_ITEMS;      // anchors per block
 constexpr int AT_WARPS = AT_THREADS / 32;
 constexpr int GCH = 128;                            // GT boxes staged per chunk
@@ -129,20 +134,27 @@ __device__ __forceinline__ void label_of(const TargetParams &p, float gcls, doub
     l_out = l; flag_out = flag;
 }
 
-__device__ __forceinline__ void store_anchor(const TargetParams &p, long o, const float4 anc, const float4 gbox, float l, bool flag)
+__device__ __forceinline__ void store_anchor(const TargetParams &p, long o, const float4 anc, const float4 gbox, float l, bool flag,
+                                             EncMemo &memo)
 {
     p.labels[o] = l;
-    p.targets[o] = encode_box(anc, gbox, p.enc);                            // anchor.py:133-135 every anchor
+    p.targets[o] = p.enc == DETBOX_ENC_FASTRCNN ? encode_fastrcnn_memo(anc, gbox, memo)   // anchor.py:133-135 every anchor
+                                                : encode_linear(anc, gbox, p.enc == DETBOX_ENC_LINEAR);
     p.inside[o] = flag ? p.bbw : make_float4(0, 0, 0, 0);                   // :136-138
 }
 
 template <int PASS>
-__global__ void __launch_bounds__(AT_THREADS, 4)      // <= 64 registers: the streaming path wants occupancy
+__global__ void __launch_bounds__(AT_THREADS, PASS == 1 ? 4 : 3)
 anchor_target_kernel(const TargetParams p)
 {
     __shared__ GtChunk sm;
+    __shared__ float4 s_wbb[AT_ITEMS * AT_WARPS];    // bounding boxes of the tile's warp slices
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const int b = blockIdx.y;
+    // loads that do not depend on the image are issued first, so their latency overlaps the GT's
+    float4 my_wbb = make_float4(0, 0, 0, 0);
+    if (tid < AT_ITEMS * AT_WARPS) my_wbb = (&p.tiles[blockIdx.x].warp[0][0])[tid];
+    const float4 tbox = p.tiles[blockIdx.x].tile;
     const int g0 = p.gt_off[b];
     const int G = p.gt_off[b + 1] - g0;
     const long tile0 = (long)blockIdx.x * AT_TILE;
@@ -168,35 +180,59 @@ anchor_target_kernel(const TargetParams p)
     }
 
     // ---- can any GT of this image touch this tile?  is any column all-zero? ---------------------
-    const float4 tbox = p.tiles[blockIdx.x].tile;
-    int cand_any = 0, zero_any = 0;
-    for (int g = tid; g < G; g += AT_THREADS) {
-        const float *q = p.gt + (size_t)(g0 + g) * 5;
-        cand_any |= may_touch(tbox, q[0], q[1], q[2], q[3]);
-        if (PASS == 2) zero_any |= (p.colmax[g0 + g] == 0ull);   // all-zero column: every anchor ties (anchor.py:46)
+    // Up to GCH GT (always, at CityPersons / COCO counts): the GT rows are read ONCE — staged in shared memory
+    // (float64 copies, areas, column maxima) and tested against the tile's box in the same step.
+    const bool single = G <= GCH;
+    if (tid < AT_ITEMS * AT_WARPS) s_wbb[tid] = my_wbb;
+    int flags = 0;                                   // bit 0: a GT may touch the tile; bit 1: some column is all-zero
+    if (single) {
+        if (tid < G) {
+            const float *q = p.gt + (size_t)(g0 + tid) * 5;
+            const float4 f = make_float4(q[0], q[1], q[2], q[3]);
+            const double x1 = f.x, y1 = f.y, x2 = f.z, y2 = f.w;
+            sm.x1[tid] = x1; sm.y1[tid] = y1; sm.x2[tid] = x2; sm.y2[tid] = y2;
+            sm.area[tid] = (x2 - x1 + 1) * (y2 - y1 + 1);                 // bbox.pyx:34-37
+            sm.cls[tid] = q[4];
+            sm.fbox[tid] = f;
+            const unsigned long long cm = (PASS == 1) ? 0ull : p.colmax[g0 + tid];
+            sm.colmax[tid] = cm;
+            flags = (may_touch(tbox, x1, y1, x2, y2) ? 1 : 0) | ((PASS == 2 && cm == 0ull) ? 2 : 0);   // all-zero column: every anchor ties (anchor.py:46)
+        }
+    } else {
+        for (int g = tid; g < G; g += AT_THREADS) {
+            const float *q = p.gt + (size_t)(g0 + g) * 5;
+            flags |= may_touch(tbox, q[0], q[1], q[2], q[3]) ? 1 : 0;
+            if (PASS == 2 && p.colmax[g0 + g] == 0ull) flags |= 2;
+        }
     }
-    cand_any = __syncthreads_or(cand_any);
+    // (__syncthreads_or is a logical OR of predicates, not a bitwise one: one call per flag; the first also
+    //  publishes the staged GT and slice boxes)
+    const int cand_any = __syncthreads_or(flags & 1);
     if (PASS == 1 && !cand_any) return;
-    if (PASS == 2) zero_any = __syncthreads_or(zero_any);
+    const int zero_any = PASS == 2 ? __syncthreads_or(flags & 2) : 0;
 
     if (PASS == 2 && !cand_any) {
         // streaming path: every row is all-zero -> argmax = GT 0, max overlap 0, no ignore overlap
-        const float *q = p.gt + (size_t)g0 * 5;
-        const float4 gbox = make_float4(q[0], q[1], q[2], q[3]);
-        const float gcls = q[4];
-        float4 anc[AT_ITEMS];
-#pragma unroll
-        for (int i = 0; i < AT_ITEMS; ++i) {
-            const long a = tile0 + i * AT_THREADS + tid;
-            anc[i] = a < p.A ? p.anchors[a] : make_float4(0, 0, 0, 0);
-        }
+        float4 gbox; float gcls;
+        if (single) { gbox = sm.fbox[0]; gcls = sm.cls[0]; }
+        else { const float *q = p.gt + (size_t)g0 * 5; gbox = make_float4(q[0], q[1], q[2], q[3]); gcls = q[4]; }
         float l0; bool f0;
         label_of(p, gcls, 0.0, zero_any != 0, 0.0, l0, f0);     // the same for every anchor of the tile
         int nfg = 0, nbg = 0;
+        EncMemo memo = enc_memo_init();
 #pragma unroll
-        for (int i = 0; i < AT_ITEMS; ++i) {
-            const long a = tile0 + i * AT_THREADS + tid;
-            if (a < p.A) { store_anchor(p, (long)b * p.A + a, anc[i], gbox, l0, f0); nfg += (l0 >= 1.0f); nbg += (l0 == 0.0f); }
+        for (int h = 0; h < AT_ITEMS; h += 4) {                 // 4 independent anchor loads in flight
+            float4 anc[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const long a = tile0 + (h + i) * AT_THREADS + tid;
+                anc[i] = a < p.A ? p.anchors[a] : make_float4(0, 0, 0, 0);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const long a = tile0 + (h + i) * AT_THREADS + tid;
+                if (a < p.A) { store_anchor(p, (long)b * p.A + a, anc[i], gbox, l0, f0, memo); nfg += (l0 >= 1.0f); nbg += (l0 == 0.0f); }
+            }
         }
         nfg = __reduce_add_sync(0xffffffffu, nfg);
         nbg = __reduce_add_sync(0xffffffffu, nbg);
@@ -230,15 +266,30 @@ anchor_target_kernel(const TargetParams p)
         if (tid < gn && sm.colmax[tid] != 0ull) atomicMax(&p.colmax[g0 + c0 + tid], sm.colmax[tid]);
     };
 
-    const bool single = G <= GCH;                    // always, at CityPersons / COCO GT counts
-    if (single) stage(0);
-    const float *q0 = p.gt + (size_t)g0 * 5;
-    const float4 gbox0 = make_float4(q0[0], q0[1], q0[2], q0[3]);
-    const float gcls0 = q0[4];
+    float4 gbox0; float gcls0;
+    if (single) { gbox0 = sm.fbox[0]; gcls0 = sm.cls[0]; }
+    else { const float *q0 = p.gt + (size_t)g0 * 5; gbox0 = make_float4(q0[0], q0[1], q0[2], q0[3]); gcls0 = q0[4]; }
     float l_zero; bool flag_zero;                    // outcome of an anchor that overlaps nothing
     label_of(p, gcls0, 0.0, zero_any != 0, 0.0, l_zero, flag_zero);
-    const float4 *wbb_base = &p.tiles[blockIdx.x].warp[0][w];
+    const float4 *wbb_base = &s_wbb[w];
     int nfg = 0, nbg = 0;
+    EncMemo memo = enc_memo_init();
+    // With at most 32 GT (one lane per GT) the cull of all the warp's slices is done up front — AT_ITEMS
+    // independent bounding-box loads and ballots — instead of one dependent load per slice inside the loop.
+    __shared__ unsigned smask[AT_ITEMS][AT_WARPS];
+    const bool use_masks = G <= 32;
+    if (use_masks) {
+        unsigned any = 0;
+#pragma unroll
+        for (int i = 0; i < AT_ITEMS; ++i) {
+            const float4 wbb = wbb_base[i * AT_WARPS];
+            const unsigned m = __ballot_sync(0xffffffffu, lane < G && may_touch32(wbb, sm.fbox[lane]));
+            if (lane == 0) smask[i][w] = m;
+            any |= m;
+        }
+        __syncwarp();
+        if (PASS == 1 && any == 0u) { flush_colmax(0); return; }      // (flush_colmax has the block's barrier)
+    }
     // One slice at a time keeps the float64 row state (argmax, ignore sum, area) of a single anchor
     // in registers; with more than GCH GT the chunks are re-staged per slice (all warps together).
 #pragma unroll 1
@@ -249,45 +300,53 @@ anchor_target_kernel(const TargetParams p)
         float4 anc = make_float4(INF, INF, -INF, -INF);
         bool have_anc = false;
         if (PASS == 2) { if (valid) anc = p.anchors[a]; have_anc = true; }
-        const float4 wbb = wbb_base[i * AT_WARPS];
         double best = 0.0, isum = 0.0;
         int best_g = 0;
         bool promoted = zero_any != 0;
-        for (int c0 = 0; c0 < G; c0 += GCH) {
-            if (!single) stage(c0);
-            const int gn = min(GCH, G - c0);
-            for (int cb = 0; cb < gn; cb += 32) {    // 32 GT at a time: one lane tests one GT against the slice's box
-                const int jl = cb + lane;
-                unsigned m = __ballot_sync(0xffffffffu, jl < gn && may_touch32(wbb, sm.fbox[jl]));
-                if (m == 0u) continue;               // warp-uniform
-                if (!have_anc) { if (valid) anc = p.anchors[a]; have_anc = true; }
-                const double ax1 = anc.x, ay1 = anc.y, ax2 = anc.z, ay2 = anc.w;
-                const double aarea = (ax2 - ax1 + 1) * (ay2 - ay1 + 1);
-                while (m) {                          // ascending GT index: first max wins (anchor.py:42)
-                    const int j = cb + __ffs(m) - 1;
-                    m &= m - 1;
-                    const double gx1 = sm.x1[j], gy1 = sm.y1[j], gx2 = sm.x2[j], gy2 = sm.y2[j];
-                    double ov = 0.0;
-                    const double iw = fmin(ax2, gx2) - fmax(ax1, gx1) + 1;          // bbox.pyx:39-42
-                    if (iw > 0) {
-                        const double ih = fmin(ay2, gy2) - fmax(ay1, gy1) + 1;      // bbox.pyx:44-47
-                        if (ih > 0) {
-                            const double inter = iw * ih;
-                            const double ua = aarea + sm.area[j] - inter;           // bbox.pyx:49-53
-                            ov = inter / ua;                                        // bbox.pyx:54
-                            if (PASS == 2 && sm.cls[j] < 0.0f)
-                                isum = isum + inter / aarea;                        // anchor.py:81-85 (bbox.pyx:93)
-                        }
-                    }
-                    if (PASS == 1) {
-                        if (ov > 0.0) atomicMax(&sm.colmax[j], iou_bits(ov));
-                    } else if (ov > 0.0) {
-                        if (ov > best) { best = ov; best_g = c0 + j; }
-                        if (valid && iou_bits(ov) == sm.colmax[j]) promoted = true; // anchor.py:46
+        // exact float64 IoU of this lane's anchor against the GT whose bits are set in m (GT index cb + bit)
+        auto eval_hits = [&](unsigned m, int cb, int c0) {
+            if (!have_anc) { if (valid) anc = p.anchors[a]; have_anc = true; }
+            const double ax1 = anc.x, ay1 = anc.y, ax2 = anc.z, ay2 = anc.w;
+            const double aarea = (ax2 - ax1 + 1) * (ay2 - ay1 + 1);
+            while (m) {                          // ascending GT index: first max wins (anchor.py:42)
+                const int j = cb + __ffs(m) - 1;
+                m &= m - 1;
+                const double gx1 = sm.x1[j], gy1 = sm.y1[j], gx2 = sm.x2[j], gy2 = sm.y2[j];
+                double ov = 0.0;
+                const double iw = fmin(ax2, gx2) - fmax(ax1, gx1) + 1;          // bbox.pyx:39-42
+                if (iw > 0) {
+                    const double ih = fmin(ay2, gy2) - fmax(ay1, gy1) + 1;      // bbox.pyx:44-47
+                    if (ih > 0) {
+                        const double inter = iw * ih;
+                        const double ua = aarea + sm.area[j] - inter;           // bbox.pyx:49-53
+                        ov = inter / ua;                                        // bbox.pyx:54
+                        if (PASS == 2 && sm.cls[j] < 0.0f)
+                            isum = isum + inter / aarea;                        // anchor.py:81-85 (bbox.pyx:93)
                     }
                 }
+                if (PASS == 1) {
+                    if (ov > 0.0) atomicMax(&sm.colmax[j], iou_bits(ov));
+                } else if (ov > 0.0) {
+                    if (ov > best) { best = ov; best_g = c0 + j; }
+                    if (valid && iou_bits(ov) == sm.colmax[j]) promoted = true; // anchor.py:46
+                }
             }
-            if (PASS == 1 && !single) flush_colmax(c0);
+        };
+        if (use_masks) {
+            const unsigned m = smask[i][w];
+            if (m) eval_hits(m, 0, 0);
+        } else {
+            const float4 wbb = wbb_base[i * AT_WARPS];
+            for (int c0 = 0; c0 < G; c0 += GCH) {
+                if (!single) stage(c0);
+                const int gn = min(GCH, G - c0);
+                for (int cb = 0; cb < gn; cb += 32) {    // 32 GT at a time: one lane tests one GT against the slice's box
+                    const int jl = cb + lane;
+                    const unsigned m = __ballot_sync(0xffffffffu, jl < gn && may_touch32(wbb, sm.fbox[jl]));
+                    if (m) eval_hits(m, cb, c0);         // warp-uniform
+                }
+                if (PASS == 1 && !single) flush_colmax(c0);
+            }
         }
         if (PASS == 2 && valid) {
             float l = l_zero; bool flag = flag_zero;
@@ -297,7 +356,7 @@ anchor_target_kernel(const TargetParams p)
                 gbox = make_float4(q[0], q[1], q[2], q[3]);
                 label_of(p, q[4], best, promoted, isum, l, flag);
             }
-            store_anchor(p, (long)b * p.A + a, anc, gbox, l, flag);
+            store_anchor(p, (long)b * p.A + a, anc, gbox, l, flag, memo);
             nfg += (l >= 1.0f); nbg += (l == 0.0f);
         }
     }
