@@ -30,18 +30,14 @@
 //
 // Monotonicity makes the culling exact: min/max are exact, and a rounded (x - y + 1) is a
 // monotone function of its operands, so iw(anchor, gt) <= iw(bbox, gt) also after rounding.
+#include <cstdlib>
 #include "box_math.cuh"
 
 using namespace detbox;
 
 namespace {
 
-// 288 = 9 warps: a multiple of 6, 9, 12, 18, 36 — the anchors-per-cell counts of the reference's configs
-// (3 scales x 2 ratios, 3 x 3, x2 shifts).  A thread's anchors are AT_THREADS apart, so with the standard
-// cell-major anchor layout they all have the same shape, and the per-shape part of the box encoding
-// (two reciprocals, and the two log terms when the matched GT is the same) is computed once per thread
-// instead of once per anchor (EncMemo; a pure memoisation keyed on the operand bits, so any layout is exact).
-constexpr int AT_THREADS = 288;
+constexpr int AT_THREADS = 256;
 constexpr int AT_ITEMS = 8;                         // anchors per thread
 constexpr int AT_TILE = AT_THREADS * AT_ITEMS;      // anchors per block
 constexpr int AT_WARPS = AT_THREADS / 32;
@@ -134,17 +130,15 @@ __device__ __forceinline__ void label_of(const TargetParams &p, float gcls, doub
     l_out = l; flag_out = flag;
 }
 
-__device__ __forceinline__ void store_anchor(const TargetParams &p, long o, const float4 anc, const float4 gbox, float l, bool flag,
-                                             EncMemo &memo)
+__device__ __forceinline__ void store_anchor(const TargetParams &p, long o, const float4 anc, const float4 gbox, float l, bool flag)
 {
     p.labels[o] = l;
-    p.targets[o] = p.enc == DETBOX_ENC_FASTRCNN ? encode_fastrcnn_memo(anc, gbox, memo)   // anchor.py:133-135 every anchor
-                                                : encode_linear(anc, gbox, p.enc == DETBOX_ENC_LINEAR);
+    p.targets[o] = encode_box(anc, gbox, p.enc);                            // anchor.py:133-135 every anchor
     p.inside[o] = flag ? p.bbw : make_float4(0, 0, 0, 0);                   // :136-138
 }
 
-template <int PASS>
-__global__ void __launch_bounds__(AT_THREADS, PASS == 1 ? 4 : 3)
+template <int PASS, int EMIT_ILP>       // EMIT_ILP: anchors encoded side by side in the emit loops
+__global__ void __launch_bounds__(AT_THREADS, 4)
 anchor_target_kernel(const TargetParams p)
 {
     __shared__ GtChunk sm;
@@ -219,19 +213,18 @@ anchor_target_kernel(const TargetParams p)
         float l0; bool f0;
         label_of(p, gcls, 0.0, zero_any != 0, 0.0, l0, f0);     // the same for every anchor of the tile
         int nfg = 0, nbg = 0;
-        EncMemo memo = enc_memo_init();
+#pragma unroll 1
+        for (int h = 0; h < AT_ITEMS; h += EMIT_ILP) {          // EMIT_ILP independent load -> encode -> store chains
+            float4 anc[EMIT_ILP];
 #pragma unroll
-        for (int h = 0; h < AT_ITEMS; h += 4) {                 // 4 independent anchor loads in flight
-            float4 anc[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
+            for (int i = 0; i < EMIT_ILP; ++i) {
                 const long a = tile0 + (h + i) * AT_THREADS + tid;
                 anc[i] = a < p.A ? p.anchors[a] : make_float4(0, 0, 0, 0);
             }
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
+            for (int i = 0; i < EMIT_ILP; ++i) {
                 const long a = tile0 + (h + i) * AT_THREADS + tid;
-                if (a < p.A) { store_anchor(p, (long)b * p.A + a, anc[i], gbox, l0, f0, memo); nfg += (l0 >= 1.0f); nbg += (l0 == 0.0f); }
+                if (a < p.A) { store_anchor(p, (long)b * p.A + a, anc[i], gbox, l0, f0); nfg += (l0 >= 1.0f); nbg += (l0 == 0.0f); }
             }
         }
         nfg = __reduce_add_sync(0xffffffffu, nfg);
@@ -273,7 +266,8 @@ anchor_target_kernel(const TargetParams p)
     label_of(p, gcls0, 0.0, zero_any != 0, 0.0, l_zero, flag_zero);
     const float4 *wbb_base = &s_wbb[w];
     int nfg = 0, nbg = 0;
-    EncMemo memo = enc_memo_init();
+    // pass 2, decide phase -> emit phase: (label, GT row | regression flag << 31) of every anchor of the tile
+    __shared__ int2 s_res[PASS == 2 ? AT_ITEMS : 1][AT_THREADS];
     // With at most 32 GT (one lane per GT) the cull of all the warp's slices is done up front — AT_ITEMS
     // independent bounding-box loads and ballots — instead of one dependent load per slice inside the loop.
     __shared__ unsigned smask[AT_ITEMS][AT_WARPS];
@@ -290,16 +284,15 @@ anchor_target_kernel(const TargetParams p)
         __syncwarp();
         if (PASS == 1 && any == 0u) { flush_colmax(0); return; }      // (flush_colmax has the block's barrier)
     }
-    // One slice at a time keeps the float64 row state (argmax, ignore sum, area) of a single anchor
-    // in registers; with more than GCH GT the chunks are re-staged per slice (all warps together).
+    // Decide phase.  One slice at a time keeps the float64 row state (argmax, ignore sum, area) of a single
+    // anchor in registers; only slices some GT may touch load their anchors here.  With more than GCH GT the
+    // chunks are re-staged per slice (all warps together).
 #pragma unroll 1
     for (int i = 0; i < AT_ITEMS; ++i) {
         const long a = tile0 + i * AT_THREADS + tid;
         const bool valid = a < p.A;
-        // pass 2 needs every anchor (targets are written for all of them); pass 1 only those of slices a GT may touch
         float4 anc = make_float4(INF, INF, -INF, -INF);
         bool have_anc = false;
-        if (PASS == 2) { if (valid) anc = p.anchors[a]; have_anc = true; }
         double best = 0.0, isum = 0.0;
         int best_g = 0;
         bool promoted = zero_any != 0;
@@ -348,21 +341,41 @@ anchor_target_kernel(const TargetParams p)
                 if (PASS == 1 && !single) flush_colmax(c0);
             }
         }
-        if (PASS == 2 && valid) {
+        if (PASS == 2) {
             float l = l_zero; bool flag = flag_zero;
-            float4 gbox = gbox0;
+            int g = 0;
             if (best > 0.0) {                        // (promotion and ignore overlap both imply best > 0)
-                const float *q = p.gt + (size_t)(g0 + best_g) * 5;
-                gbox = make_float4(q[0], q[1], q[2], q[3]);
-                label_of(p, q[4], best, promoted, isum, l, flag);
+                g = best_g;
+                label_of(p, p.gt[(size_t)(g0 + g) * 5 + 4], best, promoted, isum, l, flag);
             }
-            store_anchor(p, (long)b * p.A + a, anc, gbox, l, flag, memo);
-            nfg += (l >= 1.0f); nbg += (l == 0.0f);
+            s_res[i][tid] = make_int2(__float_as_int(l), g | (flag ? (int)0x80000000 : 0));
+            if (valid) { nfg += (l >= 1.0f); nbg += (l == 0.0f); }
         }
     }
     if (PASS == 1) {
         if (single) flush_colmax(0);
         return;
+    }
+    // Emit phase: a plain streaming loop over the tile — anchor in, 36 bytes out — with EMIT_ILP independent
+    // encode chains per thread (the encode is a long dependent sequence: reciprocal, log, divisions).
+    // Every thread reads back only what it wrote itself, so no barrier is needed in between.
+#pragma unroll 1
+    for (int h = 0; h < AT_ITEMS; h += EMIT_ILP) {
+        float4 anc[EMIT_ILP], gbox[EMIT_ILP]; int2 r[EMIT_ILP];
+#pragma unroll
+        for (int i = 0; i < EMIT_ILP; ++i) {
+            const long a = tile0 + (h + i) * AT_THREADS + tid;
+            anc[i] = a < p.A ? p.anchors[a] : make_float4(0, 0, 0, 0);
+            r[i] = s_res[h + i][tid];
+            const int g = r[i].y & 0x7fffffff;
+            if (single) gbox[i] = sm.fbox[g];
+            else { const float *q = p.gt + (size_t)(g0 + g) * 5; gbox[i] = make_float4(q[0], q[1], q[2], q[3]); }
+        }
+#pragma unroll
+        for (int i = 0; i < EMIT_ILP; ++i) {
+            const long a = tile0 + (h + i) * AT_THREADS + tid;
+            if (a < p.A) store_anchor(p, (long)b * p.A + a, anc[i], gbox[i], __int_as_float(r[i].x), r[i].y < 0);
+        }
     }
     nfg = __reduce_add_sync(0xffffffffu, nfg);
     nbg = __reduce_add_sync(0xffffffffu, nbg);
@@ -445,12 +458,15 @@ extern "C" int detbox_anchor_target(const float *anchors, long A, const float *g
         anchor_bbox_kernel<<<n_tiles, AT_THREADS, 0, st>>>((const float4 *)anchors, A, tiles);
         DETBOX_LAUNCH_CHECK();
         DETBOX_TRACE_BEGIN(DETBOX_K_TARGET_COLMAX, st);
-        anchor_target_kernel<1><<<grid, AT_THREADS, 0, st>>>(p);
+        anchor_target_kernel<1, 1><<<grid, AT_THREADS, 0, st>>>(p);
         DETBOX_TRACE_END(DETBOX_K_TARGET_COLMAX, st);
         DETBOX_LAUNCH_CHECK();
     }
     DETBOX_TRACE_BEGIN(DETBOX_K_TARGET_ASSIGN, st);
-    anchor_target_kernel<2><<<grid, AT_THREADS, 0, st>>>(p);
+    static const int ilp = []() { const char *e = getenv("DETBOX_AT_ILP"); return e ? atoi(e) : 1; }();   // measured: 1 and 2 tie, 4 spills
+    if (ilp == 2) anchor_target_kernel<2, 2><<<grid, AT_THREADS, 0, st>>>(p);
+    else if (ilp == 4) anchor_target_kernel<2, 4><<<grid, AT_THREADS, 0, st>>>(p);
+    else anchor_target_kernel<2, 1><<<grid, AT_THREADS, 0, st>>>(p);
     DETBOX_TRACE_END(DETBOX_K_TARGET_ASSIGN, st);
     DETBOX_LAUNCH_CHECK();
     long wb = (A / 4 + 255) / 256;
