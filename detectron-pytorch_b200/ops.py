@@ -181,19 +181,26 @@ def make_target_cfg(bg, fg, clobber=True, ignore_fraction=0.3, bbweights=(1., 1.
     return c
 
 
-def anchor_target(anchors, gt, gt_offsets, tcfg, return_counts=False):
+def anchor_target(anchors, gt, gt_offsets, tcfg, return_counts=False, out=None):
     """Batched libs/layers/anchor.py:17-145.  anchors [A,4]; gt [sumG,5] (images concatenated);
     gt_offsets int32 [B+1] (CUDA).  Returns labels [B,A], label_weights [B,A], bbox_targets [B,A,4],
-    bbox_inside_weights [B,A,4] (+ counts int32 [B,2] = (#fg, #bg))."""
+    bbox_inside_weights [B,A,4] (+ counts int32 [B,2] = (#fg, #bg)).  `out`: the four tensors to write
+    into (contiguous float32 CUDA tensors of those shapes) instead of fresh allocations."""
     a = _dev(anchors).view(-1, 4)
     g = _dev(gt).view(-1, 5)
     off = _dev(gt_offsets, torch.int32, "gt_offsets")
     B, A, G = off.numel() - 1, a.shape[0], g.shape[0]
     dev = a.device
-    labels = torch.empty((B, A), dtype=torch.float32, device=dev)
-    lw = torch.empty((B, A), dtype=torch.float32, device=dev)
-    bt = torch.empty((B, A, 4), dtype=torch.float32, device=dev)
-    bw = torch.empty((B, A, 4), dtype=torch.float32, device=dev)
+    if out is not None:
+        labels, lw, bt, bw = out
+        for t, shape in ((labels, (B, A)), (lw, (B, A)), (bt, (B, A, 4)), (bw, (B, A, 4))):
+            if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and tuple(t.shape) == shape):
+                raise _lib.DetboxError("anchor_target(out=...): expected contiguous float32 CUDA tensors of shape %s" % (shape,))
+    else:
+        labels = torch.empty((B, A), dtype=torch.float32, device=dev)
+        lw = torch.empty((B, A), dtype=torch.float32, device=dev)
+        bt = torch.empty((B, A, 4), dtype=torch.float32, device=dev)
+        bw = torch.empty((B, A, 4), dtype=torch.float32, device=dev)
     counts = torch.empty((B, 2), dtype=torch.int32, device=dev) if return_counts else None
     nbytes = lib().detbox_anchor_target_workspace_bytes(A, B, G)
     ws = _ws.get(nbytes, dev)

@@ -90,14 +90,25 @@ class BoxOpsSession:
             self.h_off[i + 1] = off
         return off
 
-    def run_host(self, gt_boxes_list, rpn_prob_host, rpn_box_host, chunk=8):
+    def run_host(self, gt_boxes_list, rpn_prob_host, rpn_box_host, chunk=8, targets="host"):
         """gt_boxes_list: B NumPy arrays [G_i,5]; rpn_prob_host [B*A,C] / rpn_box_host [B*A,4]:
         float32 host tensors (pinned for asynchronous copies).  Returns pinned host tensors; the
         call returns after all streams have drained, so they are ready to read.
 
         The batch is cut into chunks of `chunk` images that flow through three streams — copy-in,
         kernels, copy-out — so the PCIe link runs in both directions while the kernels of the
-        neighbouring chunk execute (images are independent: no result changes)."""
+        neighbouring chunk execute (images are independent: no result changes).
+
+        targets="device": the four anchor-target tensors stay in HBM ([B,A] / [B,A,4] CUDA tensors in the result)
+        for a loss that runs on the GPU — the training integration of INTEGRATION.md §2, where the reference
+        itself copies its CPU-computed targets TO the device — and only the detections travel back."""
+        if targets not in ("host", "device"):
+            raise DetboxError("targets must be 'host' or 'device'")
+        on_dev = targets == "device"
+        if on_dev and getattr(self, "d_labels", None) is None:
+            dv = lambda shape: torch.empty(shape, dtype=torch.float32, device=self.dev)
+            self.d_labels, self.d_lw = dv((self.B, self.A)), dv((self.B, self.A))
+            self.d_bt, self.d_bw = dv((self.B, self.A, 4)), dv((self.B, self.A, 4))
         B, A, C = self.B, self.A, self.C
         G = self.stage_gt(gt_boxes_list)
         s_in, s_k, s_out = self._streams
@@ -139,7 +150,8 @@ class BoxOpsSession:
             ev_k = torch.cuda.Event()
             with torch.cuda.stream(s_k):
                 s_k.wait_event(ev_in)
-                labels, lw, bt, bw = ops.anchor_target(self.anchors, self.d_gt[:G], self.d_off[c0:c0 + n + 1], self.tcfg)
+                out = (self.d_labels[c0:c0 + n], self.d_lw[c0:c0 + n], self.d_bt[c0:c0 + n], self.d_bw[c0:c0 + n]) if on_dev else None
+                labels, lw, bt, bw = ops.anchor_target(self.anchors, self.d_gt[:G], self.d_off[c0:c0 + n + 1], self.tcfg, out=out)
                 sel = ops_post.topk_decode(self.d_box[r0:r1], self.d_prob[r0:r1], self.anchors, self.top_n, self.activation,
                                            "fastrcnn", per_image=True, want=("img_ids", "scores"))
                 keep, n_keep = ops_post.nms(sel["boxes"], sel["scores"], self.nms_thresh, self.nms_cmp,
@@ -147,9 +159,11 @@ class BoxOpsSession:
                 ev_k.record(s_k)
                 mark("krn%d" % c0, s_k)
             k0, k1 = c0 * kper, (c0 + n) * kper
-            pairs = [(self.h_labels[c0:c0 + n], labels), (self.h_lw[c0:c0 + n], lw), (self.h_bt[c0:c0 + n], bt),
-                     (self.h_bw[c0:c0 + n], bw), (self.h_boxes[k0:k1], sel["boxes"]), (self.h_scores[k0:k1], sel["scores"]),
+            pairs = [(self.h_boxes[k0:k1], sel["boxes"]), (self.h_scores[k0:k1], sel["scores"]),
                      (self.h_img[k0:k1], sel["img_ids"]), (self.h_keep[k0:k1], keep), (h_nk[ci, :n + 1], n_keep)]
+            if not on_dev:
+                pairs = [(self.h_labels[c0:c0 + n], labels), (self.h_lw[c0:c0 + n], lw), (self.h_bt[c0:c0 + n], bt),
+                         (self.h_bw[c0:c0 + n], bw)] + pairs
             with torch.cuda.stream(s_out):
                 s_out.wait_event(ev_k)
                 for h, d in pairs:
@@ -176,8 +190,9 @@ class BoxOpsSession:
         self.h_nkeep.numpy()[:] = nk_all
         self.h2d_bytes = G * 20 + self.h_off.numel() * 4 + self.d_prob.numel() * 4 + self.d_box.numel() * 4
         self.d2h_bytes = d2h
-        return {"labels": self.h_labels, "label_weights": self.h_lw, "bbox_targets": self.h_bt,
-                "bbox_inside_weights": self.h_bw, "boxes": self.h_boxes, "scores": self.h_scores,
+        tg = (self.d_labels, self.d_lw, self.d_bt, self.d_bw) if on_dev else (self.h_labels, self.h_lw, self.h_bt, self.h_bw)
+        return {"labels": tg[0], "label_weights": tg[1], "bbox_targets": tg[2],
+                "bbox_inside_weights": tg[3], "boxes": self.h_boxes, "scores": self.h_scores,
                 "img_ids": self.h_img, "keep": self._keep_out, "n_keep": self.h_nkeep}
 
     def detections(self, host_out):

@@ -62,3 +62,21 @@ def test_run_host_matches_oracle(B, chunk):
         pos += nk[b]
     dets = sess.detections(out)
     assert len(dets) == B and all(d.shape[1] == 5 for d in dets)
+
+
+def test_run_host_targets_on_device():
+    """targets="device": the same numbers as the host-buffer mode, the four target tensors left in HBM."""
+    pipeline = import_module("detectron-pytorch_b200.pipeline")
+    B, ih, iw, top_n = 5, 256, 512, 200
+    cfg, strides, scales, anc, gts, deltas, prob = make_case(B, ih, iw, 3)
+    sess = pipeline.BoxOpsSession(strides, ih, iw, scales, cfg.anchor_ratios, cfg.anchor_base, B, 2, top_n=top_n,
+                                  nms_thresh=0.5, bg=cfg.rpn_bg_threshold, fg=cfg.rpn_fg_threshold, max_gt_total=16 * B)
+    h_prob, h_box = torch.from_numpy(prob).pin_memory(), torch.from_numpy(deltas).pin_memory()
+    host = {k: v.clone() for k, v in sess.run_host(gts, h_prob, h_box, chunk=2).items()}
+    d2h_host = sess.d2h_bytes
+    dev = sess.run_host(gts, h_prob, h_box, chunk=2, targets="device")
+    assert sess.d2h_bytes < d2h_host // 10
+    for k in ("labels", "label_weights", "bbox_targets", "bbox_inside_weights"):
+        assert dev[k].is_cuda and torch.equal(dev[k].cpu(), host[k])
+    for k in ("boxes", "scores", "img_ids", "keep", "n_keep"):
+        assert not dev[k].is_cuda and torch.equal(dev[k], host[k])
