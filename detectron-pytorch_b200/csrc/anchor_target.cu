@@ -399,14 +399,20 @@ label_weight_kernel(const float *__restrict__ labels, long A, const int32_t *__r
     const float *l = labels + (size_t)b * A;
     float *w = weights + (size_t)b * A;
     const long A4 = ((A & 3) == 0 && ((size_t)b * A & 3) == 0) ? A / 4 : 0;
-    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < A4; i += (long)gridDim.x * blockDim.x) {
+    auto wt = [&](float v) { return v >= 1.0f ? 1.0f : (v == 0.0f ? wbg : 0.0f); };
+    const long stride = (long)gridDim.x * blockDim.x;
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i + 3 * stride < A4; i += 4 * stride) {              // four independent 16-byte loads in flight per thread
+        float4 v[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) v[k] = __ldcs(reinterpret_cast<const float4 *>(l) + i + k * stride);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            __stcs(reinterpret_cast<float4 *>(w) + i + k * stride, make_float4(wt(v[k].x), wt(v[k].y), wt(v[k].z), wt(v[k].w)));
+    }
+    for (; i < A4; i += stride) {
         const float4 v = reinterpret_cast<const float4 *>(l)[i];
-        float4 o;
-        o.x = v.x >= 1.0f ? 1.0f : (v.x == 0.0f ? wbg : 0.0f);
-        o.y = v.y >= 1.0f ? 1.0f : (v.y == 0.0f ? wbg : 0.0f);
-        o.z = v.z >= 1.0f ? 1.0f : (v.z == 0.0f ? wbg : 0.0f);
-        o.w = v.w >= 1.0f ? 1.0f : (v.w == 0.0f ? wbg : 0.0f);
-        reinterpret_cast<float4 *>(w)[i] = o;
+        reinterpret_cast<float4 *>(w)[i] = make_float4(wt(v.x), wt(v.y), wt(v.z), wt(v.w));
     }
     for (long i = A4 * 4 + (long)blockIdx.x * blockDim.x + threadIdx.x; i < A; i += (long)gridDim.x * blockDim.x) {
         const float v = l[i];
@@ -471,7 +477,8 @@ extern "C" int detbox_anchor_target(const float *anchors, long A, const float *g
     DETBOX_LAUNCH_CHECK();
     long wb = (A / 4 + 255) / 256;
     if (wb < 1) wb = 1;
-    if (wb > 4 * kNumSMs) wb = 4 * kNumSMs;
+    wb = (wb + 3) / 4;                       // 4 float4 per thread per trip
+    if (wb < 1) wb = 1;
     DETBOX_TRACE_BEGIN(DETBOX_K_TARGET_WEIGHTS, st);
     label_weight_kernel<<<dim3((unsigned)wb, (unsigned)batch), 256, 0, st>>>(labels, A, counts, label_weights, counts_out);
     DETBOX_TRACE_END(DETBOX_K_TARGET_WEIGHTS, st);
