@@ -256,8 +256,11 @@ cand_write_kernel(const uint32_t *__restrict__ keys, long seg_len, const SegStat
 // the 53-bit composite (low 21 key bits, flat index) — unique values, so the tie rule "lower flat index
 // first" is part of the order.  This replaces two refine passes and the count / scan / write compaction
 // (four reads of the key array) by one.
-constexpr int PT_ITEMS = 4;
+constexpr int PT_ITEMS = 8;            // keys per thread and trip (grid sizing)
 
+// VEC: 16-byte key loads (segment start and length multiples of 4).  Nearly all keys are neither winners nor
+// candidates, so a warp first asks with ONE ballot whether any of its 128 keys is; only then the per-key code runs.
+template <bool VEC>
 __global__ void __launch_bounds__(TK_THREADS)
 partition_kernel(const uint32_t *__restrict__ keys, long seg_len, const SegState *__restrict__ state, long K,
                  uint32_t *__restrict__ ckeys, uint32_t *__restrict__ cvals,
@@ -265,42 +268,57 @@ partition_kernel(const uint32_t *__restrict__ keys, long seg_len, const SegState
 {
     const int tid = threadIdx.x, lane = tid & 31;
     const uint32_t b0 = state[blockIdx.y].prefix;
+    const uint32_t limit = ((b0 + 1u) << 21) - 1u;      // key <= limit  <=>  bin <= b0  (b0 <= 2047: no overflow past 2^32 - 1)
     const long seg0 = (long)blockIdx.y * seg_len;
     const uint32_t *k = keys + seg0;
     uint32_t *win_cnt = cnt + 2 * blockIdx.y, *cand_cnt = win_cnt + 1;
     const uint32_t below = (1u << lane) - 1u;
-    for (long r0 = (long)blockIdx.x * TK_THREADS * PT_ITEMS; r0 < seg_len; r0 += (long)gridDim.x * TK_THREADS * PT_ITEMS) {
-        uint32_t v[PT_ITEMS];
-#pragma unroll
-        for (int j = 0; j < PT_ITEMS; ++j) {
-            const long r = r0 + j * TK_THREADS + tid;
-            v[j] = r < seg_len ? k[r] : 0xffffffffu;
+    auto emit = [&](uint32_t key, long r, bool ok) {    // warp-collective: every lane calls it
+        const uint32_t bin = key >> 21;
+        const bool better = ok && bin < b0, cand = ok && bin == b0;
+        const unsigned mb = __ballot_sync(0xffffffffu, better), mc = __ballot_sync(0xffffffffu, cand);
+        if (mb) {
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(win_cnt, (uint32_t)__popc(mb));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (better) {
+                const size_t pos = (size_t)blockIdx.y * K + base + __popc(mb & below);
+                ckeys[pos] = key; cvals[pos] = (uint32_t)(seg0 + r);
+            }
         }
+        if (mc) {
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(cand_cnt, (uint32_t)__popc(mc));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (cand) {
+                const size_t pos = (size_t)seg0 + base + __popc(mc & below);
+                cand_keys[pos] = key; cand_idx[pos] = (uint32_t)(seg0 + r);
+            }
+        }
+    };
+    if (VEC) {
+        const long n4 = seg_len >> 2;
+        const uint4 *k4 = reinterpret_cast<const uint4 *>(k);
+        for (long q0 = (long)blockIdx.x * TK_THREADS * 2; q0 < n4; q0 += (long)gridDim.x * TK_THREADS * 2) {
+            uint4 v[2]; bool ok[2];
 #pragma unroll
-        for (int j = 0; j < PT_ITEMS; ++j) {
-            const long r = r0 + j * TK_THREADS + tid;
-            const bool ok = r < seg_len;
-            const uint32_t bin = v[j] >> 21;
-            const bool better = ok && bin < b0, cand = ok && bin == b0;
-            const unsigned mb = __ballot_sync(0xffffffffu, better), mc = __ballot_sync(0xffffffffu, cand);
-            if (mb) {
-                uint32_t base = 0;
-                if (lane == 0) base = atomicAdd(win_cnt, (uint32_t)__popc(mb));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (better) {
-                    const size_t pos = (size_t)blockIdx.y * K + base + __popc(mb & below);
-                    ckeys[pos] = v[j]; cvals[pos] = (uint32_t)(seg0 + r);
-                }
+            for (int j = 0; j < 2; ++j) {
+                const long q = q0 + j * TK_THREADS + tid;
+                ok[j] = q < n4;
+                v[j] = ok[j] ? __ldcs(k4 + q) : make_uint4(~0u, ~0u, ~0u, ~0u);
             }
-            if (mc) {
-                uint32_t base = 0;
-                if (lane == 0) base = atomicAdd(cand_cnt, (uint32_t)__popc(mc));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (cand) {
-                    const size_t pos = (size_t)seg0 + base + __popc(mc & below);
-                    cand_keys[pos] = v[j]; cand_idx[pos] = (uint32_t)(seg0 + r);
-                }
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const uint32_t lo = min(min(v[j].x, v[j].y), min(v[j].z, v[j].w));
+                if (!__any_sync(0xffffffffu, ok[j] && lo <= limit)) continue;
+                const long r = (q0 + j * TK_THREADS + tid) << 2;
+                emit(v[j].x, r, ok[j]); emit(v[j].y, r + 1, ok[j]); emit(v[j].z, r + 2, ok[j]); emit(v[j].w, r + 3, ok[j]);
             }
+        }
+    } else {
+        for (long r0 = (long)blockIdx.x * TK_THREADS; r0 < seg_len; r0 += (long)gridDim.x * TK_THREADS) {
+            const long r = r0 + tid;
+            emit(r < seg_len ? k[r] : 0xffffffffu, r, r < seg_len);
         }
     }
 }
@@ -530,8 +548,9 @@ extern "C" int detbox_topk_decode(const float *prob, int C, const float *deltas,
         // 3'. one pass: outright winners + candidates of the threshold bin; then select among the candidates
         long px = (p.seg_len + TK_THREADS * PT_ITEMS - 1) / (TK_THREADS * PT_ITEMS);
         { long capx = (long)kNumSMs * 8 / p.n_seg; if (capx < 1) capx = 1; if (px > capx) px = capx; }
-        partition_kernel<<<dim3((unsigned)px, (unsigned)p.n_seg), TK_THREADS, 0, st>>>(keys, p.seg_len, state, p.K, cka, cva,
-                                                                                     cand_keys, cand_idx, part_cnt);
+        const dim3 pgrid((unsigned)px, (unsigned)p.n_seg);
+        if ((p.seg_len & 3) == 0) partition_kernel<true><<<pgrid, TK_THREADS, 0, st>>>(keys, p.seg_len, state, p.K, cka, cva, cand_keys, cand_idx, part_cnt);
+        else partition_kernel<false><<<pgrid, TK_THREADS, 0, st>>>(keys, p.seg_len, state, p.K, cka, cva, cand_keys, cand_idx, part_cnt);
         DETBOX_LAUNCH_CHECK();
         cand_select_kernel<<<p.n_seg, 1024, 0, st>>>(cand_keys, cand_idx, p.seg_len, state, part_cnt, p.K, cka, cva);
         DETBOX_LAUNCH_CHECK();
