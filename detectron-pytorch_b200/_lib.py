@@ -81,6 +81,9 @@ SIGNATURES = {
                                       c_void, c_void, c_void, c_void, c_void, c_void, c_void]),
     "detbox_sample_gather": (c_int, [c_void, c_void, c_void, c_void, c_void, c_void, c_int, c_void, c_int,
                                      c_void, c_void, c_void, c_void]),
+    "detbox_threshold_segments": (c_int, [c_void, c_void, c_long, c_int, c_float, c_void, c_void, c_void]),
+    "detbox_to_dets": (c_int, [c_void, c_void, c_int, c_void, c_void, c_void, c_long, c_int, c_int, c_int, c_float,
+                               c_void, c_long, c_void, c_void]),
     "_nms": (None, [c_void, c_void, c_void, c_int, c_int, c_float, c_int]),
     "detbox_nms_host": (c_int, [c_void, c_int, c_double, c_int, c_void, c_void, c_int]),
     "detbox_anchor_target_host": (c_int, [c_void, c_long, c_void, c_int, ctypes.POINTER(TargetCfg),

@@ -1,0 +1,183 @@
+// dets.cu — the device-side epilogue of stage one.
+// Replaces: the NumPy `to_Dets*` conversions of libs/nets/model.py:357-469 (D2H of boxes / probs / ids, a Python
+//           loop over images, np.where + np.concatenate per image) and the score thresholding of
+//           _decoding_and_thresholding_stage1 (model.py:323-340: nonzero() + a host-side fallback).
+// Both are ordered expansions of a few thousand rows, so each is one single-block kernel: every step is a block
+// scan, nothing is read back, and the NMS in between keeps its own sync-free pipeline.
+#include "common.cuh"
+
+using namespace detbox;
+
+namespace {
+
+constexpr int DT_THREADS = 1024;
+constexpr int DT_MAX_IMAGES = 2048;
+
+__device__ __forceinline__ int block_excl_scan_i(int v, int *warp_sum, int &total)
+{
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    int incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    __syncthreads();
+    if (lane == 31) warp_sum[w] = incl;
+    __syncthreads();
+    if (w == 0) {
+        const int s = warp_sum[lane]; int is = s;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, is, o); if (lane >= o) is += t; }
+        warp_sum[lane] = is - s;
+        if (lane == 31) warp_sum[32] = is;
+    }
+    __syncthreads();
+    total = warp_sum[32];
+    return warp_sum[w] + incl - v;
+}
+
+// ---- model.py:326-333: objectness >= threshold, or the single best row when nothing passes ---------------
+// Rows failing the test are not removed (that would need their count on the host): they are moved to a
+// dummy segment `n_images`, so the segmented NMS keeps them apart and the epilogue drops them.
+__global__ void __launch_bounds__(DT_THREADS)
+threshold_segments_kernel(const float *__restrict__ scores, const int64_t *__restrict__ img_ids, long n, int n_images,
+                          float thr, int32_t *__restrict__ seg32, int64_t *__restrict__ seg64)
+{
+    __shared__ unsigned long long best;      // (ordered score << 32) | ~index : max = best score, lowest index
+    __shared__ int any_pass;
+    const int tid = threadIdx.x;
+    if (tid == 0) { best = 0ull; any_pass = 0; }
+    __syncthreads();
+    unsigned long long mine = 0ull; int pass = 0;
+    for (long i = tid; i < n; i += DT_THREADS) {
+        const float s = scores[i];
+        pass |= s >= thr;
+        const unsigned long long c = ((unsigned long long)float_to_ordered(s) << 32) | (unsigned)(~(unsigned)i);
+        mine = c > mine ? c : mine;
+    }
+    if (__any_sync(0xffffffffu, pass) && (tid & 31) == 0) any_pass = 1;
+    if (n > 0) atomicMax(&best, mine);
+    __syncthreads();
+    const bool none = any_pass == 0;
+    const long best_i = (long)(unsigned)(~(unsigned)best);
+    for (long i = tid; i < n; i += DT_THREADS) {
+        const bool valid = none ? (i == best_i) : (scores[i] >= thr);
+        const int64_t im = img_ids[i];
+        const int64_t s = (valid && im >= 0 && im < n_images) ? im : (int64_t)n_images;
+        seg32[i] = (int32_t)s; seg64[i] = s;
+    }
+}
+
+// ---- to_Dets / to_Dets_sigmoid / to_Dets2 / to_Dets2_sigmoid ------------------------------------------------
+// Row r of the input is row keep[r] (or r) of boxes / probs; rows must be image-major.  first = index of the
+// first foreground column (1 softmax, 0 sigmoid), class id = column - first + 1.
+struct DetsArgs {
+    const float4 *boxes; const float *probs; int C; const int64_t *img_ids; const int64_t *keep;
+    const int32_t *m_dev; long m_max; int n_images; int first; int multi; float thr;
+    double *dets; long cap; int32_t *offsets;
+};
+
+__global__ void __launch_bounds__(DT_THREADS)
+to_dets_kernel(const DetsArgs a)
+{
+    __shared__ int tot[DT_MAX_IMAGES + 1];     // (row, class) pairs above the threshold, then rows emitted, per image
+    __shared__ int fin[DT_MAX_IMAGES + 1];
+    __shared__ int warp_sum[33];
+    const int tid = threadIdx.x;
+    long m = a.m_dev ? (long)*a.m_dev : a.m_max;
+    if (m > a.m_max) m = a.m_max;
+    const int nfg = a.C - a.first;              // foreground columns
+    const bool single = nfg <= 1;               // two-class softmax / one-logit sigmoid: one detection per row, no threshold
+    for (int i = tid; i <= a.n_images; i += DT_THREADS) { tot[i] = 0; fin[i] = 0; }
+    __syncthreads();
+    auto row_of = [&](long r) { return a.keep ? (long)a.keep[r] : r; };
+    auto count_above = [&](const float *p) { int c = 0; for (int k = a.first; k < a.C; ++k) c += p[k] > a.thr; return c; };
+    if (a.multi && !single) {
+        for (long r = tid; r < m; r += DT_THREADS) {
+            const long src = row_of(r);
+            const int64_t im = a.img_ids[src];
+            if (im < 0 || im >= a.n_images) continue;
+            const int c = count_above(a.probs + (size_t)src * a.C);
+            if (c) atomicAdd(&tot[(int)im], c);
+        }
+        __syncthreads();
+    }
+    int running = 0;
+    for (long r0 = 0; r0 < m; r0 += DT_THREADS) {
+        const long r = r0 + tid;
+        int c = 0; long src = 0; int im = -1; bool fallback = false;
+        if (r < m) {
+            src = row_of(r);
+            const int64_t i64 = a.img_ids[src];
+            if (i64 >= 0 && i64 < a.n_images) {
+                im = (int)i64;
+                if (single || !a.multi) c = 1;
+                else if (tot[im] == 0) { c = 1; fallback = true; }               // model.py:428-434: argmax for every row
+                else c = count_above(a.probs + (size_t)src * a.C);
+            }
+        }
+        int total;
+        long pos = running + block_excl_scan_i(c, warp_sum, total);
+        running += total;
+        if (c) {
+            atomicAdd(&fin[im], c);
+            const float4 b = a.boxes[src];
+            const float *p = a.probs + (size_t)src * a.C;
+            auto put = [&](float prob, int cls) {
+                if (pos < a.cap) {
+                    double *d = a.dets + (size_t)pos * 6;
+                    d[0] = b.x; d[1] = b.y; d[2] = b.z; d[3] = b.w; d[4] = prob; d[5] = cls;
+                }
+                ++pos;
+            };
+            if (single) {
+                put(p[a.C - 1], 1);                                               // model.py:365-367, 387-389
+            } else if (!a.multi || fallback) {
+                int arg = a.first; float best = p[a.first];                       // first maximum (np.argmax)
+                for (int k = a.first + 1; k < a.C; ++k) if (p[k] > best) { best = p[k]; arg = k; }
+                put(best, arg - a.first + 1);
+            } else {
+                for (int k = a.first; k < a.C; ++k) if (p[k] > a.thr) put(p[k], k - a.first + 1);   // np.where order: row, then class
+            }
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int run = 0;
+        for (int i = 0; i < a.n_images; ++i) { a.offsets[i] = run; run += fin[i]; }
+        a.offsets[a.n_images] = run;             // true total: > cap means the output was truncated
+    }
+}
+
+}  // namespace
+
+extern "C" int detbox_threshold_segments(const float *scores, const int64_t *img_ids, long n, int n_images,
+                                         float score_threshold, int32_t *seg32, int64_t *seg64, void *stream)
+{
+    if (n < 0 || n_images < 1) return DETBOX_ERR_INVALID;
+    if (n == 0) return DETBOX_OK;
+    if (!scores || !img_ids || !seg32 || !seg64) return DETBOX_ERR_INVALID;
+    if (n >= (1L << 31)) return DETBOX_ERR_UNSUPPORTED;
+    threshold_segments_kernel<<<1, DT_THREADS, 0, as_stream(stream)>>>(scores, img_ids, n, n_images, score_threshold, seg32, seg64);
+    DETBOX_LAUNCH_CHECK();
+    return DETBOX_OK;
+}
+
+extern "C" int detbox_to_dets(const float *boxes, const float *probs, int C, const int64_t *img_ids,
+                              const int64_t *keep, const int32_t *m_dev, long m_max, int n_images,
+                              int activation, int multi_label, float score_threshold,
+                              double *dets, long cap, int32_t *det_offsets, void *stream)
+{
+    if (C < 1 || m_max < 0 || n_images < 1 || cap < 0 || !det_offsets) return DETBOX_ERR_INVALID;
+    if (activation != DETBOX_ACT_SOFTMAX && activation != DETBOX_ACT_SIGMOID) return DETBOX_ERR_INVALID;
+    if (n_images > DT_MAX_IMAGES) return DETBOX_ERR_UNSUPPORTED;
+    if (m_max > 0 && (!boxes || !probs || !img_ids || (cap > 0 && !dets))) return DETBOX_ERR_INVALID;
+    if ((uintptr_t)boxes & 15) return DETBOX_ERR_INVALID;
+    DetsArgs a;
+    a.boxes = (const float4 *)boxes; a.probs = probs; a.C = C; a.img_ids = img_ids; a.keep = keep;
+    a.m_dev = m_dev; a.m_max = m_max; a.n_images = n_images;
+    a.first = activation == DETBOX_ACT_SOFTMAX ? 1 : 0;
+    a.multi = multi_label != 0; a.thr = score_threshold;
+    a.dets = dets; a.cap = cap; a.offsets = det_offsets;
+    to_dets_kernel<<<1, DT_THREADS, 0, as_stream(stream)>>>(a);
+    DETBOX_LAUNCH_CHECK();
+    return DETBOX_OK;
+}

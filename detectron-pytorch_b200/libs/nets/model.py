@@ -2,7 +2,9 @@
 free functions with the methods' names, arguments and return tuples.  Tensors stay on the device."""
 import torch
 
-from ... import ops, ops_post
+import numpy as np
+
+from ... import fused, ops, ops_post
 from ..configs import config as cfg
 
 
@@ -71,9 +73,50 @@ def _stage_one_results(rpn_box, rpn_prob, anchors, top_n=2000, overlap_threshold
     return boxes, probs, img_ids
 
 
-def get_final_results_stage1(rpn_box, rpn_prob, anchors, score_threshold=0.1, max_dets=100, overlap_threshold=0.5, activation=None):
-    """model.py:474-497 up to the NumPy conversion: threshold (top max_dets*9) -> per-image NMS."""
+def _to_dets(boxes, probs, img_ids, activation, multi_label, score_threshold, batch_size):
+    """Shared body of the four to_Dets* conversions: tensors (or NumPy arrays) in, list of `batch_size` float64
+    arrays [m_i,6] out, like upstream's everything2numpy + per-image loop (model.py:357-469)."""
+    dev = boxes.device if torch.is_tensor(boxes) and boxes.is_cuda else torch.device("cuda")
+    t = lambda x, dt: (x if torch.is_tensor(x) else torch.from_numpy(np.ascontiguousarray(x))).to(dev, dt)
+    boxes, probs, img_ids = t(boxes, torch.float32).reshape(-1, 4), t(probs, torch.float32), t(img_ids, torch.int64).reshape(-1)
+    n = cfg.batch_size if batch_size is None else int(batch_size)
+    if boxes.shape[0] == 0:
+        return [np.zeros((0, 6)) for _ in range(n)]
+    probs = probs.reshape(boxes.shape[0], -1)
+    if boxes.shape[0] > 1 and not bool((img_ids[1:] >= img_ids[:-1]).all()):     # upstream selects rows per image: any order works
+        order = torch.sort(img_ids, stable=True)[1]
+        boxes, probs, img_ids = boxes[order], probs[order], img_ids[order]
+    return fused.split(*ops_post.to_dets(boxes.contiguous(), probs.contiguous(), img_ids, n, activation, multi_label, score_threshold))
+
+
+def to_Dets(boxes, probs, img_ids, batch_size=None):
+    """model.py:358-378: one detection per box, arg-max foreground class of a softmax head."""
+    return _to_dets(boxes, probs, img_ids, 'softmax', False, 0.0, batch_size)
+
+
+def to_Dets_sigmoid(boxes, probs, img_ids, batch_size=None):
+    """model.py:381-402."""
+    return _to_dets(boxes, probs, img_ids, 'sigmoid', False, 0.0, batch_size)
+
+
+def to_Dets2(boxes, probs, img_ids, score_threshold=0.1, batch_size=None):
+    """model.py:405-436: every (box, class) with prob > threshold; arg-max rows for an image where none passes."""
+    return _to_dets(boxes, probs, img_ids, 'softmax', True, score_threshold, batch_size)
+
+
+def to_Dets2_sigmoid(boxes, probs, img_ids, score_threshold=0.1, batch_size=None):
+    """model.py:439-469."""
+    return _to_dets(boxes, probs, img_ids, 'sigmoid', True, score_threshold, batch_size)
+
+
+def get_final_results_stage1(rpn_box, rpn_prob, anchors, score_threshold=0.1, max_dets=100, overlap_threshold=0.5, activation=None,
+                             batch_size=None):
+    """model.py:474-497: top max_dets*3 -> threshold -> per-image NMS -> to_Dets2 / to_Dets2_sigmoid.  Returns the list
+    of per-image float64 arrays [m,6] upstream returns; everything before the final copy runs on the device without a
+    host synchronisation (detbox.fused.stage_one)."""
     activation = cfg.class_activation if activation is None else activation
-    boxes, probs, img_ids, anc = _decoding_and_thresholding_stage1(rpn_box, rpn_prob, anchors, score_threshold=score_threshold,
-                                                                  max_dets=max_dets * 3, activation=activation)
-    return _apply_nms_in_batch(boxes, probs, img_ids, anc, activation=activation, overlap_threshold=overlap_threshold)
+    if activation not in ('softmax', 'sigmoid'):
+        raise ValueError('Unknown activation function %s' % activation)
+    n = cfg.batch_size if batch_size is None else int(batch_size)
+    return fused.split(*fused.stage_one(rpn_box, rpn_prob, anchors, n, score_threshold, max_dets, overlap_threshold, activation,
+                                        cfg.rpn_box_encoding))

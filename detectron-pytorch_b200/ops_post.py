@@ -107,3 +107,46 @@ def nms(boxes, scores, thresh, cmp_mode=NMS_GT_F32, seg_ids=None, n_seg=1, retur
     _count((0 if presorted else (2 if n <= 4096 and n_seg == 1 else 14)) + 3 + ((2 if presorted else 5) if n_seg > 1 else 0)
            + (1 if want_clusters else 0))
     return (keep, n_keep, clusters) if want_clusters else (keep, n_keep)
+
+
+def threshold_segments(scores, img_ids, n_images, score_threshold):
+    """detbox_threshold_segments: (seg int32 [n], seg int64 [n]) — the image id of rows with score >= threshold (or of
+    the single best row when none passes, model.py:331-333), `n_images` for every other row.  No host sync."""
+    s = _dev(scores).view(-1)
+    ids = _dev(img_ids, torch.int64, "img_ids").view(-1)
+    n = s.numel()
+    if ids.numel() != n:
+        raise _lib.DetboxError("threshold_segments: %d scores but %d image ids" % (n, ids.numel()))
+    seg32 = torch.empty((n,), dtype=torch.int32, device=s.device)
+    seg64 = torch.empty((n,), dtype=torch.int64, device=s.device)
+    check(lib().detbox_threshold_segments(_ptr(s), _ptr(ids), n, int(n_images), float(score_threshold),
+                                          _ptr(seg32), _ptr(seg64), _stream()), "threshold_segments")
+    _count(1 if n else 0)
+    return seg32, seg64
+
+
+def to_dets(boxes, probs, img_ids, n_images, activation="softmax", multi_label=True, score_threshold=0.1,
+            keep=None, n_keep=None, cap=None):
+    """detbox_to_dets (model.py:357-469 on the device): rows keep[:n_keep] (or all rows) -> (dets float64 [cap,6],
+    offsets int32 [n_images+1]) device tensors; image i owns dets[offsets[i]:offsets[i+1]].  `n_keep` is a device
+    scalar (int32 tensor, e.g. nms()'s n_keep[-1:]) so nothing is read back here."""
+    b = _dev(boxes)
+    if b.dim() != 2 or b.shape[1] != 4:
+        raise _lib.DetboxError("to_dets: boxes must be [n,4]")
+    p = _dev(probs)
+    p = p.view(b.shape[0], -1)
+    ids = _dev(img_ids, torch.int64, "img_ids").view(-1)
+    C = p.shape[1]
+    k = _dev(keep, torch.int64, "keep").view(-1) if keep is not None else None
+    m_max = k.numel() if k is not None else b.shape[0]
+    nk = _dev(n_keep, torch.int32, "n_keep").view(-1) if n_keep is not None else None
+    first = 1 if activation == "softmax" else 0
+    per_row = max(C - first, 1) if multi_label else 1
+    cap = int(cap) if cap is not None else max(m_max * per_row, 1)
+    dets = torch.empty((cap, 6), dtype=torch.float64, device=b.device)
+    off = torch.zeros((int(n_images) + 1,), dtype=torch.int32, device=b.device)
+    check(lib().detbox_to_dets(_ptr(b), _ptr(p), C, _ptr(ids), _ptr(k), _ptr(nk), m_max, int(n_images), ACT[activation],
+                               int(bool(multi_label)), float(score_threshold), dets.data_ptr(), cap, off.data_ptr(), _stream()),
+          "to_dets")
+    _count(1)
+    return dets, off

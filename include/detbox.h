@@ -297,6 +297,30 @@ int detbox_sample_gather(const float *boxes_dev, const int64_t *labels_dev, cons
                          float *out_boxes_dev, int64_t *out_labels_dev, int64_t *out_image_inds_dev, void *stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Stage-one epilogue on the device: score thresholding without a host round trip
+ * and the `to_Dets*` conversions of libs/nets/model.py:357-469.
+ * ------------------------------------------------------------------------------------------- */
+/* libs/nets/model.py:326-333 (_decoding_and_thresholding_stage1): rows with score >= threshold stay
+ * in their image's segment; if NO row passes, only the single best row does (lowest index on ties).
+ * All other rows (and rows with an image index outside [0, n_images)) go to the dummy segment
+ * n_images.  Writes the segment ids twice: int32 for detbox_nms, int64 for detbox_to_dets. */
+int detbox_threshold_segments(const float *scores_dev, const int64_t *img_ids_dev, long n, int n_images,
+                              float score_threshold, int32_t *seg32_dev, int64_t *seg64_dev, void *stream);
+/* to_Dets (:358-378), to_Dets_sigmoid (:381-402), to_Dets2 (:405-436), to_Dets2_sigmoid (:439-469):
+ * rows keep[0..m) (or 0..m) of boxes [.,4] / probs [.,C] / img_ids, image-major, m = *m_dev when given
+ * (e.g. detbox_nms's n_keep[n_seg]) else m_max.  multi_label = 0: one detection per row, arg-max class;
+ * multi_label = 1: every (row, class) with prob > score_threshold, in row-major order, and the arg-max
+ * rule for an image where no pair passes.  softmax: column 0 is background; C == 2 (softmax) or C == 1
+ * (sigmoid): one detection per row, class 1, no threshold.  Rows whose image id is outside
+ * [0, n_images) are dropped.  dets [cap,6] float64 = (x1,y1,x2,y2,prob,class) (NumPy's result type of
+ * the reference's concatenate), det_offsets int32 [n_images+1]; det_offsets[n_images] > cap means the
+ * output was truncated.  n_images <= 2048. */
+int detbox_to_dets(const float *boxes_dev, const float *probs_dev, int C, const int64_t *img_ids_dev,
+                   const int64_t *keep_dev, const int32_t *m_dev, long m_max, int n_images,
+                   int activation, int multi_label, float score_threshold,
+                   double *dets_dev, long cap, int32_t *det_offsets_dev, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
  * HOST-buffer entry points (copies inside; synchronous; scratch cached per device).
  * ------------------------------------------------------------------------------------------- */
 /* Exactly the reference's FFI symbol `_nms` (libs/nms/gpu_nms.hpp:1-2, bound by gpu_nms.pyx:14):

@@ -131,9 +131,61 @@ def nms_variants_golden(r):
     np.savez_compressed(os.path.join(GOLD, "nms_variants.npz"), **out)
 
 
+def to_dets_cases():
+    """(name, activation, multi_label, C, threshold, batch, sorted ids) for the to_Dets* conversions."""
+    return [("softmax2", "softmax", True, 2, 0.1, 3, True), ("softmax5", "softmax", True, 5, 0.3, 4, True),
+            ("softmax5_unsorted", "softmax", True, 5, 0.45, 4, False), ("softmax5_single", "softmax", False, 5, 0.0, 3, True),
+            ("sigmoid4", "sigmoid", True, 4, 0.5, 4, True), ("sigmoid4_single", "sigmoid", False, 4, 0.0, 3, False)]
+
+
+def to_dets_inputs(case):
+    name, act, multi, C, thr, B, sorted_ids = case
+    import zlib
+    rng = np.random.RandomState(zlib.crc32(name.encode()) % 1000)
+    n = 120
+    xy = rng.uniform(0, 300, (n, 2)); wh = rng.uniform(5, 80, (n, 2))
+    boxes = np.concatenate([xy, xy + wh], 1).astype(np.float32)
+    probs = rng.dirichlet(np.ones(C) * 0.7, n).astype(np.float32) if act == "softmax" else rng.rand(n, C).astype(np.float32)
+    ids = rng.randint(0, B - 1, n)                       # the last image has no rows
+    if sorted_ids:
+        ids = np.sort(ids)
+    if C > 2:
+        probs[ids == 0] *= np.float32(0.2)               # image 0: nothing above the threshold -> arg-max rule
+    return boxes, probs, ids.astype(np.int64)
+
+
+def to_dets_golden(ref_root="/root/reference"):
+    """to_Dets / to_Dets_sigmoid / to_Dets2 / to_Dets2_sigmoid: the four static methods are taken out of the
+    reference's libs/nets/model.py:357-469 AT RUN TIME (ast) and executed on NumPy inputs — model.py itself imports
+    the whole network stack and cannot be imported here.  Nothing of the reference's text is stored."""
+    import ast, textwrap, types
+    src = open(os.path.join(ref_root, "libs/nets/model.py")).read()
+    tree = ast.parse(src)
+    ns = {"np": np, "everything2numpy": lambda xs: [np.asarray(x) for x in xs], "cfg": types.SimpleNamespace(batch_size=0)}
+    for node in ast.walk(tree):
+        if isinstance(node, ast.FunctionDef) and node.name in ("to_Dets", "to_Dets_sigmoid", "to_Dets2", "to_Dets2_sigmoid"):
+            node.decorator_list = []
+            exec(compile(ast.Module(body=[node], type_ignores=[]), "<reference model.py>", "exec"), ns)
+    out = {}
+    for case in to_dets_cases():
+        name, act, multi, C, thr, B, _ = case
+        boxes, probs, ids = to_dets_inputs(case)
+        ns["cfg"].batch_size = B
+        fn = ns[{("softmax", False): "to_Dets", ("sigmoid", False): "to_Dets_sigmoid",
+                 ("softmax", True): "to_Dets2", ("sigmoid", True): "to_Dets2_sigmoid"}[(act, multi)]]
+        dets = fn(boxes, probs, ids, thr) if multi else fn(boxes, probs, ids)
+        out[name + "_boxes"], out[name + "_probs"], out[name + "_ids"] = boxes, probs, ids
+        out[name + "_dets"] = np.concatenate([np.asarray(d, np.float64).reshape(-1, 6) for d in dets], 0)
+        out[name + "_offsets"] = np.cumsum([0] + [np.asarray(d).reshape(-1, 6).shape[0] for d in dets]).astype(np.int32)
+    np.savez_compressed(os.path.join(GOLD, "to_dets.npz"), **out)
+
+
 def main():
     r = ref_loader.load()
     os.makedirs(GOLD, exist_ok=True)
+    if "--only-to-dets" in sys.argv:
+        to_dets_golden()
+        return
     if "--only-roi-sampling" in sys.argv:
         roi_sampling_golden(r)
         return
@@ -281,6 +333,7 @@ def main():
 
     roi_sampling_golden(r)
     nms_variants_golden(r)
+    to_dets_golden()
 
     sz = sum(os.path.getsize(os.path.join(GOLD, f)) for f in os.listdir(GOLD))
     print("golden vectors written to", GOLD, "(%d KiB)" % (sz // 1024))

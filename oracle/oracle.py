@@ -578,3 +578,45 @@ def nms_new(dets, thresh):
 
 def nms_multianchor(dets, thresh):
     return _nms_variant(dets, thresh, "multianchor")
+
+
+# ------------------------------------------------------------------------------------------------
+# to_Dets* epilogues and the stage-one composite
+# ------------------------------------------------------------------------------------------------
+def to_dets(boxes, probs, img_ids, batch_size, activation="softmax", multi_label=True, score_threshold=0.1):
+    """libs/nets/model.py:357-469 restated (to_Dets / to_Dets_sigmoid for multi_label=False, to_Dets2 /
+    to_Dets2_sigmoid for True): list of `batch_size` arrays [m,6] = (x1,y1,x2,y2,prob,class), float64."""
+    boxes = np.asarray(boxes, np.float32).reshape(-1, 4); img_ids = np.asarray(img_ids).reshape(-1)
+    probs = np.asarray(probs, np.float32).reshape(boxes.shape[0], -1)
+    first = 1 if activation == "softmax" else 0
+    out = []
+    for i in range(batch_size):
+        inds = np.where(img_ids == i)[0]
+        p, b = probs[inds], boxes[inds]
+        fg = p[:, first:]
+        if fg.shape[1] == 1:                                               # :365-367 / :387-389
+            cls_ids = np.ones((p.shape[0],), np.int32); cls_probs = fg[:, 0]
+        else:
+            d0, d1 = np.where(fg > score_threshold) if multi_label else (np.zeros(0, np.int64), np.zeros(0, np.int64))
+            if d0.size > 0:                                                # :421-427
+                cls_ids = d1 + 1; cls_probs = fg[d0, d1]; b = b[d0, :]
+            else:                                                          # :369-370 / :428-431
+                am = fg.argmax(axis=1) if fg.shape[0] else np.zeros(0, np.int64)
+                cls_ids = am + 1; cls_probs = fg[np.arange(fg.shape[0]), am]
+        out.append(np.concatenate((b.reshape(-1, 4), cls_probs[:, None], cls_ids[:, None]), axis=1).astype(np.float64))
+    return out
+
+
+def final_results_stage1(rpn_box, rpn_prob, anchors_, batch_size, score_threshold=0.1, max_dets=100, overlap_threshold=0.5,
+                         activation="softmax", box_encoding="fastrcnn"):
+    """libs/nets/model.py:474-497 composed from the pieces above: top 9*max_dets (:483, :326) -> objectness >=
+    threshold with the single-best fallback (:329-333) -> per-image NMS ('>' comparator of the CUDA path) ->
+    to_Dets2 / to_Dets2_sigmoid."""
+    boxes, probs, img_ids, _, _ = decode_and_choose_top_n(rpn_box, rpn_prob, anchors_, max_dets * 9, activation, box_encoding)
+    obj = objectness(probs, activation)
+    inds = np.nonzero(obj >= np.float32(score_threshold))[0]
+    if inds.size == 0:
+        inds = stable_desc_order(obj)[:1]
+    boxes, probs, img_ids = boxes[inds], probs[inds], img_ids[inds]
+    keep = apply_nms_in_batch(boxes, probs, img_ids, activation, overlap_threshold, NMS_GT_F32)
+    return to_dets(boxes[keep], probs[keep], img_ids[keep], batch_size, activation, True, score_threshold)

@@ -158,3 +158,16 @@ def test_nms_variants(golden, seed, thr):
     keep, clusters = O.nms_multianchor(d, thr)
     np.testing.assert_array_equal(keep, g["d%d_multi_keep_%g" % (seed, thr)])
     np.testing.assert_array_equal(clusters, g["d%d_multi_clusters_%g" % (seed, thr)])
+
+
+def test_to_dets(golden):
+    """to_Dets* conversions (libs/nets/model.py:357-469): outputs recorded from the reference's own methods."""
+    from oracle.make_golden import to_dets_cases, to_dets_inputs
+    g = golden("to_dets")
+    for case in to_dets_cases():
+        name, act, multi, C, thr, B, _ = case
+        b, p, i = to_dets_inputs(case)
+        assert np.array_equal(b, g[name + "_boxes"]) and np.array_equal(p, g[name + "_probs"]) and np.array_equal(i, g[name + "_ids"])
+        d = O.to_dets(b, p, i, B, act, multi, thr)
+        assert np.array_equal(np.cumsum([0] + [x.shape[0] for x in d]), g[name + "_offsets"])
+        assert np.array_equal(np.concatenate(d, 0), g[name + "_dets"])
