@@ -162,3 +162,24 @@ def test_linearity_and_constant_plane_at_baseline_shape():
     lhs = float((fx.double() * go.double()).sum())
     rhs = float(sum((a.double() * b.double()).sum() for a, b in zip(x, gi)))
     assert abs(lhs - rhs) <= 1e-5 * max(abs(lhs), 1.0) + 1e-2
+
+
+@pytest.mark.parametrize("mode", ["tf", "grid"])
+def test_backward_is_the_gradient_finite_differences(mode):
+    """The reference's commented-out gradcheck (roi_align_tf/test.py:101-120: RoIAlign(3,3) on 2x2x10x10) as a
+    central finite-difference test in float64 arithmetic on the host: d<fwd(x), g>/dx == bwd(g)."""
+    rng = np.random.RandomState(5)
+    B, C, H, W, ph, pw = 2, 2, 10, 10, 3, 3
+    feat = rng.normal(0, 1, (B, C, H, W)).astype(np.float32)
+    rois = np.asarray([[0, 1.3, 2.2, 7.9, 8.4], [1, 0.0, 0.0, 9.0, 9.0], [1, 3.5, 4.1, 5.2, 6.6], [0, -2.0, 1.0, 4.0, 12.0]], np.float32)
+    m = detbox.ROI_BIN_CENTRE if mode == "tf" else detbox.ROI_GRID_POINT
+    g = rng.normal(0, 1, (rois.shape[0], C, ph, pw)).astype(np.float32)
+    gi = detbox.roi_align_backward(cu(g), [feat.shape], cu(rois), [1.0], m)[0].cpu().numpy()
+    f = lambda x: float((detbox.roi_align_forward([cu(x)], cu(rois), [1.0], ph, pw, m).cpu().numpy().astype(np.float64) * g).sum())
+    eps = 0.5                                             # the op is linear in the features: any step gives the exact slope
+    for _ in range(25):
+        idx = tuple(rng.randint(0, s) for s in feat.shape)
+        xp, xm = feat.copy(), feat.copy()
+        xp[idx] += eps; xm[idx] -= eps
+        num = (f(xp) - f(xm)) / (2 * eps)
+        assert abs(num - gi[idx]) <= 1e-4 * max(1.0, abs(num)), (idx, num, gi[idx])

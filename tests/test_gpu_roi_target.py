@@ -114,3 +114,27 @@ def test_roi_target_vs_oracle_and_reference_kernel(seed, R, G, Bn):
     torch.cuda.synchronize()
     assert torch.equal(labels, rl) and torch.equal(bbw, rw)
     assert (deltas - rd).abs().max().item() <= 1e-5 * max(1.0, rd.abs().max().item())
+
+
+def test_roi_target_reference_fixture():
+    """The reference's own smoke fixture (libs/layers/roi_target/modules/roi_target_test.py:15-40: 10 RoIs in two
+    images, 6 GT of class 0 / -1 / 3 / 4, RoITarget(0.55)); upstream only prints.  Checked against the oracle and,
+    when present, the reference kernel compiled unmodified."""
+    _, T = mirror()
+    rois = np.asarray([[120, 120, 140, 150], [95, 100, 120, 130], [120, 120, 125, 125], [40, 50, 50, 60], [95, 100, 120, 130],
+                       [0, 0, 9, 9], [1, 1, 8, 8], [10, 10, 20, 20], [16, 10, 26, 20], [70, 60, 80, 90]], np.float32)
+    rid = np.asarray([0, 0, 0, 0, 1, 1, 1, 1, 1, 0], np.int64)
+    gt = np.asarray([[121, 120, 140, 150, 0], [100, 100, 120, 130, 0], [121, 120, 140, 150, -1], [100, 100, 120, 130, -1],
+                     [1, 1, 8, 8, 3], [13, 10, 23, 20, 4]], np.float32)
+    gid = np.asarray([0, 0, 1, 1, 1, 1], np.int64)
+    labels, deltas, bbw = T.RoITarget(0.55)(cu(rois), cu(rid), cu(gt), cu(gid))
+    wl, wd, ww = O.roi_target(rois, rid, gt, gid, 0.55)
+    np.testing.assert_array_equal(labels.cpu().numpy(), wl)
+    np.testing.assert_array_equal(bbw.cpu().numpy(), ww)
+    np.testing.assert_allclose(deltas.cpu().numpy(), wd, rtol=1e-5, atol=1e-6)
+    # known answers: RoIs 0-2 and 4 sit inside class-0 / class -1 GT (inter / area(roi) >= 0.55 -> label -1: the kernel scores
+    # ignore boxes by coverage of the RoI), RoI 6 IS the GT (1,1,8,8,3), RoI 5 contains it, RoIs 7 / 8 flank the class-4 GT
+    assert labels.cpu().tolist() == [-1, -1, -1, 0, -1, 3, 3, 4, 4, 0]
+    assert bbw.cpu().numpy()[:, 0].tolist() == [0, 0, 0, 0, 0, 1, 1, 1, 1, 0]
+    assert np.abs(deltas.cpu().numpy()[6]).max() == 0
+    np.testing.assert_allclose(deltas.cpu().numpy()[7:9, 0], [30.0 / 11, -30.0 / 11], rtol=1e-6)
