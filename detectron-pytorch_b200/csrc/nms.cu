@@ -87,14 +87,17 @@ nms_gather_kernel(const float *__restrict__ boxes, int stride, const uint32_t *_
 
 // segment sizes -> offsets in the (segment-major) processing order.  One atomic per distinct id per warp
 // (__match_any): ids arrive sorted or in long runs, so a warp usually issues one or two.
+// ID = int64_t (DETBOX_NMS_SEG_I64): the ids are narrowed into `narrow` on the way, so every later pass reads int32.
+template <typename ID>
 __global__ void __launch_bounds__(256)
-nms_seg_count_kernel(const int32_t *__restrict__ seg_ids, long n, int n_seg, int32_t *__restrict__ seg_off)
+nms_seg_count_kernel(const ID *__restrict__ seg_ids, long n, int n_seg, int32_t *__restrict__ seg_off, int32_t *__restrict__ narrow)
 {
     const int lane = threadIdx.x & 31;
     for (long base = (long)blockIdx.x * blockDim.x; base < n; base += (long)gridDim.x * blockDim.x) {   // block-uniform trip count
         const long i = base + threadIdx.x;
-        int s = i < n ? seg_ids[i] : -1;
-        if (s < 0 || s >= n_seg) s = -1;
+        const ID raw = i < n ? seg_ids[i] : (ID)-1;
+        int s = (raw < 0 || raw >= (ID)n_seg) ? -1 : (int)raw;
+        if (narrow && i < n) narrow[i] = s;
         const unsigned peers = __match_any_sync(0xffffffffu, s);
         if (s >= 0 && lane == __ffs(peers) - 1) atomicAdd(&seg_off[s + 1], __popc(peers));
     }
@@ -269,11 +272,11 @@ nms_resolve_kernel(const u64 *__restrict__ mask, int n, int ncol, const int32_t 
 constexpr int RSEG_THREADS = 1024;
 
 __global__ void __launch_bounds__(RSEG_THREADS)
-nms_resolve_seg_kernel(const u64 *__restrict__ mask, int ncol, const int32_t *__restrict__ seg_off,
+nms_resolve_seg_kernel(const u64 *__restrict__ mask, int n, int ncol, const int32_t *__restrict__ seg_off,
                        u64 *__restrict__ kept_g, int smem_words)
 {
     extern __shared__ u64 rsm[];
-    const int b0 = seg_off[blockIdx.x], b1 = seg_off[blockIdx.x + 1];
+    const int b0 = seg_off ? seg_off[blockIdx.x] : 0, b1 = seg_off ? seg_off[blockIdx.x + 1] : n;   // no offsets: one segment = everything
     if (b1 <= b0) return;
     const int w0 = b0 >> 6, w = ((b1 - 1) >> 6) - w0 + 1, cnt = b1 - b0;
     const int ws = w | 1;                                  // odd row stride: 64-bit column reads hit distinct banks
@@ -345,63 +348,66 @@ nms_cluster_kernel(const u64 *__restrict__ mask, const u64 *__restrict__ kept, i
     clusters[self] = cl;
 }
 
+// Ordered compaction of the kept bits -> original indices, and the per-segment counts.  A block owns CP_WORDS words
+// (2048 boxes): it counts the kept boxes in front of its words (every block re-reads at most ncol words — cheaper than
+// a second launch), ranks its own words with one warp scan, and then every thread places ONE box, so the dependent
+// order[] loads of a word's 64 boxes overlap instead of queueing behind each other in one thread.
+// Per-segment count = rank(end) - rank(begin): the block that owns a boundary adds / subtracts its rank (integer
+// atomics on the zeroed n_keep — order-independent).
+constexpr int CP_WORDS = 32;
+
 __global__ void __launch_bounds__(1024)
 nms_compact_kernel(const u64 *__restrict__ kept, int n, int ncol, const uint32_t *__restrict__ order,
-                   const int32_t *__restrict__ seg_off, int n_seg, uint32_t *__restrict__ wrank /*[ncol + 1]*/,
-                   int64_t *__restrict__ keep, int32_t *__restrict__ n_keep)
+                   const int32_t *__restrict__ seg_off, int n_seg, int64_t *__restrict__ keep, int32_t *__restrict__ n_keep)
 {
     __shared__ int warp_sum[32];
-    __shared__ int running;
+    __shared__ int s_rank[CP_WORDS + 1];
+    __shared__ u64 s_word[CP_WORDS];
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    if (tid == 0) running = 0;
+    const int w_lo = blockIdx.x * CP_WORDS;
+    const bool last = blockIdx.x == gridDim.x - 1;
+    int c = 0;
+    for (int i = tid; i < w_lo; i += 1024) c += __popcll(kept[i]);
+    c = __reduce_add_sync(0xffffffffu, c);
+    if (lane == 0) warp_sum[w] = c;
     __syncthreads();
-    for (int base = 0; base < ncol; base += 1024) {
-        const int wi = base + tid;
-        u64 word = wi < ncol ? kept[wi] : 0ull;
-        const int c = __popcll(word);
-        int incl = c;
+    if (w == 0) {
+        const int base = __reduce_add_sync(0xffffffffu, warp_sum[lane]);
+        const int wi = w_lo + lane;
+        const u64 word = wi < ncol ? kept[wi] : 0ull;
+        const int pc = __popcll(word);
+        int incl = pc;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
-        if (lane == 31) warp_sum[w] = incl;
-        __syncthreads();
-        if (w == 0) {
-            const int v = warp_sum[lane]; int iv = v;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, iv, o); if (lane >= o) iv += t; }
-            warp_sum[lane] = iv - v;
-        }
-        __syncthreads();
-        int pos = running + warp_sum[w] + incl - c;
-        if (wi < ncol) wrank[wi] = (uint32_t)pos;            // kept boxes before this word
-        while (word) {
-            const int bit = __ffsll((long long)word) - 1;
-            word &= word - 1;
-            const int sp = wi * 64 + bit;
-            keep[pos++] = (int64_t)(order ? order[sp] : (uint32_t)sp);
-        }
-        __syncthreads();
-        if (tid == 1023) running = pos;          // last thread's end == running + block total
-        __syncthreads();
+        s_word[lane] = word;
+        s_rank[lane] = base + incl - pc;                      // kept boxes before this word
+        if (lane == 31) s_rank[CP_WORDS] = base + incl;
     }
-    if (tid == 0) { wrank[ncol] = (uint32_t)running; n_keep[n_seg] = running; if (n_seg == 1) n_keep[0] = running; }
+    __syncthreads();
+    for (int t = tid; t < CP_WORDS * 64; t += 1024) {
+        const int wl = t >> 6, bit = t & 63;
+        const u64 word = s_word[wl];
+        if ((word >> bit) & 1ull) {
+            const int sp = (w_lo + wl) * 64 + bit;
+            keep[s_rank[wl] + __popcll(word & ((1ull << bit) - 1ull))] = (int64_t)(order ? order[sp] : (uint32_t)sp);
+        }
+    }
+    if (last && tid == 0) { n_keep[n_seg] = s_rank[CP_WORDS]; if (n_seg == 1) n_keep[0] = s_rank[CP_WORDS]; }
     if (n_seg > 1) {
-        // kept boxes of a segment = rank(end) - rank(begin); rank(p) = kept boxes at positions < p
-        __syncthreads();
-        for (int s = tid; s < n_seg; s += 1024) {
-            int r[2];
-            for (int e = 0; e < 2; ++e) {
-                const int p = seg_off[s + e];
-                const int wi = p >> 6;
-                r[e] = wi >= ncol ? running : (int)wrank[wi] + __popcll(kept[wi] & ((1ull << (p & 63)) - 1ull));
-            }
-            n_keep[s] = r[1] - r[0];
+        for (int s = tid; s <= n_seg; s += 1024) {
+            const int p = seg_off[s];
+            const int wl = (p >> 6) - w_lo;
+            if (wl < 0 || (wl >= CP_WORDS && !last)) continue;    // another block's boundary
+            const int r = wl >= CP_WORDS ? s_rank[CP_WORDS] : s_rank[wl] + __popcll(s_word[wl] & ((1ull << (p & 63)) - 1ull));
+            if (s < n_seg) atomicSub(&n_keep[s], r);
+            if (s > 0) atomicAdd(&n_keep[s - 1], r);
         }
     }
 }
 
 struct NmsBuffers {
     uint32_t *ka, *kb, *va, *vb, *counts;
-    float4 *sorted; int32_t *seg_sorted, *seg_off; u64 *mask, *kept, *supp; unsigned *cnt; uint32_t *wrank;
+    float4 *sorted; int32_t *seg_sorted, *seg_narrow, *seg_off; u64 *mask, *kept, *supp; unsigned *cnt;
     size_t total;
 };
 
@@ -414,11 +420,11 @@ NmsBuffers carve_nms(void *ws, long n, int n_seg) {
     b.counts = cv.take<uint32_t>(sort_counts_bytes(n) / 4);
     b.sorted = cv.take<float4>(n);
     b.seg_sorted = cv.take<int32_t>(n_seg > 1 ? n : 1);
+    b.seg_narrow = cv.take<int32_t>(n_seg > 1 ? n : 1);
     b.seg_off = cv.take<int32_t>(n_seg + 2);
     b.kept = cv.take<u64>(2 * ncol + 2);           // kept | supp | round counters, cleared together
     b.supp = b.kept + ncol;
     b.cnt = reinterpret_cast<unsigned *>(b.supp + ncol);
-    b.wrank = cv.take<uint32_t>(ncol + 1);
     b.mask = cv.take<u64>((size_t)n * ncol);
     b.total = cv.off;
     return b;
@@ -468,7 +474,8 @@ int nms_sorted(const NmsBuffers &b, const uint32_t *order, long n, int n_seg,
     DETBOX_CUDA_TRY(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64) return DETBOX_ERR_UNSUPPORTED;
     const long wmax = (n >> 6) + 2, smem_cap = 200 * 1024 / 8;      // 64-bit words
-    if (small_segs && 2 * wmax <= smem_cap) {
+    const bool one_small = !seg_sorted && n * (wmax | 1) + 2 * wmax <= smem_cap;   // a single segment whose rows fit one block's smem
+    if ((small_segs && 2 * wmax <= smem_cap) || one_small) {
         // one block per segment; shared memory sized for the largest segment n allows, capped at 200 KB
         // (the two bitsets always fit; rows that do not are read from global memory)
         static thread_local bool smem_set[64] = {false};
@@ -480,7 +487,7 @@ int nms_sorted(const NmsBuffers &b, const uint32_t *order, long n, int n_seg,
             smem_set[dev] = true;
         }
         DETBOX_TRACE_BEGIN(DETBOX_K_NMS_SCAN, st);
-        nms_resolve_seg_kernel<<<(unsigned)n_seg, RSEG_THREADS, (size_t)bytes, st>>>(b.mask, ncol, seg_off, b.kept, (int)words);
+        nms_resolve_seg_kernel<<<(unsigned)n_seg, RSEG_THREADS, (size_t)bytes, st>>>(b.mask, (int)n, ncol, seg_sorted ? seg_off : nullptr, b.kept, (int)words);
         DETBOX_TRACE_END(DETBOX_K_NMS_SCAN, st);
         DETBOX_LAUNCH_CHECK();
     } else {
@@ -506,7 +513,7 @@ int nms_sorted(const NmsBuffers &b, const uint32_t *order, long n, int n_seg,
         DETBOX_TRACE_END(DETBOX_K_NMS_SCAN, st);
     }
     }
-    nms_compact_kernel<<<1, 1024, 0, st>>>(b.kept, (int)n, ncol, order, seg_sorted ? seg_off : nullptr, n_seg, b.wrank, keep, n_keep);
+    nms_compact_kernel<<<(unsigned)((ncol + CP_WORDS - 1) / CP_WORDS), 1024, 0, st>>>(b.kept, (int)n, ncol, order, seg_sorted ? seg_off : nullptr, n_seg, keep, n_keep);
     DETBOX_LAUNCH_CHECK();
     if (clusters) {
         nms_cluster_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(b.mask, b.kept, (int)n, ncol, order, seg_sorted,
@@ -530,7 +537,8 @@ static int nms_impl(const float *boxes, int box_stride, const float *scores, lon
 {
     if (variant < 0 || variant > 2) return DETBOX_ERR_INVALID;
     const bool presorted = (cmp_mode & DETBOX_NMS_PRESORTED) != 0;
-    cmp_mode &= ~DETBOX_NMS_PRESORTED;
+    const bool seg_i64 = (cmp_mode & DETBOX_NMS_SEG_I64) != 0;
+    cmp_mode &= ~(DETBOX_NMS_PRESORTED | DETBOX_NMS_SEG_I64);
     if (n < 0 || box_stride < 4 || cmp_mode < 0 || cmp_mode > 2 || !n_keep) return DETBOX_ERR_INVALID;
     if (presorted && (box_stride != 4 || ((uintptr_t)boxes & 15))) return DETBOX_ERR_INVALID;
     if (!seg_ids || n_seg <= 1) { n_seg = 1; seg_ids = nullptr; }
@@ -541,14 +549,21 @@ static int nms_impl(const float *boxes, int box_stride, const float *scores, lon
     if (!ws || ws_bytes < detbox_nms_workspace_bytes(n, n_seg)) return DETBOX_ERR_WORKSPACE;
     NmsBuffers b = carve_nms(ws, n, n_seg);
     long gb0 = (n + 255) / 256; if (gb0 > kNumSMs * 8) gb0 = kNumSMs * 8;
-    if (presorted) {                              // rows are in processing order: no sort, no gather
-        if (n_seg > 1) {
-            DETBOX_CUDA_TRY(cudaMemsetAsync(b.seg_off, 0, (size_t)(n_seg + 2) * sizeof(int32_t), st));
-            nms_seg_count_kernel<<<(unsigned)gb0, 256, 0, st>>>(seg_ids, n, n_seg, b.seg_off);
-            DETBOX_LAUNCH_CHECK();
-            nms_seg_scan_kernel<<<1, 32, 0, st>>>(b.seg_off, n_seg);
-            DETBOX_LAUNCH_CHECK();
+    auto count_segments = [&]() -> int {          // segment offsets; int64 ids are narrowed into the workspace
+        DETBOX_CUDA_TRY(cudaMemsetAsync(b.seg_off, 0, (size_t)(n_seg + 2) * sizeof(int32_t), st));
+        if (seg_i64) {
+            nms_seg_count_kernel<int64_t><<<(unsigned)gb0, 256, 0, st>>>(reinterpret_cast<const int64_t *>(seg_ids), n, n_seg, b.seg_off, b.seg_narrow);
+            seg_ids = b.seg_narrow;
+        } else {
+            nms_seg_count_kernel<int32_t><<<(unsigned)gb0, 256, 0, st>>>(seg_ids, n, n_seg, b.seg_off, nullptr);
         }
+        DETBOX_LAUNCH_CHECK();
+        nms_seg_scan_kernel<<<1, 32, 0, st>>>(b.seg_off, n_seg);
+        DETBOX_LAUNCH_CHECK();
+        return DETBOX_OK;
+    };
+    if (presorted) {                              // rows are in processing order: no sort, no gather
+        if (n_seg > 1) { const int rcs = count_segments(); if (rcs != DETBOX_OK) return rcs; }
         b.sorted = const_cast<float4 *>(reinterpret_cast<const float4 *>(boxes));
         b.seg_sorted = const_cast<int32_t *>(seg_ids);
         return nms_sorted(b, nullptr, n, n_seg, make_cmp(thresh, cmp_mode, variant), keep, n_keep, st, clusters);
@@ -566,11 +581,8 @@ static int nms_impl(const float *boxes, int box_stride, const float *scores, lon
     uint32_t *order = b.va;
     long gb = (n + 255) / 256; if (gb > kNumSMs * 8) gb = kNumSMs * 8;
     if (n_seg > 1) {                              // stable grouping by segment: 1 pass per 8 bits of id
-        DETBOX_CUDA_TRY(cudaMemsetAsync(b.seg_off, 0, (size_t)(n_seg + 2) * sizeof(int32_t), st));
-        nms_seg_count_kernel<<<(unsigned)gb, 256, 0, st>>>(seg_ids, n, n_seg, b.seg_off);
-        DETBOX_LAUNCH_CHECK();
-        nms_seg_scan_kernel<<<1, 32, 0, st>>>(b.seg_off, n_seg);
-        DETBOX_LAUNCH_CHECK();
+        rc = count_segments();
+        if (rc != DETBOX_OK) return rc;
         uint32_t *ki = b.ka, *vi = b.va, *ko = b.kb, *vo = b.vb;
         for (int shift = 0; (n_seg - 1) >> shift; shift += 8) {
             DigitSrc d{2, shift, 1u, seg_ids};

@@ -33,7 +33,7 @@ def apply_nms_in_batch(boxes, scores, img_ids, n_images, overlap_threshold=0.5, 
     (keep int64 [n] buffer, n_keep int32 [n_images+1]) on the device, without host synchronisation:
     keep[:n_keep[-1]] is image-major, score-descending inside an image."""
     return ops_post.nms(boxes[:, :4], scores.reshape(-1), float(overlap_threshold), cmp_mode,
-                        seg_ids=img_ids.to(torch.int32), n_seg=int(n_images))
+                        seg_ids=img_ids, n_seg=int(n_images))
 
 
 def _image_major(image_inds):

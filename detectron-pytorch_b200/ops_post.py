@@ -82,20 +82,24 @@ def nms(boxes, scores, thresh, cmp_mode=NMS_GT_F32, seg_ids=None, n_seg=1, retur
     n = b.shape[0]
     if s.numel() != n:
         raise _lib.DetboxError("nms: %d boxes but %d scores" % (n, s.numel()))
-    seg = None
+    seg, seg_i64 = None, False
     if seg_ids is not None and n_seg > 1:
-        seg = _dev(seg_ids, torch.int32, "seg_ids").view(-1)
+        seg_i64 = torch.is_tensor(seg_ids) and seg_ids.dtype == torch.int64       # narrowed inside the library
+        seg = _dev(seg_ids, torch.int64 if seg_i64 else torch.int32, "seg_ids").view(-1)
+        if seg.numel() != n:
+            raise _lib.DetboxError("nms: %d boxes but %d segment ids" % (n, seg.numel()))
     else:
         n_seg = 1
     keep = torch.empty((n,), dtype=torch.int64, device=b.device)
-    n_keep = torch.zeros((n_seg + 1,), dtype=torch.int32, device=b.device)
+    n_keep = torch.empty((n_seg + 1,), dtype=torch.int32, device=b.device)          # zeroed by the library
     clusters = torch.empty((n,), dtype=torch.int64, device=b.device) if want_clusters else None
     if n == 0:
+        n_keep.zero_()
         return (keep, n_keep, clusters) if want_clusters else (keep, n_keep)
     ws = _ws.get(lib().detbox_nms_workspace_bytes(n, n_seg), b.device)
     if presorted and b.shape[1] != 4:
         raise _lib.DetboxError("nms(presorted=True) needs boxes of shape [n,4]")
-    mode = int(cmp_mode) | (0x100 if presorted else 0)
+    mode = int(cmp_mode) | (0x100 if presorted else 0) | (0x200 if seg_i64 else 0)
     if NMS_VARIANTS[variant] or want_clusters:
         check(lib().detbox_nms_variant(b.data_ptr(), b.shape[1], s.data_ptr(), n, _ptr(seg), n_seg, float(thresh), mode,
                                        NMS_VARIANTS[variant], keep.data_ptr(), n_keep.data_ptr(), _ptr(clusters),

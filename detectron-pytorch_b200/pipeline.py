@@ -68,7 +68,7 @@ class BoxOpsSession:
         sel = ops_post.topk_decode(rpn_box, rpn_prob, self.anchors, self.top_n, self.activation, "fastrcnn",
                                    per_image=True, want=("img_ids", "scores"))
         keep, n_keep = ops_post.nms(sel["boxes"], sel["scores"], self.nms_thresh, self.nms_cmp,
-                                    seg_ids=sel["img_ids"].to(torch.int32), n_seg=self.B, presorted=True)
+                                    seg_ids=sel["img_ids"], n_seg=self.B, presorted=True)
         return {"labels": labels, "label_weights": lw, "bbox_targets": bt, "bbox_inside_weights": bw,
                 "boxes": sel["boxes"], "scores": sel["scores"], "img_ids": sel["img_ids"],
                 "keep": keep, "n_keep": n_keep}
@@ -155,7 +155,7 @@ class BoxOpsSession:
                 sel = ops_post.topk_decode(self.d_box[r0:r1], self.d_prob[r0:r1], self.anchors, self.top_n, self.activation,
                                            "fastrcnn", per_image=True, want=("img_ids", "scores"))
                 keep, n_keep = ops_post.nms(sel["boxes"], sel["scores"], self.nms_thresh, self.nms_cmp,
-                                            seg_ids=sel["img_ids"].to(torch.int32), n_seg=n, presorted=True)
+                                            seg_ids=sel["img_ids"], n_seg=n, presorted=True)
                 ev_k.record(s_k)
                 mark("krn%d" % c0, s_k)
             k0, k1 = c0 * kper, (c0 + n) * kper

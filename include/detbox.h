@@ -51,6 +51,9 @@ extern "C" {
  * scores non-increasing inside a segment (what detbox_topk_decode(per_image=1) emits) — so the
  * sort and the gather are skipped.  Needs box_stride == 4 and 16-byte aligned boxes. */
 #define DETBOX_NMS_PRESORTED 0x100
+/* OR-able into cmp_mode: seg_ids_dev points at int64 ids (what detbox_topk_decode writes as img_ids_dev);
+ * they are narrowed inside the segment-count pass, so the caller needs no conversion kernel. */
+#define DETBOX_NMS_SEG_I64 0x200
 /* suppression rule variants of libs/boxes/nms.pyx (detbox_nms_variant) */
 #define DETBOX_NMS_VARIANT_PLAIN       0   /* nms             nms.pyx:17-68   IoU only                                    */
 #define DETBOX_NMS_VARIANT_NEW         1   /* nms_new         nms.pyx:70-123  + inter/area_i > 0.95 or inter/area_j > 0.95 */
