@@ -45,6 +45,7 @@ struct GtChunk {
     double x1[GCH], y1[GCH], x2[GCH], y2[GCH], area[GCH];
     unsigned long long colmax[GCH];
     float4 fbox[GCH];                                // the same boxes as float32, for the conservative slice test
+    float4 genc[GCH];                                // box_math.cuh::gt_pre — the GT half of the encode, once per GT
     float cls[GCH];
 };
 
@@ -215,14 +216,18 @@ __device__ __forceinline__ void label_of(const TargetParams &p, float gcls, doub
     l_out = l; flag_out = flag;
 }
 
-__device__ __forceinline__ void store_anchor(const TargetParams &p, long o, const float4 anc, const float4 gbox, float l, bool flag)
+// One anchor's three outputs.  FRCNN: `ge` is gt_pre() of the matched GT and raw_gt() fetches the row itself for the
+// rare plain-division path; otherwise raw_gt() feeds the linear encodings.
+template <bool FRCNN, typename RawGt>
+__device__ __forceinline__ void store_anchor(const TargetParams &p, long o, const float4 anc, const float4 ge, RawGt raw_gt, float l, bool flag)
 {
     p.labels[o] = l;
-    p.targets[o] = encode_box(anc, gbox, p.enc);                            // anchor.py:133-135 every anchor
+    if (FRCNN) p.targets[o] = encode_fastrcnn_pre(anc, ge, raw_gt);         // anchor.py:133-135 every anchor
+    else p.targets[o] = encode_linear(anc, raw_gt(), p.enc == DETBOX_ENC_LINEAR);
     p.inside[o] = flag ? p.bbw : make_float4(0, 0, 0, 0);                   // :136-138
 }
 
-template <int EMIT_ILP>                 // EMIT_ILP: anchors encoded side by side in the emit loops
+template <int EMIT_ILP, bool FRCNN>     // EMIT_ILP: anchors encoded side by side in the emit loops
 __global__ void __launch_bounds__(AT_THREADS, 4)
 anchor_target_kernel(const TargetParams p)
 {
@@ -237,6 +242,7 @@ anchor_target_kernel(const TargetParams p)
     const int g0 = p.gt_off[b];
     const int G = p.gt_off[b + 1] - g0;
     const long tile0 = (long)blockIdx.x * AT_TILE;
+    const int rem = (int)min((long)AT_TILE, p.A - tile0);      // anchors of this tile (the last one may be partial)
     const float INF = __int_as_float(0x7f800000);
 
     if (G == 0) {                                    // anchor.py:89-91,133: all background, zero targets
@@ -273,6 +279,7 @@ anchor_target_kernel(const TargetParams p)
             sm.area[tid] = (x2 - x1 + 1) * (y2 - y1 + 1);                 // bbox.pyx:34-37
             sm.cls[tid] = q[4];
             sm.fbox[tid] = f;
+            sm.genc[tid] = gt_pre(f);
             const unsigned long long cm = p.colmax[g0 + tid];
             sm.colmax[tid] = cm;
             flags = (may_touch(tbox, x1, y1, x2, y2) ? 1 : 0) | (cm == 0ull ? 2 : 0);   // all-zero column: every anchor ties (anchor.py:46)
@@ -296,26 +303,26 @@ anchor_target_kernel(const TargetParams p)
         else { const float *q = p.gt + (size_t)g0 * 5; gbox = make_float4(q[0], q[1], q[2], q[3]); gcls = q[4]; }
         float l0; bool f0;
         label_of(p, gcls, 0.0, zero_any != 0, 0.0, l0, f0);     // the same for every anchor of the tile
-        int nfg = 0, nbg = 0;
+        const float4 ge = gt_pre(gbox);
+        const float4 *anc_t = p.anchors + tile0;
+        const long o0 = (long)b * p.A + tile0;
 #pragma unroll 1
         for (int h = 0; h < AT_ITEMS; h += EMIT_ILP) {          // EMIT_ILP independent load -> encode -> store chains
             float4 anc[EMIT_ILP];
 #pragma unroll
             for (int i = 0; i < EMIT_ILP; ++i) {
-                const long a = tile0 + (h + i) * AT_THREADS + tid;
-                anc[i] = a < p.A ? p.anchors[a] : make_float4(0, 0, 0, 0);
+                const int off = (h + i) * AT_THREADS + tid;
+                anc[i] = off < rem ? anc_t[off] : make_float4(0, 0, 0, 0);
             }
 #pragma unroll
             for (int i = 0; i < EMIT_ILP; ++i) {
-                const long a = tile0 + (h + i) * AT_THREADS + tid;
-                if (a < p.A) { store_anchor(p, (long)b * p.A + a, anc[i], gbox, l0, f0); nfg += (l0 >= 1.0f); nbg += (l0 == 0.0f); }
+                const int off = (h + i) * AT_THREADS + tid;
+                if (off < rem) store_anchor<FRCNN>(p, o0 + off, anc[i], ge, [&]() { return gbox; }, l0, f0);
             }
         }
-        nfg = __reduce_add_sync(0xffffffffu, nfg);
-        nbg = __reduce_add_sync(0xffffffffu, nbg);
-        if (lane == 0) {
-            if (nfg) atomicAdd(&p.counts[b * 2 + 0], nfg);
-            if (nbg) atomicAdd(&p.counts[b * 2 + 1], nbg);
+        if (tid == 0) {                                          // every anchor of the tile has the label l0
+            if (l0 >= 1.0f) atomicAdd(&p.counts[b * 2 + 0], rem);
+            if (l0 == 0.0f) atomicAdd(&p.counts[b * 2 + 1], rem);
         }
         return;
     }
@@ -333,6 +340,7 @@ anchor_target_kernel(const TargetParams p)
             sm.area[tid] = (x2 - x1 + 1) * (y2 - y1 + 1);                 // bbox.pyx:34-37
             sm.cls[tid] = q[4];
             sm.fbox[tid] = make_float4(q[0], q[1], q[2], q[3]);
+            sm.genc[tid] = gt_pre(sm.fbox[tid]);
             sm.colmax[tid] = p.colmax[g0 + c0 + tid];
         }
         __syncthreads();
@@ -428,22 +436,29 @@ anchor_target_kernel(const TargetParams p)
     // Emit phase: a plain streaming loop over the tile — anchor in, 36 bytes out — with EMIT_ILP independent
     // encode chains per thread (the encode is a long dependent sequence: reciprocal, log, divisions).
     // Every thread reads back only what it wrote itself, so no barrier is needed in between.
+    const float4 *anc_t = p.anchors + tile0;
+    const long o0 = (long)b * p.A + tile0;
 #pragma unroll 1
     for (int h = 0; h < AT_ITEMS; h += EMIT_ILP) {
-        float4 anc[EMIT_ILP], gbox[EMIT_ILP]; int2 r[EMIT_ILP];
+        float4 anc[EMIT_ILP], ge[EMIT_ILP]; int2 r[EMIT_ILP];
 #pragma unroll
         for (int i = 0; i < EMIT_ILP; ++i) {
-            const long a = tile0 + (h + i) * AT_THREADS + tid;
-            anc[i] = a < p.A ? p.anchors[a] : make_float4(0, 0, 0, 0);
+            const int off = (h + i) * AT_THREADS + tid;
+            anc[i] = off < rem ? anc_t[off] : make_float4(0, 0, 0, 0);
             r[i] = s_res[h + i][tid];
             const int g = r[i].y & 0x7fffffff;
-            if (single) gbox[i] = sm.fbox[g];
-            else { const float *q = p.gt + (size_t)(g0 + g) * 5; gbox[i] = make_float4(q[0], q[1], q[2], q[3]); }
+            if (single) ge[i] = sm.genc[g];
+            else { const float *q = p.gt + (size_t)(g0 + g) * 5; ge[i] = gt_pre(make_float4(q[0], q[1], q[2], q[3])); }
         }
 #pragma unroll
         for (int i = 0; i < EMIT_ILP; ++i) {
-            const long a = tile0 + (h + i) * AT_THREADS + tid;
-            if (a < p.A) store_anchor(p, (long)b * p.A + a, anc[i], gbox[i], __int_as_float(r[i].x), r[i].y < 0);
+            const int off = (h + i) * AT_THREADS + tid;
+            const int g = r[i].y & 0x7fffffff;
+            auto raw_gt = [&]() {
+                if (single) return sm.fbox[g];
+                const float *q = p.gt + (size_t)(g0 + g) * 5; return make_float4(q[0], q[1], q[2], q[3]);
+            };
+            if (off < rem) store_anchor<FRCNN>(p, o0 + off, anc[i], ge[i], raw_gt, __int_as_float(r[i].x), r[i].y < 0);
         }
     }
     nfg = __reduce_add_sync(0xffffffffu, nfg);
@@ -540,9 +555,10 @@ extern "C" int detbox_anchor_target(const float *anchors, long A, const float *g
     }
     DETBOX_TRACE_BEGIN(DETBOX_K_TARGET_ASSIGN, st);
     static const int ilp = []() { const char *e = getenv("DETBOX_AT_ILP"); return e ? atoi(e) : 1; }();   // measured: 1 and 2 tie, 4 spills
-    if (ilp == 2) anchor_target_kernel<2><<<grid, AT_THREADS, 0, st>>>(p);
-    else if (ilp == 4) anchor_target_kernel<4><<<grid, AT_THREADS, 0, st>>>(p);
-    else anchor_target_kernel<1><<<grid, AT_THREADS, 0, st>>>(p);
+    const bool frcnn = p.enc == DETBOX_ENC_FASTRCNN;
+    if (!frcnn) anchor_target_kernel<1, false><<<grid, AT_THREADS, 0, st>>>(p);
+    else if (ilp == 2) anchor_target_kernel<2, true><<<grid, AT_THREADS, 0, st>>>(p);
+    else anchor_target_kernel<1, true><<<grid, AT_THREADS, 0, st>>>(p);
     DETBOX_TRACE_END(DETBOX_K_TARGET_ASSIGN, st);
     DETBOX_LAUNCH_CHECK();
     long wb = (A / 4 + 255) / 256;
