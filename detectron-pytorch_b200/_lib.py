@@ -49,6 +49,7 @@ SIGNATURES = {
     "detbox_version": (c_int, []),
     "detbox_last_cuda_error": (c_int, []),
     "detbox_trace_kernel": (c_int, [c_int, c_void, c_void]),
+    "detbox_selftest_rcp": (c_int, [ctypes.c_uint32, ctypes.c_uint32, c_void, c_void]),
     "detbox_base_anchors_host": (c_int, [P_double, c_int, P_double, c_int, c_long, P_double]),
     "detbox_anchor_pyramid": (c_int, [c_void, c_int, P_int, P_int, P_int, P_int, c_void, c_int, c_void]),
     "detbox_bbox_overlaps_f64": (c_int, [c_void, c_long, c_void, c_long, c_void, c_void]),

@@ -82,8 +82,8 @@ int detbox_last_cuda_error(void);
  * cudaEventRecord calls, nothing else; results are unaffected. */
 #define DETBOX_K_NONE            0
 #define DETBOX_K_ANCHORS         1   /* anchor_pyramid_kernel                       */
-#define DETBOX_K_TARGET_COLMAX   2   /* anchor_target_kernel<1>  per-GT column max  */
-#define DETBOX_K_TARGET_ASSIGN   3   /* anchor_target_kernel<2>  labels + targets   */
+#define DETBOX_K_TARGET_COLMAX   2   /* colmax_kernel            per-GT column max  */
+#define DETBOX_K_TARGET_ASSIGN   3   /* anchor_target_kernel     labels + targets   */
 #define DETBOX_K_TARGET_WEIGHTS  4   /* label_weight_kernel                         */
 #define DETBOX_K_OBJECTNESS      5   /* objectness_kernel (score keys + histogram)  */
 #define DETBOX_K_NMS_MASK        6   /* mask_kernel                                 */
@@ -92,6 +92,10 @@ int detbox_last_cuda_error(void);
 #define DETBOX_K_ROI_BWD         9   /* roi_bwd_kernel (without the zero fill)      */
 #define DETBOX_K_ROI_ZERO       10   /* zero fill of the dense gradient maps        */
 int detbox_trace_kernel(int kernel_id, void *start_event, void *stop_event);
+/* Diagnostics: the in-range reciprocal of the encode (box_math.cuh::rcp_rn_inrange) against the IEEE
+ * round-to-nearest reciprocal for every float whose bit pattern lies in [bits_lo, bits_hi];
+ * *mismatches_dev (device, uint64) receives the number of differing results. */
+int detbox_selftest_rcp(uint32_t bits_lo, uint32_t bits_hi, unsigned long long *mismatches_dev, void *stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Anchors — replaces libs/boxes/anchor.py:101-189 (anchors / generate_anchors) and :30-70

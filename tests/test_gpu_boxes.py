@@ -194,6 +194,51 @@ def test_anchor_target_random_small(seed):
         check_target(got, b, gt, anc, cfg)
 
 
+def test_rcp_inrange_exhaustive():
+    """box_math.cuh::rcp_rn_inrange == the IEEE round-to-nearest reciprocal for EVERY float32 in [2^-20, 2^20]
+    (3.4e8 values, the range the encode's single test admits)."""
+    import torch
+    lo = int(np.float32(2.0 ** -20).view(np.uint32))
+    hi = int(np.float32(2.0 ** 20).view(np.uint32))
+    bad = torch.zeros(1, dtype=torch.int64, device="cuda")
+    rc = detbox.lib().detbox_selftest_rcp(lo, hi, bad.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    assert rc == 0
+    assert int(bad.item()) == 0
+
+
+def test_anchor_target_encode_paths_bit_exact():
+    """The assign kernel's encode takes FMA-corrected reciprocals when every numerator and divisor is inside
+    [2^-20, 2^20] and the plain IEEE divisions otherwise (box_math.cuh::encode_fastrcnn_pre).  Either way dx, dy must
+    equal the oracle's divisions BIT FOR BIT; dw, dh differ only through logf.  GT rows here force both paths:
+    a GT equal to an anchor (zero numerators), a huge GT, a width below 2^-20, an inverted GT (log of a negative)."""
+    scales = [[2, 2.52, 3.175], [4, 5.04, 6.349], [8, 10.079, 12.7]]
+    anc = O.anchor_pyramid([8, 16, 32], 192, 320, scales, [1, 2.5], 16).astype(np.float32)
+    tiny = [0.5, 5.0, np.float32(-0.5 + 1.2e-7), 40.0, 1]            # gw = x2 - x1 + 1 ~ 1.2e-7 < 2^-20
+    special = [
+        np.r_[anc[1234], 1], np.r_[anc[17], 2],                     # zero numerators / log(1) = +0
+        [-3e6, -2e6, 4e6, 3e6, 1],                                   # gw, gh > 2^20
+        tiny,
+        [90, 80, 40, 30, 2],                                         # inverted: gw, gh < 0 -> NaN targets, as NumPy
+        [33.25, 41.5, 97.75, 160.125, 3],
+        [7, 5, 6, 40, 1],                                            # gw = 0: log(0) = -inf
+    ]
+    gts = [np.asarray(special, np.float32)]                          # (the huge GT overlaps every anchor)
+    for first in range(len(special)):                                # each special row as GT 0: the target of every
+        rows = [special[first], special[5], special[0]]              # anchor that overlaps nothing (argmax of a zero row)
+        gts.append(np.asarray(rows, np.float32))
+    got = run_target(anc, gts, CPR)
+    for b, gt in enumerate(gts):
+        with np.errstate(all="ignore"):
+            lab, lw, bt, bw = O.anchor_encode(gt, anc, CPR)[:4]
+        np.testing.assert_array_equal(got[0][b], lab)
+        g, w = got[2][b], bt
+        nan_g, nan_w = np.isnan(g), np.isnan(w)
+        np.testing.assert_array_equal(nan_g, nan_w)
+        ok = ~nan_w[:, :2]
+        assert np.array_equal(g[:, :2].view(np.uint32)[ok], w[:, :2].view(np.uint32)[ok])
+        np.testing.assert_allclose(g[:, 2:], w[:, 2:], rtol=RTOL, atol=ATOL, equal_nan=True)
+
+
 def test_anchor_target_host_entry(cpr_anchors, golden):
     """detbox_anchor_target_host: host arrays in/out through the C ABI (the end-to-end boundary)."""
     import ctypes
