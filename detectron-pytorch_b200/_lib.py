@@ -85,6 +85,7 @@ SIGNATURES = {
     "detbox_threshold_segments": (c_int, [c_void, c_void, c_long, c_int, c_float, c_void, c_void, c_void]),
     "detbox_to_dets": (c_int, [c_void, c_void, c_int, c_void, c_void, c_void, c_long, c_int, c_int, c_int, c_float,
                                c_void, c_long, c_void, c_void]),
+    "detbox_dets_cluster": (c_int, [c_void, c_long, c_void, c_void, c_long, c_void, c_void, c_void]),
     "_nms": (None, [c_void, c_void, c_void, c_int, c_int, c_float, c_int]),
     "detbox_nms_host": (c_int, [c_void, c_int, c_double, c_int, c_void, c_void, c_int]),
     "detbox_anchor_target_host": (c_int, [c_void, c_long, c_void, c_int, ctypes.POINTER(TargetCfg),

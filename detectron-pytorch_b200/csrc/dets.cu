@@ -147,6 +147,77 @@ to_dets_kernel(const DetsArgs a)
     }
 }
 
+
+// ---- single_shot.py:401-415 dets_cluster: score-weighted box voting over nms_multianchor's clusters -----------
+// One thread per kept box.  clusters[] is read by every thread of a warp at the same index (broadcast), members are
+// met in ascending index order — np.where's order — so the float32 sums below reproduce NumPy's: the score sum is
+// np.sum's pairwise scheme (8 running sums over blocks of 8, halves above 128 elements), the row sum over axis 0 is
+// sequential.  Three passes over clusters[] (count, score sum, vote); n and n_keep are a few thousand here.
+struct ClusterCursor {
+    const int64_t *cl; const float *dets; long i; int64_t mine;
+    __device__ __forceinline__ long next() { while (cl[i] != mine) ++i; return i++; }
+    __device__ __forceinline__ float next_score() { return dets[next() * 5 + 4]; }
+};
+
+__device__ float pairwise_sum(ClusterCursor &c, int n)       // numpy/_core/src/umath/loops_utils.h.src pairwise sum
+{
+    if (n < 8) {
+        float r = 0.0f;
+        for (int i = 0; i < n; ++i) r += c.next_score();
+        return r;
+    }
+    if (n <= 128) {
+        float r[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) r[j] = c.next_score();
+        int i = 8;
+        for (; i < n - (n % 8); i += 8) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) r[j] += c.next_score();
+        }
+        float res = ((r[0] + r[1]) + (r[2] + r[3])) + ((r[4] + r[5]) + (r[6] + r[7]));
+        for (; i < n; ++i) res += c.next_score();
+        return res;
+    }
+    int n2 = n / 2; n2 -= n2 % 8;
+    const float a = pairwise_sum(c, n2);
+    return a + pairwise_sum(c, n - n2);
+}
+
+__global__ void __launch_bounds__(128)
+dets_cluster_kernel(const float *__restrict__ dets, long n, const int64_t *__restrict__ keep, const int32_t *__restrict__ n_keep_dev,
+                    long n_keep_max, const int64_t *__restrict__ clusters, float *__restrict__ out)
+{
+    const long k = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long nk = n_keep_dev ? min((long)*n_keep_dev, n_keep_max) : n_keep_max;
+    if (k >= nk) return;
+    const int64_t mine = keep[k];
+    int m = 0; long first = -1;
+    for (long i = 0; i < n; ++i) if (clusters[i] == mine) { if (m == 0) first = i; ++m; }
+    float *o = out + k * 5;
+    if (m <= 1) {                                  // a cluster of one keeps its row (m == 0: the keeper's own row)
+        const long src = m == 1 ? first : (long)mine;
+        const bool ok = src >= 0 && src < n;
+        for (int c = 0; c < 5; ++c) o[c] = ok ? dets[src * 5 + c] : 0.0f;
+        return;
+    }
+    ClusterCursor cur{clusters, dets, first, mine};
+    const float S = pairwise_sum(cur, m);
+    cur.i = first;
+    float acc[4], best = 0.0f;
+    for (int j = 0; j < m; ++j) {
+        const long i = cur.next();
+        const float s = dets[i * 5 + 4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const float v = dets[i * 5 + c] * s / S;
+            acc[c] = j == 0 ? v : acc[c] + v;
+        }
+        best = (j == 0 || s > best) ? s : best;    // np.max
+    }
+    o[0] = acc[0]; o[1] = acc[1]; o[2] = acc[2]; o[3] = acc[3]; o[4] = best;
+}
+
 }  // namespace
 
 extern "C" int detbox_threshold_segments(const float *scores, const int64_t *img_ids, long n, int n_images,
@@ -178,6 +249,19 @@ extern "C" int detbox_to_dets(const float *boxes, const float *probs, int C, con
     a.multi = multi_label != 0; a.thr = score_threshold;
     a.dets = dets; a.cap = cap; a.offsets = det_offsets;
     to_dets_kernel<<<1, DT_THREADS, 0, as_stream(stream)>>>(a);
+    DETBOX_LAUNCH_CHECK();
+    return DETBOX_OK;
+}
+
+extern "C" int detbox_dets_cluster(const float *dets, long n, const int64_t *keep, const int32_t *n_keep_dev, long n_keep_max,
+                                   const int64_t *clusters, float *out, void *stream)
+{
+    if (n < 0 || n_keep_max < 0) return DETBOX_ERR_INVALID;
+    if (n == 0 || n_keep_max == 0) return DETBOX_OK;
+    if (!dets || !keep || !clusters || !out) return DETBOX_ERR_INVALID;
+    const long blocks = (n_keep_max + 127) / 128;
+    if (blocks >= (1L << 31)) return DETBOX_ERR_UNSUPPORTED;
+    dets_cluster_kernel<<<(unsigned)blocks, 128, 0, as_stream(stream)>>>(dets, n, keep, n_keep_dev, n_keep_max, clusters, out);
     DETBOX_LAUNCH_CHECK();
     return DETBOX_OK;
 }

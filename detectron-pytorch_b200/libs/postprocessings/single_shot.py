@@ -1,10 +1,13 @@
 """libs.postprocessings.single_shot (reference libs/postprocessings/single_shot.py): the NumPy-facing
 post-processing — compute_detection (:13-60: decode + clip every anchor, per class threshold -> NMS -> top
 max_det_num), compute_detection_new (:62-126: class-agnostic NMS on the objectness, then per-class rows),
-nms_advanced (:128-152) and nms_stitch (:154-177) over nms_multianchor.  Decode and every NMS run on the
+nms_advanced (:128-152) and nms_stitch (:154-177) over nms_multianchor, dets_cluster (:401-415, box voting).  Decode and every NMS run on the
 device; the per-image / per-class Python loops are upstream's."""
 import numpy as np
+import torch
 
+from ... import ops_post
+from ..._lib import DetboxError
 from ..boxes.cython_nms import nms_multianchor
 from ..boxes.nms_wrapper import nms
 from ..configs import config as cfg
@@ -115,3 +118,17 @@ def nms_stitch(Dets):
             dets = dets[np.setdiff1d(all_inds, np.unique(np.hstack(drops_inds)))]
         Dets_new.append(dets)
     return Dets_new
+
+
+def dets_cluster(dets, keeps, clusters):
+    """single_shot.py:401-415: score-weighted box voting — one row per kept index, the score-weighted mean box of
+    its cluster and the cluster's best score (`keeps`, `clusters` as nms_multianchor returns them).  Runs on the
+    device (detbox_dets_cluster); an empty `keeps` returns `dets` like upstream."""
+    keeps = np.asarray(keeps, dtype=np.int64).reshape(-1)
+    if keeps.size == 0:
+        return dets
+    if not torch.cuda.is_available():
+        raise DetboxError("detbox has no CPU path: a CUDA device is required")
+    d = torch.from_numpy(np.ascontiguousarray(dets[:, :5], dtype=np.float32)).cuda()
+    out = ops_post.dets_cluster(d, torch.from_numpy(keeps).cuda(), torch.from_numpy(np.asarray(clusters, dtype=np.int64)).cuda())
+    return out.cpu().numpy()

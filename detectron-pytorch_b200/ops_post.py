@@ -154,3 +154,22 @@ def to_dets(boxes, probs, img_ids, n_images, activation="softmax", multi_label=T
           "to_dets")
     _count(1)
     return dets, off
+
+
+def dets_cluster(dets, keep, clusters, n_keep=None):
+    """detbox_dets_cluster (single_shot.py:401-415 on the device): score-weighted box voting.  dets float32 [n,5],
+    keep int64 [k] / clusters int64 [n] as nms(..., variant="multianchor", want_clusters=True) returns them, `n_keep`
+    an optional device int32 scalar (nms()'s n_keep[-1:]).  Returns float32 [k,5]; rows past n_keep are zero."""
+    d = _dev(dets)
+    if d.dim() != 2 or d.shape[1] != 5:
+        raise _lib.DetboxError("dets_cluster: dets must be [n,5]")
+    k = _dev(keep, torch.int64, "keep").view(-1)
+    c = _dev(clusters, torch.int64, "clusters").view(-1)
+    if c.numel() != d.shape[0]:
+        raise _lib.DetboxError("dets_cluster: clusters must have one entry per row of dets")
+    nk = _dev(n_keep, torch.int32, "n_keep").view(-1) if n_keep is not None else None
+    out = torch.zeros((k.numel(), 5), dtype=torch.float32, device=d.device)
+    check(lib().detbox_dets_cluster(_ptr(d), d.shape[0], _ptr(k), _ptr(nk), k.numel(), _ptr(c), out.data_ptr(), _stream()),
+          "dets_cluster")
+    _count(1)
+    return out

@@ -327,6 +327,15 @@ int detbox_to_dets(const float *boxes_dev, const float *probs_dev, int C, const 
                    int activation, int multi_label, float score_threshold,
                    double *dets_dev, long cap, int32_t *det_offsets_dev, void *stream);
 
+/* libs/postprocessings/single_shot.py:401-415 dets_cluster — score-weighted box voting over the clusters
+ * detbox_nms_variant(MULTIANCHOR) returns: out row k (float32 [5]) = sum over the members i of cluster
+ * keep[k] (clusters[i] == keep[k], ascending i) of dets[i,:4] * score_i / sum(score), score = the members'
+ * maximum; a cluster of one copies its row.  Sums follow NumPy's float32 order (pairwise score sum,
+ * sequential row sum).  n_keep = *n_keep_dev when given (clamped to n_keep_max), else n_keep_max.
+ * dets [n,5] float32 contiguous, keep / clusters int64 (original indices), out [n_keep_max,5]. */
+int detbox_dets_cluster(const float *dets_dev, long n, const int64_t *keep_dev, const int32_t *n_keep_dev,
+                        long n_keep_max, const int64_t *clusters_dev, float *out_dev, void *stream);
+
 /* ---------------------------------------------------------------------------------------------
  * HOST-buffer entry points (copies inside; synchronous; scratch cached per device).
  * ------------------------------------------------------------------------------------------- */

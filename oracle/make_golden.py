@@ -180,11 +180,52 @@ def to_dets_golden(ref_root="/root/reference"):
     np.savez_compressed(os.path.join(GOLD, "to_dets.npz"), **out)
 
 
+def dets_cluster_cases():
+    """Synthetic (dets, keep, clusters) with clusters of 1, 2, 7, 8, 9, 130 and 400 members (NumPy's pairwise
+    summation changes shape at 8 and at 128 elements); members interleaved, keepers not in index order."""
+    rng = np.random.RandomState(11)
+    sizes = [1, 2, 7, 8, 9, 130, 400, 1, 33]
+    n = sum(sizes)
+    owner = rng.permutation(np.repeat(np.arange(len(sizes)), sizes))
+    keep = np.asarray([np.where(owner == c)[0][0] for c in range(len(sizes))], np.int64)
+    clusters = keep[owner]
+    xy = rng.uniform(0, 1800, (n, 2)); wh = rng.uniform(5, 200, (n, 2))
+    dets = np.concatenate([xy, xy + wh, rng.uniform(0.01, 1, (n, 1))], 1).astype(np.float32)
+    return [("synth", dets, keep[rng.permutation(len(sizes))], clusters)]
+
+
+def dets_cluster_golden(ref_root="/root/reference"):
+    """dets_cluster of libs/postprocessings/single_shot.py:401-415, lifted out of the module with `ast` at run time
+    (single_shot.py imports cv2-based code) and run on nms_multianchor's golden (keep, clusters) plus a synthetic
+    case with large clusters.  Nothing of the reference's text is stored."""
+    import ast
+    tree = ast.parse(open(os.path.join(ref_root, "libs/postprocessings/single_shot.py")).read())
+    ns = {"np": np}
+    for node in ast.walk(tree):
+        if isinstance(node, ast.FunctionDef) and node.name == "dets_cluster":
+            exec(compile(ast.Module(body=[node], type_ignores=[]), "<reference single_shot.py>", "exec"), ns)
+    g = np.load(os.path.join(GOLD, "nms_variants.npz"))
+    out = {}
+    for seed in range(4):
+        for thr in (0.3, 0.5):
+            d = g["d%d" % seed]
+            out["d%d_voted_%g" % (seed, thr)] = np.asarray(
+                ns["dets_cluster"](d.copy(), g["d%d_multi_keep_%g" % (seed, thr)], g["d%d_multi_clusters_%g" % (seed, thr)]), np.float32)
+    for name, d, keep, clusters in dets_cluster_cases():
+        out[name + "_dets"], out[name + "_keep"], out[name + "_clusters"] = d, keep, clusters
+        out[name + "_voted"] = np.asarray(ns["dets_cluster"](d.copy(), keep, clusters), np.float32)
+    out["numpy_version"] = np.asarray(np.__version__)
+    np.savez_compressed(os.path.join(GOLD, "dets_cluster.npz"), **out)
+
+
 def main():
     r = ref_loader.load()
     os.makedirs(GOLD, exist_ok=True)
     if "--only-to-dets" in sys.argv:
         to_dets_golden()
+        return
+    if "--only-dets-cluster" in sys.argv:
+        dets_cluster_golden()
         return
     if "--only-roi-sampling" in sys.argv:
         roi_sampling_golden(r)
@@ -334,6 +375,7 @@ def main():
     roi_sampling_golden(r)
     nms_variants_golden(r)
     to_dets_golden()
+    dets_cluster_golden()
 
     sz = sum(os.path.getsize(os.path.join(GOLD, f)) for f in os.listdir(GOLD))
     print("golden vectors written to", GOLD, "(%d KiB)" % (sz // 1024))

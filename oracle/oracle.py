@@ -620,3 +620,22 @@ def final_results_stage1(rpn_box, rpn_prob, anchors_, batch_size, score_threshol
     boxes, probs, img_ids = boxes[inds], probs[inds], img_ids[inds]
     keep = apply_nms_in_batch(boxes, probs, img_ids, activation, overlap_threshold, NMS_GT_F32)
     return to_dets(boxes[keep], probs[keep], img_ids[keep], batch_size, activation, True, score_threshold)
+
+
+# ------------------------------------------------------------------------------------------------
+# dets_cluster: score-weighted box voting over nms_multianchor's clusters
+# ------------------------------------------------------------------------------------------------
+def dets_cluster(dets, keeps, clusters):
+    """libs/postprocessings/single_shot.py:401-415 restated: per kept index, the rows of its cluster
+    (`clusters == ind`, ascending) are averaged with their scores as weights (float32, NumPy's own summation
+    order), the score becomes the cluster's maximum; a cluster of one keeps its row; no keeps -> `dets`."""
+    dets = np.asarray(dets, np.float32); clusters = np.asarray(clusters).reshape(-1)
+    rows = []
+    for ind in np.asarray(keeps).reshape(-1):
+        members = dets[np.where(clusters == ind)[0], :]
+        if members.shape[0] > 1:
+            score = members[:, 4]
+            voted = np.sum(members[:, :4] * score[:, None] / np.sum(score), axis=0)
+            members = np.concatenate([voted, [np.max(score)]]).astype(np.float32)
+        rows.append(members)
+    return np.vstack(rows) if rows else dets

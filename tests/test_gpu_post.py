@@ -320,3 +320,36 @@ def test_nms_variants_segmented_vs_oracle():
         np.testing.assert_array_equal(keep, np.concatenate(want_keep))
         if variant == "multianchor":
             np.testing.assert_array_equal(cl, want_cl)
+
+
+# ------------------------------------------------------------------------------ dets_cluster ----
+def test_dets_cluster_golden(golden):
+    """dets_cluster (single_shot.py:401-415) through the mirror against the reference's own outputs: float32 sums in
+    NumPy's order (pairwise score sum, sequential row sum), so rows agree to the last bit with the NumPy that recorded
+    the vectors; the stated bound is 1e-5 relative (north_star's float tolerance)."""
+    import importlib
+    ss = importlib.import_module(detbox.libs.__name__ + ".postprocessings.single_shot")
+    g = golden("dets_cluster"); nv = golden("nms_variants")
+    cases = [(nv["d%d" % s], nv["d%d_multi_keep_%g" % (s, t)], nv["d%d_multi_clusters_%g" % (s, t)], g["d%d_voted_%g" % (s, t)])
+             for s in range(4) for t in (0.3, 0.5)]
+    cases.append((g["synth_dets"], g["synth_keep"], g["synth_clusters"], g["synth_voted"]))
+    n_exact = 0
+    for d, keep, clusters, want in cases:
+        got = ss.dets_cluster(d, keep, clusters)
+        assert got.shape == want.shape and got.dtype == np.float32
+        np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-5 * 2048)
+        n_exact += int(np.array_equal(got, want))
+    assert n_exact == len(cases), "%d of %d cases bit-exact" % (n_exact, len(cases))
+    assert ss.dets_cluster(cases[0][0], [], cases[0][2]) is cases[0][0]          # upstream: no keeps -> dets
+
+
+def test_dets_cluster_after_device_nms():
+    """nms(variant='multianchor') -> dets_cluster without leaving the device (n_keep stays a device scalar)."""
+    from oracle.make_golden import variant_dets
+    d = variant_dets(5)
+    keep, nk, cl = detbox.nms(cu(d[:, :4]), cu(d[:, 4]), 0.4, detbox.NMS_GE_F64, variant="multianchor", want_clusters=True)
+    out = detbox.dets_cluster(cu(d), keep, cl, n_keep=nk[-1:])
+    m = int(nk[-1])
+    want = O.dets_cluster(d, keep[:m].cpu().numpy(), cl.cpu().numpy())
+    np.testing.assert_array_equal(out[:m].cpu().numpy(), want)
+    assert not out[m:].any()

@@ -160,6 +160,26 @@ def test_nms_variants(golden, seed, thr):
     np.testing.assert_array_equal(clusters, g["d%d_multi_clusters_%g" % (seed, thr)])
 
 
+def test_dets_cluster(golden):
+    """dets_cluster (single_shot.py:401-415): the oracle against outputs of the reference's own function.  The sums are
+    NumPy's on both sides, so the comparison is exact with the NumPy that recorded the vectors and within float32
+    rounding of the pairwise order otherwise."""
+    g = golden("dets_cluster")
+    nv = golden("nms_variants")
+    exact = str(g["numpy_version"]) == np.__version__
+    cases = [(nv["d%d" % s], nv["d%d_multi_keep_%g" % (s, t)], nv["d%d_multi_clusters_%g" % (s, t)], g["d%d_voted_%g" % (s, t)])
+             for s in range(4) for t in (0.3, 0.5)]
+    cases.append((g["synth_dets"], g["synth_keep"], g["synth_clusters"], g["synth_voted"]))
+    for d, keep, clusters, want in cases:
+        got = O.dets_cluster(d, keep, clusters)
+        assert got.shape == want.shape and got.dtype == np.float32
+        if exact:
+            np.testing.assert_array_equal(got, want)
+        else:
+            np.testing.assert_allclose(got, want, rtol=1e-6, atol=1e-4)
+    assert O.dets_cluster(cases[0][0], [], cases[0][2]) is not None and O.dets_cluster(cases[0][0], [], cases[0][2]).shape == cases[0][0].shape
+
+
 def test_to_dets(golden):
     """to_Dets* conversions (libs/nets/model.py:357-469): outputs recorded from the reference's own methods."""
     from oracle.make_golden import to_dets_cases, to_dets_inputs
