@@ -373,6 +373,7 @@ anchor_target_kernel(const TargetParams p)
     // chunks are re-staged per slice (all warps together).
 #pragma unroll 1
     for (int i = 0; i < AT_ITEMS; ++i) {
+        if (use_masks && smask[i][w] == 0) continue;             // no GT near this slice: the emit phase uses (l_zero, GT 0)
         const long a = tile0 + i * AT_THREADS + tid;
         const bool valid = a < p.A;
         float4 anc = make_float4(INF, INF, -INF, -INF);
@@ -438,6 +439,8 @@ anchor_target_kernel(const TargetParams p)
     // Every thread reads back only what it wrote itself, so no barrier is needed in between.
     const float4 *anc_t = p.anchors + tile0;
     const long o0 = (long)b * p.A + tile0;
+    const int2 r_zero = make_int2(__float_as_int(l_zero), flag_zero ? (int)0x80000000 : 0);
+    int nskip = 0;                                   // anchors of skipped slices: all carry l_zero
 #pragma unroll 1
     for (int h = 0; h < AT_ITEMS; h += EMIT_ILP) {
         float4 anc[EMIT_ILP], ge[EMIT_ILP]; int2 r[EMIT_ILP];
@@ -445,7 +448,9 @@ anchor_target_kernel(const TargetParams p)
         for (int i = 0; i < EMIT_ILP; ++i) {
             const int off = (h + i) * AT_THREADS + tid;
             anc[i] = off < rem ? anc_t[off] : make_float4(0, 0, 0, 0);
-            r[i] = s_res[h + i][tid];
+            const bool skipped = use_masks && smask[h + i][w] == 0;
+            r[i] = skipped ? r_zero : s_res[h + i][tid];
+            nskip += (skipped && off < rem);
             const int g = r[i].y & 0x7fffffff;
             if (single) ge[i] = sm.genc[g];
             else { const float *q = p.gt + (size_t)(g0 + g) * 5; ge[i] = gt_pre(make_float4(q[0], q[1], q[2], q[3])); }
@@ -461,6 +466,8 @@ anchor_target_kernel(const TargetParams p)
             if (off < rem) store_anchor<FRCNN>(p, o0 + off, anc[i], ge[i], raw_gt, __int_as_float(r[i].x), r[i].y < 0);
         }
     }
+    if (l_zero >= 1.0f) nfg += nskip;
+    if (l_zero == 0.0f) nbg += nskip;
     nfg = __reduce_add_sync(0xffffffffu, nfg);
     nbg = __reduce_add_sync(0xffffffffu, nbg);
     if (lane == 0) {

@@ -268,7 +268,7 @@ partition_kernel(const uint32_t *__restrict__ keys, long seg_len, const SegState
 {
     const int tid = threadIdx.x, lane = tid & 31;
     const uint32_t b0 = state[blockIdx.y].prefix;
-    const uint32_t limit = ((b0 + 1u) << 21) - 1u;      // key <= limit  <=>  bin <= b0  (b0 <= 2047: no overflow past 2^32 - 1)
+
     const long seg0 = (long)blockIdx.y * seg_len;
     const uint32_t *k = keys + seg0;
     uint32_t *win_cnt = cnt + 2 * blockIdx.y, *cand_cnt = win_cnt + 1;
@@ -297,23 +297,57 @@ partition_kernel(const uint32_t *__restrict__ keys, long seg_len, const SegState
         }
     };
     if (VEC) {
+        // 8 keys per thread and trip.  The thread classifies its own keys, ONE packed warp scan (winners in the low
+        // half, candidates in the high half) turns the counts into positions, and ONE 64-bit atomic per warp and trip
+        // reserves both ranges — the pair of 32-bit counters is one aligned word.  (A ballot + atomic per key made
+        // every trip wait for up to 16 round trips to L2.)  The next trip's loads are issued before that wait.
         const long n4 = seg_len >> 2;
         const uint4 *k4 = reinterpret_cast<const uint4 *>(k);
-        for (long q0 = (long)blockIdx.x * TK_THREADS * 2; q0 < n4; q0 += (long)gridDim.x * TK_THREADS * 2) {
-            uint4 v[2]; bool ok[2];
+        unsigned long long *cnt64 = reinterpret_cast<unsigned long long *>(win_cnt);
+        const long stride = (long)gridDim.x * TK_THREADS * 2;
+        long q0 = (long)blockIdx.x * TK_THREADS * 2;
+        uint4 v[2], nv[2];
+        auto load = [&](long base, uint4 *dst) {
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
-                const long q = q0 + j * TK_THREADS + tid;
-                ok[j] = q < n4;
-                v[j] = ok[j] ? __ldcs(k4 + q) : make_uint4(~0u, ~0u, ~0u, ~0u);
+                const long q = base + j * TK_THREADS + tid;
+                dst[j] = q < n4 ? __ldcs(k4 + q) : make_uint4(~0u, ~0u, ~0u, ~0u);      // bin 2047 > b0 unless b0 == 2047: see `ok`
             }
+        };
+        if (q0 < n4) load(q0, v);
+        for (; q0 < n4; q0 += stride) {
+            if (q0 + stride < n4) load(q0 + stride, nv);
+            uint32_t kk[8] = {v[0].x, v[0].y, v[0].z, v[0].w, v[1].x, v[1].y, v[1].z, v[1].w};
+            unsigned packed = 0;
 #pragma unroll
-            for (int j = 0; j < 2; ++j) {
-                const uint32_t lo = min(min(v[j].x, v[j].y), min(v[j].z, v[j].w));
-                if (!__any_sync(0xffffffffu, ok[j] && lo <= limit)) continue;
-                const long r = (q0 + j * TK_THREADS + tid) << 2;
-                emit(v[j].x, r, ok[j]); emit(v[j].y, r + 1, ok[j]); emit(v[j].z, r + 2, ok[j]); emit(v[j].w, r + 3, ok[j]);
+            for (int j = 0; j < 8; ++j) {
+                const bool ok = q0 + (j >> 2) * TK_THREADS + tid < n4;
+                const uint32_t bin = kk[j] >> 21;
+                packed += (ok && bin < b0 ? 1u : 0u) + (ok && bin == b0 ? 0x10000u : 0u);
             }
+            if (__any_sync(0xffffffffu, packed != 0)) {
+                unsigned incl = packed;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+                unsigned long long base = 0;
+                if (lane == 31) base = atomicAdd(cnt64, (unsigned long long)(incl & 0xffffu) | ((unsigned long long)(incl >> 16) << 32));
+                base = __shfl_sync(0xffffffffu, base, 31);
+                size_t wpos = (size_t)blockIdx.y * K + (uint32_t)base + ((incl - packed) & 0xffffu);
+                size_t cpos = (size_t)seg0 + (uint32_t)(base >> 32) + ((incl - packed) >> 16);
+                if (packed) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const long q = q0 + (j >> 2) * TK_THREADS + tid;
+                        const uint32_t bin = kk[j] >> 21;
+                        if (q < n4 && bin <= b0) {
+                            const uint32_t idx = (uint32_t)(seg0 + (q << 2) + (j & 3));
+                            if (bin < b0) { ckeys[wpos] = kk[j]; cvals[wpos] = idx; ++wpos; }
+                            else { cand_keys[cpos] = kk[j]; cand_idx[cpos] = idx; ++cpos; }
+                        }
+                    }
+                }
+            }
+            v[0] = nv[0]; v[1] = nv[1];
         }
     } else {
         for (long r0 = (long)blockIdx.x * TK_THREADS; r0 < seg_len; r0 += (long)gridDim.x * TK_THREADS) {

@@ -12,6 +12,8 @@ intermediate host synchronisation, and the results are copied back into pinned h
 """
 from __future__ import annotations
 
+import os
+
 import numpy as np
 import torch
 
@@ -56,22 +58,73 @@ class BoxOpsSession:
         self._keep_out = pin((self.K,), torch.int64)
         self._h_nk = None
         self._streams = [torch.cuda.Stream(self.dev) for _ in range(3)]     # copy-in, kernels, copy-out
+        # run_device's second stream (detection chain).  DETBOX_SIDE_PRIORITY: 0 = same priority, -1 = above the
+        # anchor-target chain's stream.
+        self._side_stream = torch.cuda.Stream(self.dev, priority=int(os.environ.get("DETBOX_SIDE_PRIORITY", "-1")))
+        self.overlap = os.environ.get("DETBOX_OVERLAP", "1") != "0"
         self.h2d_bytes = 0
         self.d2h_bytes = 0
 
     # ------------------------------------------------------------------ device-resident path --
-    def run_device(self, gt, gt_offsets, rpn_prob, rpn_box, regenerate_anchors=True):
-        """gt [sumG,5], gt_offsets int32 [B+1], rpn_prob [B*A,C], rpn_box [B*A,4] — CUDA tensors."""
+    def run_device(self, gt, gt_offsets, rpn_prob, rpn_box, regenerate_anchors=True, overlap=None):
+        """gt [sumG,5], gt_offsets int32 [B+1], rpn_prob [B*A,C], rpn_box [B*A,4] — CUDA tensors.
+
+        The two halves of the path share nothing but the anchors: the anchor-target chain (tile boxes ->
+        column max -> assign -> label weights; long, bandwidth-heavy kernels) and the detection chain
+        (objectness -> top-k -> decode -> NMS; a dozen short kernels, several with one block per image).
+        `overlap` (default: self.overlap) forks the detection chain onto a second stream after the anchors
+        exist and joins it before returning, so its latency-bound kernels run in the gaps of the other chain.
+        Results are identical either way; fork / join are stream waits, so the whole call stays capturable
+        in one CUDA graph."""
+        overlap = self.overlap if overlap is None else overlap
         if regenerate_anchors:      # the reference rebuilds the pyramid for every batch (data_layer.py:138)
             self.anchors = ops.anchor_pyramid(*self.anchor_args, device=self.dev)
-        labels, lw, bt, bw = ops.anchor_target(self.anchors, gt, gt_offsets, self.tcfg)
-        sel = ops_post.topk_decode(rpn_box, rpn_prob, self.anchors, self.top_n, self.activation, "fastrcnn",
-                                   per_image=True, want=("img_ids", "scores"))
-        keep, n_keep = ops_post.nms(sel["boxes"], sel["scores"], self.nms_thresh, self.nms_cmp,
-                                    seg_ids=sel["img_ids"], n_seg=self.B, presorted=True)
+
+        def detections():
+            sel = ops_post.topk_decode(rpn_box, rpn_prob, self.anchors, self.top_n, self.activation, "fastrcnn",
+                                       per_image=True, want=("img_ids", "scores"))
+            keep, n_keep = ops_post.nms(sel["boxes"], sel["scores"], self.nms_thresh, self.nms_cmp,
+                                        seg_ids=sel["img_ids"], n_seg=self.B, presorted=True)
+            return sel, keep, n_keep
+
+        if overlap:
+            cur = torch.cuda.current_stream(self.dev)
+            side = self._side_stream
+            side.wait_stream(cur)                                  # fork: after the anchors and every earlier use of the inputs
+            with torch.cuda.stream(side):
+                sel, keep, n_keep = detections()
+            labels, lw, bt, bw = ops.anchor_target(self.anchors, gt, gt_offsets, self.tcfg)
+            cur.wait_stream(side)                                  # join
+        else:
+            labels, lw, bt, bw = ops.anchor_target(self.anchors, gt, gt_offsets, self.tcfg)
+            sel, keep, n_keep = detections()
         return {"labels": labels, "label_weights": lw, "bbox_targets": bt, "bbox_inside_weights": bw,
                 "boxes": sel["boxes"], "scores": sel["scores"], "img_ids": sel["img_ids"],
                 "keep": keep, "n_keep": n_keep}
+
+    def run_device_graph(self, gt, gt_offsets, rpn_prob, rpn_box):
+        """run_device captured ONCE in a CUDA graph (both streams, fork and join included) and replayed: one
+        launch call per step instead of ~17, so the host never paces the device.  The graph is bound to the
+        argument tensors (addresses and shapes): refill them in place between calls; a different tensor
+        re-captures.  Returns the SAME output tensors on every call — each replay overwrites them."""
+        key = tuple((t.data_ptr(), tuple(t.shape)) for t in (gt, gt_offsets, rpn_prob, rpn_box))
+        if getattr(self, "_graph_key", None) != key:
+            cur = torch.cuda.current_stream(self.dev)
+            warm = torch.cuda.Stream(self.dev)
+            warm.wait_stream(cur)
+            with torch.cuda.stream(warm):                          # workspaces and allocator pools settle before capture
+                for _ in range(2):
+                    self.run_device(gt, gt_offsets, rpn_prob, rpn_box)
+            cur.wait_stream(warm)
+            torch.cuda.synchronize(self.dev)
+            graph = torch.cuda.CUDAGraph()
+            n0 = ops.launches()
+            with torch.cuda.graph(graph):
+                out = self.run_device(gt, gt_offsets, rpn_prob, rpn_box)
+            self.graph_launches = ops.launches() - n0              # kernels per replay
+            self._graph, self._graph_out, self._graph_key = graph, out, key
+        self._graph.replay()
+        return self._graph_out
 
     # ----------------------------------------------------------------------- host-buffer path --
     def stage_gt(self, gt_boxes_list):

@@ -80,3 +80,34 @@ def test_run_host_targets_on_device():
         assert dev[k].is_cuda and torch.equal(dev[k].cpu(), host[k])
     for k in ("boxes", "scores", "img_ids", "keep", "n_keep"):
         assert not dev[k].is_cuda and torch.equal(dev[k], host[k])
+
+
+def test_run_device_two_streams_matches_one_stream():
+    """run_device forks the detection chain onto a second stream (pipeline.py): same bits as the serial order,
+    also when the call is repeated back to back (the fork waits for every earlier use of the inputs); and the
+    same again as one CUDA-graph replay (run_device_graph), including after the inputs were refilled in place."""
+    pipeline = import_module("detectron-pytorch_b200.pipeline")
+    B, ih, iw, top_n = 6, 256, 512, 300
+    cfg, strides, scales, anc, gts, deltas, prob = make_case(B, ih, iw, 23)
+    sess = pipeline.BoxOpsSession(strides, ih, iw, scales, cfg.anchor_ratios, cfg.anchor_base, B, 2, top_n=top_n,
+                                  nms_thresh=0.5, bg=cfg.rpn_bg_threshold, fg=cfg.rpn_fg_threshold, max_gt_total=16 * B)
+    sess.stage_gt(gts)
+    args = (torch.from_numpy(np.concatenate(gts, 0)).cuda(), sess.h_off.cuda(), torch.from_numpy(prob).cuda(), torch.from_numpy(deltas).cuda())
+
+    def same(x, y):
+        torch.cuda.synchronize()
+        n = int(x["n_keep"][-1])
+        assert n == int(y["n_keep"][-1]) and n > 0
+        for k in x:                                   # rows of `keep` past n_keep[-1] are not written
+            assert torch.equal(x[k][:n] if k == "keep" else x[k], y[k][:n] if k == "keep" else y[k]), k
+
+    serial = sess.run_device(*args, overlap=False)
+    for _ in range(3):
+        forked = sess.run_device(*args, overlap=True)
+    same(serial, forked)
+    same(serial, sess.run_device_graph(*args))
+    assert sess.graph_launches >= 10
+    args[2].copy_(args[2].flip(0)); args[3].copy_(args[3].flip(0))
+    want = sess.run_device(*args, overlap=False)
+    assert not torch.equal(want["scores"], serial["scores"])
+    same(want, sess.run_device_graph(*args))
