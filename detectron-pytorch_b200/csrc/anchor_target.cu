@@ -113,92 +113,123 @@ anchor_bbox_kernel(const float4 *__restrict__ anchors, long A, TileBoxes *__rest
 }
 
 // ---- pass 1: per-GT column maxima ---------------------------------------------------------------
-// GT-centric: a block owns CM_SLICES consecutive warp slices (32 anchors each) of one image.  Round by
-// round of 32 GT: every thread tests a few slice boxes against the staged GT (conservative float32 test),
-// slices with a non-empty GT mask go on a shared-memory work list, and the warps then take slices off the
-// list — 32 anchors, exact float64 IoU (bbox.pyx:33-54) against the GT of the mask, shared-memory atomicMax
-// on the order-preserving bit pattern.  The block prologue (offsets, GT staging) is paid once per 16 K
-// anchors instead of once per 2 K, and only slices that can overlap a GT ever load their anchors.
+// The column maximum of a GT row is taken over ALL anchors and the anchors are shared by the whole batch, so this
+// pass has no per-image structure at all: a block owns CM_SLICES warp slices (32 anchors each; dealt round-robin) and
+// CM_GT consecutive rows of the concatenated GT array, whichever images they belong to.  At 64 images x 12 GT
+// that is 64 x 6 blocks — ONE wave — where a (slice group, image) grid was 4096 blocks of a few hundred
+// instructions each, i.e. seven waves of pure load latency.  Inside a block: the slice boxes and the GT rows are
+// fetched together (one latency), every (slice, 32-GT word) pair is culled with the conservative float32 test,
+// pairs with a non-empty mask go on a shared work list, and the warps take pairs off the list — 32 anchors, exact
+// float64 IoU (bbox.pyx:33-54) against the GT of the mask, warp maximum, one shared-memory atomicMax on the
+// order-preserving bit pattern; the block's maxima leave through fire-and-forget global atomics.
 constexpr int CM_THREADS = 256;
 constexpr int CM_SLICES = 128;
+constexpr int CM_GT = 128;                           // GT rows per block (4 mask words per slice)
+constexpr int CM_WORDS = CM_GT / 32;
 
 __global__ void __launch_bounds__(CM_THREADS)
-colmax_kernel(const TargetParams p, int n_slices)
+colmax_kernel(const TargetParams p, int n_slices, int total_gt)
 {
-    __shared__ double gx1[32], gy1[32], gx2[32], gy2[32], garea[32];
-    __shared__ float4 gbox[32];
-    __shared__ unsigned long long cmax[32];
-    __shared__ unsigned s_mask[CM_SLICES];
-    __shared__ unsigned short s_list[CM_SLICES];
+    __shared__ double gx1[CM_GT], gy1[CM_GT], gx2[CM_GT], gy2[CM_GT], garea[CM_GT];
+    __shared__ float4 gbox[CM_GT];
+    __shared__ unsigned long long cmax[CM_GT];
+    __shared__ float4 s_bb[CM_SLICES];
+    __shared__ unsigned s_mask[CM_SLICES * CM_WORDS];
+    __shared__ unsigned short s_list[CM_SLICES * CM_WORDS];
     __shared__ int s_n;
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    const int b = blockIdx.y;
-    const int g0 = p.gt_off[b];
-    const int G = p.gt_off[b + 1] - g0;
-    if (G == 0) return;
-    const int s0 = blockIdx.x * CM_SLICES;
-    const int ns = min(CM_SLICES, n_slices - s0);
+    const int r0 = blockIdx.y * CM_GT;                        // first GT row of this block
+    const int gn = min(CM_GT, total_gt - r0);
+    // slices are dealt round-robin (local slice s = global slice s * gridDim.x + blockIdx.x): the slices of the coarse
+    // levels, which nearly every GT touches, are contiguous in memory and would otherwise all land in one block
+    const int nb = gridDim.x;
+    const int ns = (n_slices - (int)blockIdx.x + nb - 1) / nb;         // <= CM_SLICES by the launch geometry
     const float INF = __int_as_float(0x7f800000);
-    for (int c0 = 0; c0 < G; c0 += 32) {
-        const int gn = min(32, G - c0);
-        __syncthreads();                                      // previous round fully consumed
-        if (tid < gn) {
-            const float *q = p.gt + (size_t)(g0 + c0 + tid) * 5;
-            const float4 f = make_float4(q[0], q[1], q[2], q[3]);
-            const double x1 = f.x, y1 = f.y, x2 = f.z, y2 = f.w;
-            gx1[tid] = x1; gy1[tid] = y1; gx2[tid] = x2; gy2[tid] = y2;
-            garea[tid] = (x2 - x1 + 1) * (y2 - y1 + 1);       // bbox.pyx:34-37
-            gbox[tid] = f;
-            cmax[tid] = 0ull;
-        }
-        if (tid == 0) s_n = 0;
-        __syncthreads();
-        for (int s = tid; s < ns; s += CM_THREADS) {          // cull: which GT may touch which slice
-            const int gs = s0 + s;                            // flat slice -> (tile, item, warp) of pass 0's layout
-            const float4 bb = (&p.tiles[gs / (AT_ITEMS * AT_WARPS)].warp[0][0])[gs % (AT_ITEMS * AT_WARPS)];
-            unsigned m = 0;
-            for (int j = 0; j < gn; ++j) m |= may_touch32(bb, gbox[j]) ? (1u << j) : 0u;
-            if (m) { s_mask[s] = m; s_list[atomicAdd(&s_n, 1)] = (unsigned short)s; }
-        }
-        __syncthreads();
-        const int n = s_n;
-        // one warp per listed slice, two slices per trip so that two anchor loads are in flight
-        auto eval = [&](const float4 anc, unsigned m) {
-            const double ax1 = anc.x, ay1 = anc.y, ax2 = anc.z, ay2 = anc.w;
-            const double aarea = (ax2 - ax1 + 1) * (ay2 - ay1 + 1);
-            while (m) {
-                const int j = __ffs(m) - 1;
-                m &= m - 1;
-                unsigned long long bits = 0ull;
-                const double iw = fmin(ax2, gx2[j]) - fmax(ax1, gx1[j]) + 1;          // bbox.pyx:39-42
-                if (iw > 0) {
-                    const double ih = fmin(ay2, gy2[j]) - fmax(ay1, gy1[j]) + 1;      // bbox.pyx:44-47
-                    if (ih > 0) {
-                        const double inter = iw * ih;
-                        const double ov = inter / (aarea + garea[j] - inter);         // bbox.pyx:49-54
-                        if (ov > 0.0) bits = iou_bits(ov);
-                    }
-                }
-                // warp maximum first (positive doubles order like their bit patterns: high word, then low word),
-                // then ONE shared-memory atomic — a 64-bit shared atomicMax is a compare-and-swap loop
-                const unsigned hi = __reduce_max_sync(0xffffffffu, (unsigned)(bits >> 32));
-                const unsigned lo = __reduce_max_sync(0xffffffffu, (unsigned)(bits >> 32) == hi ? (unsigned)bits : 0u);
-                if (lane == 0 && (hi | lo)) atomicMax(&cmax[j], ((unsigned long long)hi << 32) | lo);
-            }
-        };
-        const float4 none = make_float4(INF, INF, -INF, -INF);
-        for (int e = w; e < n; e += 2 * (CM_THREADS / 32)) {
-            const int e1 = e + CM_THREADS / 32;
-            const int sa = s_list[e], sb = e1 < n ? s_list[e1] : -1;
-            const long a0 = ((long)(s0 + sa) << 5) + lane, a1 = ((long)(s0 + max(sb, 0)) << 5) + lane;
-            const float4 anc0 = a0 < p.A ? p.anchors[a0] : none;
-            const float4 anc1 = (sb >= 0 && a1 < p.A) ? p.anchors[a1] : none;
-            eval(anc0, s_mask[sa]);
-            if (sb >= 0) eval(anc1, s_mask[sb]);
-        }
-        __syncthreads();
-        if (tid < gn && cmax[tid] != 0ull) atomicMax(&p.colmax[g0 + c0 + tid], cmax[tid]);
+    if (tid < ns) {                                           // flat slice -> (tile, item, warp) of pass 0's layout
+        const int gs = tid * nb + blockIdx.x;
+        s_bb[tid] = (&p.tiles[gs / (AT_ITEMS * AT_WARPS)].warp[0][0])[gs % (AT_ITEMS * AT_WARPS)];
     }
+    if (tid < gn) {
+        const float *q = p.gt + (size_t)(r0 + tid) * 5;
+        const float4 f = make_float4(q[0], q[1], q[2], q[3]);
+        const double x1 = f.x, y1 = f.y, x2 = f.z, y2 = f.w;
+        gx1[tid] = x1; gy1[tid] = y1; gx2[tid] = x2; gy2[tid] = y2;
+        garea[tid] = (x2 - x1 + 1) * (y2 - y1 + 1);           // bbox.pyx:34-37
+        gbox[tid] = f;
+        cmax[tid] = 0ull;
+    }
+    if (tid == 0) s_n = 0;
+    __syncthreads();
+    const int nw = (gn + 31) >> 5;                            // mask words in use
+    for (int t = tid; t < ns * nw; t += CM_THREADS) {         // cull: which GT of word `wd` may touch slice `sl`
+        const int sl = t / nw, wd = t - sl * nw;
+        const float4 bb = s_bb[sl];
+        const int jn = min(32, gn - wd * 32);
+        unsigned m = 0;
+        for (int j = 0; j < jn; ++j) m |= may_touch32(bb, gbox[wd * 32 + j]) ? (1u << j) : 0u;
+        if (m) { const int e = atomicAdd(&s_n, 1); s_mask[e] = m; s_list[e] = (unsigned short)(sl * CM_WORDS + wd); }
+    }
+    __syncthreads();
+    const int n = s_n;
+    // one warp per listed (slice, word), two per trip so that two anchor loads are in flight
+    auto eval = [&](const float4 anc, unsigned m, const int jb) {
+        const double ax1 = anc.x, ay1 = anc.y, ax2 = anc.z, ay2 = anc.w;
+        const double aarea = (ax2 - ax1 + 1) * (ay2 - ay1 + 1);
+        const float aarea32 = (anc.z - anc.x + 1.0f) * (anc.w - anc.y + 1.0f);
+        while (m) {
+            const int j = jb + __ffs(m) - 1;
+            m &= m - 1;
+            // Float32 screen: only a slice whose best overlap comes within 2 % of the GT's current maximum can raise
+            // it.  The float32 quotient is within ~1e-3 relative of the exact one when both intersection sides are
+            // at least 2^-10 and coordinates stay below 2^15 (inputs are exact, every rounding is relative to its
+            // result, the worst term is span / side * 2^-24); anything outside that, or a non-positive union, is
+            // "uncertain" and takes the exact path.  A stale (smaller) maximum only screens less.
+            {
+                const float4 g = gbox[j];
+                const float iw = fminf(anc.z, g.z) - fmaxf(anc.x, g.x) + 1.0f, ih = fminf(anc.w, g.w) - fmaxf(anc.y, g.y) + 1.0f;
+                float ov32 = 0.0f; bool unsure = false;
+                if (iw > 0.0f && ih > 0.0f) {
+                    const float inter = iw * ih;
+                    const float uni = aarea32 + (g.z - g.x + 1.0f) * (g.w - g.y + 1.0f) - inter;
+                    ov32 = __fdividef(inter, uni);
+                    unsure = !(iw >= 9.765625e-4f && ih >= 9.765625e-4f && uni > 0.0f && ov32 < 4.0f) ||
+                             fmaxf(fmaxf(fabsf(anc.x), fabsf(anc.z)), fmaxf(fabsf(anc.y), fabsf(anc.w))) > 32768.0f ||
+                             fmaxf(fmaxf(fabsf(g.x), fabsf(g.z)), fmaxf(fabsf(g.y), fabsf(g.w))) > 32768.0f;
+                }
+                const unsigned a32 = __reduce_max_sync(0xffffffffu, __float_as_uint(ov32));
+                if (!__any_sync(0xffffffffu, unsure) &&
+                    (double)__uint_as_float(a32) * 1.02 < __longlong_as_double((long long)cmax[j])) continue;
+            }
+            unsigned long long bits = 0ull;
+            const double iw = fmin(ax2, gx2[j]) - fmax(ax1, gx1[j]) + 1;          // bbox.pyx:39-42
+            if (iw > 0) {
+                const double ih = fmin(ay2, gy2[j]) - fmax(ay1, gy1[j]) + 1;      // bbox.pyx:44-47
+                if (ih > 0) {
+                    const double inter = iw * ih;
+                    const double ov = inter / (aarea + garea[j] - inter);         // bbox.pyx:49-54
+                    if (ov > 0.0) bits = iou_bits(ov);
+                }
+            }
+            // warp maximum first (positive doubles order like their bit patterns: high word, then low word),
+            // then ONE shared-memory atomic — a 64-bit shared atomicMax is a compare-and-swap loop
+            const unsigned hi = __reduce_max_sync(0xffffffffu, (unsigned)(bits >> 32));
+            const unsigned lo = __reduce_max_sync(0xffffffffu, (unsigned)(bits >> 32) == hi ? (unsigned)bits : 0u);
+            if (lane == 0 && (hi | lo)) atomicMax(&cmax[j], ((unsigned long long)hi << 32) | lo);
+        }
+    };
+    const float4 none = make_float4(INF, INF, -INF, -INF);
+    for (int e = w; e < n; e += 2 * (CM_THREADS / 32)) {
+        const int e1 = e + CM_THREADS / 32;
+        const int ia = s_list[e], ib = e1 < n ? s_list[e1] : -1;
+        const int sa = ia / CM_WORDS, sb = max(ib, 0) / CM_WORDS;
+        const long a0 = ((long)(sa * nb + (int)blockIdx.x) << 5) + lane, a1 = ((long)(sb * nb + (int)blockIdx.x) << 5) + lane;
+        const float4 anc0 = a0 < p.A ? p.anchors[a0] : none;
+        const float4 anc1 = (ib >= 0 && a1 < p.A) ? p.anchors[a1] : none;
+        eval(anc0, s_mask[e], (ia % CM_WORDS) * 32);
+        if (ib >= 0) eval(anc1, s_mask[e1], (ib % CM_WORDS) * 32);
+    }
+    __syncthreads();
+    if (tid < gn && cmax[tid] != 0ull) atomicMax(&p.colmax[r0 + tid], cmax[tid]);
 }
 
 // label and regression flag of one anchor from its row summary — anchor.py:49-62,86-87
@@ -556,7 +587,7 @@ extern "C" int detbox_anchor_target(const float *anchors, long A, const float *g
         DETBOX_LAUNCH_CHECK();
         DETBOX_TRACE_BEGIN(DETBOX_K_TARGET_COLMAX, st);
         const int n_slices = (int)n_tiles * AT_ITEMS * AT_WARPS;
-        colmax_kernel<<<dim3((unsigned)((n_slices + CM_SLICES - 1) / CM_SLICES), (unsigned)batch), CM_THREADS, 0, st>>>(p, n_slices);
+        colmax_kernel<<<dim3((unsigned)((n_slices + CM_SLICES - 1) / CM_SLICES), (unsigned)((total_gt + CM_GT - 1) / CM_GT)), CM_THREADS, 0, st>>>(p, n_slices, (int)total_gt);
         DETBOX_TRACE_END(DETBOX_K_TARGET_COLMAX, st);
         DETBOX_LAUNCH_CHECK();
     }
