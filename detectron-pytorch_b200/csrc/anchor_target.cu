@@ -116,15 +116,15 @@ anchor_bbox_kernel(const float4 *__restrict__ anchors, long A, TileBoxes *__rest
 // The column maximum of a GT row is taken over ALL anchors and the anchors are shared by the whole batch, so this
 // pass has no per-image structure at all: a block owns CM_SLICES warp slices (32 anchors each; dealt round-robin) and
 // CM_GT consecutive rows of the concatenated GT array, whichever images they belong to.  At 64 images x 12 GT
-// that is 64 x 6 blocks — ONE wave — where a (slice group, image) grid was 4096 blocks of a few hundred
+// that is 16 x 24 blocks — ONE wave — where a (slice group, image) grid was 4096 blocks of a few hundred
 // instructions each, i.e. seven waves of pure load latency.  Inside a block: the slice boxes and the GT rows are
 // fetched together (one latency), every (slice, 32-GT word) pair is culled with the conservative float32 test,
 // pairs with a non-empty mask go on a shared work list, and the warps take pairs off the list — 32 anchors, exact
 // float64 IoU (bbox.pyx:33-54) against the GT of the mask, warp maximum, one shared-memory atomicMax on the
 // order-preserving bit pattern; the block's maxima leave through fire-and-forget global atomics.
 constexpr int CM_THREADS = 256;
-constexpr int CM_SLICES = 128;
-constexpr int CM_GT = 128;                           // GT rows per block (4 mask words per slice)
+constexpr int CM_SLICES = 512;
+constexpr int CM_GT = 32;                           // GT rows per block: few GT x many slices, so that the running maximum screens
 constexpr int CM_WORDS = CM_GT / 32;
 
 __global__ void __launch_bounds__(CM_THREADS)
@@ -145,9 +145,9 @@ colmax_kernel(const TargetParams p, int n_slices, int total_gt)
     const int nb = gridDim.x;
     const int ns = (n_slices - (int)blockIdx.x + nb - 1) / nb;         // <= CM_SLICES by the launch geometry
     const float INF = __int_as_float(0x7f800000);
-    if (tid < ns) {                                           // flat slice -> (tile, item, warp) of pass 0's layout
-        const int gs = tid * nb + blockIdx.x;
-        s_bb[tid] = (&p.tiles[gs / (AT_ITEMS * AT_WARPS)].warp[0][0])[gs % (AT_ITEMS * AT_WARPS)];
+    for (int t = tid; t < ns; t += CM_THREADS) {              // flat slice -> (tile, item, warp) of pass 0's layout
+        const int gs = t * nb + blockIdx.x;
+        s_bb[t] = (&p.tiles[gs / (AT_ITEMS * AT_WARPS)].warp[0][0])[gs % (AT_ITEMS * AT_WARPS)];
     }
     if (tid < gn) {
         const float *q = p.gt + (size_t)(r0 + tid) * 5;
@@ -160,6 +160,15 @@ colmax_kernel(const TargetParams p, int n_slices, int total_gt)
     }
     if (tid == 0) s_n = 0;
     __syncthreads();
+    // coordinates beyond 2^15 void the float32 screen's error bound (slice boxes bound their anchors): decided once per block
+    bool mybig = false;
+    for (int t = tid; t < ns; t += CM_THREADS) {              // (an all-padding slice has an infinite box and never passes the cull)
+        const float4 q = s_bb[t];
+        const float v = fmaxf(fmaxf(fabsf(q.x), fabsf(q.z)), fmaxf(fabsf(q.y), fabsf(q.w)));
+        mybig |= !(v <= 32768.0f) && v != INF;
+    }
+    if (tid < gn) { const float4 q = gbox[tid]; mybig |= !(fmaxf(fmaxf(fabsf(q.x), fabsf(q.z)), fmaxf(fabsf(q.y), fabsf(q.w))) <= 32768.0f); }
+    const bool big = __syncthreads_or(mybig) != 0;
     const int nw = (gn + 31) >> 5;                            // mask words in use
     for (int t = tid; t < ns * nw; t += CM_THREADS) {         // cull: which GT of word `wd` may touch slice `sl`
         const int sl = t / nw, wd = t - sl * nw;
@@ -181,7 +190,7 @@ colmax_kernel(const TargetParams p, int n_slices, int total_gt)
             m &= m - 1;
             // Float32 screen: only a slice whose best overlap comes within 2 % of the GT's current maximum can raise
             // it.  The float32 quotient is within ~1e-3 relative of the exact one when both intersection sides are
-            // at least 2^-10 and coordinates stay below 2^15 (inputs are exact, every rounding is relative to its
+            // at least 2^-10 and coordinates stay below 2^15 (`big`, per block) (inputs are exact, every rounding is relative to its
             // result, the worst term is span / side * 2^-24); anything outside that, or a non-positive union, is
             // "uncertain" and takes the exact path.  A stale (smaller) maximum only screens less.
             {
@@ -192,12 +201,10 @@ colmax_kernel(const TargetParams p, int n_slices, int total_gt)
                     const float inter = iw * ih;
                     const float uni = aarea32 + (g.z - g.x + 1.0f) * (g.w - g.y + 1.0f) - inter;
                     ov32 = __fdividef(inter, uni);
-                    unsure = !(iw >= 9.765625e-4f && ih >= 9.765625e-4f && uni > 0.0f && ov32 < 4.0f) ||
-                             fmaxf(fmaxf(fabsf(anc.x), fabsf(anc.z)), fmaxf(fabsf(anc.y), fabsf(anc.w))) > 32768.0f ||
-                             fmaxf(fmaxf(fabsf(g.x), fabsf(g.z)), fmaxf(fabsf(g.y), fabsf(g.w))) > 32768.0f;
+                    unsure = !(iw >= 9.765625e-4f && ih >= 9.765625e-4f && uni > 0.0f && ov32 < 4.0f);
                 }
                 const unsigned a32 = __reduce_max_sync(0xffffffffu, __float_as_uint(ov32));
-                if (!__any_sync(0xffffffffu, unsure) &&
+                if (!big && !__any_sync(0xffffffffu, unsure) &&
                     (double)__uint_as_float(a32) * 1.02 < __longlong_as_double((long long)cmax[j])) continue;
             }
             unsigned long long bits = 0ull;
@@ -258,8 +265,8 @@ __device__ __forceinline__ void store_anchor(const TargetParams &p, long o, cons
     p.inside[o] = flag ? p.bbw : make_float4(0, 0, 0, 0);                   // :136-138
 }
 
-template <int EMIT_ILP, bool FRCNN>     // EMIT_ILP: anchors encoded side by side in the emit loops
-__global__ void __launch_bounds__(AT_THREADS, 4)
+template <int EMIT_ILP, bool FRCNN, int MINB>     // EMIT_ILP: anchors encoded side by side in the emit loops; MINB: blocks per SM
+__global__ void __launch_bounds__(AT_THREADS, MINB)
 anchor_target_kernel(const TargetParams p)
 {
     __shared__ GtChunk sm;
@@ -472,13 +479,18 @@ anchor_target_kernel(const TargetParams p)
     const long o0 = (long)b * p.A + tile0;
     const int2 r_zero = make_int2(__float_as_int(l_zero), flag_zero ? (int)0x80000000 : 0);
     int nskip = 0;                                   // anchors of skipped slices: all carry l_zero
+    float4 nxt[EMIT_ILP];                            // the next trip's anchors are requested before this trip's encode
+#pragma unroll
+    for (int i = 0; i < EMIT_ILP; ++i) { const int off = i * AT_THREADS + tid; nxt[i] = off < rem ? anc_t[off] : make_float4(0, 0, 0, 0); }
 #pragma unroll 1
     for (int h = 0; h < AT_ITEMS; h += EMIT_ILP) {
         float4 anc[EMIT_ILP], ge[EMIT_ILP]; int2 r[EMIT_ILP];
 #pragma unroll
         for (int i = 0; i < EMIT_ILP; ++i) {
             const int off = (h + i) * AT_THREADS + tid;
-            anc[i] = off < rem ? anc_t[off] : make_float4(0, 0, 0, 0);
+            anc[i] = nxt[i];
+            const int noff = off + EMIT_ILP * AT_THREADS;
+            if (MINB < 4) nxt[i] = (h + EMIT_ILP < AT_ITEMS && noff < rem) ? anc_t[noff] : make_float4(0, 0, 0, 0);
             const bool skipped = use_masks && smask[h + i][w] == 0;
             r[i] = skipped ? r_zero : s_res[h + i][tid];
             nskip += (skipped && off < rem);
@@ -495,6 +507,13 @@ anchor_target_kernel(const TargetParams p)
                 const float *q = p.gt + (size_t)(g0 + g) * 5; return make_float4(q[0], q[1], q[2], q[3]);
             };
             if (off < rem) store_anchor<FRCNN>(p, o0 + off, anc[i], ge[i], raw_gt, __int_as_float(r[i].x), r[i].y < 0);
+        }
+        if (MINB >= 4) {                             // 64 registers: no room to hold the next anchors across the encode
+#pragma unroll
+            for (int i = 0; i < EMIT_ILP; ++i) {
+                const int noff = (h + EMIT_ILP + i) * AT_THREADS + tid;
+                nxt[i] = (h + EMIT_ILP < AT_ITEMS && noff < rem) ? anc_t[noff] : make_float4(0, 0, 0, 0);
+            }
         }
     }
     if (l_zero >= 1.0f) nfg += nskip;
@@ -594,9 +613,12 @@ extern "C" int detbox_anchor_target(const float *anchors, long A, const float *g
     DETBOX_TRACE_BEGIN(DETBOX_K_TARGET_ASSIGN, st);
     static const int ilp = []() { const char *e = getenv("DETBOX_AT_ILP"); return e ? atoi(e) : 1; }();   // measured: 1 and 2 tie, 4 spills
     const bool frcnn = p.enc == DETBOX_ENC_FASTRCNN;
-    if (!frcnn) anchor_target_kernel<1, false><<<grid, AT_THREADS, 0, st>>>(p);
-    else if (ilp == 2) anchor_target_kernel<2, true><<<grid, AT_THREADS, 0, st>>>(p);
-    else anchor_target_kernel<1, true><<<grid, AT_THREADS, 0, st>>>(p);
+    static const int minb = []() { const char *e = getenv("DETBOX_AT_MINB"); return e ? atoi(e) : 4; }();
+    if (!frcnn) anchor_target_kernel<1, false, 4><<<grid, AT_THREADS, 0, st>>>(p);
+    else if (minb == 3 && ilp == 2) anchor_target_kernel<2, true, 3><<<grid, AT_THREADS, 0, st>>>(p);
+    else if (minb == 3) anchor_target_kernel<1, true, 3><<<grid, AT_THREADS, 0, st>>>(p);
+    else if (ilp == 2) anchor_target_kernel<2, true, 4><<<grid, AT_THREADS, 0, st>>>(p);
+    else anchor_target_kernel<1, true, 4><<<grid, AT_THREADS, 0, st>>>(p);
     DETBOX_TRACE_END(DETBOX_K_TARGET_ASSIGN, st);
     DETBOX_LAUNCH_CHECK();
     long wb = (A / 4 + 255) / 256;

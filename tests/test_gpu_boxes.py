@@ -194,6 +194,31 @@ def test_anchor_target_random_small(seed):
         check_target(got, b, gt, anc, cfg)
 
 
+def test_anchor_target_large_coordinates():
+    """Coordinates beyond 2^15 switch the column-max pass's float32 screen off (its error bound no longer holds);
+    sub-pixel intersections and far-apart boxes take its `unsure` route.  Labels stay bit-exact either way."""
+    rng = np.random.RandomState(321)
+    scales = [[2, 2.52, 3.175], [4, 5.04, 6.349], [8, 10.079, 12.7]]
+    base = O.anchor_pyramid([8, 16, 32], 192, 320, scales, [1, 2.5], 16).astype(np.float32)
+    cfg = O.Cfg(rpn_bg_threshold=0.4, rpn_fg_threshold=0.6)
+    for shift, mul in ((0.0, 1.0), (40000.0, 1.0), (0.0, 300.0)):
+        anc = (base * np.float32(mul) + np.float32(shift)).astype(np.float32)
+        gts = []
+        for G in [2, 12, 40]:
+            gt = synth_gt(rng, G, 192, 320, 0.2, ncls=3)
+            gt[:, :4] = gt[:, :4] * np.float32(mul) + np.float32(shift)
+            gts.append(gt.astype(np.float32))
+        # a GT that only grazes anchors: intersections a fraction of a pixel wide
+        g = anc[rng.choice(anc.shape[0], 6, replace=False)].copy()
+        w = g[:, 2] - g[:, 0]
+        g[:, 0] = g[:, 2] + np.float32(1.0) - np.float32(3e-4) * np.maximum(np.float32(1.0), np.abs(g[:, 2]) * np.float32(1e-3))
+        g[:, 2] = g[:, 0] + w
+        gts.append(np.concatenate([g, np.ones((6, 1), np.float32)], 1))
+        got = run_target(anc, gts, cfg)
+        for b, gt in enumerate(gts):
+            check_target(got, b, gt, anc, cfg)
+
+
 def test_rcp_inrange_exhaustive():
     """box_math.cuh::rcp_rn_inrange == the IEEE round-to-nearest reciprocal for EVERY float32 in [2^-20, 2^20]
     (3.4e8 values, the range the encode's single test admits)."""
