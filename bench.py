@@ -389,6 +389,33 @@ def roi_align_bench(torch, detbox, hbm_peak):
     return res
 
 
+def coco_post_bench(torch, detbox, hbm_peak):
+    """BASELINE configs[3]: COCO-shape 800x1333 RetinaNet post-processing, A = 132,450 anchors/img, batch 16, 80 sigmoid
+    classes: objectness -> top-k -> decode -> per-image NMS (0.5), inputs resident in HBM.  Two budgets: 1000 per image
+    and the reference's global 900*B (libs/nets/model.py:311-312).  Algorithmic bytes ~ 4*C*A per image (the class
+    scores are read once; SURVEY 8d: 678 MB per batch)."""
+    B, A, C = 16, 132450, 80
+    gen = torch.Generator(device="cuda").manual_seed(5)
+    prob = torch.sigmoid(torch.randn((B * A, C), generator=gen, device="cuda") - 4.6)
+    deltas = torch.randn((B * A, 4), generator=gen, device="cuda") * 0.5
+    xy = torch.rand((A, 2), generator=gen, device="cuda") * torch.tensor([1333.0, 800.0], device="cuda")
+    wh = torch.exp(torch.rand((A, 2), generator=gen, device="cuda") * 3.0 + 2.5)
+    anc = torch.cat([xy - wh / 2, xy + wh / 2], 1).contiguous()
+    out = {"workload": "B=16, A=132450, C=80 sigmoid, fp32; inputs %.0f MB > L2" % ((prob.numel() + deltas.numel()) * 4 / 1e6)}
+    for name, top_n, per_image in (("per_image_1000", 1000, True), ("global_14400", 900 * B, False)):
+        def step():
+            sel = detbox.topk_decode(deltas, prob, anc, top_n, "sigmoid", "fastrcnn", per_image, want=("img_ids", "scores"))
+            return detbox.nms(sel["boxes"], sel["scores"], NMS_THR, detbox.NMS_GT_F32, seg_ids=sel["img_ids"], n_seg=B,
+                              presorted=per_image)
+        t_topk = median_ms(torch, lambda: detbox.topk_decode(deltas, prob, anc, top_n, "sigmoid", "fastrcnn", per_image,
+                                                             want=("img_ids", "scores")))
+        t = median_ms(torch, step)
+        out[name] = {"ms": round(t, 4), "topk_decode_ms": round(t_topk, 4), "images_per_s": round(B / (t / 1e3), 1),
+                     "score_read_gbs": round(prob.numel() * 4 / t_topk / 1e6, 1),
+                     "score_read_frac_hbm": round(prob.numel() * 4 / t_topk / 1e6 / hbm_peak, 3)}
+    return out
+
+
 # -------------------------------------------------------------------------------------- main ----
 def single_image_latency(torch, detbox, gt1, h_prob, h_box, A):
     """one CP-R image per call (the launch-latency regime) — the whole device-resident path
@@ -566,6 +593,7 @@ def main():
         extras["nms_us"] = nms_sweep(torch, detbox)
         extras["roi_align"] = roi_align_bench(torch, detbox, hbm_peak)
         extras["single_image"] = single_image_latency(torch, detbox, gts[0], h_prob, h_box, A)
+        extras["coco_r_post"] = coco_post_bench(torch, detbox, hbm_peak)
 
     if rank == 0:
         total_images = B * world
