@@ -26,8 +26,8 @@ namespace {
 
 constexpr int NB0 = 2048;            // bins of level 0 / 1 (11 bits); level 2 uses 1024 (10 bits)
 constexpr int TK_THREADS = 256;
-constexpr int TK_ROWS = 128;         // sigmoid staging tile: rows
-constexpr int TK_COLS = 64;          // sigmoid staging tile: class columns per chunk
+constexpr int TK_WROWS = 8;          // sigmoid, C > 4: rows per warp and trip
+constexpr int TK_WCH = 4;            // ... and 32-float chunks of a row loaded side by side
 
 struct SegState { uint32_t prefix; uint32_t k_rem; uint32_t n_better; uint32_t pad; };
 
@@ -38,7 +38,6 @@ objectness_kernel(const float *__restrict__ prob, int C, long seg_len, uint32_t 
                   uint32_t *__restrict__ hist /*[n_seg][NB0]*/)
 {
     __shared__ uint32_t sh[NB0];
-    __shared__ float stage[ACT == DETBOX_ACT_SIGMOID ? TK_ROWS * (TK_COLS + 1) : 1];
     const int tid = threadIdx.x;
     for (int i = tid; i < NB0; i += TK_THREADS) sh[i] = 0;
     __syncthreads();
@@ -54,25 +53,41 @@ objectness_kernel(const float *__restrict__ prob, int C, long seg_len, uint32_t 
             atomicAdd(&sh[k >> 21], 1u);
         }
     } else {
-        // max over C classes: stage [TK_ROWS x <=TK_COLS] through shared memory so that global reads
-        // are contiguous runs and the per-row reduction is bank-conflict free (odd row pitch)
-        for (long r0 = (long)blockIdx.x * TK_ROWS; r0 < seg_len; r0 += (long)gridDim.x * TK_ROWS) {
-            const int rn = (int)min((long)TK_ROWS, seg_len - r0);
-            float m = -__int_as_float(0x7f800000);
-            for (int c0 = 0; c0 < C; c0 += TK_COLS) {
-                const int cn = min(TK_COLS, C - c0);
-                __syncthreads();
-                for (int i = tid; i < rn * cn; i += TK_THREADS) {
-                    const int r = i / cn, c = i - r * cn;
-                    stage[r * (TK_COLS + 1) + c] = prob[(size_t)(seg0 + r0 + r) * C + c0 + c];
-                }
-                __syncthreads();
-                if (tid < rn) for (int c = 0; c < cn; ++c) m = fmaxf(m, stage[tid * (TK_COLS + 1) + c]);
+        // max over C classes: one warp per row, TK_WROWS rows per warp and trip.  A row is C contiguous floats, so the
+        // lanes' 4-byte loads are full 128-byte requests; TK_WROWS * ceil(C/32) independent loads per lane are in flight
+        // before the first maximum, and a row's result is one warp reduction on the order-preserving key (the maximum
+        // of the floats is the minimum of the descending keys).  No shared-memory staging, no barrier.
+        const int lane = tid & 31, w = tid >> 5;
+        const float NINF = -__int_as_float(0x7f800000);
+        for (long r0 = ((long)blockIdx.x * (TK_THREADS / 32) + w) * TK_WROWS; r0 < seg_len;
+             r0 += (long)gridDim.x * (TK_THREADS / 32) * TK_WROWS) {
+            float m[TK_WROWS];
+#pragma unroll
+            for (int j = 0; j < TK_WROWS; ++j) m[j] = NINF;
+            const float *p0 = prob + (size_t)(seg0 + r0) * C;
+            for (int c0 = lane; c0 < C; c0 += 32 * TK_WCH) {     // one trip for C <= 128
+                float v[TK_WROWS][TK_WCH];                       // every load of the trip is issued before the first use
+#pragma unroll
+                for (int j = 0; j < TK_WROWS; ++j)
+#pragma unroll
+                    for (int q = 0; q < TK_WCH; ++q) {
+                        const int c = c0 + 32 * q;
+                        v[j][q] = (r0 + j < seg_len && c < C) ? __ldcs(p0 + (size_t)j * C + c) : NINF;   // read once: streaming
+                    }
+#pragma unroll
+                for (int j = 0; j < TK_WROWS; ++j)
+#pragma unroll
+                    for (int q = 0; q < TK_WCH; ++q) m[j] = fmaxf(m[j], v[j][q]);
             }
-            if (tid < rn) {
-                const uint32_t k = ~float_to_ordered(m);
-                keys[seg0 + r0 + tid] = k;
-                atomicAdd(&sh[k >> 21], 1u);
+            uint32_t mine = 0;
+#pragma unroll
+            for (int j = 0; j < TK_WROWS; ++j) {
+                const uint32_t k = __reduce_min_sync(0xffffffffu, ~float_to_ordered(m[j]));
+                if (lane == j) mine = k;
+            }
+            if (lane < TK_WROWS && r0 + lane < seg_len) {
+                keys[seg0 + r0 + lane] = mine;
+                atomicAdd(&sh[mine >> 21], 1u);
             }
         }
     }
@@ -559,7 +574,7 @@ extern "C" int detbox_topk_decode(const float *prob, int C, const float *deltas,
     // 1. objectness + level-0 histogram
     {
         const bool staged = activation == DETBOX_ACT_SIGMOID && C > 4;
-        const long rows_per_block = staged ? TK_ROWS : TK_THREADS;
+        const long rows_per_block = staged ? (TK_THREADS / 32) * TK_WROWS : TK_THREADS;
         long gx = (p.seg_len + rows_per_block - 1) / rows_per_block;
         const long cap = (long)kNumSMs * 8 / (p.n_seg < 8 ? 1 : 1);
         long capx = cap / p.n_seg; if (capx < 1) capx = 1; if (p.n_seg == 1) capx = cap;
