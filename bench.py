@@ -321,6 +321,25 @@ def nms_sweep(torch, detbox):
     return out
 
 
+def measure_l2_peak(torch):
+    """the L2 denominator — device-to-device copy over a resident set (2 x 24 MB, inside the 126 MB L2),
+    read + write bytes over CUDA-event time, best of 5 batches of 20 copies (the way MEASURED_PEAKS.json's HBM figure
+    was taken, on a set that never leaves L2)."""
+    n = 6 * 1024 * 1024
+    a = torch.randn(n, device="cuda"); b = torch.empty_like(a)
+    for _ in range(5):
+        b.copy_(a)
+    best = 0.0
+    for _ in range(5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(20):
+            b.copy_(a)
+        e1.record(); torch.cuda.synchronize()
+        best = max(best, 20 * 2 * n * 4 / (e0.elapsed_time(e1) * 1e-3) / 1e9)
+    return round(best, 1)
+
+
 def roi_align_bench(torch, detbox, hbm_peak):
     """BASELINE configs[2]: 512 RoIs/img x 256 ch x 7x7 over P2-P5 of a 1024x2048 canvas, batch 8,
     fp32, bin-centre sampling (the variant MaskRCNN wires in), level assigned in-kernel."""
@@ -384,6 +403,13 @@ def roi_align_bench(torch, detbox, hbm_peak):
                        "bwd_ms": round(t_b, 4), "bwd_gbs": round(bb / t_b / 1e6, 1), "bwd_frac_hbm": round(bb / t_b / 1e6 / hbm_peak, 3),
                        "bwd_scatter_only_ms": round(t_s, 4)}
         del feats, grads, gout, y
+    # L2-level view of the forward gather: 4 taps x 4 B per output element (SURVEY 8d upper bound) + the output write
+    l2_peak = measure_l2_peak(torch)
+    gather = out_bytes * 4 + out_bytes
+    res["l2"] = {"peak_gbs": l2_peak, "how": "copy over a 48 MB resident set (read + write), best of 5 x 20",
+                 "fwd_gather_bytes": gather,
+                 "nchw_fwd_frac": round(gather / res["nchw"]["fwd_ms"] / 1e6 / l2_peak, 3),
+                 "nhwc_fwd_frac": round(gather / res["nhwc"]["fwd_ms"] / 1e6 / l2_peak, 3)}
     res["bytes"] = {"out": out_bytes, "features_touched": feat_bytes_by_layout, "dense_grad_zero_fill": dense_bytes}
     res["workload"] = "B=8, R=4096, C=256, 7x7, P2-P5 @1024x2048, bin-centre, level assigned in-kernel, fp32; L2 flushed between iterations"
     return res
