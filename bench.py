@@ -408,8 +408,10 @@ def roi_align_bench(torch, detbox, hbm_peak):
     gather = out_bytes * 4 + out_bytes
     res["l2"] = {"peak_gbs": l2_peak, "how": "copy over a 48 MB resident set (read + write), best of 5 x 20",
                  "fwd_gather_bytes": gather,
-                 "nchw_fwd_frac": round(gather / res["nchw"]["fwd_ms"] / 1e6 / l2_peak, 3),
-                 "nhwc_fwd_frac": round(gather / res["nhwc"]["fwd_ms"] / 1e6 / l2_peak, 3)}
+                 "nchw_fwd_gather_gbs": round(gather / res["nchw"]["fwd_ms"] / 1e6, 1),
+                 "nhwc_fwd_gather_gbs": round(gather / res["nhwc"]["fwd_ms"] / 1e6, 1),
+                 "note": "fwd_gather_bytes is the 4-tap upper bound: taps shared by neighbouring bins are L1 hits, so the L2-level "
+                         "rate is below these figures (ncu lts__t_bytes in profiles/r01_ncu_roi.txt is the measured one)"}
     res["bytes"] = {"out": out_bytes, "features_touched": feat_bytes_by_layout, "dense_grad_zero_fill": dense_bytes}
     res["workload"] = "B=8, R=4096, C=256, 7x7, P2-P5 @1024x2048, bin-centre, level assigned in-kernel, fp32; L2 flushed between iterations"
     return res

@@ -133,7 +133,7 @@ nms_mask_kernel(const float4 *__restrict__ boxes, const int32_t *__restrict__ se
     const int ct_base = first_ct & ~(MASK_CT - 1);
     if (ct_base + (int)blockIdx.x * cg > rt_last) return;      // strictly right of the diagonal
     __shared__ float4 cb[64 * MASK_CT];
-    __shared__ float4 ccull[64 * MASK_CT];      // (x1 - 1 rounded down, y1 - 1 down, x2 + 1 up, y2 + 1 up)
+    __shared__ float4 ccull[64 * MASK_CT];      // (-(x1 - 1 rounded down), -(y1 - 1 down), x2 + 1 up, y2 + 1 up)
     __shared__ float carea[64 * MASK_CT];
     const int tid = threadIdx.x, sub = tid >> 6, rl = tid & 63;
     float4 a[MASK_RT]; float aarea[MASK_RT]; int astart[MASK_RT];
@@ -156,7 +156,7 @@ nms_mask_kernel(const float4 *__restrict__ boxes, const int32_t *__restrict__ se
             if (c <= row_last) {
                 const float4 b = boxes[c];
                 cb[tid] = b;
-                ccull[tid] = make_float4(__fadd_rd(b.x, -1.0f), __fadd_rd(b.y, -1.0f), __fadd_ru(b.z, 1.0f), __fadd_ru(b.w, 1.0f));
+                ccull[tid] = make_float4(-__fadd_rd(b.x, -1.0f), -__fadd_rd(b.y, -1.0f), __fadd_ru(b.z, 1.0f), __fadd_ru(b.w, 1.0f));
                 carea[tid] = (b.z - b.x + 1) * (b.w - b.y + 1);    // cpu_nms.pyx:24
             }
         }
@@ -169,11 +169,13 @@ nms_mask_kernel(const float4 *__restrict__ boxes, const int32_t *__restrict__ se
         // convention.  Exact by monotone rounding: a.x > up(b.x2 + 1) means min(x2) - max(x1) < -1 in real
         // arithmetic, so the reference's fl(fl(min - max) + 1) is <= 0 and the intersection is empty.
         unsigned lo[MASK_RT], hi[MASK_RT];
+        float2 naxy[MASK_RT], azw[MASK_RT];
 #pragma unroll
-        for (int k = 0; k < MASK_RT; ++k) { lo[k] = 0; hi[k] = 0; }
+        for (int k = 0; k < MASK_RT; ++k) { lo[k] = 0; hi[k] = 0; naxy[k] = make_float2(-a[k].x, -a[k].y); azw[k] = make_float2(a[k].z, a[k].w); }
         // The four strict comparisons are evaluated as sign bits of float differences (FADD runs on the FMA
         // pipe; FSETP would saturate the half-rate ALU pipe): a.x > q.z  <=>  sign(q.z - a.x).  A difference is
-        // -0 only for (-0) - (+0), which the directed roundings above exclude (q.z is never -0, q.x never +0);
+        // -0 only for (-0) - (+0), which the directed roundings above exclude (q.z is never -0, q.x never +0; the
+        // staged -q.x is therefore never -0);
         // NaN / Inf operands may set a sign bit, but such pairs have an empty intersection (fmaxf(0, NaN) = 0).
 #pragma unroll 1
         for (int ib = 0; ib < 32; ib += 8) {         // 8 + 8 column boxes per trip keeps the live registers bounded
@@ -182,10 +184,12 @@ nms_mask_kernel(const float4 *__restrict__ boxes, const int32_t *__restrict__ se
                 const float4 q0 = ccull[cbase + ib + j], q1 = ccull[cbase + 32 + ib + j];
 #pragma unroll
                 for (int k = 0; k < MASK_RT; ++k) {
-                    const unsigned o0 = __float_as_uint(q0.z - a[k].x) | __float_as_uint(a[k].z - q0.x) |
-                                        __float_as_uint(q0.w - a[k].y) | __float_as_uint(a[k].w - q0.y);
-                    const unsigned o1 = __float_as_uint(q1.z - a[k].x) | __float_as_uint(a[k].z - q1.x) |
-                                        __float_as_uint(q1.w - a[k].y) | __float_as_uint(a[k].w - q1.y);
+                    // packed float32 adds (FADD2): (q.z, q.w) + (-a.x, -a.y) and (a.z, a.w) + (-q.x, -q.y) — the four
+                    // differences of a pair in two instructions, each lane the same IEEE subtraction as before
+                    const float2 d0 = __fadd2_rn(make_float2(q0.z, q0.w), naxy[k]), e0 = __fadd2_rn(azw[k], make_float2(q0.x, q0.y));
+                    const float2 d1 = __fadd2_rn(make_float2(q1.z, q1.w), naxy[k]), e1 = __fadd2_rn(azw[k], make_float2(q1.x, q1.y));
+                    const unsigned o0 = __float_as_uint(d0.x) | __float_as_uint(e0.x) | __float_as_uint(d0.y) | __float_as_uint(e0.y);
+                    const unsigned o1 = __float_as_uint(d1.x) | __float_as_uint(e1.x) | __float_as_uint(d1.y) | __float_as_uint(e1.y);
                     lo[k] = (lo[k] >> 1) | (~o0 & 0x80000000u);      // bit 31 <- "not outside"; 32 shifts put box i at bit i
                     hi[k] = (hi[k] >> 1) | (~o1 & 0x80000000u);
                 }

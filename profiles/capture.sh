@@ -13,6 +13,9 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-fil
 ncu --set full --clock-control none --import-source on \
     -k regex:"anchor_target_kernel|colmax_kernel|label_weight_kernel|objectness_kernel|partition_kernel|nms_mask_kernel|nms_resolve_seg" \
     -s 14 -c 7 -o gpurun_out/box_full -f python bench.py --steps 2 --warmup 1 --no-cpu --no-extras > gpurun_out/ncu_box.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:"roi_fwd_kernel|roi_bwd_kernel" -c 4 -o gpurun_out/roi_full -f \
+# roi_probe launches: 14 x fwd NCHW, 28 x bwd NCHW, 14 x fwd NHWC, 28 x bwd NHWC -> the last NCHW and the first NHWC of each
+ncu --set full --clock-control none --import-source on -k regex:roi_fwd_kernel -s 13 -c 2 -o gpurun_out/roi_fwd_full -f \
     python profiles/roi_probe.py > gpurun_out/ncu_roi.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:roi_bwd_kernel -s 27 -c 2 -o gpurun_out/roi_bwd_full -f \
+    python profiles/roi_probe.py >> gpurun_out/ncu_roi.log 2>&1
 ls -la gpurun_out/*.ncu-rep gpurun_out/launches.csv
