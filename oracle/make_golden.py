@@ -180,6 +180,56 @@ def to_dets_golden(ref_root="/root/reference"):
     np.savez_compressed(os.path.join(GOLD, "to_dets.npz"), **out)
 
 
+def real_gt_sets(ref_root="/root/reference", picks=6):
+    """GT sets of real CityPersons validation images: data/citypersons/annotations/anno_val.mat rows
+    (class, x, y, w, h, instance, x_vis, y_vis, w_vis, h_vis) -> [x1, y1, x2, y2, class] with the conversion of
+    libs/datasets/citypersons2.py:85-89 (x2 = x + w) and the class / ignore rules of :801-812 (0, 4, 5 -> -1; 2, 3 -> 1;
+    visible fraction < 0.3 or height < 32 -> -1).  Picks image 0, the images with the most GT / most ignore boxes /
+    most pedestrians, and two more."""
+    import scipy.io as sio
+    ann = sio.loadmat(os.path.join(ref_root, "data/citypersons/annotations/anno_val.mat"))["anno_val_aligned"].reshape(-1)
+    sets = []
+    for a in ann:
+        bbs = a.reshape(-1)[0][2].astype(np.float32)
+        if bbs.size == 0:
+            sets.append(np.zeros((0, 5), np.float32)); continue
+        cls, box, vis = bbs[:, 0].astype(np.int32), bbs[:, 1:5].copy(), bbs[:, 6:10].copy()
+        box[:, 2:4] += box[:, 0:2]; vis[:, 2:4] += vis[:, 0:2]
+        cls[cls == 0] = -1; cls[cls == 2] = 1; cls[cls == 3] = 1; cls[cls == 4] = -1; cls[cls == 5] = -1
+        frac = ((vis[:, 3] - vis[:, 1] + 1) * (vis[:, 2] - vis[:, 0] + 1)) / ((box[:, 3] - box[:, 1] + 1) * (box[:, 2] - box[:, 0] + 1))
+        cls[frac < 0.3] = -1; cls[(box[:, 3] - box[:, 1] + 1) < 32] = -1
+        sets.append(np.concatenate([box, cls[:, None].astype(np.float32)], 1).astype(np.float32))
+    n = np.asarray([g.shape[0] for g in sets]); ign = np.asarray([(g[:, 4] < 0).sum() for g in sets]); ped = n - ign
+    chosen = []
+    for i in [0, int(n.argmax()), int(ign.argmax()), int(ped.argmax()), 123, 377]:
+        if i not in chosen:
+            chosen.append(i)
+    return [(i, sets[i]) for i in chosen[:picks]]
+
+
+def real_gt_golden(r):
+    """anchor.encode of the compiled reference on real CityPersons GT x the CP-R pyramid (rpn_bg 0.5 / rpn_fg 0.6, the
+    yaml's thresholds): labels stored sparsely, label-weight values, every 1009th target row plus the rows that carry
+    inside weights."""
+    A, cfg = r.boxes_anchor, r.cfg
+    pyr = A.anchor_pyramid(CPR_STRIDES, 1024, 2048, CPR_SCALES, CPR_RATIOS, 16).astype(np.float32)
+    set_cfg(cfg, 0.5, 0.6)
+    out = {"image_ids": np.asarray([i for i, _ in real_gt_sets()], np.int64)}
+    for i, gt in real_gt_sets():
+        lab, lw, bt, bw = r.layers_anchor.encode(gt.copy(), pyr.copy())
+        k = "img%d_" % i
+        nz = np.nonzero(lab != 0)[0]
+        out[k + "gt"] = gt
+        out[k + "labels_nz_idx"], out[k + "labels_nz_val"] = nz, lab[nz]
+        out[k + "counts"] = np.asarray([(lab >= 1).sum(), (lab == 0).sum(), (lab < 0).sum()])
+        out[k + "bg_weight"] = lw[lab == 0][:1]
+        wrows = np.nonzero(bw.any(1))[0]
+        rows = np.union1d(np.arange(0, pyr.shape[0], 1009), wrows)
+        out[k + "inside_rows"] = wrows
+        out[k + "rows_idx"], out[k + "bbox_targets_rows"] = rows, bt[rows]
+    np.savez_compressed(os.path.join(GOLD, "anchor_target_real.npz"), **out)
+
+
 def dets_cluster_cases():
     """Synthetic (dets, keep, clusters) with clusters of 1, 2, 7, 8, 9, 130 and 400 members (NumPy's pairwise
     summation changes shape at 8 and at 128 elements); members interleaved, keepers not in index order."""
@@ -226,6 +276,9 @@ def main():
         return
     if "--only-dets-cluster" in sys.argv:
         dets_cluster_golden()
+        return
+    if "--only-real-gt" in sys.argv:
+        real_gt_golden(r)
         return
     if "--only-roi-sampling" in sys.argv:
         roi_sampling_golden(r)
@@ -376,6 +429,7 @@ def main():
     nms_variants_golden(r)
     to_dets_golden()
     dets_cluster_golden()
+    real_gt_golden(r)
 
     sz = sum(os.path.getsize(os.path.join(GOLD, f)) for f in os.listdir(GOLD))
     print("golden vectors written to", GOLD, "(%d KiB)" % (sz // 1024))

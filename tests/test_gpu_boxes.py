@@ -174,6 +174,27 @@ def test_anchor_target_cpr_batch(cpr_anchors, golden):
         check_target(got, b, gt, anc, CPR)
 
 
+def test_anchor_target_real_citypersons_gt(cpr_anchors, golden):
+    """six real CityPersons validation GT sets as ONE batch against the CP-R pyramid; labels, label
+    weights and the rows carrying inside weights bit-exact against the compiled reference's recorded outputs, the
+    sampled target rows within the float tolerance."""
+    ref, _ = cpr_anchors
+    anc = ref.astype(np.float32)
+    g = golden("anchor_target_real")
+    ids = [int(i) for i in g["image_ids"]]
+    got = run_target(anc, [g["img%d_gt" % i] for i in ids], CPR)
+    for b, i in enumerate(ids):
+        k = "img%d_" % i
+        want = np.zeros(anc.shape[0], np.float32)
+        want[g[k + "labels_nz_idx"]] = g[k + "labels_nz_val"]
+        np.testing.assert_array_equal(got[0][b], want)
+        np.testing.assert_array_equal(got[4][b], g[k + "counts"][:2])
+        np.testing.assert_array_equal(got[1][b][want == 0][:1], g[k + "bg_weight"])
+        assert (got[1][b][want >= 1] == 1).all() and (got[1][b][want < 0] == 0).all()
+        np.testing.assert_array_equal(np.nonzero(got[3][b].any(1))[0], g[k + "inside_rows"])
+        np.testing.assert_allclose(got[2][b][g[k + "rows_idx"]], g[k + "bbox_targets_rows"], rtol=RTOL, atol=ATOL)
+
+
 @pytest.mark.parametrize("seed", range(6))
 def test_anchor_target_random_small(seed):
     rng = np.random.RandomState(100 + seed)

@@ -90,6 +90,25 @@ def test_anchor_target_cpr_image(golden):
     np.testing.assert_array_equal(bw.sum(0), g["cpr_bbox_inside_weights_sum"])
 
 
+def test_anchor_target_real_citypersons_gt(golden):
+    """GT sets of real CityPersons validation images (6..60 boxes, up to 31 ignore regions) against the
+    CP-R pyramid — outputs recorded from the compiled reference (oracle/make_golden.py::real_gt_golden).  Image 0 has
+    35 positive / 259,248 negative / 2,605 ignored anchors."""
+    g = golden("anchor_target_real")
+    pyr = O.anchor_pyramid(CPR.strides, 1024, 2048, CPR.anchor_scales, CPR.anchor_ratios, 16).astype(np.float32)
+    np.testing.assert_array_equal(g["img0_counts"], [35, 259248, 2605])
+    for i in g["image_ids"][:3]:                       # (three of the six keep the CPU suite short; the GPU test runs all)
+        k = "img%d_" % i
+        lab, lw, bt, bw = O.anchor_encode(g[k + "gt"], pyr, CPR)
+        ref = np.zeros_like(lab)
+        ref[g[k + "labels_nz_idx"]] = g[k + "labels_nz_val"]
+        np.testing.assert_array_equal(lab, ref)
+        np.testing.assert_array_equal([(lab >= 1).sum(), (lab == 0).sum(), (lab < 0).sum()], g[k + "counts"])
+        np.testing.assert_array_equal(lw[lab == 0][:1], g[k + "bg_weight"])
+        np.testing.assert_array_equal(np.nonzero(bw.any(1))[0], g[k + "inside_rows"])
+        np.testing.assert_allclose(bt[g[k + "rows_idx"]], g[k + "bbox_targets_rows"], rtol=RTOL, atol=ATOL)
+
+
 @pytest.mark.parametrize("name", ["rand1k", "rand3k", "clustered2k", "intgrid600"])
 @pytest.mark.parametrize("thr", [0.5, 0.3, 0.7])
 def test_nms(golden, name, thr):
