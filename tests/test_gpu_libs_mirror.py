@@ -318,3 +318,33 @@ def test_single_shot_new_advanced_stitch(golden):
         inds = np.where((p > 0.1) & (p <= 0.5))[0]
         keep = O.nms_multianchor(dets_i[:, :5].astype(np.float32), 0.95)[0]
         assert np.array_equal(got_i, dets_i[np.setdiff1d(np.arange(p.size), np.setdiff1d(inds, keep))])
+
+
+def test_pyramid_roi_align_reference_fixture():
+    """The reference's own script (roi_align_tf/pyramid_roi_align.py:96-135): five boxes that land one per level of the
+    default 5-level pyramid, level i's plane holding the plateau value i under its box; then the same call with the boxes
+    permuted.  Box i must come back from level i (its 5x5 crop reads the plateau), in the caller's order either way."""
+    import libs.configs.config as cfg
+    from libs.layers.roi_align_tf.pyramid_roi_align import PyramidRoIAlign
+    assert tuple(cfg.strides) == (8, 16, 32, 64, 128)
+    bboxes = np.asarray([[100, 100, 120, 130], [10, 10, 70, 70], [200, 200, 350, 350], [0, 0, 250, 250], [0, 0, 500, 500]], np.float32)
+    rng = np.random.RandomState(0)
+    pyramid, batch_inds = [], []
+    for i, s in enumerate(cfg.strides):
+        t = np.zeros((2, 1, 512 // s, 512 // s), np.float32)
+        ind = int(rng.randint(0, 2))
+        box = bboxes[i] // s
+        t[ind, :, int(box[1]):int(box[3] + 1), int(box[0]):int(box[2] + 1)] = i
+        pyramid.append(t); batch_inds.append(ind)
+    batch_inds = np.asarray(batch_inds, np.float32)
+    ra = (np.asarray(cfg.anchor_scales, np.float32).mean(axis=1) * cfg.anchor_base) ** 2
+    np.testing.assert_array_equal(O.assign_levels(bboxes, ra), np.arange(5))            # one box per level
+    crop = PyramidRoIAlign(5, 5)
+    out = crop([cu(f) for f in pyramid], cu(bboxes), cu(batch_inds)).cpu().numpy()
+    want = O.pyramid_roi_align(pyramid, bboxes, batch_inds, cfg.strides, ra, 5, 5, "tf")
+    assert out.shape == (5, 1, 5, 5) and np.array_equal(out, want)
+    for i in range(5):
+        assert out[i].max() == i and (i == 0 or out[i, 0, 1:4, 1:4].min() > 0), "box %d did not read level %d" % (i, i)
+    perm = rng.permutation(5)
+    out_p = crop([cu(f) for f in pyramid], cu(bboxes[perm]), cu(batch_inds[perm])).cpu().numpy()
+    assert np.array_equal(out_p, out[perm])
