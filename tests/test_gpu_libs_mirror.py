@@ -194,6 +194,25 @@ def test_crop_and_resize_function_matches_golden(golden):
     assert np.array_equal(ext, O.crop_and_resize_fwd(g["image"], g["boxes"], g["box_ind"], -3.5, 7, 7))
 
 
+def test_crop_and_resize_at_the_reference_test_shape():
+    """The reference's own comparison recipe (roi_align_tf/test.py:25-56): image 16 x 256 x 200 x 300, 100 random boxes in
+    normalised (y1, x1, y2, x2) form, 7 x 7 crops, forward and backward — here against the restated crop_and_resize.c
+    (pinned bit-exactly to the compiled reference): forward bit-exact, backward within the atomic-order tolerance."""
+    from libs.layers.roi_align_tf.crop_and_resize import CropAndResizeFunction
+    rng = np.random.RandomState(1234)
+    B, C, H, W, n = 16, 256, 200, 300, 100
+    xs = np.sort(rng.uniform(0, W, (n, 2)) / (W - 1), axis=1); ys = np.sort(rng.uniform(0, H, (n, 2)) / (H - 1), axis=1)
+    boxes = np.stack((ys[:, 0], xs[:, 0], ys[:, 1], xs[:, 1]), axis=-1).astype(np.float32)      # some reach past 1: extrapolation
+    ind = rng.randint(0, B, n).astype(np.int32)
+    image = rng.randn(B, C, H, W).astype(np.float32)
+    img = cu(image).requires_grad_(True)
+    out = CropAndResizeFunction(7, 7, 0)(img, cu(boxes), cu(ind))
+    assert np.array_equal(out.detach().cpu().numpy(), O.crop_and_resize_fwd(image, boxes, ind, 0.0, 7, 7))
+    g = rng.randn(n, C, 7, 7).astype(np.float32)
+    out.backward(cu(g))
+    np.testing.assert_allclose(img.grad.cpu().numpy(), O.crop_and_resize_bwd(g, boxes, ind, image.shape), rtol=1e-4, atol=1e-5)
+
+
 def make_pyramid(rng, B=2, C=6, ih=128, iw=256, strides=(4, 8, 16, 32)):
     return [rng.normal(0, 1, (B, C, ih // s, iw // s)).astype(np.float32) for s in strides]
 
