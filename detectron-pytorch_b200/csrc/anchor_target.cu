@@ -260,9 +260,11 @@ template <bool FRCNN, typename RawGt>
 __device__ __forceinline__ void store_anchor(const TargetParams &p, long o, const float4 anc, const float4 ge, RawGt raw_gt, float l, bool flag)
 {
     p.labels[o] = l;
-    if (FRCNN) p.targets[o] = encode_fastrcnn_pre(anc, ge, raw_gt);         // anchor.py:133-135 every anchor
-    else p.targets[o] = encode_linear(anc, raw_gt(), p.enc == DETBOX_ENC_LINEAR);
-    p.inside[o] = flag ? p.bbw : make_float4(0, 0, 0, 0);                   // :136-138
+    // targets and inside weights (32 of the 36 bytes) are streaming stores: they are not read again on the device, and
+    // evicting them first lets the 4-byte labels stay in L2 for the label-weight pass that follows
+    if (FRCNN) __stcs(&p.targets[o], encode_fastrcnn_pre(anc, ge, raw_gt));   // anchor.py:133-135 every anchor
+    else __stcs(&p.targets[o], encode_linear(anc, raw_gt(), p.enc == DETBOX_ENC_LINEAR));
+    __stcs(&p.inside[o], flag ? p.bbw : make_float4(0, 0, 0, 0));             // :136-138
 }
 
 template <int EMIT_ILP, bool FRCNN, int MINB>     // EMIT_ILP: anchors encoded side by side in the emit loops; MINB: blocks per SM
@@ -546,7 +548,7 @@ label_weight_kernel(const float *__restrict__ labels, long A, const int32_t *__r
     for (; i + 3 * stride < A4; i += 4 * stride) {              // four independent 16-byte loads in flight per thread
         float4 v[4];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) v[k] = __ldcs(reinterpret_cast<const float4 *>(l) + i + k * stride);
+        for (int k = 0; k < 4; ++k) v[k] = __ldg(reinterpret_cast<const float4 *>(l) + i + k * stride);
 #pragma unroll
         for (int k = 0; k < 4; ++k)
             __stcs(reinterpret_cast<float4 *>(w) + i + k * stride, make_float4(wt(v[k].x), wt(v[k].y), wt(v[k].z), wt(v[k].w)));
