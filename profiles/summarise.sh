@@ -36,4 +36,4 @@ PY
 { echo "# ncu --set full, anchor_target_kernel inside bench.py --steps 2 --warmup 1 --no-cpu --no-extras (B200, round 1, profiles/capture.sh)"
   python ../profiles/ncu_summary.py at_only.csv; echo
   echo "# executed warp instructions by CUDA line (profiles/sass_lines.py)"
-  python ../profiles/sass_lines.py at_src.csv ../detectron-pytorch_b200/build/anchor_target.o anchor_target_kernelILi1ELb1ELi4 25 2>&1 | tail -26; } > ../profiles/r01_ncu_anchor_target.txt
+  python ../profiles/sass_lines.py at_src.csv ../detectron-pytorch_b200/build/anchor_target.o anchor_target_kernelILi2ELb1ELi4 25 2>&1 | tail -26; } > ../profiles/r01_ncu_anchor_target.txt
