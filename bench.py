@@ -91,6 +91,17 @@ def synth_head(rng, n_rows, boost_rows=None):
     return deltas, prob
 
 
+def bench_config(B, world):
+    """`config` of the JSON line — the SAME dict for both arms (the reference arm runs this workload, B images per step,
+    on the host cores)."""
+    return {"workload": "BASELINE configs[4] shard: %d CP-R images per GPU per step @1024x2048, 261888 anchors/img, "
+                        "G=%d/img, anchor pyramid + anchor-target + per-image top-%d + decode + NMS(%.1f)"
+                        % (B, GT_PER_IMAGE, TOP_N, NMS_THR),
+            "images_per_gpu": B, "global_images": B * world, "parallelism": "per-image shard x%d, no collective" % world,
+            "l2_policy": "inputs larger than L2 (%.0f MB of head outputs per step, never re-used inside a step)"
+                         % (B * A_TOTAL * (NUM_CLASSES + 4) * 4 / 1e6)}
+
+
 # --------------------------------------------------- the reference's CPU path for one image ----
 _CPU = {}
 
@@ -169,6 +180,8 @@ class CpuPool:
     def __init__(self, cores):
         import multiprocessing as mp
         self.cores = cores
+        _cpu_setup()          # in the PARENT, before the fork: oracle/_ref/*.so are mapped here too (the driver's
+                              # native-library hook watches this process) and the workers inherit them
         self.pool = mp.get_context("fork").Pool(cores)
         self.kind = self.pool.map(_cpu_warm, range(1000, 1000 + cores), chunksize=1)[0]
 
@@ -487,14 +500,15 @@ def trace_bytes(kid, B, A, G_total, C):
 
 
 def run_reference(args):
-    """--impl reference: the reference's own CPU implementation of the step on all host cores.
-    Every step is a bounded sample: one image per worker process."""
+    """--impl reference: the reference's own CPU implementation of the step on all host cores.  A step is the SAME
+    batch the GPU arm processes per GPU (--batch images, default 64), one image per worker call, round-robin over
+    one worker process per core (the reference parallelises this path over DataLoader workers)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     cores = host_cores()
     pool = CpuPool(cores)
-    per_step = cores
+    per_step = args.batch
     for _ in range(args.warmup):
         pool.step(per_step)
     wall = sum(pool.step(per_step) for _ in range(args.steps))
@@ -504,11 +518,12 @@ def run_reference(args):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * wall / args.steps, 3),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64 IoU / f32 boxes",
             "data": "synthetic",
-            "config": {"workload": "CP-R box path @1024x2048: anchor_pyramid + anchor.encode + top-%d/decode + cpu_nms(%.1f), "
-                                   "261888 anchors/img, G=%d; bounded sample of %d images per step (1 per host core)"
-                                   % (TOP_N, NMS_THR, GT_PER_IMAGE, per_step)},
+            "config": bench_config(per_step, max(1, args.gpus)),
+            "reference_path": "oracle/_ref (the reference's own Cython / NumPy compiled in place): anchor_pyramid + layers.anchor.encode + "
+                              "objectness argsort + bbox_transform_inv on the top-%d rows only (conservative: single_shot.compute_detection "
+                              "decodes all 261888 rows) + cpu_nms; %d images per step over %d worker processes" % (TOP_N, per_step, cores),
             "cpu_baseline": {"value": round(v, 3), "unit": UNIT, "cores": cores, "kind": pool.kind,
-                             "sample": "%d images per step x %d steps, one image per worker process" % (per_step, args.steps)},
+                             "sample": "%d images per step x %d steps, one image per worker call, %d worker processes" % (per_step, args.steps, cores)},
             "e2e": {"value": round(v, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -584,20 +599,34 @@ def main():
     L.detbox_trace_kernel(0, None, None)
     k_ms = float(np.mean([a.elapsed_time(b) for a, b in pairs])) if args.trace else None
     # ---- end-to-end leg: pinned host buffers in, host buffers out --------------------------------
-    step_host = lambda: sess.run_host(gts, h_prob, h_box)
-    ms_e2e = timed_loop(torch, dist, step_host, args.steps, args.warmup)
-    e2e_h2d, e2e_d2h = int(sess.h2d_bytes), int(sess.d2h_bytes)
+    # e2e: the session's compact host format (packed label byte + float32 targets + per-image counts: 17 B / anchor
+    # instead of the reference's 40, same information, detbox.expand_targets rebuilds the four arrays bit for bit) and the
+    # regression deltas gathered from the pinned host buffer (only the top-900 rows per image cross the link).
+    def e2e_leg(fn, note=None):
+        ms = timed_loop(torch, dist, fn, args.steps, args.warmup)
+        d = {"value": round(B * world * args.steps / (ms / 1e3), 1), "unit": UNIT, "ms_per_step": round(ms / args.steps, 4),
+             "h2d_bytes_per_step": int(sess.h2d_bytes), "d2h_bytes_per_step": int(sess.d2h_bytes)}
+        if note:
+            d["note"] = note
+        return d
+    e2e = e2e_leg(lambda: sess.run_host(gts, h_prob, h_box, format="compact"))
+    e2e["format"] = "compact: uint8 (label+1 | inside-weight flag<<7) [B,A] + bbox_targets f32 [B,A,4] + counts i32 [B,2]; rpn_box rows gathered from pinned host memory"
     if sampler:
         sampler.end()
     clocks = sampler.stop() if sampler else None
-    # the same call with the anchor targets left in HBM for a GPU-side loss: host head
-    # outputs in, detections out.  Reported beside e2e, not instead of it.
-    e2e_resident = None
+    e2e_more = {}
     if not args.no_extras:
-        ms_res = timed_loop(torch, dist, lambda: sess.run_host(gts, h_prob, h_box, targets="device"), args.steps, args.warmup)
-        e2e_resident = {"value": round(B * world * args.steps / (ms_res / 1e3), 1), "unit": UNIT, "ms_per_step": round(ms_res / args.steps, 4),
-                        "h2d_bytes_per_step": int(sess.h2d_bytes), "d2h_bytes_per_step": int(sess.d2h_bytes),
-                        "note": "anchor targets stay on the device; detections (boxes, scores, keep) are read back"}
+        e2e_more["e2e_reference_format"] = e2e_leg(lambda: sess.run_host(gts, h_prob, h_box, format="reference", box_rows="copy"),
+                                                   "round-1 path: the reference's four float32 arrays (40 B / anchor) copied back, all of rpn_box staged on the device")
+        e2e_more["e2e_reference_format_mapped_rows"] = e2e_leg(lambda: sess.run_host(gts, h_prob, h_box, format="reference"),
+                                                               "the four float32 arrays copied back; rpn_box rows gathered from pinned host memory")
+        ncore = host_cores()
+        e2e_more["e2e_compact_expanded"] = e2e_leg(lambda: sess.expand(sess.run_host(gts, h_prob, h_box, format="compact"), n_threads=ncore),
+                                                   "compact over the link, then detbox_expand_targets_host (%d threads) materialises the reference's four arrays on the host inside the timed region" % ncore)
+        # the same call with the anchor targets left in HBM for a GPU-side loss: host head
+        # outputs in, detections out.  Reported beside e2e, not instead of it.
+        e2e_more["e2e_targets_resident"] = e2e_leg(lambda: sess.run_host(gts, h_prob, h_box, targets="device"),
+                                                   "anchor targets stay on the device; detections (boxes, scores, keep) are read back")
 
     if args.breakdown and rank == 0:
         anc = sess.anchors
@@ -645,23 +674,15 @@ def main():
                 "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_dev / args.steps, 4),
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64 IoU / f32 boxes",
                 "data": "synthetic",
-                "config": {"workload": "BASELINE configs[4] shard: %d CP-R images per GPU per step @1024x2048, 261888 anchors/img, "
-                                       "G=%d/img, anchor pyramid + anchor-target + per-image top-%d + decode + NMS(%.1f)"
-                                       % (B, GT_PER_IMAGE, TOP_N, NMS_THR),
-                           "launch": "one CUDA-graph replay per step; anchor-target chain and detection chain on two streams inside the graph",
-                           "images_per_gpu": B, "global_images": total_images, "parallelism": "per-image shard x%d, no collective" % world,
-                           "l2_policy": "inputs larger than L2 (%.0f MB of head outputs per step, never re-used inside a step)"
-                                        % ((d_prob.numel() + d_box.numel()) * 4 / 1e6)},
-                "e2e": {"value": round(total_images * args.steps / (ms_e2e / 1e3), 1), "unit": UNIT,
-                        "ms_per_step": round(ms_e2e / args.steps, 4),
-                        "h2d_bytes_per_step": e2e_h2d, "d2h_bytes_per_step": e2e_d2h},
+                "config": bench_config(B, world),
+                "launch": "one CUDA-graph replay per step; anchor-target chain and detection chain on two streams inside the graph",
+                "e2e": e2e,
                 "gpu_launches": int(launches), "clocks": clocks,
                 "step_modes_ms": {"graph_two_streams": round(ms_dev / args.steps, 4), "eager_two_streams": round(ms_eager / args.steps, 4),
                                   "eager_one_stream": round(ms_serial / args.steps, 4)}}
         if roof:
             line["roofline"] = roof
-        if e2e_resident:
-            line["e2e_targets_resident"] = e2e_resident
+        line.update(e2e_more)
         if cpu_base:
             line["cpu_baseline"] = cpu_base
         line.update(extras)

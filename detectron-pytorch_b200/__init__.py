@@ -14,8 +14,8 @@ from ._lib import DetboxError, lib  # noqa: F401
 from . import ops, ops_post, ops_roi, ops_target, parallel, pipeline, fused  # noqa: F401
 from . import libs  # noqa: F401  (reference-shaped mirror: detbox.libs.install() aliases it as `libs`)
 from .ops import (anchor_pyramid, anchor_target, base_anchors, bbox_exclude_ignored_areas,  # noqa: F401
-                  bbox_intersections, bbox_overlaps, box_decode, box_encode, clip_boxes_, launches,
-                  make_target_cfg, NMS_GE_F32, NMS_GE_F64, NMS_GT_F32, ROI_BIN_CENTRE, ROI_CROP_NORM, ROI_GRID_POINT)
+                  bbox_intersections, bbox_overlaps, box_decode, box_encode, clip_boxes_, expand_targets, launches,
+                  make_pyramid_desc, make_target_cfg, pyramid_desc, NMS_GE_F32, NMS_GE_F64, NMS_GT_F32, ROI_BIN_CENTRE, ROI_CROP_NORM, ROI_GRID_POINT)
 from .ops_post import dets_cluster, nms, sort_desc, threshold_segments, to_dets, topk_decode  # noqa: F401
 from .ops_roi import assign_levels, roi_align_backward, roi_align_forward  # noqa: F401
 from .ops_target import match_boxes, roi_target  # noqa: F401

@@ -27,6 +27,11 @@ class TargetCfg(ctypes.Structure):
                 ("clobber_positives", c_int), ("box_encoding", c_int), ("bbweights", c_float * 4)]
 
 
+class PyramidDesc(ctypes.Structure):
+    """detbox_pyramid_desc (include/detbox.h)."""
+    _fields_ = [("n_levels", c_int), ("n_cell", c_int * MAX_LEVELS), ("height", c_int * MAX_LEVELS), ("width", c_int * MAX_LEVELS)]
+
+
 class RoiCfg(ctypes.Structure):
     """detbox_roi_cfg (include/detbox.h)."""
     _fields_ = [("n_levels", c_int),
@@ -61,6 +66,12 @@ SIGNATURES = {
     "detbox_anchor_target_workspace_bytes": (c_size, [c_long, c_int, c_long]),
     "detbox_anchor_target": (c_int, [c_void, c_long, c_void, c_void, c_int, c_long, ctypes.POINTER(TargetCfg),
                                      c_void, c_void, c_void, c_void, c_void, c_void, c_size, c_void]),
+    "detbox_anchor_target_ex_workspace_bytes": (c_size, [c_long, c_int, c_long, ctypes.POINTER(PyramidDesc)]),
+    "detbox_anchor_target_ex": (c_int, [c_void, c_long, ctypes.POINTER(PyramidDesc), c_void, c_void, c_int, c_long,
+                                        ctypes.POINTER(TargetCfg), c_int, c_void, c_void, c_void, c_void, c_void, c_void,
+                                        c_void, c_size, c_void]),
+    "detbox_pack_padded_gt": (c_int, [c_void, c_void, c_int, c_int, c_void, c_void, c_void]),
+    "detbox_expand_targets_host": (c_int, [c_void, c_void, c_long, c_int, P_float, c_void, c_void, c_void, c_int]),
     "detbox_topk_decode_workspace_bytes": (c_size, [c_int, c_long, c_long, c_int]),
     "detbox_topk_decode": (c_int, [c_void, c_int, c_void, c_void, c_int, c_long, c_int, c_long, c_int, c_int,
                                    c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_size, c_void]),
@@ -86,6 +97,7 @@ SIGNATURES = {
     "detbox_to_dets": (c_int, [c_void, c_void, c_int, c_void, c_void, c_void, c_long, c_int, c_int, c_int, c_float,
                                c_void, c_long, c_void, c_void]),
     "detbox_dets_cluster": (c_int, [c_void, c_long, c_void, c_void, c_long, c_void, c_void, c_void]),
+    "detbox_host_device_pointer": (c_int, [c_void, ctypes.POINTER(c_void)]),
     "_nms": (None, [c_void, c_void, c_void, c_int, c_int, c_float, c_int]),
     "detbox_nms_host": (c_int, [c_void, c_int, c_double, c_int, c_void, c_void, c_int]),
     "detbox_anchor_target_host": (c_int, [c_void, c_long, c_void, c_int, ctypes.POINTER(TargetCfg),

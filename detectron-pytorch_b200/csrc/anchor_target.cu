@@ -27,6 +27,11 @@
 // Monotonicity makes the culling exact: min/max are exact, and a rounded (x - y + 1) is a
 // monotone function of its operands, so iw(anchor, gt) <= iw(bbox, gt) also after rounding.
 #include <cstdlib>
+#include <cstring>
+#include <algorithm>
+#include <atomic>
+#include <thread>
+#include <vector>
 #include "box_math.cuh"
 
 using namespace detbox;
@@ -67,6 +72,16 @@ __device__ __forceinline__ bool may_touch32(const float4 bb, const float4 g) {
     return (fminf(bb.z, g.z) - fmaxf(bb.x, g.x) >= -1.0f) && (fminf(bb.w, g.w) - fmaxf(bb.y, g.y) >= -1.0f);
 }
 
+// Pyramid geometry on the device (detbox_pyramid_desc + derived constants).  Anchor row i of level l is
+// (y, x, cell) with i - off[l] = (y * W + x) * ncell + cell, so rel = row * rowlen + xin with rowlen = W * ncell.
+struct PyrDev {
+    int n_levels, E;                                  // E: table entries per image
+    long long off[DETBOX_MAX_LEVELS + 1];             // first anchor row of every level
+    unsigned rowlen[DETBOX_MAX_LEVELS], m_rowlen[DETBOX_MAX_LEVELS];   // divisor and floor(2^32 / divisor)
+    unsigned ncell[DETBOX_MAX_LEVELS], m_ncell[DETBOX_MAX_LEVELS];
+    int eoff[DETBOX_MAX_LEVELS];                      // first table entry of the level: rowlen X entries, then H * ncell Y entries
+};
+
 struct TargetParams {
     const float4 *anchors; long A;
     const float *gt; const int32_t *gt_off;
@@ -76,23 +91,108 @@ struct TargetParams {
     int clobber, enc;
     float4 bbw;
     float *labels; float4 *targets; float4 *inside;
+    uint8_t *packed;                                  // DETBOX_TARGETS_COMPACT: (label + 1) | flag << 7, one byte per anchor
+    const float2 *tab;                                // [batch, E] separable GT-0 targets (pass 0), or NULL
+    const int32_t *sep_bad;                           // != 0: the anchors are not separable over the pyramid -> tables unused
+    PyrDev pyr;
 };
 
+// n / d and n % d for a divisor known on the host: m = floor(2^32 / d) under-estimates the quotient by at most one
+__device__ __forceinline__ void divmod(const unsigned n, const unsigned d, const unsigned m, unsigned &q, unsigned &r) {
+    q = __umulhi(n, m); r = n - q * d;
+    if (r >= d) { ++q; r -= d; }
+}
+__device__ __forceinline__ int level_of(const PyrDev &y, const long long a) {
+    int l = 0;
+#pragma unroll
+    for (int k = 1; k < DETBOX_MAX_LEVELS; ++k)
+        if (k < y.n_levels && a >= y.off[k]) l = k;
+    return l;
+}
+constexpr int TAB_SENT = 0x7fc0dead;                 // "take the full encode" marker in a table entry's second half
+
 // ---- pass 0 ------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(AT_THREADS)
-anchor_bbox_kernel(const float4 *__restrict__ anchors, long A, TileBoxes *__restrict__ tiles)
+// Blocks [0, n_tiles): tile / warp-slice bounding boxes and, given a pyramid descriptor, the separability check:
+// anchor (l, y, x, c) must repeat the x-interval of (l, 0, x, c) and the y-interval of (l, y, 0, c) bit for bit (what
+// anchor.py:47-70 produces: x1 = base_x1 + x * stride does not depend on y).  Any mismatch raises *sep_bad and the emit
+// pass ignores the tables.  Blocks [n_tiles, ...): the separable GT-0 tables, see table_entry().
+//
+// The fastrcnn encode is separable per axis: (dx, dw) depend on the anchor's x-interval and the GT's (cx, w) only,
+// (dy, dh) on the y-interval and (cy, h).  92 % of the CP-R anchors overlap no GT and are encoded against GT 0 of their
+// image (np.argmax of an all-zero row), so per image 2 * E half-encodes (E = sum_l ncell * (W_l + H_l) = 4,464 for
+// CP-R) replace 261,888 full ones; the emit pass then needs two 8-byte loads per anchor.  One axis of
+// encode_fastrcnn_pre, same operations in the same order; *ok = this axis passes the range test of the fast path.
+__device__ __forceinline__ float2 axis_encode(const float lo, const float hi, const float gc, const float gs, const float gmark, bool &ok)
 {
-    __shared__ unsigned bb[4];
+    const float e = (hi - lo) + 1.0f;
+    const float ec = __fmaf_rn(e, 0.5f, lo);
+    const float n = gc - ec;
+    const float mn = fminf(fabsf(n), e), mx = fmaxf(fmaxf(fabsf(n), e), gmark);
+    ok = mn >= 9.5367431640625e-07f && mx <= 1048576.0f;
+    if (!ok) return make_float2(0.0f, 0.0f);
+    const float y = rcp_rn_inrange(e);
+    float qc = __fmul_rn(n, y), qs = __fmul_rn(gs, y);
+    qc = __fmaf_rn(__fmaf_rn(-e, qc, n), y, qc);
+    qs = log_inrange(__fmaf_rn(__fmaf_rn(-e, qs, gs), y, qs));
+    float tc = __fmul_rn(qc, 10.0f), ts = __fmul_rn(qs, 5.0f);
+    tc = __fmaf_rn(__fmaf_rn(-0.1f, tc, qc), 10.0f, tc);
+    ts = __fmaf_rn(__fmaf_rn(-0.2f, ts, qs), 5.0f, ts);
+    return make_float2(tc, ts);
+}
+
+__global__ void __launch_bounds__(AT_THREADS)
+anchor_bbox_kernel(const float4 *__restrict__ anchors, long A, TileBoxes *__restrict__ tiles, int n_tiles,
+                   const PyrDev pyr, const float *__restrict__ gt, const int32_t *__restrict__ gt_off,
+                   float2 *__restrict__ tab, int32_t *__restrict__ sep_bad)
+{
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    if ((int)blockIdx.x >= n_tiles) {                 // ---- table blocks: (image, 256 entries) --------------------
+        const int per_img = (pyr.E + AT_THREADS - 1) / AT_THREADS;
+        const int k = (int)blockIdx.x - n_tiles;
+        const int b = k / per_img, e = (k - b * per_img) * AT_THREADS + tid;
+        const int g0 = gt_off[b];
+        if (e >= pyr.E || gt_off[b + 1] == g0) return;                         // no GT: the emit pass writes zeros
+        int l = 0;
+#pragma unroll
+        for (int q = 1; q < DETBOX_MAX_LEVELS; ++q)
+            if (q < pyr.n_levels && e >= pyr.eoff[q]) l = q;
+        const float *q = gt + (size_t)g0 * 5;
+        const float4 ge = gt_pre(make_float4(q[0], q[1], q[2], q[3]));         // (gcx, gcy, gw | inf, gh)
+        const unsigned k_in = (unsigned)(e - pyr.eoff[l]);
+        bool ok; float2 t;
+        if (k_in < pyr.rowlen[l]) {                                             // X entry: row y = 0
+            const float4 a = anchors[pyr.off[l] + k_in];
+            t = axis_encode(a.x, a.z, ge.x, ge.z, ge.z, ok);
+        } else {                                                                // Y entry: column x = 0
+            unsigned row, cell;
+            divmod(k_in - pyr.rowlen[l], pyr.ncell[l], pyr.m_ncell[l], row, cell);
+            const float4 a = anchors[pyr.off[l] + (long long)row * pyr.rowlen[l] + cell];
+            t = axis_encode(a.y, a.w, ge.y, ge.w, 0.0f, ok);
+        }
+        if (!ok) t.y = __int_as_float(TAB_SENT);
+        tab[(size_t)b * pyr.E + e] = t;
+        return;
+    }
+    __shared__ unsigned bb[4];
     const long tile0 = (long)blockIdx.x * AT_TILE;
     const float INF = __int_as_float(0x7f800000);
     if (tid < 4) bb[tid] = (tid < 2) ? 0xffffffffu : 0u;
     __syncthreads();
     unsigned m0 = 0xffffffffu, m1 = 0xffffffffu, m2 = 0u, m3 = 0u;
+    bool bad = false;
 #pragma unroll
     for (int i = 0; i < AT_ITEMS; ++i) {
         const long a = tile0 + i * AT_THREADS + tid;
         const float4 v = a < A ? anchors[a] : make_float4(INF, INF, -INF, -INF);
+        if (tab && a < A) {                           // separability over the pyramid
+            const int l = level_of(pyr, a);
+            unsigned row, xin, pos, cell;
+            divmod((unsigned)(a - pyr.off[l]), pyr.rowlen[l], pyr.m_rowlen[l], row, xin);
+            divmod(xin, pyr.ncell[l], pyr.m_ncell[l], pos, cell);
+            const float4 rx = anchors[pyr.off[l] + xin];
+            const float4 ry = anchors[pyr.off[l] + (long long)row * pyr.rowlen[l] + cell];
+            bad |= !(v.x == rx.x && v.z == rx.z && v.y == ry.y && v.w == ry.w);
+        }
         const unsigned r0 = __reduce_min_sync(0xffffffffu, float_to_ordered(v.x));
         const unsigned r1 = __reduce_min_sync(0xffffffffu, float_to_ordered(v.y));
         const unsigned r2 = __reduce_max_sync(0xffffffffu, float_to_ordered(v.z));
@@ -102,6 +202,7 @@ anchor_bbox_kernel(const float4 *__restrict__ anchors, long A, TileBoxes *__rest
                                                        ordered_to_float(r2), ordered_to_float(r3));
         m0 = min(m0, r0); m1 = min(m1, r1); m2 = max(m2, r2); m3 = max(m3, r3);
     }
+    if (__any_sync(0xffffffffu, bad) && lane == 0) atomicOr(sep_bad, 1);
     if (lane == 0) {
         atomicMin(&bb[0], m0); atomicMin(&bb[1], m1);
         atomicMax(&bb[2], m2); atomicMax(&bb[3], m3);
@@ -254,25 +355,64 @@ __device__ __forceinline__ void label_of(const TargetParams &p, float gcls, doub
     l_out = l; flag_out = flag;
 }
 
-// One anchor's three outputs.  FRCNN: `ge` is gt_pre() of the matched GT and raw_gt() fetches the row itself for the
-// rare plain-division path; otherwise raw_gt() feeds the linear encodings.
-template <bool FRCNN, typename RawGt>
-__device__ __forceinline__ void store_anchor(const TargetParams &p, long o, const float4 anc, const float4 ge, RawGt raw_gt, float l, bool flag)
+// One anchor's outputs.  Reference format: label, targets, inside weights (36 B).  Compact format: the targets and one
+// byte (label + 1) | flag << 7 staged in shared memory (flushed 16 bytes per thread by pk_flush) — the inside weights
+// are flag ? bbweights : 0 and the label weights a function of the label and the image's (nfg, nbg), so the byte and
+// the two counts carry everything (detbox_expand_targets_host rebuilds the reference's arrays bit for bit).
+__device__ __forceinline__ unsigned pack_label(const float l, const bool flag) {
+    const int li = (int)l;
+    const bool ok = (l == (float)li) && li >= -1 && li <= 125;
+    return (ok ? (unsigned)(li + 1) : 127u) | (flag ? 0x80u : 0u);
+}
+template <bool COMPACT>
+__device__ __forceinline__ void store_anchor(const TargetParams &p, const long o, const int off, uint8_t *s_pk,
+                                             const float4 t, const float l, const bool flag)
 {
-    p.labels[o] = l;
     // targets and inside weights (32 of the 36 bytes) are streaming stores: they are not read again on the device, and
     // evicting them first lets the 4-byte labels stay in L2 for the label-weight pass that follows
-    if (FRCNN) __stcs(&p.targets[o], encode_fastrcnn_pre(anc, ge, raw_gt));   // anchor.py:133-135 every anchor
-    else __stcs(&p.targets[o], encode_linear(anc, raw_gt(), p.enc == DETBOX_ENC_LINEAR));
-    __stcs(&p.inside[o], flag ? p.bbw : make_float4(0, 0, 0, 0));             // :136-138
+    __stcs(&p.targets[o], t);                                                   // anchor.py:133-135 every anchor
+    if (COMPACT) s_pk[off] = (uint8_t)pack_label(l, flag);
+    else {
+        p.labels[o] = l;
+        __stcs(&p.inside[o], flag ? p.bbw : make_float4(0, 0, 0, 0));           // :136-138
+    }
+}
+// tile's packed bytes -> global: 16 bytes per thread when the tile is whole and its first byte 16-byte aligned
+__device__ __forceinline__ void pk_flush(const TargetParams &p, const uint8_t *s_pk, const long o0, const int rem)
+{
+    __syncthreads();
+    uint8_t *dst = p.packed + o0;
+    if (rem == AT_TILE && ((size_t)dst & 15) == 0) {
+        if (threadIdx.x < AT_TILE / 16)
+            reinterpret_cast<uint4 *>(dst)[threadIdx.x] = reinterpret_cast<const uint4 *>(s_pk)[threadIdx.x];
+    } else {
+        for (int i = threadIdx.x; i < rem; i += AT_THREADS) dst[i] = s_pk[i];
+    }
 }
 
-template <int EMIT_ILP, bool FRCNN, int MINB>     // EMIT_ILP: anchors encoded side by side in the emit loops; MINB: blocks per SM
+// GT-0 targets of anchor row ai from the separable tables of its image (tb = tab + b * E); false: an entry carries the
+// "full encode" marker.  lvl >= 0: the level is known (tile inside one level).
+__device__ __forceinline__ bool tab_targets(const PyrDev &y, const float2 *__restrict__ tb, const int lvl, const long long ai, float4 &t)
+{
+    const int l = lvl >= 0 ? lvl : level_of(y, ai);
+    unsigned row, xin, pos, cell;
+    divmod((unsigned)(ai - y.off[l]), y.rowlen[l], y.m_rowlen[l], row, xin);
+    divmod(xin, y.ncell[l], y.m_ncell[l], pos, cell);
+    const float2 X = __ldg(tb + y.eoff[l] + xin);
+    const float2 Y = __ldg(tb + y.eoff[l] + y.rowlen[l] + row * y.ncell[l] + cell);
+    t = make_float4(X.x, Y.x, X.y, Y.y);
+    return (__float_as_int(X.y) != TAB_SENT) & (__float_as_int(Y.y) != TAB_SENT);
+}
+
+// EMIT_ILP: anchors encoded side by side in the emit loops; MINB: blocks per SM; TABLE: GT-0 targets come from the
+// separable tables when the pyramid check passed; COMPACT: output format
+template <int EMIT_ILP, bool FRCNN, int MINB, bool TABLE, bool COMPACT>
 __global__ void __launch_bounds__(AT_THREADS, MINB)
 anchor_target_kernel(const TargetParams p)
 {
     __shared__ GtChunk sm;
     __shared__ float4 s_wbb[AT_ITEMS * AT_WARPS];    // bounding boxes of the tile's warp slices
+    __shared__ __align__(16) uint8_t s_pk[COMPACT ? AT_TILE : 16];
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const int b = blockIdx.y;
     // loads that do not depend on the image are issued first, so their latency overlaps the GT's
@@ -284,24 +424,37 @@ anchor_target_kernel(const TargetParams p)
     const long tile0 = (long)blockIdx.x * AT_TILE;
     const int rem = (int)min((long)AT_TILE, p.A - tile0);      // anchors of this tile (the last one may be partial)
     const float INF = __int_as_float(0x7f800000);
+    const long o0 = (long)b * p.A + tile0;
 
     if (G == 0) {                                    // anchor.py:89-91,133: all background, zero targets
         {
             int nbg = 0;
 #pragma unroll
             for (int i = 0; i < AT_ITEMS; ++i) {
-                const long a = tile0 + i * AT_THREADS + tid;
-                if (a >= p.A) continue;
-                const long o = (long)b * p.A + a;
-                p.labels[o] = 0.0f;
+                const int off = i * AT_THREADS + tid;
+                if (off >= rem) continue;
+                const long o = o0 + off;
                 p.targets[o] = make_float4(0, 0, 0, 0);
-                p.inside[o] = make_float4(0, 0, 0, 0);
+                if (COMPACT) s_pk[off] = 1;
+                else {
+                    p.labels[o] = 0.0f;
+                    p.inside[o] = make_float4(0, 0, 0, 0);
+                }
                 ++nbg;
             }
             nbg = __reduce_add_sync(0xffffffffu, nbg);
             if (lane == 0 && nbg) atomicAdd(&p.counts[b * 2 + 1], nbg);
         }
+        if (COMPACT) pk_flush(p, s_pk, o0, rem);
         return;
+    }
+    // tables: usable when pass 0 found the anchors separable; the tile's level when it lies inside one
+    const bool use_tab = TABLE && p.tab != nullptr && *p.sep_bad == 0;
+    const float2 *tb = nullptr; int lvl = -1;
+    if (TABLE && use_tab) {
+        tb = p.tab + (size_t)b * p.pyr.E;
+        const int l0 = level_of(p.pyr, tile0), l1 = level_of(p.pyr, tile0 + rem - 1);
+        lvl = l0 == l1 ? l0 : -1;
     }
 
     // ---- can any GT of this image touch this tile?  is any column all-zero? ---------------------
@@ -335,35 +488,58 @@ anchor_target_kernel(const TargetParams p)
     //  publishes the staged GT and slice boxes)
     const int cand_any = __syncthreads_or(flags & 1);
     const int zero_any = __syncthreads_or(flags & 2);
+    const float4 *anc_t = p.anchors + tile0;
+
+    float4 gbox0; float gcls0;
+    if (single) { gbox0 = sm.fbox[0]; gcls0 = sm.cls[0]; }
+    else { const float *q0 = p.gt + (size_t)g0 * 5; gbox0 = make_float4(q0[0], q0[1], q0[2], q0[3]); gcls0 = q0[4]; }
+    float l_zero; bool flag_zero;                    // outcome of an anchor that overlaps nothing: argmax = GT 0, max overlap 0
+    label_of(p, gcls0, 0.0, zero_any != 0, 0.0, l_zero, flag_zero);
 
     if (!cand_any) {
-        // streaming path: every row is all-zero -> argmax = GT 0, max overlap 0, no ignore overlap
-        float4 gbox; float gcls;
-        if (single) { gbox = sm.fbox[0]; gcls = sm.cls[0]; }
-        else { const float *q = p.gt + (size_t)g0 * 5; gbox = make_float4(q[0], q[1], q[2], q[3]); gcls = q[4]; }
-        float l0; bool f0;
-        label_of(p, gcls, 0.0, zero_any != 0, 0.0, l0, f0);     // the same for every anchor of the tile
-        const float4 ge = gt_pre(gbox);
-        const float4 *anc_t = p.anchors + tile0;
-        const long o0 = (long)b * p.A + tile0;
+        // streaming path: every row is all-zero -> (l_zero, GT 0) for every anchor of the tile
+        const float4 ge = gt_pre(gbox0);
+        if (TABLE && use_tab) {
 #pragma unroll 1
-        for (int h = 0; h < AT_ITEMS; h += EMIT_ILP) {          // EMIT_ILP independent load -> encode -> store chains
-            float4 anc[EMIT_ILP];
+            for (int h = 0; h < AT_ITEMS; h += 2) {              // two lookups (four 8-byte loads) in flight
+                float4 t[2]; bool ok[2];
 #pragma unroll
-            for (int i = 0; i < EMIT_ILP; ++i) {
-                const int off = (h + i) * AT_THREADS + tid;
-                anc[i] = off < rem ? anc_t[off] : make_float4(0, 0, 0, 0);
+                for (int i = 0; i < 2; ++i) {
+                    const int off = min((h + i) * AT_THREADS + tid, rem - 1);
+                    ok[i] = tab_targets(p.pyr, tb, lvl, tile0 + off, t[i]);
+                }
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    const int off = (h + i) * AT_THREADS + tid;
+                    if (off >= rem) continue;
+                    if (!ok[i]) t[i] = FRCNN ? encode_fastrcnn_pre(anc_t[off], ge, [&]() { return gbox0; }) : t[i];
+                    store_anchor<COMPACT>(p, o0 + off, off, s_pk, t[i], l_zero, flag_zero);
+                }
             }
+        } else {
+#pragma unroll 1
+            for (int h = 0; h < AT_ITEMS; h += EMIT_ILP) {      // EMIT_ILP independent load -> encode -> store chains
+                float4 anc[EMIT_ILP];
 #pragma unroll
-            for (int i = 0; i < EMIT_ILP; ++i) {
-                const int off = (h + i) * AT_THREADS + tid;
-                if (off < rem) store_anchor<FRCNN>(p, o0 + off, anc[i], ge, [&]() { return gbox; }, l0, f0);
+                for (int i = 0; i < EMIT_ILP; ++i) {
+                    const int off = (h + i) * AT_THREADS + tid;
+                    anc[i] = off < rem ? anc_t[off] : make_float4(0, 0, 0, 0);
+                }
+#pragma unroll
+                for (int i = 0; i < EMIT_ILP; ++i) {
+                    const int off = (h + i) * AT_THREADS + tid;
+                    if (off >= rem) continue;
+                    const float4 t = FRCNN ? encode_fastrcnn_pre(anc[i], ge, [&]() { return gbox0; })
+                                           : encode_linear(anc[i], gbox0, p.enc == DETBOX_ENC_LINEAR);
+                    store_anchor<COMPACT>(p, o0 + off, off, s_pk, t, l_zero, flag_zero);
+                }
             }
         }
-        if (tid == 0) {                                          // every anchor of the tile has the label l0
-            if (l0 >= 1.0f) atomicAdd(&p.counts[b * 2 + 0], rem);
-            if (l0 == 0.0f) atomicAdd(&p.counts[b * 2 + 1], rem);
+        if (tid == 0) {                                          // every anchor of the tile has the label l_zero
+            if (l_zero >= 1.0f) atomicAdd(&p.counts[b * 2 + 0], rem);
+            if (l_zero == 0.0f) atomicAdd(&p.counts[b * 2 + 1], rem);
         }
+        if (COMPACT) pk_flush(p, s_pk, o0, rem);
         return;
     }
 
@@ -386,11 +562,6 @@ anchor_target_kernel(const TargetParams p)
         __syncthreads();
     };
 
-    float4 gbox0; float gcls0;
-    if (single) { gbox0 = sm.fbox[0]; gcls0 = sm.cls[0]; }
-    else { const float *q0 = p.gt + (size_t)g0 * 5; gbox0 = make_float4(q0[0], q0[1], q0[2], q0[3]); gcls0 = q0[4]; }
-    float l_zero; bool flag_zero;                    // outcome of an anchor that overlaps nothing
-    label_of(p, gcls0, 0.0, zero_any != 0, 0.0, l_zero, flag_zero);
     const float4 *wbb_base = &s_wbb[w];
     int nfg = 0, nbg = 0;
     // pass 2, decide phase -> emit phase: (label, GT row | regression flag << 31) of every anchor of the tile
@@ -474,47 +645,69 @@ anchor_target_kernel(const TargetParams p)
             if (valid) { nfg += (l >= 1.0f); nbg += (l == 0.0f); }
         }
     }
-    // Emit phase: a plain streaming loop over the tile — anchor in, 36 bytes out — with EMIT_ILP independent
-    // encode chains per thread (the encode is a long dependent sequence: reciprocal, log, divisions).
-    // Every thread reads back only what it wrote itself, so no barrier is needed in between.
-    const float4 *anc_t = p.anchors + tile0;
-    const long o0 = (long)b * p.A + tile0;
+    // Emit phase: a plain streaming loop over the tile — anchor in, 36 bytes out.  Every thread reads back only
+    // what it wrote itself, so no barrier is needed in between.
     const int2 r_zero = make_int2(__float_as_int(l_zero), flag_zero ? (int)0x80000000 : 0);
     int nskip = 0;                                   // anchors of skipped slices: all carry l_zero
-    float4 nxt[EMIT_ILP];                            // the next trip's anchors are requested before this trip's encode
-#pragma unroll
-    for (int i = 0; i < EMIT_ILP; ++i) { const int off = i * AT_THREADS + tid; nxt[i] = off < rem ? anc_t[off] : make_float4(0, 0, 0, 0); }
+    auto raw_gt_of = [&](const int g) {
+        if (single) return sm.fbox[g];
+        const float *q = p.gt + (size_t)(g0 + g) * 5; return make_float4(q[0], q[1], q[2], q[3]);
+    };
+    if (TABLE && use_tab) {
+        // GT 0 (every anchor that overlaps nothing, 92 % at CP-R) comes from the tables; only the lanes matched to
+        // another GT, or whose entry carries the marker, load their anchor and run the encode
 #pragma unroll 1
-    for (int h = 0; h < AT_ITEMS; h += EMIT_ILP) {
-        float4 anc[EMIT_ILP], ge[EMIT_ILP]; int2 r[EMIT_ILP];
-#pragma unroll
-        for (int i = 0; i < EMIT_ILP; ++i) {
-            const int off = (h + i) * AT_THREADS + tid;
-            anc[i] = nxt[i];
-            const int noff = off + EMIT_ILP * AT_THREADS;
-            if (MINB < 4) nxt[i] = (h + EMIT_ILP < AT_ITEMS && noff < rem) ? anc_t[noff] : make_float4(0, 0, 0, 0);
-            const bool skipped = use_masks && smask[h + i][w] == 0;
-            r[i] = skipped ? r_zero : s_res[h + i][tid];
+        for (int h = 0; h < AT_ITEMS; ++h) {
+            const int off = h * AT_THREADS + tid;
+            const bool skipped = use_masks && smask[h][w] == 0;
+            const int2 r = skipped ? r_zero : s_res[h][tid];
             nskip += (skipped && off < rem);
-            const int g = r[i].y & 0x7fffffff;
-            if (single) ge[i] = sm.genc[g];
-            else { const float *q = p.gt + (size_t)(g0 + g) * 5; ge[i] = gt_pre(make_float4(q[0], q[1], q[2], q[3])); }
+            const int g = r.y & 0x7fffffff;
+            float4 t;
+            const bool ok = tab_targets(p.pyr, tb, lvl, tile0 + min(off, rem - 1), t);
+            if (off >= rem) continue;
+            if (g != 0 || !ok) {
+                const float4 ge = single ? sm.genc[g] : gt_pre(raw_gt_of(g));
+                t = FRCNN ? encode_fastrcnn_pre(anc_t[off], ge, [&]() { return raw_gt_of(g); }) : t;
+            }
+            store_anchor<COMPACT>(p, o0 + off, off, s_pk, t, __int_as_float(r.x), r.y < 0);
         }
+    } else {
+        // EMIT_ILP independent encode chains per thread (the encode is a long dependent sequence: reciprocal, log, divisions)
+        float4 nxt[EMIT_ILP];                            // the next trip's anchors are requested before this trip's encode
 #pragma unroll
-        for (int i = 0; i < EMIT_ILP; ++i) {
-            const int off = (h + i) * AT_THREADS + tid;
-            const int g = r[i].y & 0x7fffffff;
-            auto raw_gt = [&]() {
-                if (single) return sm.fbox[g];
-                const float *q = p.gt + (size_t)(g0 + g) * 5; return make_float4(q[0], q[1], q[2], q[3]);
-            };
-            if (off < rem) store_anchor<FRCNN>(p, o0 + off, anc[i], ge[i], raw_gt, __int_as_float(r[i].x), r[i].y < 0);
-        }
-        if (MINB >= 4) {                             // 64 registers: no room to hold the next anchors across the encode
+        for (int i = 0; i < EMIT_ILP; ++i) { const int off = i * AT_THREADS + tid; nxt[i] = off < rem ? anc_t[off] : make_float4(0, 0, 0, 0); }
+#pragma unroll 1
+        for (int h = 0; h < AT_ITEMS; h += EMIT_ILP) {
+            float4 anc[EMIT_ILP], ge[EMIT_ILP]; int2 r[EMIT_ILP];
 #pragma unroll
             for (int i = 0; i < EMIT_ILP; ++i) {
-                const int noff = (h + EMIT_ILP + i) * AT_THREADS + tid;
-                nxt[i] = (h + EMIT_ILP < AT_ITEMS && noff < rem) ? anc_t[noff] : make_float4(0, 0, 0, 0);
+                const int off = (h + i) * AT_THREADS + tid;
+                anc[i] = nxt[i];
+                const int noff = off + EMIT_ILP * AT_THREADS;
+                if (MINB < 4) nxt[i] = (h + EMIT_ILP < AT_ITEMS && noff < rem) ? anc_t[noff] : make_float4(0, 0, 0, 0);
+                const bool skipped = use_masks && smask[h + i][w] == 0;
+                r[i] = skipped ? r_zero : s_res[h + i][tid];
+                nskip += (skipped && off < rem);
+                const int g = r[i].y & 0x7fffffff;
+                if (single) ge[i] = sm.genc[g];
+                else ge[i] = gt_pre(raw_gt_of(g));
+            }
+#pragma unroll
+            for (int i = 0; i < EMIT_ILP; ++i) {
+                const int off = (h + i) * AT_THREADS + tid;
+                const int g = r[i].y & 0x7fffffff;
+                if (off >= rem) continue;
+                const float4 t = FRCNN ? encode_fastrcnn_pre(anc[i], ge[i], [&]() { return raw_gt_of(g); })
+                                       : encode_linear(anc[i], raw_gt_of(g), p.enc == DETBOX_ENC_LINEAR);
+                store_anchor<COMPACT>(p, o0 + off, off, s_pk, t, __int_as_float(r[i].x), r[i].y < 0);
+            }
+            if (MINB >= 4) {                             // 64 registers: no room to hold the next anchors across the encode
+#pragma unroll
+                for (int i = 0; i < EMIT_ILP; ++i) {
+                    const int noff = (h + EMIT_ILP + i) * AT_THREADS + tid;
+                    nxt[i] = (h + EMIT_ILP < AT_ITEMS && noff < rem) ? anc_t[noff] : make_float4(0, 0, 0, 0);
+                }
             }
         }
     }
@@ -526,6 +719,7 @@ anchor_target_kernel(const TargetParams p)
         if (nfg) atomicAdd(&p.counts[b * 2 + 0], nfg);
         if (nbg) atomicAdd(&p.counts[b * 2 + 1], nbg);
     }
+    if (COMPACT) pk_flush(p, s_pk, o0, rem);
 }
 
 // pass 3 — anchor.py:111-118: fg weight 1, bg weight 3*max(nfg,1)/max(nbg,nfg,1), others 0.
@@ -565,46 +759,107 @@ label_weight_kernel(const float *__restrict__ labels, long A, const int32_t *__r
 
 }  // namespace
 
+// detbox_pyramid_desc -> device constants; false when the descriptor does not describe exactly A rows
+static bool make_pyr(const detbox_pyramid_desc *d, long A, PyrDev &y)
+{
+    memset(&y, 0, sizeof(y));
+    if (!d || d->n_levels < 1 || d->n_levels > DETBOX_MAX_LEVELS) return false;
+    long long off = 0; long long e = 0;
+    y.n_levels = d->n_levels;
+    for (int l = 0; l < DETBOX_MAX_LEVELS; ++l) {
+        y.off[l] = off;
+        y.rowlen[l] = y.ncell[l] = 1; y.m_rowlen[l] = y.m_ncell[l] = 0xffffffffu; y.eoff[l] = (int)e;
+        if (l >= d->n_levels) continue;
+        const long long nc = d->n_cell[l], H = d->height[l], W = d->width[l];
+        if (nc < 1 || H < 0 || W < 0) return false;
+        if (H == 0 || W == 0) continue;                                   // empty level: no rows, no entries
+        const long long rowlen = W * nc, rows = H * rowlen;
+        if (rowlen >= (1ll << 31) || rows >= (1ll << 31)) return false;
+        y.rowlen[l] = (unsigned)rowlen; y.m_rowlen[l] = (unsigned)(0x100000000ull / (unsigned long long)rowlen > 0xffffffffull ? 0xffffffffull : 0x100000000ull / (unsigned long long)rowlen);
+        y.ncell[l] = (unsigned)nc; y.m_ncell[l] = (unsigned)(0x100000000ull / (unsigned long long)nc > 0xffffffffull ? 0xffffffffull : 0x100000000ull / (unsigned long long)nc);
+        off += rows;
+        e += rowlen + H * nc;
+        if (e >= (1ll << 30)) return false;
+    }
+    y.off[DETBOX_MAX_LEVELS] = off;
+    for (int l = d->n_levels; l <= DETBOX_MAX_LEVELS; ++l) y.off[l] = off;
+    y.E = (int)e;
+    return off == A && e > 0;
+}
+
+static size_t target_ws_bytes(long A, int batch, long total_gt, long E)
+{
+    return align_up((size_t)(total_gt > 0 ? total_gt : 1) * sizeof(unsigned long long)) +
+           align_up((size_t)(batch > 0 ? batch : 1) * 2 * sizeof(int32_t)) + align_up(4 * sizeof(int32_t)) +
+           align_up((size_t)((A + AT_TILE - 1) / AT_TILE + 1) * sizeof(TileBoxes)) +
+           align_up((size_t)(batch > 0 ? batch : 1) * (size_t)E * sizeof(float2));
+}
+
 extern "C" size_t detbox_anchor_target_workspace_bytes(long A, int batch, long total_gt)
 {
     if (A < 0 || batch < 0 || total_gt < 0) return 0;
-    return align_up((size_t)(total_gt > 0 ? total_gt : 1) * sizeof(unsigned long long)) +
-           align_up((size_t)(batch > 0 ? batch : 1) * 2 * sizeof(int32_t)) +
-           align_up((size_t)((A + AT_TILE - 1) / AT_TILE + 1) * sizeof(TileBoxes));
+    return target_ws_bytes(A, batch, total_gt, 0);
 }
 
-extern "C" int detbox_anchor_target(const float *anchors, long A, const float *gt, const int32_t *gt_off,
-                                    int batch, long total_gt, const detbox_target_cfg *cfg,
-                                    float *labels, float *label_weights, float *bbox_targets,
-                                    float *bbox_inside_weights, int32_t *counts_out,
-                                    void *ws, size_t ws_bytes, void *stream)
+extern "C" size_t detbox_anchor_target_ex_workspace_bytes(long A, int batch, long total_gt, const detbox_pyramid_desc *pyr)
+{
+    if (A < 0 || batch < 0 || total_gt < 0) return 0;
+    PyrDev y;
+    return target_ws_bytes(A, batch, total_gt, make_pyr(pyr, A, y) ? y.E : 0);
+}
+
+extern "C" int detbox_anchor_target_ex(const float *anchors, long A, const detbox_pyramid_desc *pyr,
+                                       const float *gt, const int32_t *gt_off, int batch, long total_gt,
+                                       const detbox_target_cfg *cfg, int format,
+                                       float *labels, float *label_weights, float *bbox_targets,
+                                       float *bbox_inside_weights, uint8_t *packed, int32_t *counts_out,
+                                       void *ws, size_t ws_bytes, void *stream)
 {
     if (A < 0 || batch < 0 || total_gt < 0 || !cfg) return DETBOX_ERR_INVALID;
     if (cfg->box_encoding != DETBOX_ENC_FASTRCNN && cfg->box_encoding != DETBOX_ENC_LINEAR) return DETBOX_ERR_INVALID;
+    if (format != DETBOX_TARGETS_REFERENCE && format != DETBOX_TARGETS_COMPACT) return DETBOX_ERR_INVALID;
+    const bool compact = format == DETBOX_TARGETS_COMPACT;
     if (A == 0 || batch == 0) return DETBOX_OK;
-    if (!anchors || !gt_off || !labels || !label_weights || !bbox_targets || !bbox_inside_weights) return DETBOX_ERR_INVALID;
+    if (!anchors || !gt_off || !bbox_targets) return DETBOX_ERR_INVALID;
+    if (compact ? (!packed || !counts_out) : (!labels || !label_weights || !bbox_inside_weights)) return DETBOX_ERR_INVALID;
     if (total_gt > 0 && !gt) return DETBOX_ERR_INVALID;
-    if (!ws || ws_bytes < detbox_anchor_target_workspace_bytes(A, batch, total_gt)) return DETBOX_ERR_WORKSPACE;
+    TargetParams p;
+    memset(&p, 0, sizeof(p));
+    const bool frcnn = cfg->box_encoding == DETBOX_ENC_FASTRCNN;
+    bool tables = false;
+    if (pyr) {
+        if (!make_pyr(pyr, A, p.pyr)) return DETBOX_ERR_INVALID;        // the descriptor must describe exactly A rows
+        static const bool off = getenv("DETBOX_AT_NOTABLE") != nullptr;
+        tables = frcnn && total_gt > 0 && !off;
+    }
+    if (!ws || ws_bytes < target_ws_bytes(A, batch, total_gt, tables ? p.pyr.E : 0)) return DETBOX_ERR_WORKSPACE;
     if (batch > 65535) return DETBOX_ERR_UNSUPPORTED;
     cudaStream_t st = as_stream(stream);
     Carver cv(ws);
     unsigned long long *colmax = cv.take<unsigned long long>(total_gt > 0 ? total_gt : 1);
     int32_t *counts = cv.take<int32_t>((size_t)batch * 2);
+    int32_t *flags = cv.take<int32_t>(4);
     DETBOX_CUDA_TRY(cudaMemsetAsync(ws, 0, cv.off, st));
     const unsigned n_tiles = (unsigned)((A + AT_TILE - 1) / AT_TILE);
-    TileBoxes *tiles = cv.take<TileBoxes>(n_tiles);
+    TileBoxes *tiles = cv.take<TileBoxes>(n_tiles + 1);
+    float2 *tab = tables ? cv.take<float2>((size_t)batch * p.pyr.E) : nullptr;
+    if (compact) {                                   // the counts are a result: accumulate straight into the caller's array
+        DETBOX_CUDA_TRY(cudaMemsetAsync(counts_out, 0, (size_t)batch * 2 * sizeof(int32_t), st));
+        counts = counts_out;
+    }
 
-    TargetParams p;
     p.anchors = (const float4 *)anchors; p.A = A; p.gt = gt; p.gt_off = gt_off;
     p.colmax = colmax; p.counts = counts; p.tiles = tiles;
     p.bg = cfg->bg_threshold; p.fg = cfg->fg_threshold; p.ign = cfg->ignore_fraction;
     p.clobber = cfg->clobber_positives; p.enc = cfg->box_encoding;
     p.bbw = make_float4(cfg->bbweights[0], cfg->bbweights[1], cfg->bbweights[2], cfg->bbweights[3]);
     p.labels = labels; p.targets = (float4 *)bbox_targets; p.inside = (float4 *)bbox_inside_weights;
+    p.packed = packed; p.tab = tab; p.sep_bad = flags;
 
     dim3 grid(n_tiles, (unsigned)batch);
     if (total_gt > 0) {
-        anchor_bbox_kernel<<<n_tiles, AT_THREADS, 0, st>>>((const float4 *)anchors, A, tiles);
+        const unsigned tab_blocks = tables ? (unsigned)batch * (unsigned)((p.pyr.E + AT_THREADS - 1) / AT_THREADS) : 0u;
+        anchor_bbox_kernel<<<n_tiles + tab_blocks, AT_THREADS, 0, st>>>((const float4 *)anchors, A, tiles, (int)n_tiles, p.pyr, gt, gt_off, tab, flags);
         DETBOX_LAUNCH_CHECK();
         DETBOX_TRACE_BEGIN(DETBOX_K_TARGET_COLMAX, st);
         const int n_slices = (int)n_tiles * AT_ITEMS * AT_WARPS;
@@ -613,16 +868,19 @@ extern "C" int detbox_anchor_target(const float *anchors, long A, const float *g
         DETBOX_LAUNCH_CHECK();
     }
     DETBOX_TRACE_BEGIN(DETBOX_K_TARGET_ASSIGN, st);
-    static const int ilp = []() { const char *e = getenv("DETBOX_AT_ILP"); return e ? atoi(e) : 2; }();   // measured with the packed encode: 2 anchors side by side 0.154 ms, 1: 0.158 ms; 4 spills
-    const bool frcnn = p.enc == DETBOX_ENC_FASTRCNN;
-    static const int minb = []() { const char *e = getenv("DETBOX_AT_MINB"); return e ? atoi(e) : 4; }();
-    if (!frcnn) anchor_target_kernel<1, false, 4><<<grid, AT_THREADS, 0, st>>>(p);
-    else if (minb == 3 && ilp == 2) anchor_target_kernel<2, true, 3><<<grid, AT_THREADS, 0, st>>>(p);
-    else if (minb == 3) anchor_target_kernel<1, true, 3><<<grid, AT_THREADS, 0, st>>>(p);
-    else if (ilp == 2) anchor_target_kernel<2, true, 4><<<grid, AT_THREADS, 0, st>>>(p);
-    else anchor_target_kernel<1, true, 4><<<grid, AT_THREADS, 0, st>>>(p);
+    if (!frcnn) {
+        if (compact) anchor_target_kernel<1, false, 4, false, true><<<grid, AT_THREADS, 0, st>>>(p);
+        else anchor_target_kernel<1, false, 4, false, false><<<grid, AT_THREADS, 0, st>>>(p);
+    } else if (tables) {
+        if (compact) anchor_target_kernel<2, true, 4, true, true><<<grid, AT_THREADS, 0, st>>>(p);
+        else anchor_target_kernel<2, true, 4, true, false><<<grid, AT_THREADS, 0, st>>>(p);
+    } else {
+        if (compact) anchor_target_kernel<2, true, 4, false, true><<<grid, AT_THREADS, 0, st>>>(p);
+        else anchor_target_kernel<2, true, 4, false, false><<<grid, AT_THREADS, 0, st>>>(p);
+    }
     DETBOX_TRACE_END(DETBOX_K_TARGET_ASSIGN, st);
     DETBOX_LAUNCH_CHECK();
+    if (compact) return DETBOX_OK;                   // label weights = f(label, counts): the expander's job
     long wb = (A / 4 + 255) / 256;
     if (wb < 1) wb = 1;
     wb = (wb + 3) / 4;                       // 4 float4 per thread per trip
@@ -632,4 +890,133 @@ extern "C" int detbox_anchor_target(const float *anchors, long A, const float *g
     DETBOX_TRACE_END(DETBOX_K_TARGET_WEIGHTS, st);
     DETBOX_LAUNCH_CHECK();
     return DETBOX_OK;
+}
+
+extern "C" int detbox_anchor_target(const float *anchors, long A, const float *gt, const int32_t *gt_off,
+                                    int batch, long total_gt, const detbox_target_cfg *cfg,
+                                    float *labels, float *label_weights, float *bbox_targets,
+                                    float *bbox_inside_weights, int32_t *counts_out,
+                                    void *ws, size_t ws_bytes, void *stream)
+{
+    if (A > 0 && batch > 0 && (!labels || !label_weights || !bbox_targets || !bbox_inside_weights)) return DETBOX_ERR_INVALID;
+    return detbox_anchor_target_ex(anchors, A, nullptr, gt, gt_off, batch, total_gt, cfg, DETBOX_TARGETS_REFERENCE,
+                                   labels, label_weights, bbox_targets, bbox_inside_weights, nullptr, counts_out,
+                                   ws, ws_bytes, stream);
+}
+
+// ---- padded GT -> concatenated rows + offsets (the collate contract of SURVEY 8f-4) -------------------------------
+__global__ void __launch_bounds__(1024)
+gt_offsets_kernel(const int32_t *__restrict__ counts, int B, int gmax, int32_t *__restrict__ off)
+{
+    __shared__ int s_warp[32];
+    __shared__ int s_carry;
+    if (threadIdx.x == 0) { s_carry = 0; off[0] = 0; }
+    __syncthreads();
+    for (int base = 0; base < B; base += 1024) {
+        const int i = base + threadIdx.x;
+        int v = i < B ? min(max(counts[i], 0), gmax) : 0;
+        int x = v;                                     // inclusive warp scan
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int y = __shfl_up_sync(0xffffffffu, x, d); if ((threadIdx.x & 31) >= d) x += y; }
+        if ((threadIdx.x & 31) == 31) s_warp[threadIdx.x >> 5] = x;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            int w = s_warp[threadIdx.x];
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const int y = __shfl_up_sync(0xffffffffu, w, d); if (threadIdx.x >= d) w += y; }
+            s_warp[threadIdx.x] = w;
+        }
+        __syncthreads();
+        const int incl = x + ((threadIdx.x >> 5) ? s_warp[(threadIdx.x >> 5) - 1] : 0) + s_carry;
+        if (i < B) off[i + 1] = incl;
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry = incl;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256)
+gt_pack_kernel(const float *__restrict__ padded, const int32_t *__restrict__ off, int B, int gmax, float *__restrict__ out)
+{
+    const long total = (long)B * gmax;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int b = (int)(i / gmax), j = (int)(i - (long)b * gmax);
+        const int o = off[b];
+        if (j >= off[b + 1] - o) continue;
+        const float *src = padded + i * 5;
+        float *dst = out + (size_t)(o + j) * 5;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) dst[k] = src[k];
+    }
+}
+
+extern "C" int detbox_pack_padded_gt(const float *gt_padded, const int32_t *gt_counts, int batch, int gmax,
+                                     float *gt_out, int32_t *gt_offsets_out, void *stream)
+{
+    if (batch < 0 || gmax < 0) return DETBOX_ERR_INVALID;
+    if (batch == 0) return DETBOX_OK;
+    if (!gt_counts || !gt_offsets_out || (gmax > 0 && (!gt_padded || !gt_out))) return DETBOX_ERR_INVALID;
+    cudaStream_t st = as_stream(stream);
+    gt_offsets_kernel<<<1, 1024, 0, st>>>(gt_counts, batch, gmax, gt_offsets_out);
+    DETBOX_LAUNCH_CHECK();
+    if (gmax > 0) {
+        DETBOX_CUDA_TRY(cudaMemsetAsync(gt_out, 0, (size_t)batch * gmax * 5 * sizeof(float), st));   // rows past offsets[batch] are unused but finite
+        long gb = ((long)batch * gmax + 255) / 256;
+        if (gb > kNumSMs * 8) gb = kNumSMs * 8;
+        gt_pack_kernel<<<(unsigned)gb, 256, 0, st>>>(gt_padded, gt_offsets_out, batch, gmax, gt_out);
+        DETBOX_LAUNCH_CHECK();
+    }
+    return DETBOX_OK;
+}
+
+// HOST: compact format -> the reference's arrays (libs/layers/anchor.py:111-118 label weights, :136-138 inside weights)
+extern "C" int detbox_expand_targets_host(const uint8_t *packed, const int32_t *counts, long A, int batch,
+                                          const float *bbweights, float *labels, float *label_weights,
+                                          float *inside, int n_threads)
+{
+    if (A < 0 || batch < 0 || !bbweights) return DETBOX_ERR_INVALID;
+    if (A == 0 || batch == 0) return DETBOX_OK;
+    if (!packed || !counts) return DETBOX_ERR_INVALID;
+    if (n_threads < 1) n_threads = 1;
+    std::atomic<int> bad(0);
+    auto work = [&](long i0, long i1) {               // rows [i0, i1) of the flattened [batch * A]
+        long i = i0;
+        while (i < i1) {
+            const int b = (int)(i / A);
+            const long e = std::min(i1, (long)(b + 1) * A);
+            const int nfg = counts[b * 2], nbg = counts[b * 2 + 1];
+            const float wbg = (float)(3 * std::max((double)nfg, 1.0) / std::max((double)std::max(nbg, nfg), 1.0));
+            float lut_l[256], lut_w[256];
+            for (int v = 0; v < 256; ++v) {
+                const int l = (v & 0x7f) - 1;
+                lut_l[v] = (float)l;
+                lut_w[v] = l >= 1 ? 1.0f : (l == 0 ? wbg : 0.0f);
+            }
+            int seen_bad = 0;
+            for (; i < e; ++i) {
+                const unsigned v = packed[i];
+                seen_bad |= ((v & 0x7f) == 127);
+                if (labels) labels[i] = lut_l[v];
+                if (label_weights) label_weights[i] = lut_w[v];
+                if (inside) {
+                    float *o = inside + i * 4;
+                    if (v & 0x80) { o[0] = bbweights[0]; o[1] = bbweights[1]; o[2] = bbweights[2]; o[3] = bbweights[3]; }
+                    else { o[0] = o[1] = o[2] = o[3] = 0.0f; }
+                }
+            }
+            if (seen_bad) bad.store(1);
+        }
+    };
+    const long total = (long)batch * A;
+    if (n_threads == 1 || total < (1 << 16)) work(0, total);
+    else {
+        std::vector<std::thread> th;
+        const long per = (total + n_threads - 1) / n_threads;
+        for (int t = 0; t < n_threads; ++t) {
+            const long i0 = std::min(total, t * per), i1 = std::min(total, i0 + per);
+            if (i0 < i1) th.emplace_back(work, i0, i1);
+        }
+        for (auto &t : th) t.join();
+    }
+    return bad.load() ? DETBOX_ERR_UNSUPPORTED : DETBOX_OK;       // a GT class outside [-1, 125] cannot be packed
 }

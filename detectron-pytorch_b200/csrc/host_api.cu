@@ -56,3 +56,15 @@ extern "C" int detbox_anchor_target_host(const float *anchors, long A, const flo
     if (cur != device_id) cudaSetDevice(cur);
     return rc;
 }
+
+// Device-side address of PINNED host memory (cudaHostAlloc / cudaHostRegister): what a kernel dereferences to read
+// the buffer over PCIe without a staging copy.  Used for the regression deltas of the top-k gather: only the
+// top_n rows per image are ever read, so copying all of rpn_box (16 B x A per image) to the device is wasted link time.
+extern "C" int detbox_host_device_pointer(const void *host_ptr, void **dev_ptr_out)
+{
+    if (!host_ptr || !dev_ptr_out) return DETBOX_ERR_INVALID;
+    void *d = nullptr;
+    DETBOX_CUDA_TRY(cudaHostGetDevicePointer(&d, const_cast<void *>(host_ptr), 0));
+    *dev_ptr_out = d;
+    return DETBOX_OK;
+}

@@ -346,6 +346,217 @@ roi_bwd_kernel(const RoiArgs a)
     }
 }
 
+// ---- NCHW, shared-memory staged (the reference's own layout: [B,C,H,W] features, [R,C,PH,PW] output) ---------------
+// In NCHW the 4 taps of an output element lie in 2 rows of ONE channel plane, and a RoI's taps of one channel cover a
+// small window of that plane (about 11 x 11 pixels after level assignment).  The generic path gathers them one scalar
+// at a time: every 32-byte sector is requested ~3 times through L1 and lanes of a request scatter over 7 rows.  Here a
+// block owns (RoI, RS_CH channels): it copies the window of each channel — whole 16-byte pieces of every row, so each
+// sector the window touches is requested exactly once — into shared memory with cp.async (no registers, every piece in
+// flight at once), then all PH x PW bins sample from shared memory and the [C,PH,PW] output is written in memory
+// order.  Backward is the mirror image: contributions are summed in a zeroed shared window (shared-memory atomics) and
+// every touched 16-byte piece leaves through ONE red.global.add.v4.f32 — block-aggregated atomics instead of 4 per
+// output element.  A window that does not fit is walked in several passes (fewer channels per pass); if not even one
+// channel fits (RoIs far larger than their level), the block falls back to the direct gather / scatter.
+constexpr int RS_THREADS = 256;
+constexpr int RS_CH = 32;                   // channels per block
+constexpr int RS_FLOATS = 10 * 1024;        // staged window floats per block (40 KB: 5 blocks per SM)
+
+struct Window { int y0, x0, wh, ww, vec; }; // ww: row pitch in floats (multiple of 4 when vec)
+
+__device__ __forceinline__ Window roi_window(const Tap *ty, const Tap *tx, int gh, int gw, int W, const float *plane0)
+{
+    __shared__ Window s;
+    if (threadIdx.x == 0) {
+        int ymin = 1 << 30, ymax = -1, xmin = 1 << 30, xmax = -1;
+        for (int i = 0; i < gh; ++i) if (ty[i].valid) { ymin = min(ymin, min(ty[i].i0, ty[i].i1)); ymax = max(ymax, max(ty[i].i0, ty[i].i1)); }
+        for (int i = 0; i < gw; ++i) if (tx[i].valid) { xmin = min(xmin, min(tx[i].i0, tx[i].i1)); xmax = max(xmax, max(tx[i].i0, tx[i].i1)); }
+        Window w;
+        w.vec = ((W & 3) == 0) && (((size_t)plane0 & 15) == 0);
+        if (ymax < 0 || xmax < 0) { w.y0 = w.x0 = 0; w.wh = w.ww = 0; }
+        else {
+            w.y0 = ymin; w.wh = ymax - ymin + 1;
+            w.x0 = w.vec ? (xmin & ~3) : xmin;
+            w.ww = w.vec ? (((xmax + 4) & ~3) - w.x0) : (xmax - xmin + 1);
+        }
+        s = w;
+    }
+    __syncthreads();
+    return s;
+}
+
+__device__ __forceinline__ void cp_async16(float *smem_dst, const float *gmem_src) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+}
+
+template <bool GRID>
+__device__ __forceinline__ float sample_smem(const float *win, int cs, int ww, int y0, int x0, const Tap &y, const Tap &x, float ext) {
+    if (!(y.valid && x.valid)) return ext;
+    const float *r0 = win + (y.i0 - y0) * ww - x0, *r1 = win + (y.i1 - y0) * ww - x0;
+    return blend<GRID>(r0[x.i0], r0[x.i1], r1[x.i0], r1[x.i1], y.w, x.w);
+}
+
+template <bool GRID>
+__global__ void __launch_bounds__(RS_THREADS)
+roi_fwd_nchw_staged_kernel(const RoiArgs a)
+{
+    __shared__ Tap ty[RA_MAXP], tx[RA_MAXP];
+    extern __shared__ __align__(16) float s_win[];
+    int gh, gw;
+    const Prologue s = roi_prologue(a, ty, tx, gh, gw);
+    const detbox_roi_cfg &c = a.cfg;
+    const int PH = c.pooled_h, PW = c.pooled_w, C = c.channels;
+    const int Ctot = c.all_levels ? C * c.n_levels : C;
+    const int coff = c.all_levels ? C * blockIdx.y : 0;
+    const int bins = PH * PW;
+    const long r = blockIdx.x;
+    const int cb = blockIdx.z * RS_CH, cn = min(RS_CH, C - cb);
+    const float *f = s.ok ? c.feat[s.level] : nullptr;
+    const int pool = (GRID && c.pool != DETBOX_POOL_NONE) ? c.pool : DETBOX_POOL_NONE;
+    const float ext = GRID ? 0.0f : c.extrapolation;
+    float *out = a.out + ((size_t)r * Ctot + coff + cb) * bins;
+    if (!f) {                                                   // bad level / batch index: zeros (as the generic path)
+        for (int i = threadIdx.x; i < cn * bins; i += RS_THREADS) out[i] = 0.0f;
+        return;
+    }
+    const size_t plane = (size_t)s.H * s.W;
+    const float *f0 = f + ((size_t)s.b * C + cb) * plane;
+    const Window w = roi_window(ty, tx, gh, gw, s.W, f0);
+    const int cs = w.wh * w.ww;                                 // floats per staged channel
+    if (cs == 0) {                                              // every sample outside the map
+        for (int i = threadIdx.x; i < cn * bins; i += RS_THREADS) out[i] = ext;
+        return;
+    }
+    if (cs > RS_FLOATS || ((plane & 3) != 0 && w.vec)) {        // window of one channel does not fit (or planes lose the alignment): direct gather
+        for (int i = threadIdx.x; i < cn * bins; i += RS_THREADS) {
+            const int ch = i / bins, bin = i - ch * bins, y = bin / PW, x = bin - y * PW;
+            float v;
+            if (pool == DETBOX_POOL_NONE) v = sample_one<GRID, false>(f, s.b, cb + ch, ty[y], tx[x], C, s.H, s.W, ext);
+            else {
+                const float v00 = sample_one<GRID, false>(f, s.b, cb + ch, ty[y], tx[x], C, s.H, s.W, ext);
+                const float v01 = sample_one<GRID, false>(f, s.b, cb + ch, ty[y], tx[x + 1], C, s.H, s.W, ext);
+                const float v10 = sample_one<GRID, false>(f, s.b, cb + ch, ty[y + 1], tx[x], C, s.H, s.W, ext);
+                const float v11 = sample_one<GRID, false>(f, s.b, cb + ch, ty[y + 1], tx[x + 1], C, s.H, s.W, ext);
+                v = (pool == DETBOX_POOL_AVG2) ? (((v00 + v01) + v10) + v11) * 0.25f : fmaxf(fmaxf(v00, v01), fmaxf(v10, v11));
+            }
+            out[i] = v;
+        }
+        return;
+    }
+    const int cpp = min(cn, RS_FLOATS / cs);                    // channels per pass
+    for (int c0 = 0; c0 < cn; c0 += cpp) {
+        const int n = min(cpp, cn - c0);
+        if (c0) __syncthreads();                                // the previous pass has been sampled
+        const float *src = f0 + (size_t)c0 * plane + (size_t)w.y0 * s.W + w.x0;
+        if (w.vec) {
+            const int rq = w.ww >> 2, per = w.wh * rq;          // 16-byte pieces per row / per channel
+            for (int i = threadIdx.x; i < n * per; i += RS_THREADS) {
+                const int ch = i / per, k = i - ch * per, y = k / rq, q = k - y * rq;
+                cp_async16(s_win + ch * cs + y * w.ww + 4 * q, src + (size_t)ch * plane + (size_t)y * s.W + 4 * q);
+            }
+            cp_async_wait_all();
+        } else {
+            for (int i = threadIdx.x; i < n * cs; i += RS_THREADS) {
+                const int ch = i / cs, k = i - ch * cs, y = k / w.ww, x = k - y * w.ww;
+                s_win[i] = __ldg(src + (size_t)ch * plane + (size_t)y * s.W + x);
+            }
+        }
+        __syncthreads();
+        float *o = out + (size_t)c0 * bins;
+        for (int i = threadIdx.x; i < n * bins; i += RS_THREADS) {
+            const int ch = i / bins, bin = i - ch * bins, y = bin / PW, x = bin - y * PW;
+            const float *win = s_win + ch * cs;
+            float v;
+            if (pool == DETBOX_POOL_NONE) v = sample_smem<GRID>(win, cs, w.ww, w.y0, w.x0, ty[y], tx[x], ext);
+            else {   // 2x2 / stride 1 pool over the (PH+1)x(PW+1) sample grid (modules/roi_align.py:23-46)
+                const float v00 = sample_smem<GRID>(win, cs, w.ww, w.y0, w.x0, ty[y], tx[x], ext);
+                const float v01 = sample_smem<GRID>(win, cs, w.ww, w.y0, w.x0, ty[y], tx[x + 1], ext);
+                const float v10 = sample_smem<GRID>(win, cs, w.ww, w.y0, w.x0, ty[y + 1], tx[x], ext);
+                const float v11 = sample_smem<GRID>(win, cs, w.ww, w.y0, w.x0, ty[y + 1], tx[x + 1], ext);
+                v = (pool == DETBOX_POOL_AVG2) ? (((v00 + v01) + v10) + v11) * 0.25f : fmaxf(fmaxf(v00, v01), fmaxf(v10, v11));
+            }
+            __stcs(o + i, v);                                   // streaming store: the output is not re-read here
+        }
+    }
+}
+
+template <bool GRID>
+__global__ void __launch_bounds__(RS_THREADS)
+roi_bwd_nchw_staged_kernel(const RoiArgs a)
+{
+    __shared__ Tap ty[RA_MAXP], tx[RA_MAXP];
+    extern __shared__ __align__(16) float s_win[];
+    int gh, gw;
+    const Prologue s = roi_prologue(a, ty, tx, gh, gw);
+    if (!s.ok) return;
+    const detbox_roi_cfg &c = a.cfg;
+    const int PH = c.pooled_h, PW = c.pooled_w, C = c.channels;
+    const int Ctot = c.all_levels ? C * c.n_levels : C;
+    const int coff = c.all_levels ? C * blockIdx.y : 0;
+    const int bins = PH * PW;
+    const long r = blockIdx.x;
+    const int cb = blockIdx.z * RS_CH, cn = min(RS_CH, C - cb);
+    const size_t plane = (size_t)s.H * s.W;
+    float *g0 = c.grad_feat[s.level] + ((size_t)s.b * C + cb) * plane;
+    const float *go = a.grad_out + ((size_t)r * Ctot + coff + cb) * bins;
+    const Window w = roi_window(ty, tx, gh, gw, s.W, g0);
+    const int cs = w.wh * w.ww;
+    if (cs == 0) return;                                        // no sample inside the map: no gradient
+    if (cs > RS_FLOATS || ((plane & 3) != 0 && w.vec)) {        // direct scatter
+        for (int i = threadIdx.x; i < cn * bins; i += RS_THREADS) {
+            const int ch = i / bins, bin = i - ch * bins, y = bin / PW, x = bin - y * PW;
+            const Tap Y = ty[y], X = tx[x];
+            if (!(Y.valid && X.valid)) continue;
+            float w00, w01, w10, w11;
+            tap_weights<GRID>(go[i], Y.w, X.w, w00, w01, w10, w11);
+            float *gp = g0 + (size_t)ch * plane;
+            atomicAdd(gp + (size_t)Y.i0 * s.W + X.i0, w00);
+            atomicAdd(gp + (size_t)Y.i0 * s.W + X.i1, w01);
+            atomicAdd(gp + (size_t)Y.i1 * s.W + X.i0, w10);
+            atomicAdd(gp + (size_t)Y.i1 * s.W + X.i1, w11);
+        }
+        return;
+    }
+    const int cpp = min(cn, RS_FLOATS / cs);
+    for (int c0 = 0; c0 < cn; c0 += cpp) {
+        const int n = min(cpp, cn - c0);
+        if (c0) __syncthreads();                                // the previous pass has been flushed
+        for (int i = threadIdx.x; i < n * cs; i += RS_THREADS) s_win[i] = 0.0f;
+        __syncthreads();
+        const float *g = go + (size_t)c0 * bins;
+        for (int i = threadIdx.x; i < n * bins; i += RS_THREADS) {
+            const int ch = i / bins, bin = i - ch * bins, y = bin / PW, x = bin - y * PW;
+            const Tap Y = ty[y], X = tx[x];
+            if (!(Y.valid && X.valid)) continue;
+            float w00, w01, w10, w11;
+            tap_weights<GRID>(__ldcs(g + i), Y.w, X.w, w00, w01, w10, w11);
+            float *r0 = s_win + ch * cs + (Y.i0 - w.y0) * w.ww - w.x0, *r1 = s_win + ch * cs + (Y.i1 - w.y0) * w.ww - w.x0;
+            atomicAdd(r0 + X.i0, w00); atomicAdd(r0 + X.i1, w01);
+            atomicAdd(r1 + X.i0, w10); atomicAdd(r1 + X.i1, w11);
+        }
+        __syncthreads();
+        float *dst = g0 + (size_t)c0 * plane + (size_t)w.y0 * s.W + w.x0;
+        if (w.vec) {
+            const int rq = w.ww >> 2, per = w.wh * rq;
+            for (int i = threadIdx.x; i < n * per; i += RS_THREADS) {
+                const int ch = i / per, k = i - ch * per, y = k / rq, q = k - y * rq;
+                const float4 v = *reinterpret_cast<const float4 *>(s_win + ch * cs + y * w.ww + 4 * q);
+                if (v.x != 0.0f || v.y != 0.0f || v.z != 0.0f || v.w != 0.0f)
+                    red_add4(dst + (size_t)ch * plane + (size_t)y * s.W + 4 * q, v);
+            }
+        } else {
+            for (int i = threadIdx.x; i < n * cs; i += RS_THREADS) {
+                const int ch = i / cs, k = i - ch * cs, y = k / w.ww, x = k - y * w.ww;
+                const float v = s_win[i];
+                if (v != 0.0f) atomicAdd(dst + (size_t)ch * plane + (size_t)y * s.W + x, v);
+            }
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256)
 assign_levels_kernel(const float *__restrict__ boxes, long R, detbox_roi_cfg c, int32_t *__restrict__ levels)
 {
@@ -401,6 +612,17 @@ extern "C" int detbox_roi_align_forward(const detbox_roi_cfg *cfg, const float *
     RoiArgs a; a.cfg = *cfg; a.rois = rois; a.R = R; a.levels = levels; a.out = out; a.grad_out = nullptr;
     dim3 grid((unsigned)R, cfg->all_levels ? cfg->n_levels : 1);
     cudaStream_t st = as_stream(stream);
+    static const bool no_staged = getenv("DETBOX_ROI_NOSTAGED") != nullptr;
+    if (cfg->layout == DETBOX_LAYOUT_NCHW && cfg->out_layout == DETBOX_LAYOUT_NCHW && !no_staged) {
+        dim3 g3((unsigned)R, cfg->all_levels ? cfg->n_levels : 1, (unsigned)((cfg->channels + RS_CH - 1) / RS_CH));
+        if (g3.z > 65535) return DETBOX_ERR_UNSUPPORTED;
+        DETBOX_TRACE_BEGIN(DETBOX_K_ROI_FWD, st);
+        if (cfg->mode == DETBOX_ROI_GRID_POINT) roi_fwd_nchw_staged_kernel<true><<<g3, RS_THREADS, RS_FLOATS * sizeof(float), st>>>(a);
+        else roi_fwd_nchw_staged_kernel<false><<<g3, RS_THREADS, RS_FLOATS * sizeof(float), st>>>(a);
+        DETBOX_TRACE_END(DETBOX_K_ROI_FWD, st);
+        DETBOX_LAUNCH_CHECK();
+        return DETBOX_OK;
+    }
     return dispatch(*cfg, [&](auto K) -> int {
         constexpr int k = decltype(K)::value;
         DETBOX_TRACE_BEGIN(DETBOX_K_ROI_FWD, st);
@@ -432,6 +654,17 @@ extern "C" int detbox_roi_align_backward(const detbox_roi_cfg *cfg, const float 
     if (!rois || !grad_out) return DETBOX_ERR_INVALID;
     RoiArgs a; a.cfg = *cfg; a.rois = rois; a.R = R; a.levels = levels; a.out = nullptr; a.grad_out = grad_out;
     dim3 grid((unsigned)R, cfg->all_levels ? cfg->n_levels : 1);
+    static const bool no_staged = getenv("DETBOX_ROI_NOSTAGED") != nullptr;
+    if (cfg->layout == DETBOX_LAYOUT_NCHW && cfg->out_layout == DETBOX_LAYOUT_NCHW && cfg->pool == DETBOX_POOL_NONE && !no_staged) {
+        dim3 g3((unsigned)R, cfg->all_levels ? cfg->n_levels : 1, (unsigned)((cfg->channels + RS_CH - 1) / RS_CH));
+        if (g3.z > 65535) return DETBOX_ERR_UNSUPPORTED;
+        DETBOX_TRACE_BEGIN(DETBOX_K_ROI_BWD, st);
+        if (cfg->mode == DETBOX_ROI_GRID_POINT) roi_bwd_nchw_staged_kernel<true><<<g3, RS_THREADS, RS_FLOATS * sizeof(float), st>>>(a);
+        else roi_bwd_nchw_staged_kernel<false><<<g3, RS_THREADS, RS_FLOATS * sizeof(float), st>>>(a);
+        DETBOX_TRACE_END(DETBOX_K_ROI_BWD, st);
+        DETBOX_LAUNCH_CHECK();
+        return DETBOX_OK;
+    }
     return dispatch(*cfg, [&](auto K) -> int {
         constexpr int k = decltype(K)::value;
         DETBOX_TRACE_BEGIN(DETBOX_K_ROI_BWD, st);

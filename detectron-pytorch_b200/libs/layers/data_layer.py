@@ -29,11 +29,21 @@ def compute_rpn_targets_in_batch(gt_boxes_list, anchors):
     return [t.cpu().numpy() for t in out]
 
 
-def compute_rpn_targets_in_batch_cuda(gt_boxes_list, anchors):
+def compute_rpn_targets_in_batch_cuda(gt_boxes_list, anchors, pyramid=None):
     """Same, device tensors in and out (no host round trip): gt_boxes_list of CUDA tensors [G_i,5],
     anchors CUDA [A,4] -> 4 CUDA tensors.  What RetinaNet.forward wants when rpn_targets is None
     (libs/nets/retinatnet.py:70-75) — the targets are consumed on the device."""
     off = torch.zeros(len(gt_boxes_list) + 1, dtype=torch.int32)
     off[1:] = torch.tensor([int(g.shape[0]) for g in gt_boxes_list]).cumsum(0)
     gt = torch.cat([g.reshape(-1, 5).float() for g in gt_boxes_list], 0) if int(off[-1]) else anchors.new_zeros((0, 5))
-    return ops.anchor_target(anchors, gt, off.to(anchors.device), _anchor._target_cfg())
+    return ops.anchor_target(anchors, gt, off.to(anchors.device), _anchor._target_cfg(), pyramid=pyramid)
+
+
+def compute_rpn_targets_padded_cuda(gt_padded, gt_counts, anchors, pyramid=None, format="reference"):
+    """The collate contract of a device-side target pipeline: gt_padded [B, Gmax, 5] and gt_counts int32
+    [B] CUDA tensors — what a collate_fn that pads the per-image GT (libs/datasets/citypersons2.py:1045-1070) uploads
+    with the images — anchors CUDA [A,4].  Nothing is concatenated or counted on the host; the targets stay in HBM for
+    the loss (libs/nets/model.py:106-128 reads rpn_labels / rpn_bboxes / rpn_bbwghts on the device).
+    format="compact": (packed uint8 [B,A], bbox_targets [B,A,4], counts int32 [B,2])."""
+    gt, off = ops.pack_padded_gt(gt_padded, gt_counts)
+    return ops.anchor_target(anchors, gt, off, _anchor._target_cfg(), pyramid=pyramid, format=format)

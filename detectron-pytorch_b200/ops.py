@@ -51,17 +51,28 @@ def _ptr(t) -> int:
 
 
 class _Workspace:
-    """Grow-only per-(device, stream) scratch buffer handed to the *_workspace_bytes() APIs."""
+    """Grow-only per-(device, stream) scratch buffer handed to the *_workspace_bytes() APIs.
+
+    A CUDA graph bakes the buffer's address into its kernel nodes, so a buffer that was handed out while a stream
+    was capturing is never freed: when a later, larger request on the same (device, stream handle) replaces it, the
+    old tensor is retired (kept alive here) and the graph keeps writing into memory nothing else owns."""
 
     def __init__(self):
         self.bufs = {}
+        self.captured = set()
+        self.retired = []
 
     def get(self, nbytes: int, device) -> torch.Tensor:
-        key = (device.index, _stream())
+        key = (device.index, torch.cuda.current_stream(device).cuda_stream)
         buf = self.bufs.get(key)
         if buf is None or buf.numel() < nbytes:
+            if buf is not None and key in self.captured:
+                self.retired.append(buf)
+                self.captured.discard(key)
             buf = torch.empty(int(nbytes * 1.25) + 1024, dtype=torch.uint8, device=device)
             self.bufs[key] = buf
+        if torch.cuda.is_current_stream_capturing():
+            self.captured.add(key)
         return buf
 
 
@@ -82,8 +93,24 @@ def base_anchors(scales, ratios, base) -> np.ndarray:
     return out
 
 
+def make_pyramid_desc(n_cell, heights, widths):
+    """detbox_pyramid_desc: the grid geometry anchor rows were expanded over (level -> y -> x -> cell anchor)."""
+    d = _lib.PyramidDesc()
+    d.n_levels = len(n_cell)
+    if d.n_levels > _lib.MAX_LEVELS:
+        raise _lib.DetboxError("at most %d pyramid levels" % _lib.MAX_LEVELS)
+    for l, (n, h, w) in enumerate(zip(n_cell, heights, widths)):
+        d.n_cell[l], d.height[l], d.width[l] = int(n), int(h), int(w)
+    return d
+
+
+def pyramid_desc(strides, ih, iw, anchor_scales, anchor_ratios, anchor_base, anchor_shift=((0.0, 0.0),), device="cuda"):
+    """The descriptor of the rows anchor_pyramid(...) returns for the same arguments."""
+    return anchor_pyramid(strides, ih, iw, anchor_scales, anchor_ratios, anchor_base, anchor_shift, device, desc_only=True)
+
+
 def anchor_pyramid(strides, ih, iw, anchor_scales, anchor_ratios, anchor_base, anchor_shift=((0.0, 0.0),),
-                   device="cuda", dtype=torch.float32) -> torch.Tensor:
+                   device="cuda", dtype=torch.float32, desc_only=False) -> torch.Tensor:
     """libs/boxes/anchor.py:30-44 on the device: [sum_l H_l*W_l*A, 4], level -> y -> x -> (shift, ratio, scale)."""
     key = (repr(list(strides)), int(ih), int(iw), repr(anchor_scales), repr(anchor_ratios), int(anchor_base),
            repr(np.asarray(anchor_shift, np.float64).tolist()), str(device))
@@ -102,6 +129,8 @@ def anchor_pyramid(strides, ih, iw, anchor_scales, anchor_ratios, anchor_base, a
             _cell_cache.clear()
         hit = _cell_cache[key] = (torch.from_numpy(np.vstack(cells)).to(device), n_cell, hs, ws)   # <= 1 KB, uploaded once
     cell_dev, n_cell, hs, ws = hit
+    if desc_only:
+        return make_pyramid_desc(n_cell, hs, ws)
     L = len(strides)
     total = sum(h * w * n for h, w, n in zip(hs, ws, n_cell))
     out = torch.empty((total, 4), dtype=dtype, device=cell_dev.device)
@@ -181,16 +210,44 @@ def make_target_cfg(bg, fg, clobber=True, ignore_fraction=0.3, bbweights=(1., 1.
     return c
 
 
-def anchor_target(anchors, gt, gt_offsets, tcfg, return_counts=False, out=None):
+def anchor_target(anchors, gt, gt_offsets, tcfg, return_counts=False, out=None, pyramid=None, format="reference"):
     """Batched libs/layers/anchor.py:17-145.  anchors [A,4]; gt [sumG,5] (images concatenated);
     gt_offsets int32 [B+1] (CUDA).  Returns labels [B,A], label_weights [B,A], bbox_targets [B,A,4],
     bbox_inside_weights [B,A,4] (+ counts int32 [B,2] = (#fg, #bg)).  `out`: the four tensors to write
-    into (contiguous float32 CUDA tensors of those shapes) instead of fresh allocations."""
+    into (contiguous float32 CUDA tensors of those shapes) instead of fresh allocations.
+
+    pyramid: the detbox_pyramid_desc of the anchors (pyramid_desc(...)): GT-0 targets then come from separable
+    per-image tables (verified on the device, bit-identical results).
+    format="compact": returns (packed uint8 [B,A], bbox_targets [B,A,4], counts int32 [B,2]) — 17 bytes per
+    anchor instead of 40; expand_targets() rebuilds the reference's arrays on the host.  `out` = those three."""
     a = _dev(anchors).view(-1, 4)
     g = _dev(gt).view(-1, 5)
     off = _dev(gt_offsets, torch.int32, "gt_offsets")
     B, A, G = off.numel() - 1, a.shape[0], g.shape[0]
     dev = a.device
+    if format not in ("reference", "compact"):
+        raise _lib.DetboxError("format must be 'reference' or 'compact'")
+    compact = format == "compact"
+    L = lib()
+    pd = ctypes.byref(pyramid) if pyramid is not None else None
+    nbytes = L.detbox_anchor_target_ex_workspace_bytes(A, B, G, pd)
+    ws = _ws.get(nbytes, dev)
+    if compact:
+        if out is not None:
+            packed, bt, counts = out
+            for t, shape, dt in ((packed, (B, A), torch.uint8), (bt, (B, A, 4), torch.float32), (counts, (B, 2), torch.int32)):
+                if not (t.is_cuda and t.dtype == dt and t.is_contiguous() and tuple(t.shape) == shape):
+                    raise _lib.DetboxError("anchor_target(format='compact', out=...): expected contiguous CUDA tensors uint8 %s, "
+                                           "float32 %s, int32 %s" % ((B, A), (B, A, 4), (B, 2)))
+        else:
+            packed = torch.empty((B, A), dtype=torch.uint8, device=dev)
+            bt = torch.empty((B, A, 4), dtype=torch.float32, device=dev)
+            counts = torch.empty((B, 2), dtype=torch.int32, device=dev)
+        check(L.detbox_anchor_target_ex(a.data_ptr(), A, pd, g.data_ptr() if G else 0, off.data_ptr(), B, G, ctypes.byref(tcfg), 1,
+                                        0, 0, bt.data_ptr(), 0, packed.data_ptr(), counts.data_ptr(),
+                                        ws.data_ptr(), ws.numel(), _stream()), "anchor_target")
+        _count((3 if G else 1) if A and B else 0)
+        return packed, bt, counts
     if out is not None:
         labels, lw, bt, bw = out
         for t, shape in ((labels, (B, A)), (lw, (B, A)), (bt, (B, A, 4)), (bw, (B, A, 4))):
@@ -202,12 +259,51 @@ def anchor_target(anchors, gt, gt_offsets, tcfg, return_counts=False, out=None):
         bt = torch.empty((B, A, 4), dtype=torch.float32, device=dev)
         bw = torch.empty((B, A, 4), dtype=torch.float32, device=dev)
     counts = torch.empty((B, 2), dtype=torch.int32, device=dev) if return_counts else None
-    nbytes = lib().detbox_anchor_target_workspace_bytes(A, B, G)
-    ws = _ws.get(nbytes, dev)
-    check(lib().detbox_anchor_target(a.data_ptr(), A, g.data_ptr() if G else 0, off.data_ptr(), B, G, ctypes.byref(tcfg),
-                                     labels.data_ptr(), lw.data_ptr(), bt.data_ptr(), bw.data_ptr(), _ptr(counts),
-                                     ws.data_ptr(), ws.numel(), _stream()), "anchor_target")
-    _count(4 if G else 2)
+    check(L.detbox_anchor_target_ex(a.data_ptr(), A, pd, g.data_ptr() if G else 0, off.data_ptr(), B, G, ctypes.byref(tcfg), 0,
+                                    labels.data_ptr(), lw.data_ptr(), bt.data_ptr(), bw.data_ptr(), 0, _ptr(counts),
+                                    ws.data_ptr(), ws.numel(), _stream()), "anchor_target")
+    _count((4 if G else 2) if A and B else 0)
     if return_counts:
         return labels, lw, bt, bw, counts
     return labels, lw, bt, bw
+
+
+def pack_padded_gt(gt_padded, gt_counts):
+    """[B, Gmax, 5] padded GT + int32 [B] counts (CUDA) -> (gt [B*Gmax, 5] buffer whose first offsets[B] rows are the
+    concatenated GT, offsets int32 [B+1]) for anchor_target, on the device (no host synchronisation: the row count
+    stays on the device, so the full-size buffer is handed on and total_gt = B*Gmax bounds the work)."""
+    g = _dev(gt_padded)
+    if g.dim() != 3 or g.shape[2] != 5:
+        raise _lib.DetboxError("pack_padded_gt: gt_padded must be [B, Gmax, 5]")
+    c = _dev(gt_counts, torch.int32, "gt_counts").view(-1)
+    B, gmax = g.shape[0], g.shape[1]
+    if c.numel() != B:
+        raise _lib.DetboxError("pack_padded_gt: %d images but %d counts" % (B, c.numel()))
+    out = torch.empty((B * gmax, 5), dtype=torch.float32, device=g.device)
+    off = torch.empty((B + 1,), dtype=torch.int32, device=g.device)
+    check(lib().detbox_pack_padded_gt(g.data_ptr(), c.data_ptr(), B, gmax, out.data_ptr(), off.data_ptr(), _stream()), "pack_padded_gt")
+    _count(2 if gmax else 1)
+    return out, off
+
+
+def expand_targets(packed, counts, bbweights=(1., 1., 1., 1.), n_threads=None, out=None):
+    """HOST: the compact anchor-target format -> the reference's labels [B,A], label_weights [B,A],
+    bbox_inside_weights [B,A,4] (libs/layers/anchor.py:111-118,136-138), bit for bit.  packed uint8 [B,A] and
+    counts int32 [B,2] are CPU tensors / arrays (e.g. pinned buffers a D2H copy filled); bbox_targets needs no work."""
+    pk = packed if isinstance(packed, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(packed))
+    ct = counts if isinstance(counts, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(counts, np.int32))
+    if pk.is_cuda or ct.is_cuda or pk.dtype != torch.uint8 or ct.dtype != torch.int32:
+        raise _lib.DetboxError("expand_targets takes HOST uint8 / int32 arrays (copy the device results first)")
+    pk, ct = pk.contiguous(), ct.contiguous()
+    B, A = pk.shape
+    if out is None:
+        out = (torch.empty((B, A), dtype=torch.float32), torch.empty((B, A), dtype=torch.float32),
+               torch.empty((B, A, 4), dtype=torch.float32))
+    labels, lw, bw = out
+    w = (ctypes.c_float * 4)(*[float(x) for x in bbweights])
+    if n_threads is None:
+        import os
+        n_threads = min(16, len(os.sched_getaffinity(0)))
+    check(lib().detbox_expand_targets_host(pk.data_ptr(), ct.data_ptr(), A, B, w, labels.data_ptr(), lw.data_ptr(),
+                                           bw.data_ptr(), int(n_threads)), "expand_targets")
+    return labels, lw, bw

@@ -2,6 +2,8 @@
 See ops.py for the conventions."""
 from __future__ import annotations
 
+import ctypes
+
 import torch
 
 from . import _lib
@@ -28,8 +30,20 @@ def topk_decode(rpn_box, rpn_prob, anchors, top_n, activation="softmax", box_enc
     """detection_model._decode_and_choose_top_n_stage1 (libs/nets/model.py:308-321).
     rpn_box [B*A,4], rpn_prob [B*A,C], anchors [A,4].  Returns a dict with 'boxes' [K,4] and, as
     requested in `want`, 'probs' [K,C], 'img_ids' int64 [K], 'anchors' [K,4], 'flat_idx' int64 [K],
-    'scores' [K]; K = min(top_n, B*A) (per_image: B*min(top_n, A), image-major)."""
-    box, prob, anc = _dev(rpn_box).view(-1, 4), _dev(rpn_prob), _dev(anchors).view(-1, 4)
+    'scores' [K]; K = min(top_n, B*A) (per_image: B*min(top_n, A), image-major).
+    rpn_box may be a PINNED HOST float32 tensor: only the selected rows are gathered, straight over PCIe through the
+    buffer's device-side address, instead of copying every row to the device first."""
+    prob, anc = _dev(rpn_prob), _dev(anchors).view(-1, 4)
+    if isinstance(rpn_box, torch.Tensor) and not rpn_box.is_cuda:
+        if not (rpn_box.is_pinned() and rpn_box.dtype == torch.float32 and rpn_box.is_contiguous()):
+            raise _lib.DetboxError("topk_decode: a host rpn_box must be a pinned contiguous float32 tensor (there is no CPU path)")
+        box = rpn_box.view(-1, 4)
+        mapped = ctypes.c_void_p()
+        check(lib().detbox_host_device_pointer(box.data_ptr(), ctypes.byref(mapped)), "host_device_pointer")
+        box_ptr = mapped.value
+    else:
+        box = _dev(rpn_box).view(-1, 4)
+        box_ptr = box.data_ptr()
     if prob.dim() == 1:
         prob = prob.view(-1, 1)
     N, C, A = box.shape[0], prob.shape[1], anc.shape[0]
@@ -38,7 +52,7 @@ def topk_decode(rpn_box, rpn_prob, anchors, top_n, activation="softmax", box_enc
                                % (N, prob.shape[0], A))
     B = N // A
     K = B * min(int(top_n), A) if per_image else min(int(top_n), N)
-    dev = box.device
+    dev = prob.device
     out = {"boxes": torch.empty((K, 4), dtype=torch.float32, device=dev)}
     if "probs" in want:
         out["probs"] = torch.empty((K, C), dtype=torch.float32, device=dev)
@@ -53,7 +67,7 @@ def topk_decode(rpn_box, rpn_prob, anchors, top_n, activation="softmax", box_enc
     if K == 0:
         return out
     ws = _ws.get(lib().detbox_topk_decode_workspace_bytes(B, A, int(top_n), int(per_image)), dev)
-    check(lib().detbox_topk_decode(prob.data_ptr(), C, box.data_ptr(), anc.data_ptr(), B, A, ACT[activation], int(top_n),
+    check(lib().detbox_topk_decode(prob.data_ptr(), C, box_ptr, anc.data_ptr(), B, A, ACT[activation], int(top_n),
                                    int(per_image), ENC[box_encoding], out["boxes"].data_ptr(), _ptr(out.get("probs")),
                                    _ptr(out.get("img_ids")), _ptr(out.get("anchors")), _ptr(out.get("flat_idx")),
                                    _ptr(out.get("scores")), ws.data_ptr(), ws.numel(), _stream()), "topk_decode")

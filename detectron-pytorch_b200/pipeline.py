@@ -39,6 +39,9 @@ class BoxOpsSession:
         self.top_n, self.nms_thresh, self.nms_cmp, self.activation = int(top_n), float(nms_thresh), nms_cmp, activation
         self.tcfg = ops.make_target_cfg(bg, fg)
         self.anchors = ops.anchor_pyramid(*self.anchor_args, device=self.dev)
+        # grid geometry of those rows: lets the anchor-target pass take GT-0 targets from separable tables (the
+        # library verifies separability on the device on every call, so this is a hint, not a promise)
+        self.pyr = ops.pyramid_desc(*self.anchor_args, device=self.dev)
         self.A = A = self.anchors.shape[0]
         B = self.B
         self.K = B * min(self.top_n, A)
@@ -55,6 +58,7 @@ class BoxOpsSession:
         self.h_boxes, self.h_scores = pin((self.K, 4), torch.float32), pin((self.K,), torch.float32)
         self.h_img = pin((self.K,), torch.int64)
         self.h_keep, self.h_nkeep = pin((self.K,), torch.int64), pin((B + 1,), torch.int32)
+        self.h_packed = self.h_counts = self.d_packed = None     # compact host format: allocated on first use
         self._keep_out = pin((self.K,), torch.int64)
         self._h_nk = None
         self._streams = [torch.cuda.Stream(self.dev) for _ in range(3)]     # copy-in, kernels, copy-out
@@ -93,10 +97,10 @@ class BoxOpsSession:
             side.wait_stream(cur)                                  # fork: after the anchors and every earlier use of the inputs
             with torch.cuda.stream(side):
                 sel, keep, n_keep = detections()
-            labels, lw, bt, bw = ops.anchor_target(self.anchors, gt, gt_offsets, self.tcfg)
+            labels, lw, bt, bw = ops.anchor_target(self.anchors, gt, gt_offsets, self.tcfg, pyramid=self.pyr)
             cur.wait_stream(side)                                  # join
         else:
-            labels, lw, bt, bw = ops.anchor_target(self.anchors, gt, gt_offsets, self.tcfg)
+            labels, lw, bt, bw = ops.anchor_target(self.anchors, gt, gt_offsets, self.tcfg, pyramid=self.pyr)
             sel, keep, n_keep = detections()
         return {"labels": labels, "label_weights": lw, "bbox_targets": bt, "bbox_inside_weights": bw,
                 "boxes": sel["boxes"], "scores": sel["scores"], "img_ids": sel["img_ids"],
@@ -143,7 +147,8 @@ class BoxOpsSession:
             self.h_off[i + 1] = off
         return off
 
-    def run_host(self, gt_boxes_list, rpn_prob_host, rpn_box_host, chunk=8, targets="host"):
+    def run_host(self, gt_boxes_list, rpn_prob_host, rpn_box_host, chunk=8, targets="host", format="reference",
+                 box_rows="auto"):
         """gt_boxes_list: B NumPy arrays [G_i,5]; rpn_prob_host [B*A,C] / rpn_box_host [B*A,4]:
         float32 host tensors (pinned for asynchronous copies).  Returns pinned host tensors; the
         call returns after all streams have drained, so they are ready to read.
@@ -154,18 +159,38 @@ class BoxOpsSession:
 
         targets="device": the four anchor-target tensors stay in HBM ([B,A] / [B,A,4] CUDA tensors in the result)
         for a loss that runs on the GPU — the training integration of INTEGRATION.md §2, where the reference
-        itself copies its CPU-computed targets TO the device — and only the detections travel back."""
+        itself copies its CPU-computed targets TO the device — and only the detections travel back.
+
+        format="reference": labels / label_weights / bbox_targets / bbox_inside_weights as float32 arrays, the
+        reference's return types (40 bytes per anchor over the link).  format="compact": 'packed' uint8 [B,A]
+        ((label + 1) | flag << 7), 'bbox_targets' [B,A,4] and 'counts' int32 [B,2] — 17 bytes per anchor, the
+        same information; `expand(result)` rebuilds the reference's arrays on the host, bit for bit.
+
+        box_rows: "copy" stages all of rpn_box on the device (16 bytes x A per image); "mapped" lets the top-k
+        gather read the top_n selected rows straight out of the pinned host buffer (model.py:314-318 indexes
+        rpn_box[order] the same way); "auto" = mapped when rpn_box_host is pinned."""
         if targets not in ("host", "device"):
             raise DetboxError("targets must be 'host' or 'device'")
-        on_dev = targets == "device"
-        if on_dev and getattr(self, "d_labels", None) is None:
-            dv = lambda shape: torch.empty(shape, dtype=torch.float32, device=self.dev)
-            self.d_labels, self.d_lw = dv((self.B, self.A)), dv((self.B, self.A))
-            self.d_bt, self.d_bw = dv((self.B, self.A, 4)), dv((self.B, self.A, 4))
+        if format not in ("reference", "compact"):
+            raise DetboxError("format must be 'reference' or 'compact'")
+        if box_rows == "auto":
+            box_rows = "mapped" if rpn_box_host.is_pinned() else "copy"
+        if box_rows not in ("copy", "mapped"):
+            raise DetboxError("box_rows must be 'auto', 'copy' or 'mapped'")
+        on_dev, compact = targets == "device", format == "compact"
         B, A, C = self.B, self.A, self.C
+        dv = lambda shape, dt=torch.float32: torch.empty(shape, dtype=dt, device=self.dev)
+        if getattr(self, "d_bt", None) is None:                   # device-side result buffers, reused by every call
+            self.d_bt = dv((B, A, 4))
+        if compact and self.d_packed is None:
+            self.d_packed, self.d_counts = dv((B, A), torch.uint8), dv((B, 2), torch.int32)
+            self.h_packed = torch.empty((B, A), dtype=torch.uint8, pin_memory=True)
+            self.h_counts = torch.empty((B, 2), dtype=torch.int32, pin_memory=True)
+        if not compact and getattr(self, "d_labels", None) is None:
+            self.d_labels, self.d_lw, self.d_bw = dv((B, A)), dv((B, A)), dv((B, A, 4))
         G = self.stage_gt(gt_boxes_list)
         s_in, s_k, s_out = self._streams
-        cur = torch.cuda.current_stream()
+        cur = torch.cuda.current_stream(self.dev)
         for s in self._streams:
             s.wait_stream(cur)
         prob_h, box_h = rpn_prob_host.view(B * A, C), rpn_box_host.view(B * A, 4)
@@ -175,7 +200,7 @@ class BoxOpsSession:
             self.d_off.copy_(self.h_off, non_blocking=True)
         self.anchors = ops.anchor_pyramid(*self.anchor_args, device=self.dev)     # data_layer.py:138, once per batch
         s_k.wait_stream(cur)
-        hold, d2h = [], 0
+        hold, d2h, h2d = [], 0, G * 20 + self.h_off.numel() * 4
         tl = getattr(self, "timeline", None)        # optional instrumentation (profiles/timeline_probe.py)
         if tl is not None:
             import time as _time
@@ -197,16 +222,27 @@ class BoxOpsSession:
             ev_in = torch.cuda.Event()
             with torch.cuda.stream(s_in):
                 self.d_prob[r0:r1].copy_(prob_h[r0:r1], non_blocking=True)
-                self.d_box[r0:r1].copy_(box_h[r0:r1], non_blocking=True)
+                h2d += (r1 - r0) * C * 4
+                if box_rows == "copy":
+                    self.d_box[r0:r1].copy_(box_h[r0:r1], non_blocking=True)
+                    h2d += (r1 - r0) * 16
+                else:
+                    h2d += n * kper * 16                           # rows the gather reads over the link
                 ev_in.record(s_in)
                 mark("h2d%d" % c0, s_in)
             ev_k = torch.cuda.Event()
             with torch.cuda.stream(s_k):
                 s_k.wait_event(ev_in)
-                out = (self.d_labels[c0:c0 + n], self.d_lw[c0:c0 + n], self.d_bt[c0:c0 + n], self.d_bw[c0:c0 + n]) if on_dev else None
-                labels, lw, bt, bw = ops.anchor_target(self.anchors, self.d_gt[:G], self.d_off[c0:c0 + n + 1], self.tcfg, out=out)
-                sel = ops_post.topk_decode(self.d_box[r0:r1], self.d_prob[r0:r1], self.anchors, self.top_n, self.activation,
-                                           "fastrcnn", per_image=True, want=("img_ids", "scores"))
+                sl = slice(c0, c0 + n)
+                if compact:
+                    tg = ops.anchor_target(self.anchors, self.d_gt[:G], self.d_off[c0:c0 + n + 1], self.tcfg, pyramid=self.pyr,
+                                           format="compact", out=(self.d_packed[sl], self.d_bt[sl], self.d_counts[sl]))
+                else:
+                    tg = ops.anchor_target(self.anchors, self.d_gt[:G], self.d_off[c0:c0 + n + 1], self.tcfg, pyramid=self.pyr,
+                                           out=(self.d_labels[sl], self.d_lw[sl], self.d_bt[sl], self.d_bw[sl]))
+                sel = ops_post.topk_decode(self.d_box[r0:r1] if box_rows == "copy" else box_h[r0:r1], self.d_prob[r0:r1],
+                                           self.anchors, self.top_n, self.activation, "fastrcnn", per_image=True,
+                                           want=("img_ids", "scores"))
                 keep, n_keep = ops_post.nms(sel["boxes"], sel["scores"], self.nms_thresh, self.nms_cmp,
                                             seg_ids=sel["img_ids"], n_seg=n, presorted=True)
                 ev_k.record(s_k)
@@ -215,15 +251,17 @@ class BoxOpsSession:
             pairs = [(self.h_boxes[k0:k1], sel["boxes"]), (self.h_scores[k0:k1], sel["scores"]),
                      (self.h_img[k0:k1], sel["img_ids"]), (self.h_keep[k0:k1], keep), (h_nk[ci, :n + 1], n_keep)]
             if not on_dev:
-                pairs = [(self.h_labels[c0:c0 + n], labels), (self.h_lw[c0:c0 + n], lw), (self.h_bt[c0:c0 + n], bt),
-                         (self.h_bw[c0:c0 + n], bw)] + pairs
+                if compact:
+                    pairs = [(self.h_packed[sl], tg[0]), (self.h_bt[sl], tg[1]), (self.h_counts[sl], tg[2])] + pairs
+                else:
+                    pairs = [(self.h_labels[sl], tg[0]), (self.h_lw[sl], tg[1]), (self.h_bt[sl], tg[2]), (self.h_bw[sl], tg[3])] + pairs
             with torch.cuda.stream(s_out):
                 s_out.wait_event(ev_k)
                 for h, d in pairs:
                     h.copy_(d, non_blocking=True)
                     d2h += h.numel() * h.element_size()
                 mark("d2h%d" % c0, s_out)
-            hold.append((labels, lw, bt, bw, sel, keep, n_keep))      # keep device buffers alive until the drain
+            hold.append((sel, keep, n_keep))                          # keep device buffers alive until the drain
         if tl is not None:
             self.issue_ms = 1e3 * (_time.perf_counter() - _t0)
         for s in self._streams:
@@ -241,12 +279,26 @@ class BoxOpsSession:
             img_np[k0:k0 + n * kper] += c0
         nk_all[B] = pos
         self.h_nkeep.numpy()[:] = nk_all
-        self.h2d_bytes = G * 20 + self.h_off.numel() * 4 + self.d_prob.numel() * 4 + self.d_box.numel() * 4
-        self.d2h_bytes = d2h
-        tg = (self.d_labels, self.d_lw, self.d_bt, self.d_bw) if on_dev else (self.h_labels, self.h_lw, self.h_bt, self.h_bw)
-        return {"labels": tg[0], "label_weights": tg[1], "bbox_targets": tg[2],
-                "bbox_inside_weights": tg[3], "boxes": self.h_boxes, "scores": self.h_scores,
-                "img_ids": self.h_img, "keep": self._keep_out, "n_keep": self.h_nkeep}
+        self.h2d_bytes, self.d2h_bytes = h2d, d2h
+        res = {"boxes": self.h_boxes, "scores": self.h_scores, "img_ids": self.h_img, "keep": self._keep_out,
+               "n_keep": self.h_nkeep, "format": format}
+        if compact:
+            tg = (self.d_packed, self.d_bt, self.d_counts) if on_dev else (self.h_packed, self.h_bt, self.h_counts)
+            res.update(packed=tg[0], bbox_targets=tg[1], counts=tg[2])
+        else:
+            tg = (self.d_labels, self.d_lw, self.d_bt, self.d_bw) if on_dev else (self.h_labels, self.h_lw, self.h_bt, self.h_bw)
+            res.update(labels=tg[0], label_weights=tg[1], bbox_targets=tg[2], bbox_inside_weights=tg[3])
+        return res
+
+    def expand(self, host_out, n_threads=None):
+        """The reference's four arrays from a format="compact" result of run_host (host side): labels [B,A],
+        label_weights [B,A], bbox_targets [B,A,4] (passed through), bbox_inside_weights [B,A,4]."""
+        if host_out.get("format") != "compact":
+            return host_out["labels"], host_out["label_weights"], host_out["bbox_targets"], host_out["bbox_inside_weights"]
+        bbw = [float(self.tcfg.bbweights[i]) for i in range(4)]
+        labels, lw, bw = ops.expand_targets(host_out["packed"], host_out["counts"], bbw, n_threads,
+                                            out=(self.h_labels, self.h_lw, self.h_bw))
+        return labels, lw, host_out["bbox_targets"], bw
 
     def detections(self, host_out):
         """Per-image [m,5] = (x1,y1,x2,y2,score) arrays from run_host()'s result (host-side views)."""

@@ -161,6 +161,49 @@ int detbox_anchor_target(const float *anchors_dev, long A, const float *gt_dev,
                          float *bbox_inside_weights_dev, int32_t *counts_dev,
                          void *workspace_dev, size_t workspace_bytes, void *stream);
 
+/* The same assignment with two additions (round 2):
+ *
+ * pyr (optional): the grid geometry the anchors were expanded over — rows ordered level -> y -> x -> cell anchor, what
+ *   detbox_anchor_pyramid / libs/boxes/anchor.py:30-70 produce; the descriptor must describe exactly A rows.  The
+ *   fastrcnn encode (bbox_transform.py:18-37) is separable per axis and anchor (l, y, x, c) shares its x-interval with
+ *   (l, 0, x, c) and its y-interval with (l, y, 0, c), so the targets of every anchor matched to GT 0 of its image (all
+ *   anchors that overlap nothing: np.argmax of an all-zero row) come from per-image tables of sum_l n_cell * (W_l + H_l)
+ *   half-encodes.  Separability is VERIFIED on the device on every call; if the check fails the generic path runs, so
+ *   the results never depend on the descriptor being right.  Bit-identical to pyr == NULL.
+ *
+ * format: DETBOX_TARGETS_REFERENCE — the four float32 arrays of libs/layers/anchor.py:17-145 (packed_dev unused);
+ *   DETBOX_TARGETS_COMPACT — bbox_targets [batch,A,4] float32 as before, plus packed_dev uint8 [batch,A] =
+ *   (label + 1) | flag << 7 and counts_dev int32 [batch,2] = (#fg, #bg) (mandatory): bbox_inside_weights is
+ *   flag ? cfg.bbweights : 0 (anchor.py:136-138) and label_weights a function of the label and the image's counts
+ *   (anchor.py:111-118), so 17 instead of 40 bytes per anchor carry the same information
+ *   (detbox_expand_targets_host rebuilds the reference's arrays bit for bit).  GT classes must be integers in
+ *   [-1, 125]; any other class is packed as label code 127, which the expander reports. */
+typedef struct {
+    int n_levels;
+    int n_cell[DETBOX_MAX_LEVELS];          /* anchors per grid cell (shifts x ratios x scales) */
+    int height[DETBOX_MAX_LEVELS], width[DETBOX_MAX_LEVELS];
+} detbox_pyramid_desc;
+#define DETBOX_TARGETS_REFERENCE 0
+#define DETBOX_TARGETS_COMPACT   1
+size_t detbox_anchor_target_ex_workspace_bytes(long A, int batch, long total_gt, const detbox_pyramid_desc *pyr);
+int detbox_anchor_target_ex(const float *anchors_dev, long A, const detbox_pyramid_desc *pyr,
+                            const float *gt_dev, const int32_t *gt_offsets_dev, int batch, long total_gt,
+                            const detbox_target_cfg *cfg, int format,
+                            float *labels_dev, float *label_weights_dev, float *bbox_targets_dev,
+                            float *bbox_inside_weights_dev, uint8_t *packed_dev, int32_t *counts_dev,
+                            void *workspace_dev, size_t workspace_bytes, void *stream);
+/* The collate contract of a device-side target pipeline (libs/datasets/citypersons2.py:1045-1070 pads per-image GT;
+ * libs/layers/data_layer.py:228-239 loops over the list on the host): gt_padded_dev [batch, gmax, 5] + gt_counts_dev
+ * int32 [batch] -> the concatenated rows gt_out_dev [<= batch*gmax, 5] and gt_offsets_out_dev int32 [batch+1] that
+ * detbox_anchor_target takes.  Counts are clamped to [0, gmax].  No host round trip. */
+int detbox_pack_padded_gt(const float *gt_padded_dev, const int32_t *gt_counts_dev, int batch, int gmax,
+                          float *gt_out_dev, int32_t *gt_offsets_out_dev, void *stream);
+/* HOST: DETBOX_TARGETS_COMPACT -> labels [batch,A], label_weights [batch,A], bbox_inside_weights [batch,A,4]
+ * (any may be NULL) with n_threads host threads.  DETBOX_ERR_UNSUPPORTED if a label code 127 is met. */
+int detbox_expand_targets_host(const uint8_t *packed_host, const int32_t *counts_host, long A, int batch,
+                               const float *bbweights_host /*[4]*/, float *labels_host, float *label_weights_host,
+                               float *bbox_inside_weights_host, int n_threads);
+
 /* ---------------------------------------------------------------------------------------------
  * Objectness + top-k + gather + decode — replaces detection_model._decode_and_choose_top_n_stage1
  * (libs/nets/model.py:308-321) incl. _objectness (:54-61).  One stable descending selection
@@ -351,6 +394,11 @@ int detbox_nms_host(const float *dets_host, int n, double thresh, int cmp_mode,
 int detbox_anchor_target_host(const float *anchors_host, long A, const float *gt_host, int G,
                               const detbox_target_cfg *cfg, float *labels_host, float *label_weights_host,
                               float *bbox_targets_host, float *bbox_inside_weights_host, int device_id);
+
+/* Device-side address of PINNED host memory (cudaHostAlloc / cudaHostRegister), for passing a host array where a
+ * *_dev pointer is expected and the kernel reads only a few rows of it: detbox_topk_decode's deltas_dev (the gather
+ * reads top_n rows per image — the reference indexes rpn_box[order] on the host, libs/nets/model.py:314-318). */
+int detbox_host_device_pointer(const void *host_ptr, void **dev_ptr_out);
 
 #ifdef __cplusplus
 }

@@ -115,13 +115,16 @@ def test_transform_full_size_roundtrip(cpr_anchors):
     np.testing.assert_allclose(enc.cpu().numpy()[idx], O.bbox_transform(anc.cpu().numpy()[idx], gt[idx]), rtol=RTOL, atol=ATOL)
 
 
-def run_target(anchors_np, gts, cfg):
+def run_target(anchors_np, gts, cfg, pyramid=None, format="reference"):
     off = np.zeros(len(gts) + 1, np.int32)
     off[1:] = np.cumsum([g.shape[0] for g in gts])
     gt_all = np.concatenate(gts, 0).astype(np.float32) if off[-1] else np.zeros((0, 5), np.float32)
     tc = detbox.make_target_cfg(cfg.rpn_bg_threshold, cfg.rpn_fg_threshold, cfg.rpn_clobber_positives,
                                 cfg.ignored_area_intersection_fraction, cfg.bbweights, cfg.rpn_box_encoding)
-    out = detbox.anchor_target(cu(anchors_np), cu(gt_all), cu(off), tc, return_counts=True)
+    if format == "compact":
+        out = detbox.anchor_target(cu(anchors_np), cu(gt_all), cu(off), tc, pyramid=pyramid, format="compact")
+    else:
+        out = detbox.anchor_target(cu(anchors_np), cu(gt_all), cu(off), tc, return_counts=True, pyramid=pyramid)
     return [o.cpu().numpy() for o in out]
 
 
@@ -308,3 +311,105 @@ def test_anchor_target_host_entry(cpr_anchors, golden):
 def test_no_cpu_fallback():
     with pytest.raises(detbox.DetboxError):
         detbox.box_decode(torch.zeros(4, 4), torch.zeros(4, 4))
+
+
+# ---- round 2: separable GT-0 tables (pyramid descriptor) and the compact output format -------------------------------
+def ragged_gts(seed, ih, iw, counts=(12, 0, 1, 32, 99, 150, 5)):
+    gts = []
+    for i, G in enumerate(counts):
+        gt = synth_gt(np.random.RandomState(seed + i), G, ih, iw, 0.15) if G else np.zeros((0, 5), np.float32)
+        if i % 2:
+            gt[:, :4] = np.round(gt[:, :4])
+        gts.append(gt)
+    return gts
+
+
+def test_anchor_target_tables_bit_identical_cpr(cpr_anchors, golden):
+    """The table path (pyramid descriptor given) must reproduce the generic path BIT FOR BIT at CP-R size — all four
+    arrays and the counts — for ragged G (0 ... 150), real CityPersons GT, and a GT row 0 placed so that one axis falls
+    outside the fast path's range (entry marker -> full encode)."""
+    ref, _ = cpr_anchors
+    anc = ref.astype(np.float32)
+    pyr = detbox.pyramid_desc(CPR.strides, 1024, 2048, CPR.anchor_scales, CPR.anchor_ratios, 16)
+    g = golden("anchor_target_real")
+    gts = ragged_gts(70, 1024, 2048) + [g["img%d_gt" % int(i)] for i in g["image_ids"][:3]]
+    # GT 0 centred exactly on anchor centres of level 0 (nx == 0 for a column of anchors -> plain-division path there)
+    a0 = anc[6 * (256 * 40 + 100)]
+    cx, cy = (a0[0] + a0[2]) / 2, (a0[1] + a0[3]) / 2
+    gts.append(np.asarray([[cx - 20, cy - 50, cx + 20, cy + 50, 1], [300, 300, 340, 400, 1]], np.float32))
+    plain = run_target(anc, gts, CPR)
+    tabled = run_target(anc, gts, CPR, pyramid=pyr)
+    for a, b, name in zip(plain, tabled, ("labels", "label_weights", "bbox_targets", "bbox_inside_weights", "counts")):
+        assert np.array_equal(a.view(np.uint32) if a.dtype == np.float32 else a, b.view(np.uint32) if b.dtype == np.float32 else b), name
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_anchor_target_tables_odd_pyramids(seed):
+    """Grids that are not powers of two, several shifts per cell, tiles straddling levels, a partial last tile."""
+    rng = np.random.RandomState(300 + seed)
+    strides = [8, 16, 32][: 2 + seed % 2]
+    ih, iw = [(200, 328), (136, 520), (96, 96), (264, 184)][seed]
+    scales = [[2, 2.52, 3.175], [4, 5.04, 6.349], [8, 10.079, 12.7]][: len(strides)]
+    shift = [[0.0, 0.0], [0.5, 0.5]] if seed % 2 else [[0.0, 0.0]]
+    args = (strides, ih, iw, scales, [1, 2.5, 0.4][: 2 + seed // 2], 16, shift)
+    anc_t = detbox.anchor_pyramid(*args)
+    anc = anc_t.cpu().numpy()
+    pyr = detbox.pyramid_desc(*args)
+    cfg = O.Cfg(rpn_bg_threshold=0.4, rpn_fg_threshold=0.6, bbweights=[1., 2., 0.5, 1.5] if seed == 3 else [1.] * 4)
+    gts = [synth_gt(rng, G, ih, iw, 0.2, ncls=3) if G else np.zeros((0, 5), np.float32) for G in (3, 0, 40, 1, 140)]
+    plain = run_target(anc, gts, cfg)
+    tabled = run_target(anc, gts, cfg, pyramid=pyr)
+    for a, b in zip(plain, tabled):
+        assert np.array_equal(a.view(np.uint32) if a.dtype == np.float32 else a, b.view(np.uint32) if b.dtype == np.float32 else b)
+    for b, gt in enumerate(gts):
+        check_target(tabled, b, gt, anc, cfg)
+
+
+def test_anchor_target_tables_reject_non_separable_anchors():
+    """A descriptor that does not describe the anchors (rows perturbed / permuted) must not change any result: the
+    device-side separability check fails and the generic path runs."""
+    args = ([8, 16], 128, 256, [[2, 3], [4, 6]], [1, 2.5], 16)
+    anc = detbox.anchor_pyramid(*args).cpu().numpy()
+    pyr = detbox.pyramid_desc(*args)
+    rng = np.random.RandomState(5)
+    gts = [synth_gt(rng, 6, 128, 256, 0.2), synth_gt(rng, 2, 128, 256, 0.0)]
+    for mode in ("jitter_one", "permute"):
+        a2 = anc.copy()
+        if mode == "jitter_one":
+            a2[1234, 2] += 0.25                      # one x2 off its column's value
+        else:
+            a2 = a2[rng.permutation(a2.shape[0])]
+        plain = run_target(a2, gts, CPR)
+        tabled = run_target(a2, gts, CPR, pyramid=pyr)
+        for a, b in zip(plain, tabled):
+            assert np.array_equal(a.view(np.uint32) if a.dtype == np.float32 else a, b.view(np.uint32) if b.dtype == np.float32 else b), mode
+    bad = detbox.make_pyramid_desc([4, 4], [16, 8], [32, 15])          # describes the wrong number of rows
+    with pytest.raises(detbox.DetboxError):
+        run_target(anc, gts, CPR, pyramid=bad)
+
+
+@pytest.mark.parametrize("with_pyr", [False, True])
+def test_anchor_target_compact_format(cpr_anchors, with_pyr):
+    """Compact format: packed byte + counts expand (detbox_expand_targets_host) to the reference-format arrays bit for
+    bit; bbox_targets are the same bits; a partial last tile and an unaligned batch stride take the byte-store path."""
+    ref, _ = cpr_anchors
+    for anc, ih, iw, pyr in ((ref.astype(np.float32), 1024, 2048,
+                              detbox.pyramid_desc(CPR.strides, 1024, 2048, CPR.anchor_scales, CPR.anchor_ratios, 16)),
+                             (detbox.anchor_pyramid([8, 16], 104, 200, [[2, 3, 4], [4, 6, 7]], [1, 2.5, 0.5], 16).cpu().numpy(), 104, 200,
+                              detbox.pyramid_desc([8, 16], 104, 200, [[2, 3, 4], [4, 6, 7]], [1, 2.5, 0.5], 16))):
+        gts = ragged_gts(90, ih, iw, counts=(12, 0, 3, 40))
+        full = run_target(anc, gts, CPR, pyramid=pyr if with_pyr else None)
+        packed, bt, counts = run_target(anc, gts, CPR, pyramid=pyr if with_pyr else None, format="compact")
+        assert np.array_equal(bt.view(np.uint32), full[2].view(np.uint32))
+        assert np.array_equal(counts, full[4])
+        labels, lw, bw = detbox.expand_targets(packed, counts, CPR.bbweights)
+        assert np.array_equal(labels.numpy(), full[0]) and np.array_equal(lw.numpy(), full[1]) and np.array_equal(bw.numpy(), full[3])
+
+
+def test_anchor_target_compact_rejects_unpackable_class():
+    anc = detbox.anchor_pyramid([8], 64, 64, [[2, 3]], [1], 16).cpu().numpy()
+    gt = np.asarray([[10, 10, 40, 50, 300]], np.float32)          # class 300 does not fit the byte
+    packed, bt, counts = run_target(anc, [gt], CPR, format="compact")
+    assert ((packed & 0x7f) == 127).any()
+    with pytest.raises(detbox.DetboxError):
+        detbox.expand_targets(packed, counts)

@@ -367,3 +367,44 @@ def test_pyramid_roi_align_reference_fixture():
     perm = rng.permutation(5)
     out_p = crop([cu(f) for f in pyramid], cu(bboxes[perm]), cu(batch_inds[perm])).cpu().numpy()
     assert np.array_equal(out_p, out[perm])
+
+
+def test_compute_rpn_targets_device_entries(golden):
+    """the device-side hooks — compute_rpn_targets_in_batch_cuda (list of CUDA GT tensors) and
+    compute_rpn_targets_padded_cuda ([B, Gmax, 5] + counts, no host concatenation) — against the host-list entry and the
+    oracle: labels / weights bit-exact, targets identical bits across the three entries."""
+    import libs.configs.config as cfg
+    from libs.layers.data_layer import (compute_rpn_targets_in_batch, compute_rpn_targets_in_batch_cuda,
+                                        compute_rpn_targets_padded_cuda)
+    from oracle.make_golden import synth_gt
+    cfg.rpn_bg_threshold, cfg.rpn_fg_threshold, cfg.rpn_clobber_positives = 0.5, 0.6, True
+    try:
+        args = ([8, 16, 32], 192, 320, [[2, 2.52, 3.175], [4, 5.04, 6.349], [8, 10.079, 12.7]], [1, 2.5], 16)
+        anchors = detbox.anchor_pyramid(*args)
+        pyr = detbox.pyramid_desc(*args)
+        anc = anchors.cpu().numpy()
+        rng = np.random.RandomState(8)
+        counts = [5, 0, 17, 1, 40]
+        gts = [synth_gt(rng, G, 192, 320, 0.2) if G else np.zeros((0, 5), np.float32) for G in counts]
+        host = compute_rpn_targets_in_batch(gts, anc)
+        dev = compute_rpn_targets_in_batch_cuda([cu(g) for g in gts], anchors, pyramid=pyr)
+        Gmax = 48
+        padded = np.full((len(gts), Gmax, 5), np.nan, np.float32)          # the padding must never be read
+        for b, g in enumerate(gts):
+            padded[b, :g.shape[0]] = g
+        pad = compute_rpn_targets_padded_cuda(cu(padded), cu(np.asarray(counts, np.int32)), anchors, pyramid=pyr)
+        for h, d, q in zip(host, dev, pad):
+            assert d.is_cuda and q.is_cuda
+            assert np.array_equal(h.view(np.uint32), d.cpu().numpy().view(np.uint32))
+            assert np.array_equal(h.view(np.uint32), q.cpu().numpy().view(np.uint32))
+        ocfg = O.Cfg(rpn_bg_threshold=0.5, rpn_fg_threshold=0.6)
+        for b, g in enumerate(gts):
+            want = O.anchor_encode(g, anc, ocfg)
+            assert np.array_equal(host[0][b], want[0]) and np.array_equal(host[1][b], want[1]) and np.array_equal(host[3][b], want[3])
+            assert_boxes_close(host[2][b], want[2], extra_scale=1.0)
+        packed, bt, cnt = compute_rpn_targets_padded_cuda(cu(padded), cu(np.asarray(counts, np.int32)), anchors, pyramid=pyr, format="compact")
+        labels, lw, bw = detbox.expand_targets(packed.cpu(), cnt.cpu())
+        assert np.array_equal(labels.numpy(), host[0]) and np.array_equal(lw.numpy(), host[1]) and np.array_equal(bw.numpy(), host[3])
+        assert np.array_equal(bt.cpu().numpy().view(np.uint32), host[2].view(np.uint32))
+    finally:
+        cfg.rpn_bg_threshold, cfg.rpn_fg_threshold, cfg.rpn_clobber_positives = 0.4, 0.6, True

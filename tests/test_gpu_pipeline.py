@@ -72,7 +72,7 @@ def test_run_host_targets_on_device():
     sess = pipeline.BoxOpsSession(strides, ih, iw, scales, cfg.anchor_ratios, cfg.anchor_base, B, 2, top_n=top_n,
                                   nms_thresh=0.5, bg=cfg.rpn_bg_threshold, fg=cfg.rpn_fg_threshold, max_gt_total=16 * B)
     h_prob, h_box = torch.from_numpy(prob).pin_memory(), torch.from_numpy(deltas).pin_memory()
-    host = {k: v.clone() for k, v in sess.run_host(gts, h_prob, h_box, chunk=2).items()}
+    host = {k: v.clone() for k, v in sess.run_host(gts, h_prob, h_box, chunk=2).items() if torch.is_tensor(v)}
     d2h_host = sess.d2h_bytes
     dev = sess.run_host(gts, h_prob, h_box, chunk=2, targets="device")
     assert sess.d2h_bytes < d2h_host // 10
@@ -111,3 +111,33 @@ def test_run_device_two_streams_matches_one_stream():
     want = sess.run_device(*args, overlap=False)
     assert not torch.equal(want["scores"], serial["scores"])
     same(want, sess.run_device_graph(*args))
+
+
+@pytest.mark.parametrize("box_rows", ["copy", "mapped"])
+def test_run_host_compact_format_expands_to_reference(box_rows):
+    """format="compact" (17 B / anchor over the link) + the host expander == format="reference" bit for bit, and the
+    top-k gather reading rpn_box rows out of the pinned host buffer == the staged copy."""
+    pipeline = import_module("detectron-pytorch_b200.pipeline")
+    B, ih, iw, top_n = 6, 256, 512, 250
+    cfg, strides, scales, anc, gts, deltas, prob = make_case(B, ih, iw, 21)
+    sess = pipeline.BoxOpsSession(strides, ih, iw, scales, cfg.anchor_ratios, cfg.anchor_base, B, 2, top_n=top_n,
+                                  nms_thresh=0.5, bg=cfg.rpn_bg_threshold, fg=cfg.rpn_fg_threshold, max_gt_total=16 * B)
+    h_prob, h_box = torch.from_numpy(prob).pin_memory(), torch.from_numpy(deltas).pin_memory()
+    ref = {k: v.clone() for k, v in sess.run_host(gts, h_prob, h_box, chunk=4, box_rows="copy").items() if torch.is_tensor(v)}
+    h2d_ref, d2h_ref = sess.h2d_bytes, sess.d2h_bytes
+    out = sess.run_host(gts, h_prob, h_box, chunk=4, format="compact", box_rows=box_rows)
+    assert out["packed"].dtype == torch.uint8 and tuple(out["packed"].shape) == (B, sess.A)
+    assert sess.d2h_bytes < 0.45 * d2h_ref
+    if box_rows == "mapped":
+        assert sess.h2d_bytes < 0.4 * h2d_ref
+    labels, lw, bt, bw = sess.expand(out)
+    for got, k in ((labels, "labels"), (lw, "label_weights"), (bt, "bbox_targets"), (bw, "bbox_inside_weights")):
+        assert torch.equal(got, ref[k]), k
+    for k in ("boxes", "scores", "img_ids", "n_keep"):
+        assert torch.equal(out[k], ref[k]), k
+    nk = int(out["n_keep"][B])
+    assert torch.equal(out["keep"][:nk], ref["keep"][:nk])
+    cnt = out["counts"].numpy()
+    for b in range(B):
+        lab = ref["labels"][b].numpy()
+        assert cnt[b, 0] == (lab >= 1).sum() and cnt[b, 1] == (lab == 0).sum()

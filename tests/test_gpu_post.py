@@ -175,6 +175,20 @@ def test_nms_100k_properties():
     np.testing.assert_array_equal(keep2, np.arange(keep.size))            # idempotent
 
 
+def test_nms_100k_exact_vs_oracle():
+    """BASELINE configs[1] top end: keep indices at n = 100,000 bit-exact against the C oracle (pinned to the compiled
+    cpu_nms / py_cpu_nms), both comparators: `>=` in float64 (libs/nms/cpu_nms.pyx:17-68) and `>` in float32
+    (libs/nms/nms_kernel.cu:46-90)."""
+    n = 100000
+    b, s = sweep_boxes(np.random.RandomState(3), n)
+    db, ds = cu(b), cu(s)
+    for _, omode, mode in MODES:
+        keep, nk = keep_list(*detbox.nms(db, ds, 0.5, mode))
+        want = O.nms(b, s, 0.5, omode)
+        assert keep.size == want.size and nk[0] == want.size
+        np.testing.assert_array_equal(keep, want)
+
+
 def test_nms_segments_match_per_image_loop():
     """_apply_nms_in_batch (model.py:343-355): segments == the reference's per-image Python loop."""
     rng = np.random.RandomState(9)

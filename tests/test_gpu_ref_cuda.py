@@ -67,6 +67,28 @@ def test_nms_gt_comparator_vs_reference_kernel(kind, n, thr):
     np.testing.assert_array_equal(keep2[:num2[0]], keep[:num[0]])
 
 
+def test_nms_100k_exact_vs_reference_kernel():
+    """BASELINE configs[1] top end: n = 100,000 boxes, keep list bit-exact against the reference's own nms_kernel.cu
+    (1.25 GB mask on the device, scanned on the host by the reference's launcher, nms_kernel.cu:103-156)."""
+    L = ref_lib("nms")
+    fn = L._Z4_nmsPiS_PKfiifi
+    fn.restype = None
+    fn.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_int]
+    n = 100000
+    rng = np.random.RandomState(3)
+    b = sweep_boxes(rng, n)
+    s = np.sort(rng.permutation(n).astype(np.float32) / n)[::-1]
+    dets = np.ascontiguousarray(np.concatenate([b, s[:, None]], 1), dtype=np.float32)
+    keep = np.zeros(n, np.int32); num = np.zeros(1, np.int32)
+    fn(keep.ctypes.data, num.ctypes.data, dets.ctypes.data, n, 5, 0.5, 0)
+    want = keep[:num[0]].astype(np.int64)
+    got, nk = detbox.nms(cu(dets[:, :4]), cu(dets[:, 4]), 0.5, detbox.NMS_GT_F32)
+    np.testing.assert_array_equal(got[:int(nk[-1])].cpu().numpy(), want)
+    keep2 = np.zeros(n, np.int32); num2 = np.zeros(1, np.int32)
+    detbox.lib()._nms(keep2.ctypes.data, num2.ctypes.data, dets.ctypes.data, n, 5, c_float(0.5), 0)
+    np.testing.assert_array_equal(keep2[:num2[0]], keep[:num[0]])
+
+
 # ------------------------------------------------------------------------- grid-point RoIAlign ----
 def make_rois(rng, R, B, ih, iw):
     h = np.exp(rng.uniform(np.log(12), np.log(400), R)); w = h / rng.uniform(0.5, 2.8, R)
@@ -100,7 +122,7 @@ def test_grid_point_roi_align_vs_reference_kernel(ph, pw):
     torch.cuda.synchronize()
     got_g = detbox.roi_align_backward(g, [tuple(feat.shape)], rois, [scale], detbox.ROI_GRID_POINT)[0]
     err = (got_g - want_g).abs().max().item()
-    assert err <= 1e-4 * max(1.0, want_g.abs().max().item()), err          # float32 atomics, different order
+    assert err <= 1e-5 * max(1.0, want_g.abs().max().item()), err          # north_star's 1e-5 relative; float32 atomics on both sides, different orders
 
 
 # ---------------------------------------------------------------------------- crop_and_resize ----
@@ -134,4 +156,4 @@ def test_crop_and_resize_vs_reference_kernel(ch, cw, ext):
     torch.cuda.synchronize()
     got_g = detbox.roi_align_backward(g, [tuple(img.shape)], rois, [1.0], detbox.ROI_CROP_NORM)[0]
     err = (got_g - want_g).abs().max().item()
-    assert err <= 1e-4 * max(1.0, want_g.abs().max().item()), err
+    assert err <= 1e-5 * max(1.0, want_g.abs().max().item()), err

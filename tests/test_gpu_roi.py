@@ -32,6 +32,66 @@ def close(got, want, scale=1.0, rtol=1e-5):
     assert err <= rtol * max(scale, float(np.abs(want).max()) if want.size else 1.0), err
 
 
+U = 2.0 ** -24                                            # float32 unit roundoff
+
+
+def tap_stats(rois, scale, ph, pw, shape, mode, g, lv_sel=None):
+    """Per element of a level's gradient map: n = number of (RoI, bin, tap) contributions and S = sum of their absolute
+    values, from an independent float64 restatement of the tap positions and weights (roi_align_tf.py:24-40 +
+    crop_and_resize.c:44-72,258-264, or roi_align_kernel.cu:32-56,147-150 — whose weights can be negative in the last
+    row / column).  They feed the summation-error bound below; slack there covers taps that a float32 rounding moves
+    across a pixel boundary (such a tap carries a weight below 1e-6)."""
+    B, C, H, W = shape
+    cnt = np.zeros((B, H, W), np.int64)
+    S = np.zeros((B, C, H, W), np.float64)
+    rs, gs = (rois, g) if lv_sel is None else (rois[lv_sel], g[lv_sel])
+    for r, gr in zip(rs, np.abs(gs.astype(np.float64))):
+        b = int(r[0])
+        if not 0 <= b < B:
+            continue
+        def axis(lo, hi, P, L):
+            if mode == "tf":
+                b1, b2 = scale * lo, scale * hi
+                sp = (b2 - b1) / P
+                v = b1 + sp / 2 - 0.5 + np.arange(P) * sp
+                ok = (v >= -1e-4) & (v <= L - 1 + 1e-4)
+                v = np.clip(v, 0, L - 1)
+                i0 = np.floor(v).astype(int); i1 = np.ceil(v).astype(int)
+            else:
+                s0, e0 = lo * scale, hi * scale
+                v = np.arange(P) * (max(e0 - s0 + 1, 0) / (P - 1)) + s0
+                ok = (v >= -1e-4) & (v < L + 1e-4)
+                v = np.clip(v, 0, L)
+                i0 = np.maximum(np.minimum(np.floor(v).astype(int), L - 2), 0); i1 = np.minimum(i0 + 1, L - 1)
+            w = v - i0
+            return i0, i1, w, ok
+        y0, y1, wy, oky = axis(float(r[2]), float(r[4]), ph, H)
+        x0, x1, wx, okx = axis(float(r[1]), float(r[3]), pw, W)
+        m = oky[:, None] & okx[None, :]
+        for ys, wys in ((y0, 1 - wy), (y1, wy)):
+            for xs, wxs in ((x0, 1 - wx), (x1, wx)):
+                yy, xx = np.broadcast_to(ys[:, None], m.shape)[m], np.broadcast_to(xs[None, :], m.shape)[m]
+                np.add.at(cnt[b], (yy, xx), 1)
+                t = gr[:, m] * np.abs(wys[:, None] * wxs[None, :])[m][None, :]
+                for c in range(C):
+                    np.add.at(S[b, c], (yy, xx), t[c])
+    return cnt, S
+
+
+def assert_bwd_within_bound(got, want, stats, gmax):
+    """|got - want| <= 2 * gamma_(n + 8) * sum|terms| per element: both sides add the SAME float32 terms
+    (crop_and_resize.c:258-264 / roi_align_kernel.cu:147-150) in different orders, and each is within
+    gamma_(n-1) * sum|terms| of the exact sum (Higham, Accuracy and Stability of Numerical Algorithms, eq. 4.4);
+    n and sum|terms| from tap_stats."""
+    counts, abs_sum = stats
+    n = counts[:, None, :, :].astype(np.float64) + 8
+    bound = 2 * (n * U / (1 - n * U)) * (abs_sum * (1 + 1e-4) + 1e-5 * gmax)
+    err = np.abs(got.astype(np.float64) - want.astype(np.float64))
+    bad = err > bound
+    assert not bad.any(), "backward outside the summation bound at %d elements, worst err/bound %.3g" % (bad.sum(), (err[bad] / bound[bad]).max())
+    assert float(err.max()) <= 1e-5 * max(1.0, float(np.abs(want).max())), "backward above 1e-5 relative"      # north_star's tolerance
+
+
 def as_layout(t, nhwc):
     return t.contiguous(memory_format=torch.channels_last) if nhwc else t.contiguous()
 
@@ -69,7 +129,8 @@ def test_single_level(nhwc, mode, ph, pw):
         close(out.cpu().numpy(), want)
     g = rng.normal(0, 1, want.shape).astype(np.float32)
     gi = detbox.roi_align_backward(as_layout(cu(g), nhwc), [feat.shape], cu(rois), [0.125], m, channels_last=nhwc)
-    close(gi[0].cpu().numpy(), bwd(g, rois, np.float32(0.125), feat.shape), scale=float(np.abs(g).max()) * 4)
+    assert_bwd_within_bound(gi[0].cpu().numpy(), bwd(g, rois, np.float32(0.125), feat.shape),
+                            tap_stats(rois, 0.125, ph, pw, feat.shape, mode, g), float(np.abs(g).max()))
 
 
 @pytest.mark.parametrize("kind", ["avg", "max"])
@@ -117,7 +178,8 @@ def test_pyramid_level_assigned(nhwc, mode):
     bwd = O.roi_align_tf_bwd if mode == "tf" else O.roi_align_grid_bwd
     for l, f in enumerate(feats):
         sel = lv_want == l
-        close(gi[l].cpu().numpy(), bwd(g[sel], rois[sel], scales[l], f.shape), scale=float(np.abs(g).max()) * 8)
+        assert_bwd_within_bound(gi[l].cpu().numpy(), bwd(g[sel], rois[sel], scales[l], f.shape),
+                                tap_stats(rois, float(scales[l]), 7, 7, f.shape, mode, g, sel), float(np.abs(g).max()))
 
 
 def test_pyramid_all_levels():
@@ -134,7 +196,9 @@ def test_pyramid_all_levels():
     g = rng.normal(0, 1, want.shape).astype(np.float32)
     gi = detbox.roi_align_backward(cu(g), [f.shape for f in feats], cu(rois), scales, detbox.ROI_BIN_CENTRE, all_levels=True)
     for l, f in enumerate(feats):
-        close(gi[l].cpu().numpy(), O.roi_align_tf_bwd(g[:, l * C:(l + 1) * C], rois, scales[l], f.shape), scale=float(np.abs(g).max()) * 8)
+        gl = np.ascontiguousarray(g[:, l * C:(l + 1) * C])
+        assert_bwd_within_bound(gi[l].cpu().numpy(), O.roi_align_tf_bwd(gl, rois, scales[l], f.shape),
+                                tap_stats(rois, float(scales[l]), 7, 7, f.shape, "tf", gl), float(np.abs(g).max()))
 
 
 def test_linearity_and_constant_plane_at_baseline_shape():
@@ -183,3 +247,68 @@ def test_backward_is_the_gradient_finite_differences(mode):
         xp[idx] += eps; xm[idx] -= eps
         num = (f(xp) - f(xm)) / (2 * eps)
         assert abs(num - gi[idx]) <= 1e-4 * max(1.0, abs(num)), (idx, num, gi[idx])
+
+
+# ---- round 2: the shared-memory staged NCHW kernels -----------------------------------------------------------------
+@pytest.mark.parametrize("mode", ["tf", "grid"])
+@pytest.mark.parametrize("W", [128, 126, 61])
+def test_nchw_staged_window_sizes(mode, W):
+    """Windows of every class the staged kernels distinguish: one pass (small RoIs), several passes (a channel's window
+    is a few thousand floats), the direct fallback (window above the 40 KB budget: a RoI covering the whole 128 x 128
+    map), 16-byte row pieces (W % 4 == 0) and scalar staging (W = 126, 61).  Forward bit-exact against crop_and_resize.c
+    in bin-centre mode; backward inside the summation bound."""
+    rng = np.random.RandomState(W)
+    B, C, H = 2, 40, 128                                   # C = 40: a partial second channel chunk
+    feat = rng.normal(0, 1, (B, C, H, W)).astype(np.float32)
+    rois = make_rois(rng, 24, B, H * 4, W * 4, 20, 200)
+    big = np.asarray([[0, -10, -10, W * 4 + 10, H * 4 + 10], [1, 0, 0, W * 4 - 1, H * 4 - 1], [1, 8, 4, W * 3, H * 3.5],
+                      [0, 30, 20, 30.5, 20.5], [1, W * 4 + 50, 10, W * 4 + 90, 60]], np.float32)      # whole map, mid, sub-pixel, outside
+    rois = np.concatenate([rois, big], 0)
+    m = detbox.ROI_BIN_CENTRE if mode == "tf" else detbox.ROI_GRID_POINT
+    fwd = O.roi_align_tf_fwd if mode == "tf" else O.roi_align_grid_fwd
+    bwd = O.roi_align_tf_bwd if mode == "tf" else O.roi_align_grid_bwd
+    out = detbox.roi_align_forward([cu(feat)], cu(rois), [0.25], 7, 7, m).cpu().numpy()
+    want = fwd(feat, rois, np.float32(0.25), 7, 7)
+    if mode == "tf":
+        np.testing.assert_array_equal(out, want)
+    else:
+        close(out, want)
+    g = rng.normal(0, 1, want.shape).astype(np.float32)
+    gi = detbox.roi_align_backward(cu(g), [feat.shape], cu(rois), [0.25], m)[0].cpu().numpy()
+    assert_bwd_within_bound(gi, bwd(g, rois, np.float32(0.25), feat.shape), tap_stats(rois, 0.25, 7, 7, feat.shape, mode, g),
+                            float(np.abs(g).max()))
+
+
+def test_config3_values_vs_openmp_reference():
+    """BASELINE configs[2] shape (B=8, C=256, P2-P5 of 1024x2048, 4096 RoIs, NCHW): VALUES of 320 RoIs of that batch
+    against the oracle of crop_and_resize.c (bit-exact: same float32 operation sequence), and the backward of those
+    RoIs into the dense config-3 gradient maps inside the summation bound."""
+    g = torch.Generator(device="cuda"); g.manual_seed(11)
+    B, C = 8, 256
+    shapes = [(B, C, 1024 // s, 2048 // s) for s in STRIDES]
+    x = [torch.randn(s, device="cuda", generator=g) for s in shapes]
+    rng = np.random.RandomState(12)
+    rois_np = make_rois(rng, 4096, B, 1024, 2048, 12, 400)
+    cfg = O.Cfg(strides=tuple(STRIDES), anchor_scales=[[2, 2.52, 3.17], [4, 5.04, 6.35], [8, 10.08, 12.7], [16, 20.16, 25.4]])
+    ref_areas = O.pyramid_ref_areas(cfg)
+    scales = [np.float32(1.0 / s) for s in STRIDES]
+    out = detbox.roi_align_forward(x, cu(rois_np), scales, 7, 7, detbox.ROI_BIN_CENTRE, ref_areas=ref_areas)
+    lv = O.assign_levels(rois_np[:, 1:], ref_areas)
+    pick = np.sort(rng.choice(4096, 320, replace=False))
+    out_np = out[torch.from_numpy(pick).cuda()].cpu().numpy()
+    go = torch.zeros(out.shape, device="cuda")
+    go_pick = rng.normal(0, 1, (320, C, 7, 7)).astype(np.float32)
+    go[torch.from_numpy(pick).cuda()] = cu(go_pick)
+    gi = detbox.roi_align_backward(go, shapes, cu(rois_np), scales, detbox.ROI_BIN_CENTRE, ref_areas=ref_areas)
+    for l in range(4):
+        sel = lv[pick] == l
+        if not sel.any():
+            continue
+        f = x[l].cpu().numpy()
+        want = O.roi_align_tf_fwd(f, rois_np[pick][sel], scales[l], 7, 7)
+        np.testing.assert_array_equal(out_np[sel], want)
+        del f
+        rs, gs = rois_np[pick][sel], go_pick[sel]
+        assert_bwd_within_bound(gi[l].cpu().numpy(), O.roi_align_tf_bwd(gs, rs, scales[l], shapes[l]),
+                                tap_stats(rs, float(scales[l]), 7, 7, shapes[l], "tf", gs), float(np.abs(gs).max()))
+    assert len(np.unique(lv[pick])) == 4
