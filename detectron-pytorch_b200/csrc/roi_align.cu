@@ -349,36 +349,46 @@ roi_bwd_kernel(const RoiArgs a)
 // ---- NCHW, shared-memory staged (the reference's own layout: [B,C,H,W] features, [R,C,PH,PW] output) ---------------
 // In NCHW the 4 taps of an output element lie in 2 rows of ONE channel plane, and a RoI's taps of one channel cover a
 // small window of that plane (about 11 x 11 pixels after level assignment).  The generic path gathers them one scalar
-// at a time: every 32-byte sector is requested ~3 times through L1 and lanes of a request scatter over 7 rows.  Here a
-// block owns (RoI, RS_CH channels): it copies the window of each channel — whole 16-byte pieces of every row, so each
-// sector the window touches is requested exactly once — into shared memory with cp.async (no registers, every piece in
-// flight at once), then all PH x PW bins sample from shared memory and the [C,PH,PW] output is written in memory
-// order.  Backward is the mirror image: contributions are summed in a zeroed shared window (shared-memory atomics) and
-// every touched 16-byte piece leaves through ONE red.global.add.v4.f32 — block-aggregated atomics instead of 4 per
-// output element.  A window that does not fit is walked in several passes (fewer channels per pass); if not even one
-// channel fits (RoIs far larger than their level), the block falls back to the direct gather / scatter.
+// at a time: every 32-byte sector is requested ~3 times through L1 and the lanes of a request scatter over 7 rows.
+// Here ONE block owns a RoI (the tap tables and the window are computed once) and walks the channels in chunks: the
+// window of every channel of the chunk — whole 16-byte pieces of each row, so a sector is requested exactly once — is
+// copied into shared memory with cp.async (no registers; the next chunk is in flight while this one is sampled), then
+// every thread samples ITS bin (tap offsets and weights held in registers) for one channel after the other and the
+// [C,PH,PW] output leaves in memory order.  Backward is the mirror image: contributions are summed in a zeroed shared
+// window (shared-memory atomics) and every touched 16-byte piece leaves through ONE red.global.add.v4.f32 —
+// block-aggregated atomics instead of 4 per output element.  A window too large for the buffer (RoIs far larger than
+// their level) falls back to the direct gather / scatter.
 constexpr int RS_THREADS = 256;
-constexpr int RS_CH = 32;                   // channels per block
-constexpr int RS_FLOATS = 10 * 1024;        // staged window floats per block (40 KB: 5 blocks per SM)
+constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr int RS_CHMAX = 32;                // channels per chunk (at most)
+constexpr int RS_HALF = 5 * 1024;           // floats per staging buffer; forward uses two (40 KB: 4-5 blocks per SM)
+constexpr int RS_FLOATS = 2 * RS_HALF;
+constexpr int RS_KREG = 3;                  // 16-byte pieces per lane whose offsets live in registers (96 per channel)
 
 struct Window { int y0, x0, wh, ww, vec; }; // ww: row pitch in floats (multiple of 4 when vec)
 
-__device__ __forceinline__ Window roi_window(const Tap *ty, const Tap *tx, int gh, int gw, int W, const float *plane0)
+__device__ __forceinline__ Window roi_window(const Tap *ty, const Tap *tx, int gh, int gw, int W, const float *plane0, size_t plane)
 {
     __shared__ Window s;
-    if (threadIdx.x == 0) {
+    if (threadIdx.x < 32) {
+        const int l = threadIdx.x;
         int ymin = 1 << 30, ymax = -1, xmin = 1 << 30, xmax = -1;
-        for (int i = 0; i < gh; ++i) if (ty[i].valid) { ymin = min(ymin, min(ty[i].i0, ty[i].i1)); ymax = max(ymax, max(ty[i].i0, ty[i].i1)); }
-        for (int i = 0; i < gw; ++i) if (tx[i].valid) { xmin = min(xmin, min(tx[i].i0, tx[i].i1)); xmax = max(xmax, max(tx[i].i0, tx[i].i1)); }
-        Window w;
-        w.vec = ((W & 3) == 0) && (((size_t)plane0 & 15) == 0);
-        if (ymax < 0 || xmax < 0) { w.y0 = w.x0 = 0; w.wh = w.ww = 0; }
-        else {
-            w.y0 = ymin; w.wh = ymax - ymin + 1;
-            w.x0 = w.vec ? (xmin & ~3) : xmin;
-            w.ww = w.vec ? (((xmax + 4) & ~3) - w.x0) : (xmax - xmin + 1);
+        for (int i = l; i < gh; i += 32) if (ty[i].valid) { ymin = min(ymin, min(ty[i].i0, ty[i].i1)); ymax = max(ymax, max(ty[i].i0, ty[i].i1)); }
+        for (int i = l; i < gw; i += 32) if (tx[i].valid) { xmin = min(xmin, min(tx[i].i0, tx[i].i1)); xmax = max(xmax, max(tx[i].i0, tx[i].i1)); }
+        ymin = __reduce_min_sync(0xffffffffu, ymin); ymax = __reduce_max_sync(0xffffffffu, ymax);
+        xmin = __reduce_min_sync(0xffffffffu, xmin); xmax = __reduce_max_sync(0xffffffffu, xmax);
+        if (l == 0) {
+            Window w;
+            // 16-byte pieces need every row of every plane 16-byte aligned: W % 4 == 0 (then plane % 4 == 0 too) and an aligned base
+            w.vec = ((W & 3) == 0) && ((plane & 3) == 0) && (((size_t)plane0 & 15) == 0);
+            if (ymax < 0 || xmax < 0) { w.y0 = w.x0 = 0; w.wh = w.ww = 0; }
+            else {
+                w.y0 = ymin; w.wh = ymax - ymin + 1;
+                w.x0 = w.vec ? (xmin & ~3) : xmin;
+                w.ww = w.vec ? (((xmax + 4) & ~3) - w.x0) : (xmax - xmin + 1);
+            }
+            s = w;
         }
-        s = w;
     }
     __syncthreads();
     return s;
@@ -388,15 +398,34 @@ __device__ __forceinline__ void cp_async16(float *smem_dst, const float *gmem_sr
     const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src) : "memory");
 }
-__device__ __forceinline__ void cp_async_wait_all() {
-    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+__device__ __forceinline__ void cp_async4(float *smem_dst, const float *gmem_src) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// piece k of a channel's window -> offsets in the staged window and in the feature plane (unit: floats)
+__device__ __forceinline__ void piece_offsets(const Window &w, int W, int k, int &so, int &go) {
+    if (w.vec) { const int rq = w.ww >> 2, y = k / rq, q = k - y * rq; so = y * w.ww + 4 * q; go = y * W + 4 * q; }
+    else { const int y = k / w.ww, x = k - y * w.ww; so = k; go = y * W + x; }
 }
 
+// One bin's four taps as offsets into a channel's staged window, with the lerp weights
+struct BinTaps { int o00, o01, o10, o11; float wy, wx; bool valid; };
+__device__ __forceinline__ BinTaps bin_taps(const Window &w, const Tap &Y, const Tap &X) {
+    BinTaps b;
+    b.valid = Y.valid && X.valid;
+    const int r0 = (Y.i0 - w.y0) * w.ww - w.x0, r1 = (Y.i1 - w.y0) * w.ww - w.x0;
+    b.o00 = r0 + X.i0; b.o01 = r0 + X.i1; b.o10 = r1 + X.i0; b.o11 = r1 + X.i1;
+    b.wy = Y.w; b.wx = X.w;
+    if (!b.valid) b.o00 = b.o01 = b.o10 = b.o11 = 0;
+    return b;
+}
 template <bool GRID>
-__device__ __forceinline__ float sample_smem(const float *win, int cs, int ww, int y0, int x0, const Tap &y, const Tap &x, float ext) {
-    if (!(y.valid && x.valid)) return ext;
-    const float *r0 = win + (y.i0 - y0) * ww - x0, *r1 = win + (y.i1 - y0) * ww - x0;
-    return blend<GRID>(r0[x.i0], r0[x.i1], r1[x.i0], r1[x.i1], y.w, x.w);
+__device__ __forceinline__ float sample_taps(const float *win, const BinTaps &b, float ext) {
+    if (!b.valid) return ext;
+    return blend<GRID>(win[b.o00], win[b.o01], win[b.o10], win[b.o11], b.wy, b.wx);
 }
 
 template <bool GRID>
@@ -413,73 +442,92 @@ roi_fwd_nchw_staged_kernel(const RoiArgs a)
     const int coff = c.all_levels ? C * blockIdx.y : 0;
     const int bins = PH * PW;
     const long r = blockIdx.x;
-    const int cb = blockIdx.z * RS_CH, cn = min(RS_CH, C - cb);
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const float *f = s.ok ? c.feat[s.level] : nullptr;
     const int pool = (GRID && c.pool != DETBOX_POOL_NONE) ? c.pool : DETBOX_POOL_NONE;
     const float ext = GRID ? 0.0f : c.extrapolation;
-    float *out = a.out + ((size_t)r * Ctot + coff + cb) * bins;
+    float *out = a.out + ((size_t)r * Ctot + coff) * bins;
     if (!f) {                                                   // bad level / batch index: zeros (as the generic path)
-        for (int i = threadIdx.x; i < cn * bins; i += RS_THREADS) out[i] = 0.0f;
+        for (int i = tid; i < C * bins; i += RS_THREADS) out[i] = 0.0f;
         return;
     }
     const size_t plane = (size_t)s.H * s.W;
-    const float *f0 = f + ((size_t)s.b * C + cb) * plane;
-    const Window w = roi_window(ty, tx, gh, gw, s.W, f0);
+    const float *f0 = f + (size_t)s.b * C * plane;
+    const Window w = roi_window(ty, tx, gh, gw, s.W, f0, plane);
     const int cs = w.wh * w.ww;                                 // floats per staged channel
     if (cs == 0) {                                              // every sample outside the map
-        for (int i = threadIdx.x; i < cn * bins; i += RS_THREADS) out[i] = ext;
+        for (int i = tid; i < C * bins; i += RS_THREADS) out[i] = ext;
         return;
     }
-    if (cs > RS_FLOATS || ((plane & 3) != 0 && w.vec)) {        // window of one channel does not fit (or planes lose the alignment): direct gather
-        for (int i = threadIdx.x; i < cn * bins; i += RS_THREADS) {
+    if (cs > RS_HALF) {                                         // a channel's window does not fit: direct gather
+        for (int i = tid; i < C * bins; i += RS_THREADS) {
             const int ch = i / bins, bin = i - ch * bins, y = bin / PW, x = bin - y * PW;
             float v;
-            if (pool == DETBOX_POOL_NONE) v = sample_one<GRID, false>(f, s.b, cb + ch, ty[y], tx[x], C, s.H, s.W, ext);
+            if (pool == DETBOX_POOL_NONE) v = sample_one<GRID, false>(f, s.b, ch, ty[y], tx[x], C, s.H, s.W, ext);
             else {
-                const float v00 = sample_one<GRID, false>(f, s.b, cb + ch, ty[y], tx[x], C, s.H, s.W, ext);
-                const float v01 = sample_one<GRID, false>(f, s.b, cb + ch, ty[y], tx[x + 1], C, s.H, s.W, ext);
-                const float v10 = sample_one<GRID, false>(f, s.b, cb + ch, ty[y + 1], tx[x], C, s.H, s.W, ext);
-                const float v11 = sample_one<GRID, false>(f, s.b, cb + ch, ty[y + 1], tx[x + 1], C, s.H, s.W, ext);
+                const float v00 = sample_one<GRID, false>(f, s.b, ch, ty[y], tx[x], C, s.H, s.W, ext);
+                const float v01 = sample_one<GRID, false>(f, s.b, ch, ty[y], tx[x + 1], C, s.H, s.W, ext);
+                const float v10 = sample_one<GRID, false>(f, s.b, ch, ty[y + 1], tx[x], C, s.H, s.W, ext);
+                const float v11 = sample_one<GRID, false>(f, s.b, ch, ty[y + 1], tx[x + 1], C, s.H, s.W, ext);
                 v = (pool == DETBOX_POOL_AVG2) ? (((v00 + v01) + v10) + v11) * 0.25f : fmaxf(fmaxf(v00, v01), fmaxf(v10, v11));
             }
             out[i] = v;
         }
         return;
     }
-    const int cpp = min(cn, RS_FLOATS / cs);                    // channels per pass
-    for (int c0 = 0; c0 < cn; c0 += cpp) {
-        const int n = min(cpp, cn - c0);
-        if (c0) __syncthreads();                                // the previous pass has been sampled
-        const float *src = f0 + (size_t)c0 * plane + (size_t)w.y0 * s.W + w.x0;
-        if (w.vec) {
-            const int rq = w.ww >> 2, per = w.wh * rq;          // 16-byte pieces per row / per channel
-            for (int i = threadIdx.x; i < n * per; i += RS_THREADS) {
-                const int ch = i / per, k = i - ch * per, y = k / rq, q = k - y * rq;
-                cp_async16(s_win + ch * cs + y * w.ww + 4 * q, src + (size_t)ch * plane + (size_t)y * s.W + 4 * q);
-            }
-            cp_async_wait_all();
-        } else {
-            for (int i = threadIdx.x; i < n * cs; i += RS_THREADS) {
-                const int ch = i / cs, k = i - ch * cs, y = k / w.ww, x = k - y * w.ww;
-                s_win[i] = __ldg(src + (size_t)ch * plane + (size_t)y * s.W + x);
+    const int CH = min(RS_CHMAX, RS_HALF / cs);                 // channels per chunk
+    const int per = w.vec ? w.wh * (w.ww >> 2) : cs;            // copies per channel (16-byte pieces, or floats)
+    const float *src0 = f0 + (size_t)w.y0 * s.W + w.x0;
+    // this lane's first RS_KREG pieces of every channel: offsets computed once, kept in registers
+    int so[RS_KREG], go[RS_KREG];
+#pragma unroll
+    for (int j = 0; j < RS_KREG; ++j) { so[j] = go[j] = 0; if (lane + 32 * j < per) piece_offsets(w, s.W, lane + 32 * j, so[j], go[j]); }
+    auto stage = [&](int c0, float *buf) {                      // warp = channel, lanes = pieces
+        const int n = min(CH, C - c0);
+        for (int ch = wid; ch < n; ch += RS_WARPS) {
+            float *d = buf + ch * cs;
+            const float *g = src0 + (size_t)(c0 + ch) * plane;
+#pragma unroll
+            for (int j = 0; j < RS_KREG; ++j)
+                if (lane + 32 * j < per) { if (w.vec) cp_async16(d + so[j], g + go[j]); else cp_async4(d + so[j], g + go[j]); }
+            for (int k = lane + 32 * RS_KREG; k < per; k += 32) {
+                int o, q; piece_offsets(w, s.W, k, o, q);
+                if (w.vec) cp_async16(d + o, g + q); else cp_async4(d + o, g + q);
             }
         }
+        cp_async_commit();
+    };
+    // this thread's bin (threads 0..63 of every group of 64 own bins 0..63; 4 channel groups)
+    const int bl = tid & 63, cg = tid >> 6;
+    stage(0, s_win);
+    int it = 0;
+    for (int c0 = 0; c0 < C; c0 += CH, ++it) {
+        float *buf = s_win + (it & 1) * RS_HALF;
+        const bool more = c0 + CH < C;
+        if (more) stage(c0 + CH, s_win + ((it + 1) & 1) * RS_HALF);
+        if (more) cp_async_wait<1>(); else cp_async_wait<0>();
         __syncthreads();
+        const int n = min(CH, C - c0);
         float *o = out + (size_t)c0 * bins;
-        for (int i = threadIdx.x; i < n * bins; i += RS_THREADS) {
-            const int ch = i / bins, bin = i - ch * bins, y = bin / PW, x = bin - y * PW;
-            const float *win = s_win + ch * cs;
-            float v;
-            if (pool == DETBOX_POOL_NONE) v = sample_smem<GRID>(win, cs, w.ww, w.y0, w.x0, ty[y], tx[x], ext);
-            else {   // 2x2 / stride 1 pool over the (PH+1)x(PW+1) sample grid (modules/roi_align.py:23-46)
-                const float v00 = sample_smem<GRID>(win, cs, w.ww, w.y0, w.x0, ty[y], tx[x], ext);
-                const float v01 = sample_smem<GRID>(win, cs, w.ww, w.y0, w.x0, ty[y], tx[x + 1], ext);
-                const float v10 = sample_smem<GRID>(win, cs, w.ww, w.y0, w.x0, ty[y + 1], tx[x], ext);
-                const float v11 = sample_smem<GRID>(win, cs, w.ww, w.y0, w.x0, ty[y + 1], tx[x + 1], ext);
-                v = (pool == DETBOX_POOL_AVG2) ? (((v00 + v01) + v10) + v11) * 0.25f : fmaxf(fmaxf(v00, v01), fmaxf(v10, v11));
+        for (int bin = bl; bin < bins; bin += 64) {
+            const int y = bin / PW, x = bin - y * PW;
+            if (pool == DETBOX_POOL_NONE) {
+                const BinTaps t = bin_taps(w, ty[y], tx[x]);
+                for (int ch = cg; ch < n; ch += RS_THREADS / 64)
+                    __stcs(o + ch * bins + bin, sample_taps<GRID>(buf + ch * cs, t, ext));   // streaming store: not re-read here
+            } else {   // 2x2 / stride 1 pool over the (PH+1)x(PW+1) sample grid (modules/roi_align.py:23-46)
+                const BinTaps t00 = bin_taps(w, ty[y], tx[x]), t01 = bin_taps(w, ty[y], tx[x + 1]);
+                const BinTaps t10 = bin_taps(w, ty[y + 1], tx[x]), t11 = bin_taps(w, ty[y + 1], tx[x + 1]);
+                for (int ch = cg; ch < n; ch += RS_THREADS / 64) {
+                    const float *win = buf + ch * cs;
+                    const float v00 = sample_taps<GRID>(win, t00, ext), v01 = sample_taps<GRID>(win, t01, ext);
+                    const float v10 = sample_taps<GRID>(win, t10, ext), v11 = sample_taps<GRID>(win, t11, ext);
+                    __stcs(o + ch * bins + bin, (pool == DETBOX_POOL_AVG2) ? (((v00 + v01) + v10) + v11) * 0.25f
+                                                                            : fmaxf(fmaxf(v00, v01), fmaxf(v10, v11)));
+                }
             }
-            __stcs(o + i, v);                                   // streaming store: the output is not re-read here
         }
+        __syncthreads();                                        // this buffer is refilled two iterations from now
     }
 }
 
@@ -498,20 +546,20 @@ roi_bwd_nchw_staged_kernel(const RoiArgs a)
     const int coff = c.all_levels ? C * blockIdx.y : 0;
     const int bins = PH * PW;
     const long r = blockIdx.x;
-    const int cb = blockIdx.z * RS_CH, cn = min(RS_CH, C - cb);
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const size_t plane = (size_t)s.H * s.W;
-    float *g0 = c.grad_feat[s.level] + ((size_t)s.b * C + cb) * plane;
-    const float *go = a.grad_out + ((size_t)r * Ctot + coff + cb) * bins;
-    const Window w = roi_window(ty, tx, gh, gw, s.W, g0);
+    float *g0 = c.grad_feat[s.level] + (size_t)s.b * C * plane;
+    const float *go_ = a.grad_out + ((size_t)r * Ctot + coff) * bins;
+    const Window w = roi_window(ty, tx, gh, gw, s.W, g0, plane);
     const int cs = w.wh * w.ww;
     if (cs == 0) return;                                        // no sample inside the map: no gradient
-    if (cs > RS_FLOATS || ((plane & 3) != 0 && w.vec)) {        // direct scatter
-        for (int i = threadIdx.x; i < cn * bins; i += RS_THREADS) {
+    if (cs > RS_FLOATS) {                                       // direct scatter
+        for (int i = tid; i < C * bins; i += RS_THREADS) {
             const int ch = i / bins, bin = i - ch * bins, y = bin / PW, x = bin - y * PW;
             const Tap Y = ty[y], X = tx[x];
             if (!(Y.valid && X.valid)) continue;
             float w00, w01, w10, w11;
-            tap_weights<GRID>(go[i], Y.w, X.w, w00, w01, w10, w11);
+            tap_weights<GRID>(go_[i], Y.w, X.w, w00, w01, w10, w11);
             float *gp = g0 + (size_t)ch * plane;
             atomicAdd(gp + (size_t)Y.i0 * s.W + X.i0, w00);
             atomicAdd(gp + (size_t)Y.i0 * s.W + X.i1, w01);
@@ -520,40 +568,55 @@ roi_bwd_nchw_staged_kernel(const RoiArgs a)
         }
         return;
     }
-    const int cpp = min(cn, RS_FLOATS / cs);
-    for (int c0 = 0; c0 < cn; c0 += cpp) {
-        const int n = min(cpp, cn - c0);
-        if (c0) __syncthreads();                                // the previous pass has been flushed
-        for (int i = threadIdx.x; i < n * cs; i += RS_THREADS) s_win[i] = 0.0f;
-        __syncthreads();
-        const float *g = go + (size_t)c0 * bins;
-        for (int i = threadIdx.x; i < n * bins; i += RS_THREADS) {
-            const int ch = i / bins, bin = i - ch * bins, y = bin / PW, x = bin - y * PW;
-            const Tap Y = ty[y], X = tx[x];
-            if (!(Y.valid && X.valid)) continue;
-            float w00, w01, w10, w11;
-            tap_weights<GRID>(__ldcs(g + i), Y.w, X.w, w00, w01, w10, w11);
-            float *r0 = s_win + ch * cs + (Y.i0 - w.y0) * w.ww - w.x0, *r1 = s_win + ch * cs + (Y.i1 - w.y0) * w.ww - w.x0;
-            atomicAdd(r0 + X.i0, w00); atomicAdd(r0 + X.i1, w01);
-            atomicAdd(r1 + X.i0, w10); atomicAdd(r1 + X.i1, w11);
-        }
-        __syncthreads();
-        float *dst = g0 + (size_t)c0 * plane + (size_t)w.y0 * s.W + w.x0;
+    const int CH = min(RS_CHMAX, RS_FLOATS / cs);               // one buffer: nothing is loaded ahead
+    const int per = w.vec ? w.wh * (w.ww >> 2) : cs;
+    float *dst0 = g0 + (size_t)w.y0 * s.W + w.x0;
+    int so[RS_KREG], go[RS_KREG];
+#pragma unroll
+    for (int j = 0; j < RS_KREG; ++j) { so[j] = go[j] = 0; if (lane + 32 * j < per) piece_offsets(w, s.W, lane + 32 * j, so[j], go[j]); }
+    for (int i = tid; i < min(C, CH) * cs; i += RS_THREADS) s_win[i] = 0.0f;
+    __syncthreads();
+    const int bl = tid & 63, cg = tid >> 6;
+    auto flush_piece = [&](float *d, float *g, int o, int q) {  // one 16-byte piece (or one float) out, zero behind it
         if (w.vec) {
-            const int rq = w.ww >> 2, per = w.wh * rq;
-            for (int i = threadIdx.x; i < n * per; i += RS_THREADS) {
-                const int ch = i / per, k = i - ch * per, y = k / rq, q = k - y * rq;
-                const float4 v = *reinterpret_cast<const float4 *>(s_win + ch * cs + y * w.ww + 4 * q);
-                if (v.x != 0.0f || v.y != 0.0f || v.z != 0.0f || v.w != 0.0f)
-                    red_add4(dst + (size_t)ch * plane + (size_t)y * s.W + 4 * q, v);
+            const float4 v = *reinterpret_cast<const float4 *>(d + o);
+            if (v.x != 0.0f || v.y != 0.0f || v.z != 0.0f || v.w != 0.0f) {
+                red_add4(g + q, v);
+                *reinterpret_cast<float4 *>(d + o) = make_float4(0, 0, 0, 0);
             }
         } else {
-            for (int i = threadIdx.x; i < n * cs; i += RS_THREADS) {
-                const int ch = i / cs, k = i - ch * cs, y = k / w.ww, x = k - y * w.ww;
-                const float v = s_win[i];
-                if (v != 0.0f) atomicAdd(dst + (size_t)ch * plane + (size_t)y * s.W + x, v);
+            const float v = d[o];
+            if (v != 0.0f) { atomicAdd(g + q, v); d[o] = 0.0f; }
+        }
+    };
+    for (int c0 = 0; c0 < C; c0 += CH) {
+        const int n = min(CH, C - c0);
+        const float *g = go_ + (size_t)c0 * bins;
+        for (int bin = bl; bin < bins; bin += 64) {
+            const int y = bin / PW, x = bin - y * PW;
+            const BinTaps t = bin_taps(w, ty[y], tx[x]);
+            if (!t.valid) continue;
+            for (int ch = cg; ch < n; ch += RS_THREADS / 64) {
+                float w00, w01, w10, w11;
+                tap_weights<GRID>(__ldcs(g + ch * bins + bin), t.wy, t.wx, w00, w01, w10, w11);
+                float *win = s_win + ch * cs;
+                atomicAdd(win + t.o00, w00); atomicAdd(win + t.o01, w01);
+                atomicAdd(win + t.o10, w10); atomicAdd(win + t.o11, w11);
             }
         }
+        __syncthreads();
+        for (int ch = wid; ch < n; ch += RS_WARPS) {            // warp = channel, lanes = pieces
+            float *d = s_win + ch * cs;
+            float *gp = dst0 + (size_t)(c0 + ch) * plane;
+#pragma unroll
+            for (int j = 0; j < RS_KREG; ++j)
+                if (lane + 32 * j < per) flush_piece(d, gp, so[j], go[j]);
+            for (int k = lane + 32 * RS_KREG; k < per; k += 32) {
+                int o, q; piece_offsets(w, s.W, k, o, q);
+                flush_piece(d, gp, o, q);
+            }
+        }
+        __syncthreads();
     }
 }
 
@@ -614,11 +677,9 @@ extern "C" int detbox_roi_align_forward(const detbox_roi_cfg *cfg, const float *
     cudaStream_t st = as_stream(stream);
     static const bool no_staged = getenv("DETBOX_ROI_NOSTAGED") != nullptr;
     if (cfg->layout == DETBOX_LAYOUT_NCHW && cfg->out_layout == DETBOX_LAYOUT_NCHW && !no_staged) {
-        dim3 g3((unsigned)R, cfg->all_levels ? cfg->n_levels : 1, (unsigned)((cfg->channels + RS_CH - 1) / RS_CH));
-        if (g3.z > 65535) return DETBOX_ERR_UNSUPPORTED;
         DETBOX_TRACE_BEGIN(DETBOX_K_ROI_FWD, st);
-        if (cfg->mode == DETBOX_ROI_GRID_POINT) roi_fwd_nchw_staged_kernel<true><<<g3, RS_THREADS, RS_FLOATS * sizeof(float), st>>>(a);
-        else roi_fwd_nchw_staged_kernel<false><<<g3, RS_THREADS, RS_FLOATS * sizeof(float), st>>>(a);
+        if (cfg->mode == DETBOX_ROI_GRID_POINT) roi_fwd_nchw_staged_kernel<true><<<grid, RS_THREADS, RS_FLOATS * sizeof(float), st>>>(a);
+        else roi_fwd_nchw_staged_kernel<false><<<grid, RS_THREADS, RS_FLOATS * sizeof(float), st>>>(a);
         DETBOX_TRACE_END(DETBOX_K_ROI_FWD, st);
         DETBOX_LAUNCH_CHECK();
         return DETBOX_OK;
@@ -654,13 +715,14 @@ extern "C" int detbox_roi_align_backward(const detbox_roi_cfg *cfg, const float 
     if (!rois || !grad_out) return DETBOX_ERR_INVALID;
     RoiArgs a; a.cfg = *cfg; a.rois = rois; a.R = R; a.levels = levels; a.out = nullptr; a.grad_out = grad_out;
     dim3 grid((unsigned)R, cfg->all_levels ? cfg->n_levels : 1);
-    static const bool no_staged = getenv("DETBOX_ROI_NOSTAGED") != nullptr;
-    if (cfg->layout == DETBOX_LAYOUT_NCHW && cfg->out_layout == DETBOX_LAYOUT_NCHW && cfg->pool == DETBOX_POOL_NONE && !no_staged) {
-        dim3 g3((unsigned)R, cfg->all_levels ? cfg->n_levels : 1, (unsigned)((cfg->channels + RS_CH - 1) / RS_CH));
-        if (g3.z > 65535) return DETBOX_ERR_UNSUPPORTED;
+    // Measured on B200 at BASELINE configs[2] (profiles/r02_roi_staged_vs_generic.txt): the staged backward scatters in
+    // 0.94 ms against 0.73 ms for the direct red.global.add path (shared-memory float atomics on taps that neighbouring
+    // bins share, plus a zero and a flush pass per chunk), so it is opt-in; the staged FORWARD is the default (0.24 vs 0.37 ms).
+    static const bool bwd_staged = getenv("DETBOX_ROI_BWD_STAGED") != nullptr;
+    if (cfg->layout == DETBOX_LAYOUT_NCHW && cfg->out_layout == DETBOX_LAYOUT_NCHW && cfg->pool == DETBOX_POOL_NONE && bwd_staged) {
         DETBOX_TRACE_BEGIN(DETBOX_K_ROI_BWD, st);
-        if (cfg->mode == DETBOX_ROI_GRID_POINT) roi_bwd_nchw_staged_kernel<true><<<g3, RS_THREADS, RS_FLOATS * sizeof(float), st>>>(a);
-        else roi_bwd_nchw_staged_kernel<false><<<g3, RS_THREADS, RS_FLOATS * sizeof(float), st>>>(a);
+        if (cfg->mode == DETBOX_ROI_GRID_POINT) roi_bwd_nchw_staged_kernel<true><<<grid, RS_THREADS, RS_FLOATS * sizeof(float), st>>>(a);
+        else roi_bwd_nchw_staged_kernel<false><<<grid, RS_THREADS, RS_FLOATS * sizeof(float), st>>>(a);
         DETBOX_TRACE_END(DETBOX_K_ROI_BWD, st);
         DETBOX_LAUNCH_CHECK();
         return DETBOX_OK;

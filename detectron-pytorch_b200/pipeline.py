@@ -30,7 +30,7 @@ class BoxOpsSession:
 
     def __init__(self, strides, ih, iw, anchor_scales, anchor_ratios, anchor_base, batch, num_classes,
                  top_n=900, nms_thresh=0.5, nms_cmp=ops.NMS_GT_F32, activation="softmax", bg=0.5, fg=0.6,
-                 max_gt_total=None, anchor_shift=((0.0, 0.0),), device="cuda"):
+                 max_gt_total=None, anchor_shift=((0.0, 0.0),), device="cuda", gt0_tables=False):
         if not torch.cuda.is_available():
             raise DetboxError("BoxOpsSession needs a CUDA device: detbox has no CPU path")
         self.dev = torch.device(device)
@@ -41,7 +41,10 @@ class BoxOpsSession:
         self.anchors = ops.anchor_pyramid(*self.anchor_args, device=self.dev)
         # grid geometry of those rows: lets the anchor-target pass take GT-0 targets from separable tables (the
         # library verifies separability on the device on every call, so this is a hint, not a promise)
-        self.pyr = ops.pyramid_desc(*self.anchor_args, device=self.dev)
+        # gt0_tables=True hands that geometry to the anchor-target pass.  Bit-identical results; measured on B200 at
+        # CP-R, batch 64 it is SLOWER (anchor_target_kernel 0.165 vs 0.153 ms: the two table loads and the index
+        # arithmetic cost more issue slots than the packed encode they replace), hence off by default.
+        self.pyr = ops.pyramid_desc(*self.anchor_args, device=self.dev) if gt0_tables else None
         self.A = A = self.anchors.shape[0]
         B = self.B
         self.K = B * min(self.top_n, A)

@@ -312,3 +312,28 @@ def test_config3_values_vs_openmp_reference():
         assert_bwd_within_bound(gi[l].cpu().numpy(), O.roi_align_tf_bwd(gs, rs, scales[l], shapes[l]),
                                 tap_stats(rs, float(scales[l]), 7, 7, shapes[l], "tf", gs), float(np.abs(gs).max()))
     assert len(np.unique(lv[pick])) == 4
+
+
+def test_nchw_staged_backward_opt_in_subprocess():
+    """The staged NCHW backward (block-aggregated red.global.add.v4) is opt-in (DETBOX_ROI_BWD_STAGED=1, read once per
+    process — it measured slower than the direct scatter on B200), so it is exercised in a process of its own: same
+    bound against the oracle as the default path."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "import numpy as np, torch, detbox\n"
+        "from oracle import oracle as O\n"
+        "import test_gpu_roi as T\n"
+        "rng = np.random.RandomState(7)\n"
+        "B, C, H, W = 2, 40, 96, 128\n"
+        "feat_shape = (B, C, H, W)\n"
+        "rois = T.make_rois(rng, 40, B, H * 4, W * 4, 20, 200)\n"
+        "g = rng.normal(0, 1, (40, C, 7, 7)).astype(np.float32)\n"
+        "for mode, m, bwd in (('tf', detbox.ROI_BIN_CENTRE, O.roi_align_tf_bwd), ('grid', detbox.ROI_GRID_POINT, O.roi_align_grid_bwd)):\n"
+        "    gi = detbox.roi_align_backward(T.cu(g), [feat_shape], T.cu(rois), [0.25], m)[0].cpu().numpy()\n"
+        "    T.assert_bwd_within_bound(gi, bwd(g, rois, np.float32(0.25), feat_shape), T.tap_stats(rois, 0.25, 7, 7, feat_shape, mode, g), float(np.abs(g).max()))\n"
+        "print('staged backward ok')\n" % (root, os.path.join(root, "tests")))
+    env = dict(os.environ, DETBOX_ROI_BWD_STAGED="1")
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "staged backward ok" in r.stdout, r.stdout + r.stderr
