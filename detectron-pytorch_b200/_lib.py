@@ -80,6 +80,7 @@ SIGNATURES = {
     "detbox_nms_workspace_bytes": (c_size, [c_long, c_int]),
     "detbox_nms": (c_int, [c_void, c_int, c_void, c_long, c_void, c_int, c_double, c_int, c_void, c_void,
                            c_void, c_size, c_void]),
+    "detbox_nms_static": (c_int, [c_void, c_int, c_void, c_long, c_void, c_int, c_double, c_int, c_void, c_void, c_void]),
     "detbox_nms_variant": (c_int, [c_void, c_int, c_void, c_long, c_void, c_int, c_double, c_int, c_int, c_void, c_void,
                                    c_void, c_void, c_size, c_void]),
     "detbox_roi_align_forward": (c_int, [ctypes.POINTER(RoiCfg), c_void, c_long, c_void, c_void, c_void]),

@@ -258,6 +258,22 @@ int detbox_nms_variant(const float *boxes_dev, int box_stride, const float *scor
                        int64_t *keep_dev, int32_t *n_keep_dev, int64_t *clusters_dev,
                        void *workspace_dev, size_t workspace_bytes, void *stream);
 
+/* detbox_nms with its scratch memory built into the library — NO counterpart in the reference: added
+ * for callers that cannot allocate (code under CUDA-graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  Same arguments and results as detbox_nms minus the workspace; the scratch is a file-scope
+ * __device__ array of 2.25 MiB (csrc/no_alloc.cu) that every GPU loading the library holds until the process exits.
+ * Limits: n <= DETBOX_NMS_STATIC_MAX_BOXES and n_seg <= DETBOX_NMS_STATIC_MAX_SEGMENTS, else DETBOX_ERR_UNSUPPORTED
+ * ("size beyond a documented limit") and nothing is enqueued.  Calls no cudaMalloc / cudaFree / allocating routine.
+ * All calls share the one array (it keeps the last call's contents; what must start at zero is cleared per call), so
+ * calls that OVERLAP on the GPU — different streams, concurrent graph branches — race: serialise them.  The stream must
+ * belong to the CURRENT device; the first call on a device looks up the array's device address
+ * (cudaGetSymbolAddress) — make that call once outside graph capture. */
+#define DETBOX_NMS_STATIC_MAX_BOXES    4096
+#define DETBOX_NMS_STATIC_MAX_SEGMENTS 64
+int detbox_nms_static(const float *boxes_dev, int box_stride, const float *scores_dev, long n,
+                      const int32_t *seg_ids_dev, int n_seg, double thresh, int cmp_mode,
+                      int64_t *keep_dev, int32_t *n_keep_dev, void *stream);
+
 /* ---------------------------------------------------------------------------------------------
  * RoIAlign over FPN levels, forward and backward — replaces
  *   roi_align_tf: crop_and_resize.c:6-268, crop_and_resize_kernel.cu:10-165, roi_align_tf.py:16-42
