@@ -59,6 +59,7 @@ def parse_args():
     ap.add_argument("--no-extras", action="store_true", help="skip the NMS sweep / RoIAlign sub-benchmarks")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--breakdown", action="store_true", help="also print per-op device times to stderr")
+    ap.add_argument("--cpu-roi-child", default=None, help=argparse.SUPPRESS)
     ap.add_argument("--trace", type=int, default=3, help="kernel id timed for the roofline (include/detbox.h)")
     return ap.parse_args()
 
@@ -212,6 +213,103 @@ def cpu_baseline_leg(budget_s=12.0):
                       "anchor_pyramid + anchor.encode + top-n/decode + cpu_nms per image" % (imgs, GT_PER_IMAGE, TOP_N, cores, wall)}
 
 
+# ------------------------------------------- CPU baselines of the two other parts of the metric ----
+def sweep_boxes(n):
+    """SURVEY 8d config-2 boxes (seed 2): the NMS sweep's inputs, shared by the GPU leg and the CPU baseline."""
+    rng = np.random.RandomState(2 + n)
+    h = np.exp(rng.uniform(np.log(12), np.log(264), n)); w = h / 2.44
+    cx, cy = rng.uniform(0, IW, n), rng.uniform(0, IH, n)
+    b = np.stack([np.clip(cx - w / 2, 0, IW - 1), np.clip(cy - h / 2, 0, IH - 1),
+                  np.clip(cx + w / 2, 0, IW - 1), np.clip(cy + h / 2, 0, IH - 1)], 1).astype(np.float32)
+    return b, rng.permutation(np.linspace(0, 1, n)).astype(np.float32)
+
+
+def cpu_nms_baseline(sizes=(1000, 5000, 20000, 100000), budget_s=25.0):
+    """the reference's compiled Cython cpu_nms (libs/nms/cpu_nms.pyx:17-68, one thread: the loop is
+    serial) on the sweep's boxes.  Bounded: a size is skipped once the budget is spent."""
+    c = _cpu_setup()
+    out, spent, last = {}, 0.0, None
+    for n in sizes:
+        if last is not None:                          # greedy NMS costs ~ n * kept ~ n^2 on this box distribution
+            predict = last[1] * (n / last[0]) ** 2
+            if spent + predict > budget_s:
+                out[str(n)] = {"skipped": "bounded sample: predicted %.0f s from the n = %d run (cost ~ n^2), budget %.0f s" % (predict, last[0], budget_s),
+                               "extrapolated_us": round(1e6 * predict, 0)}
+                continue
+        b, s = sweep_boxes(n)
+        dets = np.ascontiguousarray(np.concatenate([b, s[:, None]], 1), np.float32)
+        reps = 3 if n <= 5000 else 1
+        ts = []
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            if c["kind"] == "reference":
+                keep = c["r"].cpu_nms.cpu_nms(dets, NMS_THR)
+            else:
+                keep = c["O"].nms(b, s, NMS_THR, c["O"].NMS_GE_F64)
+            ts.append(time.perf_counter() - t0)
+        spent += sum(ts)
+        last = (n, float(np.median(ts)))
+        out[str(n)] = {"us": round(1e6 * float(np.median(ts)), 1), "kept": int(len(keep))}
+    out["kind"], out["cores"] = c["kind"], 1
+    out["what"] = "libs/nms/cpu_nms.pyx cpu_nms(dets, 0.5) ('>=' in float64), serial by construction"
+    return out
+
+
+def _cpu_roi_child(with_backward):
+    """Child process of cpu_roi_align_baseline (OMP_NUM_THREADS is set in its environment, the only way to be sure which
+    OpenMP runtime instance the reference's .so is bound to obeys it): prints one JSON line."""
+    from oracle import oracle as O
+    c = _cpu_setup()
+    if c["kind"] != "reference":
+        print(json.dumps({"unavailable": "oracle/_ref (compiled crop_and_resize.c) not built"})); return
+    r = c["r"]
+    _, _, P, strides, shapes, ref_areas, rois = roi_bench_inputs()
+    levels = O.assign_levels(rois[:, 1:], np.asarray(ref_areas, np.float32))
+    gen = np.random.default_rng(3)
+    t_f = t_b = 0.0
+    for l, (st, shp) in enumerate(zip(strides, shapes)):
+        sel = levels == l
+        if not sel.any():
+            continue
+        feat = gen.standard_normal(shp, dtype=np.float32)
+        boxes, ind = O.tf_boxes(rois[sel], np.float32(1.0 / st), P, P, shp[2], shp[3])
+        t0 = time.perf_counter()
+        crops = r.crop_and_resize_forward(feat, boxes, ind, 0.0, P, P)
+        t_f += time.perf_counter() - t0
+        if with_backward:
+            t0 = time.perf_counter()
+            r.crop_and_resize_backward(crops, boxes, ind, shp)
+            t_b += time.perf_counter() - t0
+        del feat, crops
+    print(json.dumps({"fwd_ms": round(1e3 * t_f, 1), "bwd_ms": round(1e3 * t_b, 1) if with_backward else None}))
+
+
+def cpu_roi_align_baseline():
+    """the reference's crop_and_resize.c (libs/layers/roi_align_tf/src/crop_and_resize.c:30 forward,
+    `#pragma omp parallel for` over boxes; :207 backward, serial) on configs[2] — the same 4096 RoIs as the GPU leg,
+    level by level as PyramidRoIAlign does (pyramid_roi_align.py:30-60).  Forward with OMP_NUM_THREADS = 1 and = all
+    cores (one child process each), backward once."""
+    cores = host_cores()
+    res = {}
+    for tag, nthr, bwd in (("omp1", 1, True), ("omp_all", cores, False)):
+        env = dict(os.environ, OMP_NUM_THREADS=str(nthr))
+        try:
+            p = subprocess.run([sys.executable, os.path.abspath(__file__), "--cpu-roi-child", "1" if bwd else "0"], env=env,
+                               capture_output=True, text=True, timeout=600)
+            d = json.loads(p.stdout.strip().splitlines()[-1])
+        except Exception as e:                          # keep the bench line; say why the row is missing
+            return {"unavailable": "cpu RoIAlign child failed: %s" % str(e)[:120]}
+        if "unavailable" in d:
+            return d
+        res["fwd_ms_" + tag] = d["fwd_ms"]
+        if bwd:
+            res["bwd_ms_serial"] = d["bwd_ms"]
+    res.update(cores=cores, kind="reference",
+               what="crop_and_resize.c forward (OpenMP over boxes; OMP_NUM_THREADS = 1 / = cores) and backward (serial) on the configs[2] "
+                    "RoIs, level by level; times include the wrapper's zero fill of the output / dense gradient map")
+    return res
+
+
 # ------------------------------------------------------------------------------- GPU helpers ----
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons of one GPU, sampled every 200 ms while active."""
@@ -318,19 +416,41 @@ def median_ms(torch, fn, iters=10, warm=3, flush=None):
 
 
 def nms_sweep(torch, detbox):
-    """BASELINE configs[1]: n in {1k,5k,20k,100k}, IoU 0.5, SURVEY §8d config-2 boxes (seed 2)."""
+    """BASELINE configs[1]: n in {1k,5k,20k,100k}, IoU 0.5, SURVEY §8d config-2 boxes (sweep_boxes).  Beside every
+    device-resident number: the reference's OWN CUDA path (libs/nms/nms_kernel.cu compiled unmodified for sm_100a,
+    oracle/_ref/libref_cuda_nms.so, called through its launcher _nms: host dets in, cudaMalloc + copies + kernel + host
+    scan inside, gpu_nms.pyx:16-31) at 20k / 100k, and this library's drop-in for the same symbol — the same-box GPU
+    baseline of SURVEY 8c."""
+    import ctypes
     out = {}
-    rng = np.random.RandomState(2)
+    ref = None
+    p = os.path.join(ROOT, "oracle", "_ref", "libref_cuda_nms.so")
+    if os.path.exists(p):
+        ref = ctypes.CDLL(p)._Z4_nmsPiS_PKfiifi
+        ref.restype = None
+        ref.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_float, ctypes.c_int]
+    ours = detbox.lib()._nms
     for n in (1000, 5000, 20000, 100000):
-        h = np.exp(rng.uniform(np.log(12), np.log(264), n)); w = h / 2.44
-        cx, cy = rng.uniform(0, IW, n), rng.uniform(0, IH, n)
-        b = np.stack([np.clip(cx - w / 2, 0, IW - 1), np.clip(cy - h / 2, 0, IH - 1),
-                      np.clip(cx + w / 2, 0, IW - 1), np.clip(cy + h / 2, 0, IH - 1)], 1).astype(np.float32)
-        s = rng.permutation(np.linspace(0, 1, n)).astype(np.float32)
+        b, s = sweep_boxes(n)
         db, ds = torch.from_numpy(b).cuda(), torch.from_numpy(s).cuda()
         ms = median_ms(torch, lambda: detbox.nms(db, ds, NMS_THR, detbox.NMS_GT_F32), iters=7 if n > 20000 else 15)
         keep, nk = detbox.nms(db, ds, NMS_THR, detbox.NMS_GT_F32)
         out[str(n)] = {"us": round(ms * 1e3, 1), "kept": int(nk[-1].item())}
+        if n >= 20000:
+            order = np.argsort(-s, kind="stable")
+            dets = np.ascontiguousarray(np.concatenate([b[order], s[order, None]], 1), np.float32)
+            for name, fn in (("reference_gpu_nms_host_us", ref), ("detbox_nms_host_us", ours)):
+                if fn is None:
+                    continue
+                kp, num = np.zeros(n, np.int32), np.zeros(1, np.int32)
+                ts = []
+                for _ in range(3):
+                    torch.cuda.synchronize()
+                    t0 = time.perf_counter()
+                    fn(kp.ctypes.data, num.ctypes.data, dets.ctypes.data, n, 5, ctypes.c_float(NMS_THR), torch.cuda.current_device())
+                    ts.append(time.perf_counter() - t0)
+                out[str(n)][name] = round(1e6 * float(np.median(ts)), 1)
+                out[str(n)][name.replace("_us", "_kept")] = int(num[0])
     return out
 
 
@@ -353,19 +473,26 @@ def measure_l2_peak(torch):
     return round(best, 1)
 
 
-def roi_align_bench(torch, detbox, hbm_peak):
-    """BASELINE configs[2]: 512 RoIs/img x 256 ch x 7x7 over P2-P5 of a 1024x2048 canvas, batch 8,
-    fp32, bin-centre sampling (the variant MaskRCNN wires in), level assigned in-kernel."""
+def roi_bench_inputs():
+    """BASELINE configs[2]: 512 RoIs/img x 256 ch x 7x7 over P2-P5 of a 1024x2048 canvas, batch 8 — shapes and RoIs,
+    shared by the GPU leg and the CPU baseline."""
     B, C, P = 8, 256, 7
     strides = [4, 8, 16, 32]
     shapes = [(B, C, IH // s, IW // s) for s in strides]
     ref_areas = [(float(np.mean(sc)) * BASE) ** 2 for sc in SCALES[:4]]
     rng = np.random.RandomState(3)
-    R = 512 * B
     g = np.concatenate([synth_gt(rng, 512)[:, :4] for _ in range(B)], 0)
     g += rng.normal(0, 4.0, g.shape).astype(np.float32)
     g[:, 2:] = np.maximum(g[:, 2:], g[:, :2] + 4)
     rois = np.concatenate([np.repeat(np.arange(B), 512)[:, None].astype(np.float32), g], 1).astype(np.float32)
+    return B, C, P, strides, shapes, ref_areas, rois
+
+
+def roi_align_bench(torch, detbox, hbm_peak):
+    """BASELINE configs[2]: 512 RoIs/img x 256 ch x 7x7 over P2-P5 of a 1024x2048 canvas, batch 8,
+    fp32, bin-centre sampling (the variant MaskRCNN wires in), level assigned in-kernel."""
+    B, C, P, strides, shapes, ref_areas, rois = roi_bench_inputs()
+    R = rois.shape[0]
     d_rois = torch.from_numpy(rois).cuda()
     gen = torch.Generator(device="cuda").manual_seed(3)
     res = {}
@@ -457,6 +584,93 @@ def coco_post_bench(torch, detbox, hbm_peak):
     return out
 
 
+# ------------------------------------------------- BASELINE configs[4] as written: strong scaling ----
+def strong_64_leg(torch, dist, detbox, rank, world, steps, warmup, n_images=64, max_dets=100):
+    """ONE batch of 64 CP-R images dealt round-robin over the GPUs (image i -> GPU i mod N, detbox.parallel.shard_images;
+    SURVEY 8d config 5), every rank running the device-resident step on ITS 64/N images (one CUDA-graph replay), then
+    the optional epilogue inside the timed region: the kept detections packed into fixed [64/N, 100, 6] buffers
+    (detbox_pack_detections) and all-gathered over NCCL (detbox.parallel.gather_detections_device), so every rank
+    ends the step with all 64 images' detections.  Images are seeded by their GLOBAL index: the batch is the same
+    for every N.  Time = CUDA events, barrier on both sides, max over ranks."""
+    P = detbox.parallel
+    mine = P.shard_images(n_images, rank, world)
+    Bl = len(mine)
+    sess = detbox.pipeline.BoxOpsSession(STRIDES, IH, IW, SCALES, RATIOS, BASE, Bl, NUM_CLASSES, top_n=TOP_N, nms_thresh=NMS_THR,
+                                         bg=BG, fg=FG, max_gt_total=GT_PER_IMAGE * Bl)
+    A = sess.A
+    gts = [synth_gt(np.random.RandomState(100 + i), GT_PER_IMAGE) for i in mine]
+    G = sess.stage_gt(gts)
+    d_gt, d_off = sess.h_gt[:G].cuda(), sess.h_off.cuda()
+    lab = detbox.anchor_target(sess.anchors, d_gt, d_off, sess.tcfg)[0].cpu().numpy()
+    d_prob = torch.empty((Bl * A, NUM_CLASSES), dtype=torch.float32, device="cuda")
+    d_box = torch.empty((Bl * A, 4), dtype=torch.float32, device="cuda")
+    for j, i in enumerate(mine):
+        deltas, prob = synth_head(np.random.RandomState(7000 + i), A, np.nonzero(lab[j] != 0)[0])
+        d_box[j * A:(j + 1) * A].copy_(torch.from_numpy(deltas)); d_prob[j * A:(j + 1) * A].copy_(torch.from_numpy(prob))
+    del lab
+    buf = torch.empty((Bl, max_dets, 6), dtype=torch.float32, device="cuda")
+    cnt = torch.empty((Bl,), dtype=torch.int32, device="cuda")
+    gathered = (torch.empty((world, Bl, max_dets, 6), dtype=torch.float32, device="cuda"),
+                torch.empty((world, Bl), dtype=torch.int32, device="cuda")) if world > 1 else None
+    state = {}
+
+    def step():
+        out = sess.run_device_graph(d_gt, d_off, d_prob, d_box)
+        P.pack_detections_device(out["boxes"], out["scores"], out["keep"], out["n_keep"], Bl, max_dets, out=(buf, cnt))
+        state["all"] = P.gather_detections_device(buf, cnt, n_images, out=gathered)
+
+    ms = timed_loop(torch, dist, step, steps, warmup)
+    ms_nogather = timed_loop(torch, dist, lambda: sess.run_device_graph(d_gt, d_off, d_prob, d_box), steps, warmup)
+    all_buf, all_cnt = state["all"]
+    torch.cuda.synchronize()
+    res = {"images": n_images, "images_per_gpu": Bl, "ms_per_step": round(ms / steps, 4),
+           "images_per_s": round(n_images * steps / (ms / 1e3), 1),
+           "ms_per_step_without_gather": round(ms_nogather / steps, 4),
+           "gather": ("NCCL all_gather_into_tensor of [%d,%d,6] f32 + counts per rank, inside the timed region" % (Bl, max_dets)) if world > 1
+                     else "none (1 GPU): pack kernel only",
+           "gather_bytes_per_rank": int(buf.numel() * 4 + cnt.numel() * 4),
+           "detections_total": int(all_cnt.sum().item()), "checksum": round(float(all_buf.double().sum().item()), 3),
+           "note": "strong scaling: total work fixed at 64 images; detections_total / checksum must be the same for every N"}
+    del sess, d_prob, d_box
+    return res
+
+
+def g_sweep_leg(torch, dist, detbox, L, steps, warmup, hbm_peak, d_prob, d_box, B):
+    """the step at G in {1, 12, 32, 99} synthetic GT per image and on one batch of 64 REAL CityPersons
+    validation GT sets (tests/golden/real_gt64.npz: G = 0 ... 46, mean 12.2, 475 ignore regions).  Per point: the
+    device-resident step (graph replay) and the dominant kernel (events around its launches in an eager one-stream run)."""
+    out = {}
+    real = np.load(os.path.join(ROOT, "tests", "golden", "real_gt64.npz"))
+    roff = real["offsets"]
+    cases = [("G=%d" % g, [synth_gt(np.random.RandomState(100 + i), g) for i in range(B)]) for g in (1, 12, 32, 99)]
+    if B <= 64:
+        cases.append(("real_anno_val_64", [real["gt"][roff[i]:roff[i + 1]] for i in range(B)]))
+    sess = detbox.pipeline.BoxOpsSession(STRIDES, IH, IW, SCALES, RATIOS, BASE, B, NUM_CLASSES, top_n=TOP_N, nms_thresh=NMS_THR,
+                                         bg=BG, fg=FG, max_gt_total=100 * B)
+    A = sess.A
+    for name, gts in cases:
+        Gt = sess.stage_gt(gts)
+        d_gt, d_off = sess.h_gt[:Gt].cuda(), sess.h_off.cuda()
+        ms = timed_loop(torch, dist, lambda: sess.run_device_graph(d_gt, d_off, d_prob, d_box), steps, warmup)
+        pairs = event_pairs(torch, steps)
+        for a, b in pairs:
+            a.record(); b.record()
+
+        def arm(i):
+            if i >= 0:
+                L.detbox_trace_kernel(3, pairs[i][0].cuda_event, pairs[i][1].cuda_event)
+            else:
+                L.detbox_trace_kernel(0, None, None)
+        timed_loop(torch, dist, lambda: sess.run_device(d_gt, d_off, d_prob, d_box, overlap=False), steps, warmup, before_step=arm)
+        L.detbox_trace_kernel(0, None, None)
+        k_ms = float(np.mean([a.elapsed_time(b) for a, b in pairs]))
+        tb = trace_bytes(3, B, A, Gt, NUM_CLASSES)
+        out[name] = {"total_gt": int(Gt), "ms_per_step": round(ms / steps, 4), "images_per_s": round(B * steps / (ms / 1e3), 1),
+                     "anchor_target_kernel_ms": round(k_ms, 4), "roofline_frac": round(tb / k_ms / 1e6 / hbm_peak, 4)}
+    del sess
+    return out
+
+
 # -------------------------------------------------------------------------------------- main ----
 def single_image_latency(torch, detbox, gt1, h_prob, h_box, A):
     """one CP-R image per call (the launch-latency regime) — the whole device-resident path
@@ -531,14 +745,19 @@ def run_reference(args):
 
 def main():
     args = parse_args()
+    if args.cpu_roi_child is not None:
+        return _cpu_roi_child(args.cpu_roi_child == "1")
     if args.impl == "reference":
         return run_reference(args)
 
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    cpu_base = None
+    cpu_base = cpu_nms = cpu_roi = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu_base = cpu_baseline_leg()                 # before CUDA is initialised (fork pool)
+        if not args.no_extras:                        # the two other parts of the metric, on the same host cores
+            cpu_nms = cpu_nms_baseline()
+            cpu_roi = cpu_roi_align_baseline()        # (the cpu_baseline leg is the one place bench.py may use oracle/)
 
     import torch
     if not torch.cuda.is_available():
@@ -646,9 +865,18 @@ def main():
         print("breakdown (ms, batch %d): %s" % (B, json.dumps({k: round(v, 4) for k, v in ops_t.items()})), file=sys.stderr)
 
     extras = {}
+    if not args.no_extras:                            # every rank: the leg ends in a collective
+        strong = strong_64_leg(torch, dist, detbox, rank, world, args.steps, args.warmup)
+        if rank == 0:
+            extras["strong_64"] = strong
     if rank == 0 and world == 1 and not args.no_extras:
+        extras["g_sweep"] = g_sweep_leg(torch, dist, detbox, L, args.steps, args.warmup, hbm_peak, d_prob, d_box, B)
         extras["nms_us"] = nms_sweep(torch, detbox)
+        if cpu_nms:
+            extras["nms_us"]["cpu_baseline"] = cpu_nms
         extras["roi_align"] = roi_align_bench(torch, detbox, hbm_peak)
+        if cpu_roi:
+            extras["roi_align"]["cpu_baseline"] = cpu_roi
         extras["single_image"] = single_image_latency(torch, detbox, gts[0], h_prob, h_box, A)
         extras["coco_r_post"] = coco_post_bench(torch, detbox, hbm_peak)
 

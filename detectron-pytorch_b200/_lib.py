@@ -97,6 +97,7 @@ SIGNATURES = {
     "detbox_threshold_segments": (c_int, [c_void, c_void, c_long, c_int, c_float, c_void, c_void, c_void]),
     "detbox_to_dets": (c_int, [c_void, c_void, c_int, c_void, c_void, c_void, c_long, c_int, c_int, c_int, c_float,
                                c_void, c_long, c_void, c_void]),
+    "detbox_pack_detections": (c_int, [c_void, c_void, c_void, c_void, c_void, c_int, c_int, c_void, c_void, c_void]),
     "detbox_dets_cluster": (c_int, [c_void, c_long, c_void, c_void, c_long, c_void, c_void, c_void]),
     "detbox_host_device_pointer": (c_int, [c_void, ctypes.POINTER(c_void)]),
     "_nms": (None, [c_void, c_void, c_void, c_int, c_int, c_float, c_int]),

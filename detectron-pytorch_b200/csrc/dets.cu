@@ -265,3 +265,51 @@ extern "C" int detbox_dets_cluster(const float *dets, long n, const int64_t *kee
     DETBOX_LAUNCH_CHECK();
     return DETBOX_OK;
 }
+
+// ---- fixed-size detection buffers for the optional all-gather epilogue -------------------------------------
+// keep[] holds the kept ORIGINAL row indices segment-major and score-descending inside a segment (detbox_nms), so the
+// first max_dets entries of a segment are its best detections.  One block per image: start = sum of the counts of the
+// earlier segments, then rows -> (x1, y1, x2, y2, score, class) with zero padding.  No host round trip.
+namespace {
+__global__ void __launch_bounds__(128)
+pack_dets_kernel(const float4 *__restrict__ boxes, const float *__restrict__ scores, const float *__restrict__ classes,
+                 const int64_t *__restrict__ keep, const int32_t *__restrict__ n_keep, int n_seg, int max_dets,
+                 float *__restrict__ out, int32_t *__restrict__ counts)
+{
+    __shared__ int s_part[4];
+    const int b = blockIdx.x, tid = threadIdx.x;
+    int part = 0;
+    for (int i = tid; i < b; i += 128) part += n_keep[i];
+    part = __reduce_add_sync(0xffffffffu, part);
+    if ((tid & 31) == 0) s_part[tid >> 5] = part;
+    __syncthreads();
+    const int start = s_part[0] + s_part[1] + s_part[2] + s_part[3];
+    const int m = min(max(n_keep[b], 0), max_dets);
+    if (tid == 0) counts[b] = m;
+    float *o = out + (size_t)b * max_dets * 6;
+    for (int j = tid; j < max_dets; j += 128) {
+        float v[6] = {0, 0, 0, 0, 0, 0};
+        if (j < m) {
+            const int64_t r = keep[start + j];
+            const float4 bx = boxes[r];
+            v[0] = bx.x; v[1] = bx.y; v[2] = bx.z; v[3] = bx.w; v[4] = scores[r]; v[5] = classes ? classes[r] : 1.0f;
+        }
+#pragma unroll
+        for (int k = 0; k < 6; ++k) o[j * 6 + k] = v[k];
+    }
+}
+}  // namespace
+
+extern "C" int detbox_pack_detections(const float *boxes, const float *scores, const float *classes,
+                                      const int64_t *keep, const int32_t *n_keep, int n_seg, int max_dets,
+                                      float *out, int32_t *counts, void *stream)
+{
+    if (n_seg < 0 || max_dets < 0) return DETBOX_ERR_INVALID;
+    if (n_seg == 0) return DETBOX_OK;
+    if (!boxes || !scores || !keep || !n_keep || !counts || (max_dets > 0 && !out)) return DETBOX_ERR_INVALID;
+    if (((uintptr_t)boxes & 15) != 0) return DETBOX_ERR_INVALID;
+    pack_dets_kernel<<<(unsigned)n_seg, 128, 0, as_stream(stream)>>>((const float4 *)boxes, scores, classes, keep, n_keep,
+                                                                    n_seg, max_dets, out, counts);
+    DETBOX_LAUNCH_CHECK();
+    return DETBOX_OK;
+}

@@ -65,3 +65,45 @@ def gather_detections(local_dets, n_images: int, max_dets: int = 100, group=None
         for j, d in enumerate(unpack_detections(bufs[r], cnts[r])[:len(shard_images(n_images, r, world))]):
             out[r + j * world] = d
     return out
+
+
+# ---------------------------------------------------------------------------------- device-side epilogue --
+def pack_detections_device(boxes, scores, keep, n_keep, n_local, max_dets=100, classes=None, out=None):
+    """Device tensors from topk_decode / nms (n_local images, per-image segments) -> (buf [n_local, max_dets, 6] float32,
+    counts int32 [n_local]) on the device with ONE kernel and no host synchronisation (detbox_pack_detections)."""
+    from . import ops
+    from ._lib import check, lib
+    b = ops._dev(boxes).view(-1, 4)
+    s = ops._dev(scores).view(-1)
+    k = ops._dev(keep, torch.int64, "keep").view(-1)
+    nk = ops._dev(n_keep, torch.int32, "n_keep").view(-1)
+    c = ops._dev(classes).view(-1) if classes is not None else None
+    if out is None:
+        out = (torch.empty((n_local, max_dets, 6), dtype=torch.float32, device=b.device),
+               torch.empty((n_local,), dtype=torch.int32, device=b.device))
+    buf, cnt = out
+    check(lib().detbox_pack_detections(b.data_ptr(), s.data_ptr(), ops._ptr(c), k.data_ptr(), nk.data_ptr(), int(n_local),
+                                       int(max_dets), buf.data_ptr(), cnt.data_ptr(), ops._stream()), "pack_detections")
+    ops._count(1 if n_local else 0)
+    return buf, cnt
+
+
+def gather_detections_device(buf, cnt, n_images: int, group=None, out=None):
+    """The optional final all-gather on CUDA buffers (NCCL over NVLink): every rank passes the packed detections of ITS
+    images (shard_images order, n_images a multiple of the world size) and receives (dets [n_images, max_dets, 6],
+    counts [n_images]) in IMAGE order — views of the gathered buffers, no copy, no host synchronisation.
+    Single process: returned as they are."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return buf, cnt
+    world = dist.get_world_size(group)
+    per = buf.shape[0]
+    if per * world != n_images:
+        raise ValueError("gather_detections_device needs n_images (%d) = world (%d) x images per rank (%d)" % (n_images, world, per))
+    if out is None:
+        out = (torch.empty((world,) + tuple(buf.shape), dtype=buf.dtype, device=buf.device),
+               torch.empty((world, per), dtype=cnt.dtype, device=cnt.device))
+    all_buf, all_cnt = out
+    dist.all_gather_into_tensor(all_buf, buf, group=group)
+    dist.all_gather_into_tensor(all_cnt, cnt, group=group)
+    # image i = r + j * world lives at [r, j]: image order is the (j, r) traversal
+    return all_buf.transpose(0, 1).reshape(n_images, buf.shape[1], buf.shape[2]), all_cnt.transpose(0, 1).reshape(n_images)

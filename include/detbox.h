@@ -386,6 +386,15 @@ int detbox_to_dets(const float *boxes_dev, const float *probs_dev, int C, const 
                    int activation, int multi_label, float score_threshold,
                    double *dets_dev, long cap, int32_t *det_offsets_dev, void *stream);
 
+/* Fixed-size detection buffers for the optional final all-gather of the per-image sharded mode (the
+ * reference gathers DataParallel outputs in one process, libs/nets/data_parallel.py:19-91, and truncates to max_det_num,
+ * libs/postprocessings/single_shot.py:59): from detbox_nms's keep / n_keep (n_seg images, segment-major, best first) the
+ * first max_dets kept rows of every image as out [n_seg, max_dets, 6] float32 = (x1,y1,x2,y2,score,class), zero padded,
+ * and counts int32 [n_seg].  classes_dev may be NULL (class 1).  boxes [.,4] 16-byte aligned.  No host round trip. */
+int detbox_pack_detections(const float *boxes_dev, const float *scores_dev, const float *classes_dev,
+                           const int64_t *keep_dev, const int32_t *n_keep_dev, int n_seg, int max_dets,
+                           float *out_dev, int32_t *counts_dev, void *stream);
+
 /* libs/postprocessings/single_shot.py:401-415 dets_cluster — score-weighted box voting over the clusters
  * detbox_nms_variant(MULTIANCHOR) returns: out row k (float32 [5]) = sum over the members i of cluster
  * keep[k] (clusters[i] == keep[k], ascending i) of dets[i,:4] * score_i / sum(score), score = the members'

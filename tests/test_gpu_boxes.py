@@ -413,3 +413,27 @@ def test_anchor_target_compact_rejects_unpackable_class():
     assert ((packed & 0x7f) == 127).any()
     with pytest.raises(detbox.DetboxError):
         detbox.expand_targets(packed, counts)
+
+
+def test_anchor_target_64_real_citypersons_images(cpr_anchors, golden):
+    """64 real anno_val.mat GT sets (G = 0 ... 46, 475 ignore regions) as ONE batch against the CP-R
+    pyramid — (#fg, #bg, #ignored) and the background label weight of every image bit-exact against what the COMPILED
+    reference's anchor.encode returned (tests/golden/real_gt64.npz, oracle/make_real_gt64.py); generic path, table path
+    and compact format agree."""
+    ref, _ = cpr_anchors
+    anc = ref.astype(np.float32)
+    g = golden("real_gt64")
+    off = g["offsets"]
+    gts = [g["gt"][off[i]:off[i + 1]] for i in range(64)]
+    got = run_target(anc, gts, CPR)
+    lab = got[0]
+    np.testing.assert_array_equal(np.stack([(lab >= 1).sum(1), (lab == 0).sum(1), (lab < 0).sum(1)], 1), g["counts"])
+    np.testing.assert_array_equal(got[4], g["counts"][:, :2])
+    for b in range(64):
+        bg = got[1][b][lab[b] == 0]
+        assert bg.size and (bg == g["bg_weight"][b]).all()
+    pyr = detbox.pyramid_desc(CPR.strides, 1024, 2048, CPR.anchor_scales, CPR.anchor_ratios, 16)
+    packed, bt, counts = run_target(anc, gts, CPR, pyramid=pyr, format="compact")
+    assert np.array_equal(bt.view(np.uint32), got[2].view(np.uint32)) and np.array_equal(counts, got[4])
+    labels, lw, bw = detbox.expand_targets(packed, counts, CPR.bbweights)
+    assert np.array_equal(labels.numpy(), lab) and np.array_equal(lw.numpy(), got[1]) and np.array_equal(bw.numpy(), got[3])

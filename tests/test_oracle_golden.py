@@ -210,3 +210,17 @@ def test_to_dets(golden):
         d = O.to_dets(b, p, i, B, act, multi, thr)
         assert np.array_equal(np.cumsum([0] + [x.shape[0] for x in d]), g[name + "_offsets"])
         assert np.array_equal(np.concatenate(d, 0), g[name + "_dets"])
+
+
+def test_anchor_target_real_gt64_counts(golden):
+    """The oracle against the compiled reference's recorded counts on real CityPersons GT (tests/golden/real_gt64.npz):
+    the densest image, an image without GT and two more, at full CP-R size."""
+    g = golden("real_gt64")
+    cfg = O.citypersons_retinanet_cfg()
+    anc = O.anchor_pyramid(cfg.strides, 1024, 2048, cfg.anchor_scales, cfg.anchor_ratios, cfg.anchor_base).astype(np.float32)
+    off = g["offsets"]
+    n = off[1:] - off[:-1]
+    for i in sorted({int(n.argmax()), int(n.argmin()), 7, 33}):
+        lab, lw, _, _ = O.anchor_encode(g["gt"][off[i]:off[i + 1]], anc, cfg)
+        assert [(lab >= 1).sum(), (lab == 0).sum(), (lab < 0).sum()] == list(g["counts"][i])
+        assert (lw[lab == 0] == g["bg_weight"][i]).all()
