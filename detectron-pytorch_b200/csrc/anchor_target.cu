@@ -216,9 +216,9 @@ anchor_bbox_kernel(const float4 *__restrict__ anchors, long A, TileBoxes *__rest
 // ---- pass 1: per-GT column maxima ---------------------------------------------------------------
 // The column maximum of a GT row is taken over ALL anchors and the anchors are shared by the whole batch, so this
 // pass has no per-image structure at all: a block owns CM_SLICES warp slices (32 anchors each; dealt round-robin) and
-// CM_GT consecutive rows of the concatenated GT array, whichever images they belong to.  At 64 images x 12 GT
-// that is 16 x 24 blocks — ONE wave — where a (slice group, image) grid was 4096 blocks of a few hundred
-// instructions each, i.e. seven waves of pure load latency.  Inside a block: the slice boxes and the GT rows are
+// CM_GT consecutive rows of the concatenated GT array, whichever images they belong to.  At CP-R (8,192 slices) with
+// 64 images x 12 GT and CM_SLICES = 512 / CM_GT = 32 that is 16 x 24 blocks — ONE wave — where a (slice group, image)
+// grid was 4096 blocks of a few hundred instructions each, i.e. seven waves of pure load latency.  Inside a block: the slice boxes and the GT rows are
 // fetched together (one latency), every (slice, 32-GT word) pair is culled with the conservative float32 test,
 // pairs with a non-empty mask go on a shared work list, and the warps take pairs off the list — 32 anchors, exact
 // float64 IoU (bbox.pyx:33-54) against the GT of the mask, warp maximum, one shared-memory atomicMax on the
@@ -305,8 +305,13 @@ colmax_kernel(const TargetParams p, int n_slices, int total_gt)
                     unsure = !(iw >= 9.765625e-4f && ih >= 9.765625e-4f && uni > 0.0f && ov32 < 4.0f);
                 }
                 const unsigned a32 = __reduce_max_sync(0xffffffffu, __float_as_uint(ov32));
+                // the running maximum is read by ONE lane and broadcast: other warps atomicMax the same word meanwhile, and
+                // the `continue` below must be taken by all 32 lanes or none (full-mask sync operations follow)
+                unsigned long long cm = 0ull;
+                if (lane == 0) cm = cmax[j];
+                cm = __shfl_sync(0xffffffffu, cm, 0);
                 if (!big && !__any_sync(0xffffffffu, unsure) &&
-                    (double)__uint_as_float(a32) * 1.02 < __longlong_as_double((long long)cmax[j])) continue;
+                    (double)__uint_as_float(a32) * 1.02 < __longlong_as_double((long long)cm)) continue;
             }
             unsigned long long bits = 0ull;
             const double iw = fmin(ax2, gx2[j]) - fmax(ax1, gx1[j]) + 1;          // bbox.pyx:39-42

@@ -96,8 +96,11 @@ nms_seg_count_kernel(const ID *__restrict__ seg_ids, long n, int n_seg, int32_t 
     for (long base = (long)blockIdx.x * blockDim.x; base < n; base += (long)gridDim.x * blockDim.x) {   // block-uniform trip count
         const long i = base + threadIdx.x;
         const ID raw = i < n ? seg_ids[i] : (ID)-1;
-        int s = (raw < 0 || raw >= (ID)n_seg) ? -1 : (int)raw;
-        if (narrow && i < n) narrow[i] = s;
+        // An id outside [0, n_seg) is a caller error.  It must never be used as an index (seg_off[id] in the later
+        // passes): the row is counted in, and handed on as, the nearest valid segment — memory-safe, its keep decision
+        // unspecified — and every later pass reads this narrowed array, whatever the width of the caller's ids.
+        int s = i < n ? (raw < 0 ? 0 : (raw >= (ID)n_seg ? n_seg - 1 : (int)raw)) : -1;
+        if (i < n) narrow[i] = s;
         const unsigned peers = __match_any_sync(0xffffffffu, s);
         if (s >= 0 && lane == __ffs(peers) - 1) atomicAdd(&seg_off[s + 1], __popc(peers));
     }
@@ -557,10 +560,10 @@ static int nms_impl(const float *boxes, int box_stride, const float *scores, lon
         DETBOX_CUDA_TRY(cudaMemsetAsync(b.seg_off, 0, (size_t)(n_seg + 2) * sizeof(int32_t), st));
         if (seg_i64) {
             nms_seg_count_kernel<int64_t><<<(unsigned)gb0, 256, 0, st>>>(reinterpret_cast<const int64_t *>(seg_ids), n, n_seg, b.seg_off, b.seg_narrow);
-            seg_ids = b.seg_narrow;
         } else {
-            nms_seg_count_kernel<int32_t><<<(unsigned)gb0, 256, 0, st>>>(seg_ids, n, n_seg, b.seg_off, nullptr);
+            nms_seg_count_kernel<int32_t><<<(unsigned)gb0, 256, 0, st>>>(seg_ids, n, n_seg, b.seg_off, b.seg_narrow);
         }
+        seg_ids = b.seg_narrow;                       // narrowed AND clamped: the only id array the later passes index with
         DETBOX_LAUNCH_CHECK();
         nms_seg_scan_kernel<<<1, 32, 0, st>>>(b.seg_off, n_seg);
         DETBOX_LAUNCH_CHECK();

@@ -21,7 +21,7 @@ class _RoiFn(Function):
                                         pool=meta.get("pool"), levels=levels, ref_areas=meta.get("ref_areas"),
                                         all_levels=meta.get("all_levels", False), extrapolation=meta.get("extrapolation", 0.0))
         ctx.meta, ctx.shapes = meta, [tuple(f.shape) for f in feats]
-        ctx.nhwc = ops_roi._is_channels_last(feats[0])
+        ctx.nhwc = all(ops_roi._is_channels_last(f) for f in feats)     # the layout _make_cfg chose: NHWC only if EVERY level is
         ctx.save_for_backward(rois, levels if levels is not None else rois.new_zeros(0), *(feats if meta.get("pool") == "max" else ()))
         ctx.has_levels = levels is not None
         return out

@@ -107,7 +107,9 @@ def roi_align_backward(grad_out, feat_shapes, rois, spatial_scales, mode=ROI_BIN
     if POOL[pool] == 2:
         if feats is None:
             raise _lib.DetboxError("roi_align_backward(pool='max') needs the forward's feature maps")
-        feats = [f if channels_last else f.contiguous() for f in feats]
+        # saved maps are converted to the chosen layout explicitly: a mixed-format pyramid ran (and saved) NCHW copies or not,
+        # and the arg-max must be recomputed on memory that really has the layout the kernel is told
+        feats = [f.contiguous(memory_format=torch.channels_last) if channels_last else f.contiguous() for f in feats]
         for l, f in enumerate(feats):
             c.feat[l] = f.data_ptr()
     lv = _dev(levels, torch.int32, "levels").view(-1) if levels is not None else None

@@ -223,8 +223,7 @@ int detbox_topk_decode(const float *prob_dev, int C, const float *deltas_dev, co
 /* ---------------------------------------------------------------------------------------------
  * Stable radix sort of float32 scores, descending (ties: lower index first).  Exposed because
  * the reference's callers sort explicitly (libs/layers/box.py:160, libs/nms/gpu_nms.pyx:25).
- * order_dev int32 [n] receives the permutation.  Segments (optional): seg_offsets_dev int32
- * [n_seg+1] sorts every segment independently (indices stay global).
+ * order_dev int32 [n] receives the permutation (one segment; segmented selection is detbox_topk_decode's job).
  * ------------------------------------------------------------------------------------------- */
 size_t detbox_sort_desc_workspace_bytes(long n);
 int detbox_sort_desc(const float *scores_dev, long n, int32_t *order_dev,
@@ -238,7 +237,9 @@ int detbox_sort_desc(const float *scores_dev, long n, int32_t *order_dev,
  * device; nothing is copied to the host.
  * boxes_dev [n, box_stride] (x1,y1,x2,y2 first), scores_dev [n].  seg_ids_dev: int32 [n], the
  * segment (image id) of every row, values in [0,n_seg); rows of different segments never
- * suppress each other (NULL or n_seg <= 1: one segment).  Rows need not be grouped.
+ * suppress each other (NULL or n_seg <= 1: one segment).  Rows need not be grouped.  An id outside
+ * [0,n_seg) is a caller error: it is never used as an index — the row is treated as part of the nearest
+ * valid segment (0 or n_seg-1), memory-safe, its own keep decision unspecified.
  * keep_dev int64 [n]: kept ORIGINAL row indices, segment-major, score-descending inside a
  * segment.  n_keep_dev int32 [n_seg+1]: [0..n_seg) per-segment counts, [n_seg] the total
  * (n_seg == 1: both entries hold the total).

@@ -367,3 +367,21 @@ def test_dets_cluster_after_device_nms():
     want = O.dets_cluster(d, keep[:m].cpu().numpy(), cl.cpu().numpy())
     np.testing.assert_array_equal(out[:m].cpu().numpy(), want)
     assert not out[m:].any()
+
+
+def test_nms_out_of_range_segment_id_is_memory_safe():
+    """a segment id outside [0, n_seg) (here == n_seg and -3, int32 and int64 ids) must never be used as an
+    index.  The call completes, and every segment that holds no bad row keeps exactly what it keeps without them."""
+    rng = np.random.RandomState(17)
+    n, n_seg = 1200, 4
+    b, s = sweep_boxes(rng, n)
+    seg = rng.randint(0, n_seg, n).astype(np.int32)
+    bad = np.nonzero(seg == n_seg - 1)[0][:5]                    # rows of the LAST segment get id n_seg, rows of segment 0 get -3
+    bad0 = np.nonzero(seg == 0)[0][:5]
+    seg_bad = seg.copy(); seg_bad[bad] = n_seg; seg_bad[bad0] = -3
+    keep_ref, nk_ref = keep_list(*detbox.nms(cu(b), cu(s), 0.5, detbox.NMS_GT_F32, seg_ids=cu(seg), n_seg=n_seg))
+    for dt in (torch.int32, torch.int64):
+        keep, nk = keep_list(*detbox.nms(cu(b), cu(s), 0.5, detbox.NMS_GT_F32, seg_ids=cu(seg_bad).to(dt), n_seg=n_seg))
+        torch.cuda.synchronize()
+        np.testing.assert_array_equal(nk, nk_ref)                # clamped to the nearest segment == their own here
+        np.testing.assert_array_equal(keep, keep_ref)
