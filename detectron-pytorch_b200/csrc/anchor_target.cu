@@ -52,7 +52,33 @@ struct GtChunk {
     float4 fbox[GCH];                                // the same boxes as float32, for the conservative slice test
     float4 genc[GCH];                                // box_math.cuh::gt_pre — the GT half of the encode, once per GT
     float cls[GCH];
+    float area32[GCH];                               // float32 screen of the decide phase: GT area ...
+    float cmlo[GCH];                                 // ... and its column maximum lowered by the screen's margin (-1: no screen for this GT)
 };
+
+// ---- float32 screen of the decide phase ---------------------------------------------------------------------------
+// The exact decide (float64 IoU in the reference's operation order, one IEEE division per overlapping pair) is needed
+// only where a decision can depend on the last bits.  Everything else is decided by float32 values with a PROVEN bound:
+// inputs are float32, so fl(m - M) is one rounding of the exact difference and s = fl(fl(m - M) + 1) satisfies
+// |s - exact| <= (2|s| + 1) * 2^-23: for |s| >= SCR_T = 2^-10 its sign is certain and, if positive, its relative error
+// is <= (2 + 1/s) * 2^-24 <= 6.2e-5.  With both intersection sides and all four box sides >= SCR_T the float32 IoU
+// (inter / (a + g - inter), fast division) is within 5e-4 relative of the exact one, and so is every term inter / a of
+// the ignore sum.  A decision is taken from float32 values only if it holds with a margin of SCR_M = 2e-3 relative:
+//   argmax    second best < best * (1 - SCR_M)                      (a tie or near-tie -> exact: first maximum wins)
+//   labels    |best - t| > SCR_M * t for t in {bg, fg, 0.5};  |ignore sum - ign| > SCR_M * ign
+//   promotion every overlap < colmax(GT) * (1 - SCR_M)              (otherwise ov == colmax must be tested exactly)
+//   zero      a side in (-SCR_T, SCR_T), a non-positive union or any NaN -> exact
+// If ANY lane of a slice is undecided the whole slice takes the exact path (warp-uniform, no divergence), whose results
+// are bit-identical by construction; decided lanes carry the same argmax, the same threshold outcomes and the same
+// ignore outcome as the exact path, which is all label_of() and the emit phase consume.
+constexpr float SCR_T = 9.765625e-4f;                // 2^-10
+constexpr float SCR_M = 2e-3f;
+__device__ __forceinline__ bool scr_near(const float v, const float t) { return !(fabsf(v - t) > SCR_M * fabsf(t) + 1e-7f); }
+__device__ __forceinline__ void scr_stage(GtChunk &sm, const int i, const float4 f, const unsigned long long cm) {
+    const float gw = f.z - f.x + 1.0f, gh = f.w - f.y + 1.0f;
+    sm.area32[i] = gw * gh;
+    sm.cmlo[i] = (gw >= SCR_T && gh >= SCR_T) ? __double2float_rd(__longlong_as_double((long long)cm)) * (1.0f - SCR_M) : -1.0f;
+}
 
 __device__ __forceinline__ unsigned long long iou_bits(double v) {
     return (unsigned long long)__double_as_longlong(v);
@@ -410,8 +436,8 @@ __device__ __forceinline__ bool tab_targets(const PyrDev &y, const float2 *__res
 }
 
 // EMIT_ILP: anchors encoded side by side in the emit loops; MINB: blocks per SM; TABLE: GT-0 targets come from the
-// separable tables when the pyramid check passed; COMPACT: output format
-template <int EMIT_ILP, bool FRCNN, int MINB, bool TABLE, bool COMPACT>
+// separable tables when the pyramid check passed; COMPACT: output format; SCREEN: float32 screen of the decide phase
+template <int EMIT_ILP, bool FRCNN, int MINB, bool TABLE, bool COMPACT, bool SCREEN>
 __global__ void __launch_bounds__(AT_THREADS, MINB)
 anchor_target_kernel(const TargetParams p)
 {
@@ -480,6 +506,7 @@ anchor_target_kernel(const TargetParams p)
             sm.genc[tid] = gt_pre(f);
             const unsigned long long cm = p.colmax[g0 + tid];
             sm.colmax[tid] = cm;
+            scr_stage(sm, tid, f, cm);
             flags = (may_touch(tbox, x1, y1, x2, y2) ? 1 : 0) | (cm == 0ull ? 2 : 0);   // all-zero column: every anchor ties (anchor.py:46)
         }
     } else {
@@ -563,6 +590,7 @@ anchor_target_kernel(const TargetParams p)
             sm.fbox[tid] = make_float4(q[0], q[1], q[2], q[3]);
             sm.genc[tid] = gt_pre(sm.fbox[tid]);
             sm.colmax[tid] = p.colmax[g0 + c0 + tid];
+            scr_stage(sm, tid, sm.fbox[tid], sm.colmax[tid]);
         }
         __syncthreads();
     };
@@ -587,6 +615,11 @@ anchor_target_kernel(const TargetParams p)
     // Decide phase.  One slice at a time keeps the float64 row state (argmax, ignore sum, area) of a single
     // anchor in registers; only slices some GT may touch load their anchors here.  With more than GCH GT the
     // chunks are re-staged per slice (all warps together).
+    // (Measured and rejected, B200, G = 12: fusing this loop into the emit loop — decision in registers from the anchor
+    //  the emit is about to encode, next anchors prefetched meanwhile — ran 0.164 vs 0.153 ms: the decide chain then sits in
+    //  front of the stores and the extra live state spills.  The float32 screen below removes the float64 division from
+    //  the common path (17 % of the kernel's instructions) but only 1 % of its time at G = 12 (7 % at G = 32): the
+    //  arithmetic of this loop is hidden, its per-slice latency chain is not.  profiles/r02_anchor_target_experiments.txt)
 #pragma unroll 1
     for (int i = 0; i < AT_ITEMS; ++i) {
         if (use_masks && smask[i][w] == 0) continue;             // no GT near this slice: the emit phase uses (l_zero, GT 0)
@@ -625,8 +658,36 @@ anchor_target_kernel(const TargetParams p)
             }
         };
         if (use_masks) {
-            const unsigned m = smask[i][w];
-            if (m) eval_hits(m, 0, 0);
+            const unsigned m = smask[i][w];                      // != 0 here
+            bool amb = !SCREEN;
+            float best32 = 0.0f, second32 = 0.0f, isum32 = 0.0f; int bj = 0;
+            if (SCREEN) {
+                if (valid) anc = p.anchors[a];
+                have_anc = true;
+                const float aw = anc.z - anc.x + 1.0f, ah = anc.w - anc.y + 1.0f, aarea32 = aw * ah;
+                if (valid && !(aw >= SCR_T && ah >= SCR_T)) amb = true;
+                unsigned mm = m;
+                while (mm) {                                     // ascending GT index, like the exact loop
+                    const int j = __ffs(mm) - 1;
+                    mm &= mm - 1;
+                    const float4 g = sm.fbox[j];
+                    const float iw = fminf(anc.z, g.z) - fmaxf(anc.x, g.x) + 1.0f, ih = fminf(anc.w, g.w) - fmaxf(anc.y, g.y) + 1.0f;
+                    if (iw <= -SCR_T || ih <= -SCR_T) continue;                       // certainly disjoint (padding lanes: -inf)
+                    if (!(iw >= SCR_T && ih >= SCR_T)) { amb = true; continue; }       // within rounding of touching, or NaN
+                    const float inter = iw * ih, ua = aarea32 + sm.area32[j] - inter;
+                    const float ov = __fdividef(inter, ua);
+                    if (!(ua > 0.0f && ov < 2.0f && ov < sm.cmlo[j])) amb = true;     // odd union / may equal the column maximum
+                    if (ov > best32) { second32 = best32; best32 = ov; bj = j; } else second32 = fmaxf(second32, ov);
+                    if (sm.cls[j] < 0.0f) isum32 += __fdividef(inter, aarea32);
+                }
+                if (best32 > 0.0f) {
+                    amb |= !(second32 < best32 * (1.0f - SCR_M));
+                    amb |= scr_near(best32, (float)p.bg) | scr_near(best32, (float)p.fg) | scr_near(best32, 0.5f);
+                    amb |= isum32 > 0.0f ? scr_near(isum32, (float)p.ign) : !(isum32 == 0.0f);
+                }
+            }
+            if (__any_sync(0xffffffffu, amb)) eval_hits(m, 0, 0);                     // exact, the whole slice
+            else { best = (double)best32; best_g = bj; isum = (double)isum32; }      // promoted stays zero_any: no overlap reaches a column maximum
         } else {
             const float4 wbb = wbb_base[i * AT_WARPS];
             for (int c0 = 0; c0 < G; c0 += GCH) {
@@ -873,16 +934,13 @@ extern "C" int detbox_anchor_target_ex(const float *anchors, long A, const detbo
         DETBOX_LAUNCH_CHECK();
     }
     DETBOX_TRACE_BEGIN(DETBOX_K_TARGET_ASSIGN, st);
-    if (!frcnn) {
-        if (compact) anchor_target_kernel<1, false, 4, false, true><<<grid, AT_THREADS, 0, st>>>(p);
-        else anchor_target_kernel<1, false, 4, false, false><<<grid, AT_THREADS, 0, st>>>(p);
-    } else if (tables) {
-        if (compact) anchor_target_kernel<2, true, 4, true, true><<<grid, AT_THREADS, 0, st>>>(p);
-        else anchor_target_kernel<2, true, 4, true, false><<<grid, AT_THREADS, 0, st>>>(p);
-    } else {
-        if (compact) anchor_target_kernel<2, true, 4, false, true><<<grid, AT_THREADS, 0, st>>>(p);
-        else anchor_target_kernel<2, true, 4, false, false><<<grid, AT_THREADS, 0, st>>>(p);
-    }
+    static const bool screen = getenv("DETBOX_AT_NOSCREEN") == nullptr;
+#define AT_LAUNCH(ILP, FR, TB, CP) do { if (screen) anchor_target_kernel<ILP, FR, 4, TB, CP, true><<<grid, AT_THREADS, 0, st>>>(p); \
+                                        else anchor_target_kernel<ILP, FR, 4, TB, CP, false><<<grid, AT_THREADS, 0, st>>>(p); } while (0)
+    if (!frcnn) { if (compact) AT_LAUNCH(1, false, false, true); else AT_LAUNCH(1, false, false, false); }
+    else if (tables) { if (compact) AT_LAUNCH(2, true, true, true); else AT_LAUNCH(2, true, true, false); }
+    else { if (compact) AT_LAUNCH(2, true, false, true); else AT_LAUNCH(2, true, false, false); }
+#undef AT_LAUNCH
     DETBOX_TRACE_END(DETBOX_K_TARGET_ASSIGN, st);
     DETBOX_LAUNCH_CHECK();
     if (compact) return DETBOX_OK;                   // label weights = f(label, counts): the expander's job

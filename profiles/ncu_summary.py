@@ -18,4 +18,5 @@ h = rows[0]
 for w in WANT:
     if w in h:
         i = h.index(w)
-        print("%-66s %-8s %s" % (w, rows[1][i], " | ".join(r[i][:44] for r in rows[2:])))
+        cell = (lambda v: v.replace("void ", "").replace("<unnamed>::", "").replace("(anonymous namespace)::", "")[:64]) if w == 'Kernel Name' else (lambda v: v[:44])
+        print("%-66s %-8s %s" % (w, rows[1][i], " | ".join(cell(r[i]) for r in rows[2:])))

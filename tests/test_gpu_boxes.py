@@ -437,3 +437,36 @@ def test_anchor_target_64_real_citypersons_images(cpr_anchors, golden):
     assert np.array_equal(bt.view(np.uint32), got[2].view(np.uint32)) and np.array_equal(counts, got[4])
     labels, lw, bw = detbox.expand_targets(packed, counts, CPR.bbweights)
     assert np.array_equal(labels.numpy(), lab) and np.array_equal(lw.numpy(), got[1]) and np.array_equal(bw.numpy(), got[3])
+
+
+@pytest.mark.parametrize("seed", range(3))
+def test_anchor_target_decide_screen_adversarial(seed):
+    """The float32 screen of the decide phase must hand every undecidable case to the exact float64 path.  GT sets built
+    FROM anchors so that the cases sit exactly on the screen's boundaries: a GT equal to an anchor (IoU 1 = its column
+    maximum: promotion), the same GT twice (argmax tie: first maximum wins), GT that touch an anchor exactly (iw = 0),
+    overlap it by exactly one pixel column (iw = 1), by 1e-4 (inside the undecided band) and by -1e-4, GT scaled so that
+    the IoU with an anchor lands on the thresholds 0.5 / 0.6 up to rounding, ignore regions whose intersection fraction
+    lands on 0.3.  Labels / weights bit-exact against the oracle, as everywhere."""
+    rng = np.random.RandomState(900 + seed)
+    scales = [[2, 2.52, 3.175], [4, 5.04, 6.349], [8, 10.079, 12.7]]
+    anc = O.anchor_pyramid([8, 16, 32], 160, 256, scales, [1, 2.5], 16).astype(np.float32)
+    cfg = O.Cfg(rpn_bg_threshold=0.5, rpn_fg_threshold=0.6)
+    gts = []
+    for _ in range(6):
+        a = anc[rng.choice(anc.shape[0], 6, replace=False)].astype(np.float64)
+        w, h = a[:, 2] - a[:, 0] + 1, a[:, 3] - a[:, 1] + 1
+        rows = [a[0], a[0],                                                     # equal to an anchor, twice
+                [a[1, 2] + 1, a[1, 1], a[1, 2] + 1 + w[1], a[1, 3]],              # touches: iw = 0
+                [a[1, 2], a[1, 1], a[1, 2] + w[1], a[1, 3]],                      # iw = 1
+                [a[2, 2] + 1 - 1e-4, a[2, 1], a[2, 2] + w[2], a[2, 3]],           # iw = 1e-4
+                [a[2, 2] + 1 + 1e-4, a[2, 1], a[2, 2] + 2 * w[2], a[2, 3]]]       # iw = -1e-4
+        for t, k in ((0.5, 3), (0.6, 4)):                                       # same corner, area ratio t: IoU = t up to rounding
+            rows.append([a[k, 0], a[k, 1], a[k, 0] + w[k] * t - 1, a[k, 3]])
+            rows.append([a[k, 0], a[k, 1], a[k, 2], a[k, 1] + h[k] / t - 1])
+        gt = np.concatenate([np.asarray(rows, np.float64), np.ones((len(rows), 1))], 1)
+        ign = [a[5, 0], a[5, 1], a[5, 0] + w[5] * 0.3 - 1, a[5, 3], -1]           # covers 0.3 of anchor 5
+        gt = np.concatenate([gt, np.asarray([ign])], 0).astype(np.float32)
+        gts.append(gt[rng.permutation(gt.shape[0])] if seed else gt)
+    got = run_target(anc, gts, cfg)
+    for b, gt in enumerate(gts):
+        check_target(got, b, gt, anc, cfg)
