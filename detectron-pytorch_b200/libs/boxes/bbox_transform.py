@@ -51,17 +51,24 @@ def clip_boxes(boxes, im_shape):
 
 
 def bbox_transform_linear(anchors, gt_boxes, alpha=10.0):
-    """bbox_transform.py:93-116 (alpha is fixed to 10 in the kernel, as at every upstream call site)."""
-    if float(alpha) != 10.0:
-        raise ValueError("bbox_transform_linear: only alpha=10.0 (the reference's default) is implemented")
+    """bbox_transform.py:93-116: (gt - anchor) / (w | h) * alpha.  alpha = 10 (every upstream call site) is one kernel;
+    any other alpha is the 'simple' encode ((gt - anchor) / size, the same first two operations) times alpha in
+    float32 — the reference's own operation order, so both are bit-exact for float32 inputs."""
     a, dt = _rows(anchors)
     if a.shape[0] == 0:
         return np.zeros((0, 4), dt)
-    return ops.box_encode(to_dev(a[:, :4], np.float32), to_dev(np.asarray(gt_boxes)[:, :4], np.float32), "linear").cpu().numpy().astype(dt, copy=False)
+    ten = float(alpha) == 10.0
+    t = ops.box_encode(to_dev(a[:, :4], np.float32), to_dev(np.asarray(gt_boxes)[:, :4], np.float32), "linear" if ten else "simple").cpu().numpy()
+    if not ten:
+        t = t * np.float32(alpha)
+    return t.astype(dt, copy=False)
 
 
 def bbox_transform_inv_linear(anchors, deltas, alpha=10.0):
-    """bbox_transform.py:118-144."""
-    if float(alpha) != 10.0:
-        raise ValueError("bbox_transform_inv_linear: only alpha=10.0 (the reference's default) is implemented")
-    return _decode(anchors, deltas, "linear")
+    """bbox_transform.py:118-144: deltas * (w | h) / alpha + anchor.  alpha = 10 is one kernel in the reference's
+    operation order; any other alpha runs the 'simple' decode on deltas / alpha — (d / alpha) * w instead of
+    (d * w) / alpha, one rounding apart, inside the 1e-5 relative bar for decoded boxes."""
+    if float(alpha) == 10.0:
+        return _decode(anchors, deltas, "linear")
+    d = np.asarray(deltas)
+    return _decode(anchors, (d.astype(np.float32) / np.float32(alpha)).astype(d.dtype if d.dtype in (np.float32, np.float64) else np.float32), "simple")

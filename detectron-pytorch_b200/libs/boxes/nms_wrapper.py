@@ -4,6 +4,14 @@ import numpy as np
 from ..nms import cpu_nms as _cpu_nms, gpu_nms as _gpu_nms
 
 
+def nms_mode(force_cpu=False):
+    """The comparator nms() applies: gpu_nms's `iou > thresh` in float32 (libs/nms/nms_kernel.cu:83) unless force_cpu,
+    then cpu_nms's `iou >= thresh` in float64 (libs/nms/cpu_nms.pyx:65).  For callers that batch several nms() calls
+    into one segmented device launch."""
+    from ...ops import NMS_GE_F64, NMS_GT_F32
+    return NMS_GE_F64 if force_cpu else NMS_GT_F32
+
+
 def nms(dets, thresh, force_cpu=False):
     """nms_wrapper.py:12-19: [] if empty; force_cpu selects cpu_nms's '>=' comparator, else gpu_nms's '>'."""
     if dets.shape[0] == 0:

@@ -12,7 +12,7 @@ rpn_fg_threshold = 0.6
 rpn_batch_size = 384
 rpn_fg_fraction = 0.25
 rpn_clobber_positives = True
-rpn_sample_strategy = 'simple'                    # only the deterministic strategy is implemented
+rpn_sample_strategy = 'simple'                    # 'simple' | 'traditional' (np.random draws in the reference's order)
 rpn_box_encoding = 'fastrcnn'                     # 'linear', 'fastrcnn'
 anchor_scales = [[2, 2.52, 3.17], [4, 5.04, 6.35], [8, 10.08, 12.70], [16, 20.16, 25.40], [32, 40.32, 50.80]]
 anchor_ratios = [0.5, 1, 2.0]

@@ -12,11 +12,28 @@ from ..configs import config as cfg
 
 
 def _target_cfg():
-    if cfg.rpn_sample_strategy != 'simple':
-        raise NotImplementedError("rpn_sample_strategy=%r: only the deterministic 'simple' strategy is implemented "
-                                  "('traditional' draws np.random.choice samples, libs/layers/anchor.py:95-109)" % (cfg.rpn_sample_strategy,))
+    if cfg.rpn_sample_strategy not in ('simple', 'traditional'):
+        raise ValueError('RPN sample strategy %s has not been implemented yet' % cfg.rpn_sample_strategy)     # anchor.py:124
     return ops.make_target_cfg(cfg.rpn_bg_threshold, cfg.rpn_fg_threshold, cfg.rpn_clobber_positives,
                                cfg.ignored_area_intersection_fraction, cfg.bbweights, cfg.rpn_box_encoding)
+
+
+def sample_traditional_(labels, label_weights):
+    """libs/layers/anchor.py:95-109 on one image's labels, IN PLACE: keep at most rpn_fg_fraction * rpn_batch_size
+    foreground and max(min(rpn_batch_size - fg, 5 fg), 128) background anchors, the rest become -1; label weights
+    stay zero for this strategy (:93, only 'simple' fills them).  The two np.random.choice draws happen in the
+    reference's order and under its conditions, so a seeded run reproduces the reference's sample."""
+    label_weights[...] = 0
+    num_fg = int(cfg.rpn_fg_fraction * cfg.rpn_batch_size)
+    fg_inds = np.where(labels >= 1)[0]
+    if len(fg_inds) > num_fg:
+        labels[np.random.choice(fg_inds, size=(len(fg_inds) - num_fg), replace=False)] = -1
+    else:
+        num_fg = len(fg_inds)
+    num_bg = max(min(cfg.rpn_batch_size - num_fg, num_fg * 5), 128)
+    bg_inds = np.where(labels == 0)[0]
+    if len(bg_inds) > num_bg:
+        labels[np.random.choice(bg_inds, size=(len(bg_inds) - num_bg), replace=False)] = -1
 
 
 def encode(gt_boxes, all_anchors):
@@ -35,6 +52,8 @@ def encode(gt_boxes, all_anchors):
                                           labels.ctypes.data, lw.ctypes.data, bt.ctypes.data, bw.ctypes.data,
                                           torch.cuda.current_device()), "anchor.encode")
     ops._count(4 if G else 2)
+    if cfg.rpn_sample_strategy == 'traditional':
+        sample_traditional_(labels, lw)
     return labels, lw, bt, bw
 
 

@@ -26,7 +26,11 @@ def compute_rpn_targets_in_batch(gt_boxes_list, anchors):
     gt = np.concatenate(gts, 0) if off[-1] else np.zeros((0, 5), np.float32)
     dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
     out = ops.anchor_target(dev(np.asarray(anchors, np.float32).reshape(-1, 4)), dev(gt), dev(off), _anchor._target_cfg())
-    return [t.cpu().numpy() for t in out]
+    res = [t.cpu().numpy() for t in out]
+    if _anchor.cfg.rpn_sample_strategy == 'traditional':         # per image, in batch order: upstream's loop calls encode() image by image
+        for b in range(B):
+            _anchor.sample_traditional_(res[0][b], res[1][b])
+    return res
 
 
 def compute_rpn_targets_in_batch_cuda(gt_boxes_list, anchors, pyramid=None):

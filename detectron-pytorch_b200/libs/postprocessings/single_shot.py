@@ -2,14 +2,14 @@
 post-processing — compute_detection (:13-60: decode + clip every anchor, per class threshold -> NMS -> top
 max_det_num), compute_detection_new (:62-126: class-agnostic NMS on the objectness, then per-class rows),
 nms_advanced (:128-152) and nms_stitch (:154-177) over nms_multianchor, dets_cluster (:401-415, box voting).  Decode and every NMS run on the
-device; the per-image / per-class Python loops are upstream's."""
+device; compute_detection runs all (image, class) pairs as segments of one NMS launch."""
 import numpy as np
 import torch
 
 from ... import ops_post
 from ..._lib import DetboxError
 from ..boxes.cython_nms import nms_multianchor
-from ..boxes.nms_wrapper import nms
+from ..boxes.nms_wrapper import nms, nms_mode
 from ..configs import config as cfg
 from ..layers import anchor
 
@@ -18,7 +18,12 @@ def compute_detection(Outputs, Anchors, ih, iw, num_classes, score_threshold=0.5
                       only_anchor=False, max_det_num=100, batch_size=None):
     """Outputs = (_, rpn_box [n*A,4], rpn_prob [n*A,C]) NumPy; Anchors [A,4].  Returns a list of n
     arrays [m,6] = (x1,y1,x2,y2,score,class) sorted by score.  `batch_size` defaults to
-    rpn_box.shape[0] // Anchors.shape[0] (upstream reads cfg.batch_size, single_shot.py:21)."""
+    rpn_box.shape[0] // Anchors.shape[0] (upstream reads cfg.batch_size, single_shot.py:21).
+
+    Upstream loops over images and classes with one NMS call each (:30-52) — for COCO that is 80 x batch tiny
+    synchronous round trips.  Here every (image, class) pair is one SEGMENT of a single detbox_nms launch (segments
+    never suppress each other, tests: segments == per-pair loop), after one decode + clip per image; the rows each pair
+    keeps, their order inside the pair, the class-major concatenation and the final score sort are upstream's."""
     _, rpn_box, rpn_prob = Outputs
     n = batch_size or rpn_box.shape[0] // Anchors.shape[0]
     assert Anchors.shape[0] * n == rpn_prob.shape[0] == rpn_box.shape[0], 'shape dont match'
@@ -26,22 +31,33 @@ def compute_detection(Outputs, Anchors, ih, iw, num_classes, score_threshold=0.5
     if only_anchor:
         rpn_box_[...] = 0.0
     out_dim = rpn_box.shape[0] // n
+    n_cls = max(num_classes - 1, 0)
+    final_boxes = np.concatenate([anchor.decode(rpn_box_[i * out_dim:(i + 1) * out_dim], rpn_prob[i * out_dim:(i + 1) * out_dim],
+                                                Anchors, ih, iw, num_classes)[0] for i in range(n)], 0) if n else np.zeros((0, 4), np.float32)
+    # candidates of every (image, class j >= 1) pair: rows with prob > threshold (:32), pair-major like upstream's loops
+    fg = rpn_prob[:, 1:num_classes]
+    rows, cls0 = np.nonzero(fg > score_threshold)                 # row-major: ascending row, then class
+    seg = (rows // out_dim) * n_cls + cls0
+    order = np.argsort(seg, kind="stable")                        # group by pair, ascending row inside a pair (np.where order)
+    rows, cls0, seg = rows[order], cls0[order], seg[order]
+    cand = np.hstack((final_boxes[rows, :], fg[rows, cls0][:, np.newaxis])).astype(np.float32, copy=False)
+    n_seg = n * n_cls
+    if cand.shape[0] and n_seg:
+        dev = lambda a, dt: torch.from_numpy(np.ascontiguousarray(a, dtype=dt)).cuda()
+        keep_d, nk_d = ops_post.nms(dev(cand[:, :4], np.float32), dev(cand[:, 4], np.float32), overlap_threshold, nms_mode(),
+                                    seg_ids=dev(seg, np.int32) if n_seg > 1 else None, n_seg=n_seg)
+        nk = nk_d.cpu().numpy()
+        keep = keep_d.cpu().numpy()[:int(nk[-1])]
+        counts = nk[:n_seg] if n_seg > 1 else nk[:1]
+    else:
+        keep, counts = np.zeros((0,), np.int64), np.zeros((max(n_seg, 1),), np.int64)
+    starts = np.concatenate([[0], np.cumsum(counts)])
     Dets = []
     for i in range(n):
-        s, e = i * out_dim, (i + 1) * out_dim
-        probs = rpn_prob[s:e]
-        final_boxes, _, _ = anchor.decode(rpn_box_[s:e], probs, Anchors, ih, iw, num_classes)
-        dets = []
-        for j in range(1, num_classes):
-            inds = np.where(probs[:, j] > score_threshold)[0]
-            cls_dets = np.hstack((final_boxes[inds, :], probs[inds, j][:, np.newaxis])).astype(np.float32, copy=False)
-            keep = nms(cls_dets, overlap_threshold)
-            cls_dets = cls_dets[keep, :]
-            tmp_det = np.zeros([cls_dets.shape[0], 6])
-            tmp_det[:, 0:5] = cls_dets
-            tmp_det[:, 5] = j
-            dets.append(tmp_det)
-        dets = np.vstack(dets) if dets else np.zeros((0, 6))
+        k = keep[starts[i * n_cls]:starts[(i + 1) * n_cls]] if n_cls else keep[:0]     # class-major, score-descending inside a class (:47-50)
+        dets = np.zeros([k.size, 6])
+        dets[:, 0:5] = cand[k]
+        dets[:, 5] = cls0[k] + 1
         order = np.argsort(-dets[:, 4], kind="stable")
         Dets.append(dets[order, :][:max_det_num, :])
     return Dets

@@ -408,3 +408,96 @@ def test_compute_rpn_targets_device_entries(golden):
         assert np.array_equal(bt.cpu().numpy().view(np.uint32), host[2].view(np.uint32))
     finally:
         cfg.rpn_bg_threshold, cfg.rpn_fg_threshold, cfg.rpn_clobber_positives = 0.4, 0.6, True
+
+
+# ---- round 2: the remaining rows of SURVEY 8a / 8f ------------------------------------------------------------------
+def test_layers_roi_encode_decode_match_reference(golden):
+    """libs/layers/roi.py:16-125 (8f-1): encode with np.random seeded like the golden run of the COMPILED reference —
+    labels identical (same draws in the same order), inside weights identical, targets within the float32 bar; the
+    no-GT branch; decode (arg-max class box, clipped)."""
+    import libs.configs.config as cfg
+    from libs.layers import roi
+    g = golden("r2_rows")
+    cfg.fg_threshold, cfg.roi_bg_threshold, cfg.rois_per_image, cfg.roi_fg_fraction = 0.5, 0.3, 128, 0.25
+    for name in ("roi_a", "roi_b", "roi_nogt"):
+        np.random.seed(int(g[name + "_seed"]))
+        lab, bt, bw = roi.encode(g[name + "_gt"].copy(), g[name + "_rois"].copy(), 5)
+        assert lab.dtype == np.float32 and np.array_equal(lab, g[name + "_labels"]), name
+        assert np.array_equal(bw, g[name + "_bbox_inside_weights"]), name
+        assert bt.shape == g[name + "_bbox_targets"].shape
+        np.testing.assert_allclose(bt, g[name + "_bbox_targets"], rtol=1e-5, atol=1e-5)
+    fb, cls, sc = roi.decode(g["dec_deltas"].copy(), g["dec_scores"].copy(), g["dec_rois"].copy(), 512, 768)
+    assert np.array_equal(cls, g["dec_classes"]) and cls.dtype == np.int32 and np.array_equal(sc, g["dec_max"])
+    assert_boxes_close(fb, g["dec_boxes"])
+
+
+@pytest.mark.parametrize("name", ["trad_a", "trad_b", "trad_c"])
+def test_anchor_encode_traditional_sampling(golden, name):
+    """libs/layers/anchor.py:95-109 'traditional': the device assignment + the reference's two np.random.choice draws in
+    its order — labels identical to the compiled reference's seeded run, label weights all zero (only 'simple' fills
+    them), inside weights unaffected by the sampling; also through the batched entry."""
+    import libs.configs.config as cfg
+    from libs.layers import anchor
+    from libs.layers.data_layer import compute_rpn_targets_in_batch
+    g = golden("r2_rows")
+    cfg.rpn_bg_threshold, cfg.rpn_fg_threshold, cfg.rpn_clobber_positives = 0.4, 0.6, True
+    cfg.rpn_sample_strategy, cfg.rpn_batch_size, cfg.rpn_fg_fraction = 'traditional', int(g[name + "_batch_size"]), 0.25
+    try:
+        np.random.seed(int(g[name + "_seed"]))
+        lab, lw, bt, bw = anchor.encode(g[name + "_gt"].copy(), g["trad_anchors"].copy())
+        assert np.array_equal(lab, g[name + "_labels"]) and not lw.any() and np.array_equal(lw, g[name + "_label_weights"])
+        assert np.array_equal(bw, g[name + "_bbox_inside_weights"])
+        assert_boxes_close(bt, g[name + "_bbox_targets"], extra_scale=1.0)
+        np.random.seed(int(g[name + "_seed"]))
+        batch = compute_rpn_targets_in_batch([g[name + "_gt"].copy()], g["trad_anchors"].copy())
+        assert np.array_equal(batch[0][0], g[name + "_labels"]) and not batch[1].any()
+    finally:
+        cfg.rpn_sample_strategy, cfg.rpn_batch_size = 'simple', 384
+
+
+def test_assign_boxes_and_linear_alpha(golden):
+    """libs/layers/assign.py:10-43 (a21) incl. areas whose sqrt / base is an exact power of two, and
+    libs/boxes/bbox_transform.py:93-144 with alpha = 4 (encode bit-exact, decode within the 1e-5 bar) and alpha = 10."""
+    from libs.boxes.bbox_transform import bbox_transform_inv_linear, bbox_transform_linear
+    from libs.layers.assign import assign_boxes
+    g = golden("r2_rows")
+    assert np.array_equal(assign_boxes(g["assign_boxes"].copy()), g["assign_default"])
+    k = assign_boxes(g["assign_boxes"].copy(), 3, 6, 112.0)
+    assert k.dtype == np.int32 and np.array_equal(k, g["assign_k36"])
+    assert assign_boxes(np.zeros((0, 5), np.float32)).shape == (0,)
+    for al in (4.0, 10.0):
+        np.testing.assert_array_equal(bbox_transform_linear(g["lin_anchors"].copy(), g["lin_gt"].copy(), al), g["lin_enc_%g" % al])
+        assert_boxes_close(bbox_transform_inv_linear(g["lin_anchors"].copy(), g["lin_deltas"].copy(), al), g["lin_dec_%g" % al])
+
+
+def test_compute_detection_batched_equals_per_pair_loop():
+    """single_shot.compute_detection (:13-60) runs every (image, class) pair as ONE segmented NMS launch: the result must
+    equal upstream's per-image x per-class loop composed from the oracle's pieces (decode + clip, per-class threshold,
+    '>' NMS, class-major concatenation, score sort, truncation) — 3 images, 5 classes, one class without candidates."""
+    from libs.postprocessings.single_shot import compute_detection
+    rng = np.random.RandomState(12)
+    n, A, C = 3, 700, 5
+    anchors = synth_boxes(rng, A)
+    deltas = rng.normal(0, 0.3, (n * A, 4)).astype(np.float32)
+    scores = rng.rand(n * A, C).astype(np.float32)
+    scores[:, 3] *= 0.4                                                   # class 3 never passes the 0.5 threshold
+    scores[A:2 * A, 1] *= 0.45                                            # image 1 has no class-1 candidate either
+    dets = compute_detection((None, deltas, scores), anchors, 480, 640, C, score_threshold=0.5, overlap_threshold=0.5, max_det_num=60)
+    assert len(dets) == n
+    for i in range(n):
+        want = O.anchor_decode(deltas[i * A:(i + 1) * A], scores[i * A:(i + 1) * A], anchors, 480, 640, C)[0]
+        rows = []
+        for j in range(1, C):
+            inds = np.where(scores[i * A:(i + 1) * A, j] > 0.5)[0]
+            d = np.hstack([want[inds], scores[i * A:(i + 1) * A][inds, j][:, None]]).astype(np.float32)
+            k = O.nms(d[:, :4], d[:, 4], 0.5, O.NMS_GT_F32) if d.shape[0] else np.zeros((0,), np.int64)
+            rows.append(np.hstack([d[k], np.full((len(k), 1), j)]))
+        w = np.vstack(rows); w = w[np.argsort(-w[:, 4], kind="stable")][:60]
+        assert dets[i].shape == w.shape and np.array_equal(dets[i][:, 4:], w[:, 4:]), i
+        assert_boxes_close(dets[i][:, :4], w[:, :4])
+
+
+def synth_boxes(rng, n):
+    h = np.exp(rng.uniform(np.log(16), np.log(200), n)); w = h / rng.uniform(0.5, 2.5, n)
+    cx, cy = rng.uniform(0, 640, n), rng.uniform(0, 480, n)
+    return np.stack([cx - w / 2, cy - h / 2, cx + w / 2, cy + h / 2], 1).astype(np.float32)
