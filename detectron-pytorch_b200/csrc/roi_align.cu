@@ -620,6 +620,129 @@ roi_bwd_nchw_staged_kernel(const RoiArgs a)
     }
 }
 
+// ---- NCHW backward as a GATHER ------------------------------------------------------------------------------------------
+// The direct NCHW backward issues 4 scalar red.global.add per output element (205 M at BASELINE configs[2]) and is bound by
+// the L2's atomic rate (ncu: 27 % issue-active, profiles/r02a_ncu_roi.txt); summing in a shared-memory window first
+// (roi_bwd_nchw_staged_kernel) lost to its shared-memory atomics.  Here the two tap tables are INVERTED once per RoI: for
+// every feature row a tap touches, the (bin row, weight) pairs that land on it; for every 16-byte piece of a feature row
+// a tap touches, the (pixel in piece, bin column, weight) triples.  Then, per channel, one thread owns one (touched row,
+// touched piece): it sums its few terms in registers from the RoI's grad_out values (staged per channel chunk with
+// coalesced loads) and emits ONE red.global.add.v4.f32 — the block-aggregated atomic north_star (4) asks for; no
+// shared-memory atomics, no window buffer, work bounded by touched rows x touched pieces whatever the RoI's size.
+// Every term is the reference's own product (crop_and_resize.c:258-264: (1-wx) * ((1-wy) * g); roi_align_kernel.cu:147-150
+// in double), only the order of the float32 additions differs (tests: the summation bound of tests/test_gpu_roi.py).
+constexpr int RG_THREADS = 256;
+constexpr int RG_MAXE = 2 * RA_MAXP;        // a bin row / column contributes to two feature rows / columns
+constexpr int RG_GFLOATS = 8192;            // staged grad_out floats per chunk (32 KB)
+
+// One axis inverted.  Entries sorted by feature pixel (stable: bins ascending); a GROUP is a feature row (shift 0) or a
+// 16-byte piece of a row (shift 2); sub[g * 4 + p] .. sub[g * 4 + p + 1] are the entries of pixel p of group g, so the
+// consumer's accumulator index is a compile-time constant.  w / wd: the weight this entry applies, resolved once —
+// (hi ? w : 1 - w) in float32 (crop_and_resize.c:258-264) or in double (roi_align_kernel.cu:147-150).
+struct InvAxis {
+    short bin[RG_MAXE]; float w[RG_MAXE]; double wd[RG_MAXE];
+    short key[RG_MAXE]; short sub[RG_MAXE * 4 + 1];
+    short pix[RG_MAXE];                     // builder's scratch: the feature pixel of every entry
+    int n_groups;
+};
+
+// Serial (one thread): at most 2 * 33 entries.
+template <bool GRID>
+__device__ __forceinline__ void invert_axis(const Tap *t, const int n_bins, const int shift, InvAxis &ax)
+{
+    short *pix = ax.pix;
+    int n = 0;
+    for (int b = 0; b < n_bins; ++b) {
+        if (!t[b].valid) continue;
+        for (int hi = 0; hi < 2; ++hi) {
+            const short px = (short)(hi ? t[b].i1 : t[b].i0);
+            const float wf = hi ? t[b].w : 1 - t[b].w;
+            const double wdd = hi ? (double)t[b].w : 1. - (double)t[b].w;
+            int k = n++;
+            while (k > 0 && pix[k - 1] > px) { pix[k] = pix[k - 1]; ax.bin[k] = ax.bin[k - 1]; ax.w[k] = ax.w[k - 1]; if (GRID) ax.wd[k] = ax.wd[k - 1]; --k; }
+            pix[k] = px; ax.bin[k] = (short)b; ax.w[k] = wf; if (GRID) ax.wd[k] = wdd;
+        }
+    }
+    int g = 0, k = 0;
+    while (k < n) {
+        const int key = pix[k] >> shift;
+        ax.key[g] = (short)key;
+        for (int p = 0; p < 4; ++p) {
+            ax.sub[g * 4 + p] = (short)k;
+            while (k < n && (pix[k] >> shift) == key && pix[k] - (key << shift) == p) ++k;
+        }
+        ++g;
+    }
+    ax.sub[g * 4] = (short)n;
+    ax.n_groups = g;
+}
+
+template <bool GRID>
+__global__ void __launch_bounds__(RG_THREADS, 4)
+roi_bwd_nchw_gather_kernel(const RoiArgs a)
+{
+    __shared__ Tap ty[RA_MAXP], tx[RA_MAXP];
+    __shared__ InvAxis s_r, s_c;
+    extern __shared__ __align__(16) float s_g[];
+    int gh, gw;
+    const Prologue s = roi_prologue(a, ty, tx, gh, gw);
+    if (!s.ok) return;
+    const detbox_roi_cfg &c = a.cfg;
+    const int PH = c.pooled_h, PW = c.pooled_w, C = c.channels;
+    const int Ctot = c.all_levels ? C * c.n_levels : C;
+    const int coff = c.all_levels ? C * blockIdx.y : 0;
+    const int bins = PH * PW;
+    const long r = blockIdx.x;
+    const int tid = threadIdx.x;
+    const size_t plane = (size_t)s.H * s.W;
+    float *g0 = c.grad_feat[s.level] + (size_t)s.b * C * plane;
+    const float *go = a.grad_out + ((size_t)r * Ctot + coff) * bins;
+    // 16-byte pieces need every row of every plane 16-byte aligned; otherwise pieces are single pixels (scalar atomics)
+    const bool vec = ((s.W & 3) == 0) && ((plane & 3) == 0) && (((size_t)g0 & 15) == 0);
+    if (tid == 0) invert_axis<GRID>(ty, gh, 0, s_r);
+    if (tid == 32) invert_axis<GRID>(tx, gw, vec ? 2 : 0, s_c);
+    __syncthreads();
+    const int nr = s_r.n_groups, nq = s_c.n_groups;
+    if (nr == 0 || nq == 0) return;                             // no sample inside the map: no gradient
+    const unsigned per = (unsigned)(nr * nq);                   // (row, piece) items per channel
+    const unsigned m_per = 0xffffffffu / per, m_nq = 0xffffffffu / (unsigned)nq;     // floor(2^32 / d) up to one: fixed below
+    const int CH = max(1, min(C, RG_GFLOATS / bins));
+    for (int c0 = 0; c0 < C; c0 += CH) {
+        const int n = min(CH, C - c0);
+        if (c0) __syncthreads();                                // the previous chunk has been consumed
+        for (int i = tid; i < n * bins; i += RG_THREADS) s_g[i] = __ldcs(go + (size_t)c0 * bins + i);
+        __syncthreads();
+        for (unsigned i = tid; i < (unsigned)n * per; i += RG_THREADS) {
+            unsigned ch = __umulhi(i, m_per), k = i - ch * per;
+            if (k >= per) { ++ch; k -= per; }
+            unsigned ri = __umulhi(k, m_nq), qi = k - ri * (unsigned)nq;
+            if (qi >= (unsigned)nq) { ++ri; qi -= (unsigned)nq; }
+            const float *g = s_g + ch * bins;
+            float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+            const int e0 = s_r.sub[ri * 4], e1 = s_r.sub[ri * 4 + 4];          // a row group holds one pixel row: all its entries
+            const short *cs = s_c.sub + qi * 4;
+            for (int er = e0; er < e1; ++er) {
+                const float *grow = g + s_r.bin[er] * PW;
+                const float rw = s_r.w[er];
+                const double rwd = GRID ? s_r.wd[er] : 0.0;
+#pragma unroll
+                for (int p = 0; p < 4; ++p) {
+                    for (int ec = cs[p]; ec < cs[p + 1]; ++ec) {
+                        const float gv = grow[s_c.bin[ec]];
+                        if (GRID) acc[p] += (float)((double)gv * rwd * s_c.wd[ec]);   // roi_align_kernel.cu:147-150
+                        else acc[p] += s_c.w[ec] * (rw * gv);                          // crop_and_resize.c:258-264: wx-factor * (wy-factor * g)
+                    }
+                }
+            }
+            float *dst = g0 + (size_t)(c0 + ch) * plane + (size_t)s_r.key[ri] * s.W;
+            if (vec) {
+                if (acc[0] != 0.0f || acc[1] != 0.0f || acc[2] != 0.0f || acc[3] != 0.0f)
+                    red_add4(dst + 4 * (int)s_c.key[qi], make_float4(acc[0], acc[1], acc[2], acc[3]));
+            } else if (acc[0] != 0.0f) atomicAdd(dst + (int)s_c.key[qi], acc[0]);
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256)
 assign_levels_kernel(const float *__restrict__ boxes, long R, detbox_roi_cfg c, int32_t *__restrict__ levels)
 {
@@ -718,6 +841,16 @@ extern "C" int detbox_roi_align_backward(const detbox_roi_cfg *cfg, const float 
     // Measured on B200 at BASELINE configs[2] (profiles/r02_roi_staged_vs_generic.txt): the staged backward scatters in
     // 0.94 ms against 0.73 ms for the direct red.global.add path (shared-memory float atomics on taps that neighbouring
     // bins share, plus a zero and a flush pass per chunk), so it is opt-in; the staged FORWARD is the default (0.24 vs 0.37 ms).
+    static const bool bwd_direct = getenv("DETBOX_ROI_BWD_DIRECT") != nullptr;
+    if (cfg->layout == DETBOX_LAYOUT_NCHW && cfg->out_layout == DETBOX_LAYOUT_NCHW && cfg->pool == DETBOX_POOL_NONE && !bwd_direct &&
+        getenv("DETBOX_ROI_BWD_STAGED") == nullptr && (long)cfg->pooled_h * cfg->pooled_w <= RG_GFLOATS) {
+        DETBOX_TRACE_BEGIN(DETBOX_K_ROI_BWD, st);
+        if (cfg->mode == DETBOX_ROI_GRID_POINT) roi_bwd_nchw_gather_kernel<true><<<grid, RG_THREADS, RG_GFLOATS * sizeof(float), st>>>(a);
+        else roi_bwd_nchw_gather_kernel<false><<<grid, RG_THREADS, RG_GFLOATS * sizeof(float), st>>>(a);
+        DETBOX_TRACE_END(DETBOX_K_ROI_BWD, st);
+        DETBOX_LAUNCH_CHECK();
+        return DETBOX_OK;
+    }
     static const bool bwd_staged = getenv("DETBOX_ROI_BWD_STAGED") != nullptr;
     if (cfg->layout == DETBOX_LAYOUT_NCHW && cfg->out_layout == DETBOX_LAYOUT_NCHW && cfg->pool == DETBOX_POOL_NONE && bwd_staged) {
         DETBOX_TRACE_BEGIN(DETBOX_K_ROI_BWD, st);
