@@ -17,6 +17,7 @@
 //   5. gather      deltas / probs / anchors of the winners, decode (box_math.cuh), image ids.
 //
 // Segments are equal-sized (A anchors per image), so a segment is identified by blockIdx.y.
+#include <cstdlib>
 #include "box_math.cuh"
 #include "sort.cuh"
 
@@ -316,8 +317,12 @@ partition_kernel(const uint32_t *__restrict__ keys, long seg_len, const SegState
         // half, candidates in the high half) turns the counts into positions, and ONE 64-bit atomic per warp and trip
         // reserves both ranges — the pair of 32-bit counters is one aligned word.  (A ballot + atomic per key made
         // every trip wait for up to 16 round trips to L2.)  The next trip's loads are issued before that wait.
-        const long n4 = seg_len >> 2;
-        const uint4 *k4 = reinterpret_cast<const uint4 *>(k);
+        // Any segment length / start: the <= 3 keys before the first 16-byte boundary and the <= 3 after the last whole
+        // vector go through emit() in one warp at the end (COCO-R's 132,450 anchors per image are not a multiple of 4: the
+        // scalar fallback — a ballot and an L2 round trip per key — cost 28 us there against 6 us for this path).
+        const int head = (int)min((long)((4 - (((size_t)k >> 2) & 3)) & 3), seg_len);
+        const long n4 = (seg_len - head) >> 2;
+        const uint4 *k4 = reinterpret_cast<const uint4 *>(k + head);
         unsigned long long *cnt64 = reinterpret_cast<unsigned long long *>(win_cnt);
         const long stride = (long)gridDim.x * TK_THREADS * 2;
         long q0 = (long)blockIdx.x * TK_THREADS * 2;
@@ -355,7 +360,7 @@ partition_kernel(const uint32_t *__restrict__ keys, long seg_len, const SegState
                         const long q = q0 + (j >> 2) * TK_THREADS + tid;
                         const uint32_t bin = kk[j] >> 21;
                         if (q < n4 && bin <= b0) {
-                            const uint32_t idx = (uint32_t)(seg0 + (q << 2) + (j & 3));
+                            const uint32_t idx = (uint32_t)(seg0 + head + (q << 2) + (j & 3));
                             if (bin < b0) { ckeys[wpos] = kk[j]; cvals[wpos] = idx; ++wpos; }
                             else { cand_keys[cpos] = kk[j]; cand_idx[cpos] = idx; ++cpos; }
                         }
@@ -363,6 +368,13 @@ partition_kernel(const uint32_t *__restrict__ keys, long seg_len, const SegState
                 }
             }
             v[0] = nv[0]; v[1] = nv[1];
+        }
+        if (blockIdx.x == 0 && tid < 32) {               // head and tail keys, warp-collective
+            const long tail0 = head + (n4 << 2);
+            const int n_tail = (int)(seg_len - tail0);
+            const long r = lane < head ? lane : tail0 + (lane - head);
+            const bool ok = lane < head + n_tail;
+            emit(ok ? k[r] : 0xffffffffu, r, ok);
         }
     } else {
         for (long r0 = (long)blockIdx.x * TK_THREADS; r0 < seg_len; r0 += (long)gridDim.x * TK_THREADS) {
@@ -453,12 +465,22 @@ cand_select_kernel(const uint32_t *__restrict__ cand_keys, const uint32_t *__res
 // ---- 4'. sort of small segments (K <= 2048 winners each): one block per segment, bitonic network in
 // shared memory over the 64-bit composites (key << 32 | flat index) — unique, so the order is the
 // stable one (ties: lower flat index first).  Segments already sit image-major in ckeys / cvals.
-constexpr int SEG_SORT_MAX = 2048;
-
-__global__ void __launch_bounds__(SEG_SORT_MAX / 2)
+// Up to 16,384 (key, index) composites per segment = 128 KB of the SM's 227 KB shared memory, so the reference's own
+// global budget (900 * batch = 14,400 at COCO-R batch 16, libs/nets/model.py:311-312) and MaskRCNN's 6,000 per image
+// (maskrcnn.py:97) take the partition + candidate-select + ONE-block sort route instead of a three-pass radix select and
+// a 12-launch global radix sort (round 2: COCO-R global_14400 top-k + decode 0.270 -> see profiles/r02_coco_path.txt).
+constexpr int SEG_SORT_MAX = 16384;                 // capacity of the one-block sort
+constexpr int SEG_SORT_THREADS = 1024;
+// up to how many winners per segment the one-block route is TAKEN (a bitonic network costs N log^2 N on one SM; above the
+// crossover the three-pass radix select + global radix sort wins).  Measured on B200: profiles/r02_coco_path.txt.
+static int seg_sort_limit() {
+    static const int v = []() { const char *e = getenv("DETBOX_SEG_SORT_LIMIT"); int x = e ? atoi(e) : 4096; return x < 2 ? 2 : (x > SEG_SORT_MAX ? SEG_SORT_MAX : x); }();
+    return v;
+}
+__global__ void __launch_bounds__(SEG_SORT_THREADS)
 seg_sort_kernel(uint32_t *__restrict__ ckeys, uint32_t *__restrict__ cvals, int K, int N /*pow2 >= K*/)
 {
-    __shared__ unsigned long long v[SEG_SORT_MAX];
+    extern __shared__ unsigned long long v[];
     const int tid = threadIdx.x;
     uint32_t *k = ckeys + (size_t)blockIdx.x * K, *x = cvals + (size_t)blockIdx.x * K;
     for (int i = tid; i < N; i += blockDim.x)
@@ -524,7 +546,7 @@ TopkPlan make_plan(int batch, long A, long top_n, int per_image) {
     p.blk_b = align_up((size_t)p.n_seg * p.nblk_c * 4);
     p.cand_b = align_up((size_t)(p.n_cand > 0 ? p.n_cand : 1) * 4);
     p.counts_b = sort_counts_bytes(p.n_cand > 0 ? p.n_cand : 1);
-    p.part_b = p.K <= SEG_SORT_MAX ? align_up((size_t)batch * A * 4) : 0;       // candidate lists of the partition path
+    p.part_b = p.K <= seg_sort_limit() ? align_up((size_t)batch * A * 4) : 0;       // candidate lists of the partition path
     p.cnt_b = align_up((size_t)p.n_seg * 2 * 4);
     p.total = p.keys_b + p.hist_b + p.cnt_b + p.state_b + 2 * p.blk_b + 4 * p.cand_b + p.counts_b + 2 * p.part_b;
     return p;
@@ -593,12 +615,13 @@ extern "C" int detbox_topk_decode(const float *prob, int C, const float *deltas,
     uint32_t *h0 = hist, *h1 = hist + (size_t)p.n_seg * NB0, *h2 = hist + (size_t)2 * p.n_seg * NB0;
     select_kernel<<<p.n_seg, 1024, 0, st>>>(h0, 2048, 11, state);
     DETBOX_LAUNCH_CHECK();
-    if (p.K <= SEG_SORT_MAX) {
+    if (p.K <= seg_sort_limit()) {
         // 3'. one pass: outright winners + candidates of the threshold bin; then select among the candidates
         long px = (p.seg_len + TK_THREADS * PT_ITEMS - 1) / (TK_THREADS * PT_ITEMS);
         { long capx = (long)kNumSMs * 8 / p.n_seg; if (capx < 1) capx = 1; if (px > capx) px = capx; }
         const dim3 pgrid((unsigned)px, (unsigned)p.n_seg);
-        if ((p.seg_len & 3) == 0) partition_kernel<true><<<pgrid, TK_THREADS, 0, st>>>(keys, p.seg_len, state, p.K, cka, cva, cand_keys, cand_idx, part_cnt);
+        static const bool scalar_part = getenv("DETBOX_TOPK_SCALAR_PARTITION") != nullptr;    // the old fallback, for A/B timing only
+        if (!scalar_part) partition_kernel<true><<<pgrid, TK_THREADS, 0, st>>>(keys, p.seg_len, state, p.K, cka, cva, cand_keys, cand_idx, part_cnt);
         else partition_kernel<false><<<pgrid, TK_THREADS, 0, st>>>(keys, p.seg_len, state, p.K, cka, cva, cand_keys, cand_idx, part_cnt);
         DETBOX_LAUNCH_CHECK();
         cand_select_kernel<<<p.n_seg, 1024, 0, st>>>(cand_keys, cand_idx, p.seg_len, state, part_cnt, p.K, cka, cva);
@@ -625,16 +648,26 @@ extern "C" int detbox_topk_decode(const float *prob, int C, const float *deltas,
     //    mode) by image id with the global radix sort
     int rc = DETBOX_OK;
     uint32_t *fk = cka, *fv = cva;
-    if (p.K <= SEG_SORT_MAX) {
+    if (p.K <= seg_sort_limit()) {
         int N = 2; while (N < p.K) N <<= 1;
-        const int threads = N / 2 < 32 ? 32 : N / 2;
-        seg_sort_kernel<<<p.n_seg, threads, 0, st>>>(cka, cva, (int)p.K, N);
+        const int threads = N / 2 < 32 ? 32 : (N / 2 > SEG_SORT_THREADS ? SEG_SORT_THREADS : N / 2);
+        const size_t smem = (size_t)N * sizeof(unsigned long long);
+        if (smem > 48 * 1024) {                       // opt in to the large carve-out once per device
+            static thread_local int ready_dev = -1;
+            int dev = 0;
+            DETBOX_CUDA_TRY(cudaGetDevice(&dev));
+            if (ready_dev != dev) {
+                DETBOX_CUDA_TRY(cudaFuncSetAttribute(seg_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SEG_SORT_MAX * (int)sizeof(unsigned long long)));
+                ready_dev = dev;
+            }
+        }
+        seg_sort_kernel<<<p.n_seg, threads, smem, st>>>(cka, cva, (int)p.K, N);
         DETBOX_LAUNCH_CHECK();
     } else {
         rc = radix_sort_pairs(cka, cva, ckb, cvb, p.n_cand, counts, st);
         if (rc != DETBOX_OK) return rc;
     }
-    if (p.K > SEG_SORT_MAX && p.n_seg > 1) {
+    if (p.K > seg_sort_limit() && p.n_seg > 1) {
         uint32_t *ki = cka, *vi = cva, *ko = ckb, *vo = cvb;
         for (int shift = 0; (p.n_seg - 1) >> shift; shift += 8) {
             DigitSrc d{1, shift, (uint32_t)A, nullptr};

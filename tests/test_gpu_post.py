@@ -77,6 +77,11 @@ def make_head_outputs(rng, B, A, C, activation, ties=False):
     (2, 20000, 2, "softmax", 6000, True, False),      # MaskRCNN test-time budget per image (maskrcnn.py:97)
     (16, 132450, 80, "sigmoid", 14400, False, False), # BASELINE configs[3]: COCO-R batch 16, global 900*B
     (16, 132450, 80, "sigmoid", 1000, True, False),   # ... and 1000 per image
+    (5, 2501, 2, "softmax", 300, True, True),         # segment starts at every alignment mod 4 (vectorised partition: head / body / tail)
+    (7, 3, 2, "softmax", 2, True, True),              # segments shorter than one vector
+    (3, 4099, 80, "sigmoid", 500, True, False),       # 4099 % 4 == 3
+    (2, 40000, 2, "softmax", 20000, False, True),     # K > 16384: three-pass radix select + global radix sort (the old K > 2048 route)
+    (2, 30000, 2, "softmax", 16384, True, False),     # exactly the one-block sort's capacity, per image
 ])
 def test_topk_decode(B, A, C, act, top_n, per_image, ties):
     rng = np.random.RandomState(B * 7 + A)
