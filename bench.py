@@ -586,6 +586,18 @@ def coco_post_bench(torch, detbox, hbm_peak):
         t_topk = median_ms(torch, lambda: detbox.topk_decode(deltas, prob, anc, top_n, "sigmoid", "fastrcnn", per_image,
                                                              want=("img_ids", "scores")))
         t = median_ms(torch, step)
+        # the score read on its own: events around objectness_kernel (C = 80 instantiation) inside one top-k call
+        ea, eb = event_pairs(torch, 1)[0]
+        ea.record(); eb.record()
+        detbox.lib().detbox_trace_kernel(5, ea.cuda_event, eb.cuda_event)
+        detbox.topk_decode(deltas, prob, anc, top_n, "sigmoid", "fastrcnn", per_image, want=("img_ids", "scores"))
+        torch.cuda.synchronize()
+        detbox.lib().detbox_trace_kernel(0, None, None)
+        t_obj = ea.elapsed_time(eb)
+        out["objectness_kernel"] = {"ms": round(t_obj, 4), "gbs": round(prob.numel() * 4 / t_obj / 1e6, 1),
+                                    "frac_hbm": round(prob.numel() * 4 / t_obj / 1e6 / hbm_peak, 3),
+                                    "note": "the 678 MB score read itself; score_read_frac_hbm below divides the same bytes by the whole top-k + decode time "
+                                            "(select, partition, candidate select, sort, gather: latency-bound tail, profiles/r02_coco_path.txt)"}
         out[name] = {"ms": round(t, 4), "topk_decode_ms": round(t_topk, 4), "images_per_s": round(B / (t / 1e3), 1),
                      "score_read_gbs": round(prob.numel() * 4 / t_topk / 1e6, 1),
                      "score_read_frac_hbm": round(prob.numel() * 4 / t_topk / 1e6 / hbm_peak, 3)}
@@ -848,8 +860,11 @@ def main():
         e2e_more["e2e_reference_format_mapped_rows"] = e2e_leg(lambda: sess.run_host(gts, h_prob, h_box, format="reference"),
                                                                "the four float32 arrays copied back; rpn_box rows gathered from pinned host memory")
         ncore = host_cores()
-        e2e_more["e2e_compact_expanded"] = e2e_leg(lambda: sess.expand(sess.run_host(gts, h_prob, h_box, format="compact"), n_threads=ncore),
-                                                   "compact over the link, then detbox_expand_targets_host (%d threads) materialises the reference's four arrays on the host inside the timed region" % ncore)
+        e2e_more["e2e_reference_arrays"] = e2e_leg(lambda: sess.run_host(gts, h_prob, h_box, format="reference", wire="compact"),
+                                                   "the reference's four float32 arrays delivered on the HOST: every chunk crosses the link in the compact format and "
+                                                   "detbox_expand_targets_host materialises them on worker threads while later chunks are in flight (inside the timed region)")
+        e2e_more["e2e_compact_expanded_serial"] = e2e_leg(lambda: sess.expand(sess.run_host(gts, h_prob, h_box, format="compact"), n_threads=ncore),
+                                                          "the same result with the expansion run AFTER the transfers (%d threads)" % ncore)
         # the same call with the anchor targets left in HBM for a GPU-side loss: host head
         # outputs in, detections out.  Reported beside e2e, not instead of it.
         e2e_more["e2e_targets_resident"] = e2e_leg(lambda: sess.run_host(gts, h_prob, h_box, targets="device"),

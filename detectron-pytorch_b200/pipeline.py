@@ -151,7 +151,7 @@ class BoxOpsSession:
         return off
 
     def run_host(self, gt_boxes_list, rpn_prob_host, rpn_box_host, chunk=8, targets="host", format="reference",
-                 box_rows="auto"):
+                 box_rows="auto", wire="same", expand_threads=None):
         """gt_boxes_list: B NumPy arrays [G_i,5]; rpn_prob_host [B*A,C] / rpn_box_host [B*A,4]:
         float32 host tensors (pinned for asynchronous copies).  Returns pinned host tensors; the
         call returns after all streams have drained, so they are ready to read.
@@ -169,6 +169,12 @@ class BoxOpsSession:
         ((label + 1) | flag << 7), 'bbox_targets' [B,A,4] and 'counts' int32 [B,2] — 17 bytes per anchor, the
         same information; `expand(result)` rebuilds the reference's arrays on the host, bit for bit.
 
+        wire="compact" (with format="reference", targets="host"): the caller still receives the reference's four float32
+        arrays, but every chunk crosses the link in the compact format and is expanded by detbox_expand_targets_host on
+        worker threads as soon as its device->host copy has landed — the expansion (400 MB of host writes per 64 CP-R
+        images) hides behind the transfers of the following chunks instead of running after them.  Bit-identical to
+        wire="same".
+
         box_rows: "copy" stages all of rpn_box on the device (16 bytes x A per image); "mapped" lets the top-k
         gather read the top_n selected rows straight out of the pinned host buffer (model.py:314-318 indexes
         rpn_box[order] the same way); "auto" = mapped when rpn_box_host is pinned."""
@@ -180,7 +186,11 @@ class BoxOpsSession:
             box_rows = "mapped" if rpn_box_host.is_pinned() else "copy"
         if box_rows not in ("copy", "mapped"):
             raise DetboxError("box_rows must be 'auto', 'copy' or 'mapped'")
-        on_dev, compact = targets == "device", format == "compact"
+        if wire not in ("same", "compact"):
+            raise DetboxError("wire must be 'same' or 'compact'")
+        on_dev = targets == "device"
+        expand_here = wire == "compact" and format == "reference" and not on_dev
+        compact = format == "compact" or expand_here
         B, A, C = self.B, self.A, self.C
         dv = lambda shape, dt=torch.float32: torch.empty(shape, dtype=dt, device=self.dev)
         if getattr(self, "d_bt", None) is None:                   # device-side result buffers, reused by every call
@@ -191,6 +201,17 @@ class BoxOpsSession:
             self.h_counts = torch.empty((B, 2), dtype=torch.int32, pin_memory=True)
         if not compact and getattr(self, "d_labels", None) is None:
             self.d_labels, self.d_lw, self.d_bw = dv((B, A)), dv((B, A)), dv((B, A, 4))
+        futures = []
+        if expand_here:
+            if getattr(self, "_pool", None) is None:
+                from concurrent.futures import ThreadPoolExecutor
+                self._pool = ThreadPoolExecutor(max_workers=2)       # two chunks' expansions in flight; each call threads itself
+            bbw = [float(self.tcfg.bbweights[i]) for i in range(4)]
+            nthr = int(expand_threads or max(1, min(16, len(os.sched_getaffinity(0))) // 2))
+
+            def expand_chunk(ev, sl):
+                ev.synchronize()                                 # this chunk's device->host copies have landed (releases the GIL)
+                ops.expand_targets(self.h_packed[sl], self.h_counts[sl], bbw, nthr, out=(self.h_labels[sl], self.h_lw[sl], self.h_bw[sl]))
         G = self.stage_gt(gt_boxes_list)
         s_in, s_k, s_out = self._streams
         cur = torch.cuda.current_stream(self.dev)
@@ -264,11 +285,17 @@ class BoxOpsSession:
                     h.copy_(d, non_blocking=True)
                     d2h += h.numel() * h.element_size()
                 mark("d2h%d" % c0, s_out)
+                if expand_here:
+                    ev_out = torch.cuda.Event()
+                    ev_out.record(s_out)
+                    futures.append(self._pool.submit(expand_chunk, ev_out, sl))
             hold.append((sel, keep, n_keep))                          # keep device buffers alive until the drain
         if tl is not None:
             self.issue_ms = 1e3 * (_time.perf_counter() - _t0)
         for s in self._streams:
             s.synchronize()
+        for f in futures:
+            f.result()                                           # the last chunks' expansions; re-raises a worker's error
         # chunk-local indices -> batch-global (host side, a few thousand integers)
         nk_all = np.zeros(B + 1, np.int32)
         keep_np, img_np, nk_np = self.h_keep.numpy(), self.h_img.numpy(), h_nk.numpy()
@@ -285,7 +312,10 @@ class BoxOpsSession:
         self.h2d_bytes, self.d2h_bytes = h2d, d2h
         res = {"boxes": self.h_boxes, "scores": self.h_scores, "img_ids": self.h_img, "keep": self._keep_out,
                "n_keep": self.h_nkeep, "format": format}
-        if compact:
+        if expand_here:
+            res.update(labels=self.h_labels, label_weights=self.h_lw, bbox_targets=self.h_bt, bbox_inside_weights=self.h_bw,
+                       counts=self.h_counts)
+        elif compact:
             tg = (self.d_packed, self.d_bt, self.d_counts) if on_dev else (self.h_packed, self.h_bt, self.h_counts)
             res.update(packed=tg[0], bbox_targets=tg[1], counts=tg[2])
         else:

@@ -141,3 +141,26 @@ def test_run_host_compact_format_expands_to_reference(box_rows):
     for b in range(B):
         lab = ref["labels"][b].numpy()
         assert cnt[b, 0] == (lab >= 1).sum() and cnt[b, 1] == (lab == 0).sum()
+
+
+def test_run_host_reference_arrays_over_compact_wire():
+    """format="reference", wire="compact": the caller gets the reference's four arrays; each chunk crosses the link in
+    the compact format and is expanded on worker threads while later chunks are in flight.  Bit-identical to wire="same",
+    on two consecutive calls (the second over the first's leftovers), with a third of the bytes device->host."""
+    pipeline = import_module("detectron-pytorch_b200.pipeline")
+    B, ih, iw, top_n = 7, 256, 512, 250
+    cfg, strides, scales, anc, gts, deltas, prob = make_case(B, ih, iw, 31)
+    sess = pipeline.BoxOpsSession(strides, ih, iw, scales, cfg.anchor_ratios, cfg.anchor_base, B, 2, top_n=top_n,
+                                  nms_thresh=0.5, bg=cfg.rpn_bg_threshold, fg=cfg.rpn_fg_threshold, max_gt_total=16 * B)
+    h_prob, h_box = torch.from_numpy(prob).pin_memory(), torch.from_numpy(deltas).pin_memory()
+    ref = {k: v.clone() for k, v in sess.run_host(gts, h_prob, h_box, chunk=2).items() if torch.is_tensor(v)}
+    d2h_ref = sess.d2h_bytes
+    for h in (sess.h_labels, sess.h_lw, sess.h_bw, sess.h_bt):
+        h.fill_(-123.0)                                        # stale contents must all be overwritten
+    for rep in range(2):
+        out = sess.run_host(gts, h_prob, h_box, chunk=2, wire="compact")
+        assert out["format"] == "reference" and sess.d2h_bytes < 0.45 * d2h_ref
+        for k in ("labels", "label_weights", "bbox_targets", "bbox_inside_weights", "boxes", "scores", "img_ids", "n_keep"):
+            assert torch.equal(out[k], ref[k]), (rep, k)
+        nk = int(out["n_keep"][B])
+        assert torch.equal(out["keep"][:nk], ref["keep"][:nk])
