@@ -150,7 +150,7 @@ class BoxOpsSession:
             self.h_off[i + 1] = off
         return off
 
-    def run_host(self, gt_boxes_list, rpn_prob_host, rpn_box_host, chunk=8, targets="host", format="reference",
+    def run_host(self, gt_boxes_list, rpn_prob_host, rpn_box_host, chunk=None, targets="host", format="reference",
                  box_rows="auto", wire="same", expand_threads=None):
         """gt_boxes_list: B NumPy arrays [G_i,5]; rpn_prob_host [B*A,C] / rpn_box_host [B*A,4]:
         float32 host tensors (pinned for asynchronous copies).  Returns pinned host tensors; the
@@ -158,7 +158,9 @@ class BoxOpsSession:
 
         The batch is cut into chunks of `chunk` images that flow through three streams — copy-in,
         kernels, copy-out — so the PCIe link runs in both directions while the kernels of the
-        neighbouring chunk execute (images are independent: no result changes).
+        neighbouring chunk execute (images are independent: no result changes).  chunk=None picks the size measured
+        best for the mode on B200 (profiles/chunk_probe_r02.py): 4 when the expansion is overlapped (more of it hides), 16
+        for the compact format and for targets="device", 8 for the four float32 arrays over the link.
 
         targets="device": the four anchor-target tensors stay in HBM ([B,A] / [B,A,4] CUDA tensors in the result)
         for a loss that runs on the GPU — the training integration of INTEGRATION.md §2, where the reference
@@ -191,6 +193,9 @@ class BoxOpsSession:
         on_dev = targets == "device"
         expand_here = wire == "compact" and format == "reference" and not on_dev
         compact = format == "compact" or expand_here
+        if chunk is None:
+            chunk = 4 if expand_here else (16 if (compact or on_dev) else 8)
+        chunk = max(1, min(int(chunk), self.B))
         B, A, C = self.B, self.A, self.C
         dv = lambda shape, dt=torch.float32: torch.empty(shape, dtype=dt, device=self.dev)
         if getattr(self, "d_bt", None) is None:                   # device-side result buffers, reused by every call

@@ -37,7 +37,7 @@ for kid, key in (("3", 'anchor_target_kernel'), ("2", 'colmax_kernel')):
 json.dump(d, open(p, 'w'), indent=1)
 PY
 { echo "# ncu --set full: RoIAlign kernels, BASELINE configs[2] (profiles/roi_ncu_probe.py), the second (warm) launch of every flavour;"
-  echo "# one column per kernel, identified by the 'Kernel Name' row: staged NCHW forward | direct NCHW backward roi_bwd_kernel<0,0,0> | channels-last forward | channels-last backward"
+  echo "# one column per kernel, identified by the 'Kernel Name' row (template arguments included): NCHW forward | NCHW backward | channels-last forward | channels-last backward"
   python ../../profiles/ncu_summary.py roi_pick.csv; } > ../../profiles/${T}_ncu_roi.txt
 K=$(grep -o "anchor_target_kernelILi[0-9]ELb[01]ELi[0-9]ELb0ELb0" ../../detectron-pytorch_b200/build/anchor_target.ptxas.log | head -1)
 { echo "# ncu --set full, anchor_target_kernel inside bench.py --steps 2 --warmup 1 --no-cpu --no-extras (B200, $T, profiles/capture_r02.sh)"
