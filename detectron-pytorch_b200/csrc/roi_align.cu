@@ -743,6 +743,83 @@ roi_bwd_nchw_gather_kernel(const RoiArgs a)
     }
 }
 
+// ---- NCHW backward, separable (bin-centre mode, PW <= 8) -------------------------------------------------------------------------
+// The gather kernel above evaluates every product colw * (roww * g) on its own: ~375 products per (RoI, channel) at BASELINE
+// configs[2], in 26 (row, piece) items of five short loops each — ncu: 87 % issue-active, L2 at 13 %.  Bilinear weights are
+// separable, so the same sums factor: T[r][bx] = sum over the bin rows landing on feature row r of roww * g[by][bx]  (7 partial
+// sums per touched row), then out[r][x] = sum over the bin columns landing on pixel x of colw * T[r][bx] — ~270 multiply-adds in
+// 2.5 x fewer items, one thread per (channel, touched row), one red.global.add.v4.f32 per touched 16-byte piece.  Each output is
+// colw * (sum roww * g) instead of sum colw * (roww * g): the same weights, one rounding apart — inside north_star's 1e-5 for the
+// RoIAlign backward and inside the summation bound tests/test_gpu_roi.py asserts (its n + 8 slack covers the extra roundings).
+constexpr int RS2_PW = 8;
+
+__global__ void __launch_bounds__(RG_THREADS, 4)
+roi_bwd_nchw_sep_kernel(const RoiArgs a)
+{
+    __shared__ Tap ty[RA_MAXP], tx[RA_MAXP];
+    __shared__ InvAxis s_r, s_c;
+    __shared__ float s_t[RS2_PW * RG_THREADS];          // T of every thread's current row: [bx][tid], conflict-free
+    extern __shared__ __align__(16) float s_g[];
+    int gh, gw;
+    const Prologue s = roi_prologue(a, ty, tx, gh, gw);
+    if (!s.ok) return;
+    const detbox_roi_cfg &c = a.cfg;
+    const int PH = c.pooled_h, PW = c.pooled_w, C = c.channels;
+    const int Ctot = c.all_levels ? C * c.n_levels : C;
+    const int coff = c.all_levels ? C * blockIdx.y : 0;
+    const int bins = PH * PW;
+    const long r = blockIdx.x;
+    const int tid = threadIdx.x;
+    const size_t plane = (size_t)s.H * s.W;
+    float *g0 = c.grad_feat[s.level] + (size_t)s.b * C * plane;
+    const float *go = a.grad_out + ((size_t)r * Ctot + coff) * bins;
+    const bool vec = ((s.W & 3) == 0) && ((plane & 3) == 0) && (((size_t)g0 & 15) == 0);
+    if (tid == 0) invert_axis<false>(ty, gh, 0, s_r);
+    if (tid == 32) invert_axis<false>(tx, gw, vec ? 2 : 0, s_c);
+    __syncthreads();
+    const int nr = s_r.n_groups, nq = s_c.n_groups;
+    if (nr == 0 || nq == 0) return;                             // no sample inside the map: no gradient
+    const unsigned m_nr = 0xffffffffu / (unsigned)nr;
+    const int CH = max(1, min(C, RG_GFLOATS / bins));
+    float *T = s_t + tid;
+    for (int c0 = 0; c0 < C; c0 += CH) {
+        const int n = min(CH, C - c0);
+        if (c0) __syncthreads();                                // the previous chunk has been consumed
+        for (int i = tid; i < n * bins; i += RG_THREADS) s_g[i] = __ldcs(go + (size_t)c0 * bins + i);
+        __syncthreads();
+        for (unsigned i = tid; i < (unsigned)(n * nr); i += RG_THREADS) {
+            unsigned ch = __umulhi(i, m_nr), ri = i - ch * (unsigned)nr;
+            if (ri >= (unsigned)nr) { ++ch; ri -= (unsigned)nr; }
+            const float *g = s_g + ch * bins;
+            // stage 1: the bin rows landing on this feature row
+            float t[RS2_PW];
+#pragma unroll
+            for (int bx = 0; bx < RS2_PW; ++bx) t[bx] = 0.0f;
+            for (int er = s_r.sub[ri * 4], e1 = s_r.sub[ri * 4 + 4]; er < e1; ++er) {
+                const float *grow = g + s_r.bin[er] * PW;
+                const float rw = s_r.w[er];
+#pragma unroll
+                for (int bx = 0; bx < RS2_PW; ++bx) if (bx < PW) t[bx] += rw * grow[bx];
+            }
+#pragma unroll
+            for (int bx = 0; bx < RS2_PW; ++bx) T[bx * RG_THREADS] = t[bx];
+            // stage 2: the bin columns landing on every touched piece of this row (only this thread reads its T: no barrier)
+            float *dst = g0 + (size_t)(c0 + ch) * plane + (size_t)s_r.key[ri] * s.W;
+            for (int qi = 0; qi < nq; ++qi) {
+                const short *cs = s_c.sub + qi * 4;
+                float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+                for (int p = 0; p < 4; ++p)
+                    for (int ec = cs[p]; ec < cs[p + 1]; ++ec) acc[p] += s_c.w[ec] * T[s_c.bin[ec] * RG_THREADS];
+                if (vec) {
+                    if (acc[0] != 0.0f || acc[1] != 0.0f || acc[2] != 0.0f || acc[3] != 0.0f)
+                        red_add4(dst + 4 * (int)s_c.key[qi], make_float4(acc[0], acc[1], acc[2], acc[3]));
+                } else if (acc[0] != 0.0f) atomicAdd(dst + (int)s_c.key[qi], acc[0]);
+            }
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256)
 assign_levels_kernel(const float *__restrict__ boxes, long R, detbox_roi_cfg c, int32_t *__restrict__ levels)
 {
@@ -845,7 +922,9 @@ extern "C" int detbox_roi_align_backward(const detbox_roi_cfg *cfg, const float 
     if (cfg->layout == DETBOX_LAYOUT_NCHW && cfg->out_layout == DETBOX_LAYOUT_NCHW && cfg->pool == DETBOX_POOL_NONE && !bwd_direct &&
         getenv("DETBOX_ROI_BWD_STAGED") == nullptr && (long)cfg->pooled_h * cfg->pooled_w <= RG_GFLOATS) {
         DETBOX_TRACE_BEGIN(DETBOX_K_ROI_BWD, st);
+        static const bool no_sep = getenv("DETBOX_ROI_BWD_GATHER") != nullptr;     // the exact-term gather kernel, for A/B timing and its own test
         if (cfg->mode == DETBOX_ROI_GRID_POINT) roi_bwd_nchw_gather_kernel<true><<<grid, RG_THREADS, RG_GFLOATS * sizeof(float), st>>>(a);
+        else if (cfg->pooled_w <= RS2_PW && !no_sep) roi_bwd_nchw_sep_kernel<<<grid, RG_THREADS, RG_GFLOATS * sizeof(float), st>>>(a);
         else roi_bwd_nchw_gather_kernel<false><<<grid, RG_THREADS, RG_GFLOATS * sizeof(float), st>>>(a);
         DETBOX_TRACE_END(DETBOX_K_ROI_BWD, st);
         DETBOX_LAUNCH_CHECK();

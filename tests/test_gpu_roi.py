@@ -315,10 +315,11 @@ def test_config3_values_vs_openmp_reference():
 
 
 def test_nchw_staged_backward_opt_in_subprocess():
-    """The default NCHW backward is the gather kernel (one red.global.add.v4 per touched 16-byte piece, sums in
-    registers).  The two older paths stay selectable per process — DETBOX_ROI_BWD_STAGED=1 (sums in a shared-memory
-    window) and DETBOX_ROI_BWD_DIRECT=1 (4 scalar reds per output element); both measured slower on B200 — so each is
-    exercised in a process of its own against the same bound as the default path."""
+    """The default NCHW backward is the separable kernel in bin-centre mode (PW <= 8) and the exact-term gather kernel in
+    grid-point mode (one red.global.add.v4 per touched 16-byte piece either way).  The other paths stay selectable per
+    process — DETBOX_ROI_BWD_GATHER=1 (exact-term gather in bin-centre mode too), DETBOX_ROI_BWD_STAGED=1 (sums in a
+    shared-memory window), DETBOX_ROI_BWD_DIRECT=1 (4 scalar reds per output element); all measured slower on B200 — so
+    each is exercised in a process of its own against the same bound as the default path."""
     import os, subprocess, sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     code = (
@@ -335,7 +336,7 @@ def test_nchw_staged_backward_opt_in_subprocess():
         "    gi = detbox.roi_align_backward(T.cu(g), [feat_shape], T.cu(rois), [0.25], m)[0].cpu().numpy()\n"
         "    T.assert_bwd_within_bound(gi, bwd(g, rois, np.float32(0.25), feat_shape), T.tap_stats(rois, 0.25, 7, 7, feat_shape, mode, g), float(np.abs(g).max()))\n"
         "print('staged backward ok')\n" % (root, os.path.join(root, "tests")))
-    for var in ("DETBOX_ROI_BWD_STAGED", "DETBOX_ROI_BWD_DIRECT"):
+    for var in ("DETBOX_ROI_BWD_STAGED", "DETBOX_ROI_BWD_DIRECT", "DETBOX_ROI_BWD_GATHER"):
         env = dict(os.environ, **{var: "1"})
         r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
         assert r.returncode == 0 and "staged backward ok" in r.stdout, var + "\n" + r.stdout + r.stderr
