@@ -40,7 +40,7 @@ class RoiCfg(ctypes.Structure):
                 ("spatial_scale", c_float * MAX_LEVELS), ("ref_area", c_float * MAX_LEVELS),
                 ("batch", c_int), ("channels", c_int), ("layout", c_int), ("out_layout", c_int),
                 ("pooled_h", c_int), ("pooled_w", c_int), ("mode", c_int), ("pool", c_int),
-                ("all_levels", c_int), ("extrapolation", c_float)]
+                ("all_levels", c_int), ("extrapolation", c_float), ("roi_order", c_void)]
 
 
 class MatchCfg(ctypes.Structure):
@@ -85,6 +85,8 @@ SIGNATURES = {
                                    c_void, c_void, c_size, c_void]),
     "detbox_roi_align_forward": (c_int, [ctypes.POINTER(RoiCfg), c_void, c_long, c_void, c_void, c_void]),
     "detbox_roi_align_backward": (c_int, [ctypes.POINTER(RoiCfg), c_void, c_long, c_void, c_void, c_int, c_void]),
+    "detbox_roi_locality_order_workspace_bytes": (c_size, [c_long]),
+    "detbox_roi_locality_order": (c_int, [c_void, c_long, c_void, P_float, c_int, c_float, c_float, c_void, c_void, c_size, c_void]),
     "detbox_assign_levels": (c_int, [c_void, c_long, P_float, c_int, c_void, c_void]),
     "detbox_match_boxes": (c_int, [c_void, c_int, c_void, c_long, c_void, c_void, c_int, ctypes.POINTER(MatchCfg),
                                    c_void, c_void, c_void, c_void]),

@@ -88,17 +88,22 @@ __device__ __forceinline__ Tap gp_tap(float lo, float hi, float scale, int G, in
     return t;
 }
 
-struct Prologue { int level, b, H, W, ok; };
+struct Prologue { int level, b, H, W, ok; long r; };   // r: the RoI this block owns (blockIdx.x, or roi_order[blockIdx.x])
 
 __device__ __forceinline__ Prologue roi_prologue(const RoiArgs &a, Tap *ty, Tap *tx, int &gh, int &gw)
 {
     __shared__ Prologue s;
     const detbox_roi_cfg &c = a.cfg;
-    const float *roi = a.rois + (size_t)blockIdx.x * 5;
+    // Which RoI a block owns is free: the result is written to that RoI's own slot.  roi_order (detbox_roi_locality_order) deals
+    // RoIs to consecutive blocks by (level, image, row band, column band), so that overlapping RoIs run close together in
+    // time and their shared feature rows are L2 hits instead of DRAM re-reads.
+    const long ridx = c.roi_order ? (long)c.roi_order[blockIdx.x] : (long)blockIdx.x;
+    const float *roi = a.rois + (size_t)ridx * 5;
     if (threadIdx.x == 0) {
         int l = 0;
+        s.r = ridx;
         if (c.all_levels) l = blockIdx.y;
-        else if (a.levels) l = a.levels[blockIdx.x];
+        else if (a.levels) l = a.levels[ridx];
         else if (c.n_levels > 1) l = pick_level(c, roi);
         s.level = l;
         s.b = (int)roi[0];
@@ -163,7 +168,7 @@ roi_fwd_kernel(const RoiArgs a)
     const int Ctot = c.all_levels ? C * c.n_levels : C;
     const int coff = c.all_levels ? C * blockIdx.y : 0;
     const int bins = PH * PW;
-    const long r = blockIdx.x;
+    const long r = s.r;
     const float *f = s.ok ? c.feat[s.level] : nullptr;
     const int pool = (GRID && c.pool != DETBOX_POOL_NONE) ? c.pool : DETBOX_POOL_NONE;
     const float ext = GRID ? 0.0f : c.extrapolation;
@@ -267,7 +272,7 @@ roi_bwd_kernel(const RoiArgs a)
     const int Ctot = c.all_levels ? C * c.n_levels : C;
     const int coff = c.all_levels ? C * blockIdx.y : 0;
     const int bins = PH * PW;
-    const long r = blockIdx.x;
+    const long r = s.r;
     float *gf = c.grad_feat[s.level];
     const int pool = (GRID && c.pool != DETBOX_POOL_NONE) ? c.pool : DETBOX_POOL_NONE;
 
@@ -441,7 +446,7 @@ roi_fwd_nchw_staged_kernel(const RoiArgs a)
     const int Ctot = c.all_levels ? C * c.n_levels : C;
     const int coff = c.all_levels ? C * blockIdx.y : 0;
     const int bins = PH * PW;
-    const long r = blockIdx.x;
+    const long r = s.r;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const float *f = s.ok ? c.feat[s.level] : nullptr;
     const int pool = (GRID && c.pool != DETBOX_POOL_NONE) ? c.pool : DETBOX_POOL_NONE;
@@ -545,7 +550,7 @@ roi_bwd_nchw_staged_kernel(const RoiArgs a)
     const int Ctot = c.all_levels ? C * c.n_levels : C;
     const int coff = c.all_levels ? C * blockIdx.y : 0;
     const int bins = PH * PW;
-    const long r = blockIdx.x;
+    const long r = s.r;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const size_t plane = (size_t)s.H * s.W;
     float *g0 = c.grad_feat[s.level] + (size_t)s.b * C * plane;
@@ -692,7 +697,7 @@ roi_bwd_nchw_gather_kernel(const RoiArgs a)
     const int Ctot = c.all_levels ? C * c.n_levels : C;
     const int coff = c.all_levels ? C * blockIdx.y : 0;
     const int bins = PH * PW;
-    const long r = blockIdx.x;
+    const long r = s.r;
     const int tid = threadIdx.x;
     const size_t plane = (size_t)s.H * s.W;
     float *g0 = c.grad_feat[s.level] + (size_t)s.b * C * plane;
@@ -768,7 +773,7 @@ roi_bwd_nchw_sep_kernel(const RoiArgs a)
     const int Ctot = c.all_levels ? C * c.n_levels : C;
     const int coff = c.all_levels ? C * blockIdx.y : 0;
     const int bins = PH * PW;
-    const long r = blockIdx.x;
+    const long r = s.r;
     const int tid = threadIdx.x;
     const size_t plane = (size_t)s.H * s.W;
     float *g0 = c.grad_feat[s.level] + (size_t)s.b * C * plane;
@@ -947,6 +952,49 @@ extern "C" int detbox_roi_align_backward(const detbox_roi_cfg *cfg, const float 
         DETBOX_LAUNCH_CHECK();
         return DETBOX_OK;
     });
+}
+
+// ---- L2-friendly RoI processing order ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+roi_order_key_kernel(const float *__restrict__ rois, long R, const int32_t *__restrict__ levels, detbox_roi_cfg c,
+                     float im_h, float im_w, float *__restrict__ keys)
+{
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < R; i += (long)gridDim.x * blockDim.x) {
+        const float *roi = rois + i * 5;
+        int l = 0;
+        if (levels) l = levels[i];
+        else if (c.n_levels > 1) l = pick_level(c, roi);
+        l = min(max(l, 0), DETBOX_MAX_LEVELS - 1);
+        const int b = min(max((int)roi[0], 0), 255);
+        const float cy = 0.5f * (roi[2] + roi[4]), cx = 0.5f * (roi[1] + roi[3]);
+        const int yb = min(max((int)(cy / im_h * 64.0f), 0), 63), xb = min(max((int)(cx / im_w * 32.0f), 0), 31);
+        // 3 + 8 + 6 + 5 = 22 bits: an exact float32 integer.  detbox_sort_desc sorts descending and stable: any monotone key does.
+        keys[i] = (float)((((l << 8) | b) << 11) | (yb << 5) | xb);
+    }
+}
+
+extern "C" size_t detbox_roi_locality_order_workspace_bytes(long R)
+{
+    if (R < 0) return 0;
+    return align_up((size_t)(R > 0 ? R : 1) * sizeof(float)) + detbox_sort_desc_workspace_bytes(R);
+}
+
+extern "C" int detbox_roi_locality_order(const float *rois, long R, const int32_t *levels, const float *ref_areas, int n_levels,
+                                         float im_h, float im_w, int32_t *order, void *ws, size_t ws_bytes, void *stream)
+{
+    if (R < 0 || n_levels < 1 || n_levels > DETBOX_MAX_LEVELS || !(im_h > 0) || !(im_w > 0)) return DETBOX_ERR_INVALID;
+    if (R == 0) return DETBOX_OK;
+    if (!rois || !order || (!levels && n_levels > 1 && !ref_areas)) return DETBOX_ERR_INVALID;
+    if (!ws || ws_bytes < detbox_roi_locality_order_workspace_bytes(R)) return DETBOX_ERR_WORKSPACE;
+    detbox_roi_cfg c{};
+    c.n_levels = n_levels;
+    for (int l = 0; l < n_levels; ++l) c.ref_area[l] = ref_areas ? ref_areas[l] : 1.0f;
+    float *keys = reinterpret_cast<float *>(ws);
+    const size_t koff = align_up((size_t)R * sizeof(float));
+    long gb = (R + 255) / 256; if (gb > kNumSMs * 8) gb = kNumSMs * 8;
+    roi_order_key_kernel<<<(unsigned)gb, 256, 0, as_stream(stream)>>>(rois, R, levels, c, im_h, im_w, keys);
+    DETBOX_LAUNCH_CHECK();
+    return detbox_sort_desc(keys, R, order, reinterpret_cast<char *>(ws) + koff, ws_bytes - koff, stream);
 }
 
 extern "C" int detbox_assign_levels(const float *boxes, long R, const float *ref_areas, int n_levels,

@@ -17,11 +17,17 @@ class _RoiFn(Function):
 
     @staticmethod
     def forward(ctx, rois, levels, meta, *feats):
-        out = ops_roi.roi_align_forward(list(feats), rois, meta["scales"], meta["ph"], meta["pw"], meta["mode"],
-                                        pool=meta.get("pool"), levels=levels, ref_areas=meta.get("ref_areas"),
-                                        all_levels=meta.get("all_levels", False), extrapolation=meta.get("extrapolation", 0.0))
         ctx.meta, ctx.shapes = meta, [tuple(f.shape) for f in feats]
         ctx.nhwc = all(ops_roi._is_channels_last(f) for f in feats)     # the layout _make_cfg chose: NHWC only if EVERY level is
+        # an L2-friendly block -> RoI order (meta["order"] = "auto" or a permutation; off by default) is computed once and
+        # shared by forward and backward
+        od = ops_roi._auto_order(meta.get("order"), ctx.nhwc, meta.get("all_levels", False), rois.view(-1, 5), meta["scales"], ctx.shapes,
+                                 levels, meta.get("ref_areas"))
+        ctx.order = od if od is not None else False
+        out = ops_roi.roi_align_forward(list(feats), rois, meta["scales"], meta["ph"], meta["pw"], meta["mode"],
+                                        pool=meta.get("pool"), levels=levels, ref_areas=meta.get("ref_areas"),
+                                        all_levels=meta.get("all_levels", False), extrapolation=meta.get("extrapolation", 0.0),
+                                        order=ctx.order)
         ctx.save_for_backward(rois, levels if levels is not None else rois.new_zeros(0), *(feats if meta.get("pool") == "max" else ()))
         ctx.has_levels = levels is not None
         return out
@@ -33,7 +39,7 @@ class _RoiFn(Function):
         m = ctx.meta
         grads = ops_roi.roi_align_backward(grad_out, ctx.shapes, rois, m["scales"], m["mode"], levels=levels,
                                            ref_areas=m.get("ref_areas"), all_levels=m.get("all_levels", False),
-                                           channels_last=ctx.nhwc, pool=m.get("pool"), feats=feats or None)
+                                           channels_last=ctx.nhwc, pool=m.get("pool"), feats=feats or None, order=ctx.order)
         return (None, None, None) + tuple(grads)
 
 

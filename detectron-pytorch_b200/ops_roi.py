@@ -8,7 +8,7 @@ import torch
 
 from . import _lib
 from ._lib import check, lib
-from .ops import POOL, ROI_BIN_CENTRE, ROI_CROP_NORM, ROI_GRID_POINT, _count, _dev, _ptr, _stream  # noqa: F401
+from .ops import _ws, POOL, ROI_BIN_CENTRE, ROI_CROP_NORM, ROI_GRID_POINT, _count, _dev, _ptr, _stream  # noqa: F401
 
 
 def _is_channels_last(t: torch.Tensor) -> bool:
@@ -47,6 +47,45 @@ def _make_cfg(feats, spatial_scales, ref_areas, ph, pw, mode, pool, all_levels, 
     return c, keep, nhwc
 
 
+ORDER_MIN_ROIS = 512        # below this the feature working set fits L2 anyway and the sort is not worth two launches
+
+
+def roi_locality_order(rois, spatial_scales, feat_shapes, levels=None, ref_areas=None):
+    """detbox_roi_locality_order: int32 [R] processing order that keeps overlapping RoIs close together in time
+    ((level, image, row band, column band) of the RoI centre), for detbox_roi_cfg.roi_order.  The canvas size is taken
+    from level 0 (H_0 / scale_0)."""
+    r = _dev(rois).view(-1, 5)
+    R = r.shape[0]
+    L = len(feat_shapes)
+    lv = _dev(levels, torch.int32, "levels").view(-1) if levels is not None else None
+    ra = np.ascontiguousarray(ref_areas, np.float32) if ref_areas is not None else None
+    im_h, im_w = feat_shapes[0][2] / float(spatial_scales[0]), feat_shapes[0][3] / float(spatial_scales[0])
+    order = torch.empty((R,), dtype=torch.int32, device=r.device)
+    ws = _ws.get(lib().detbox_roi_locality_order_workspace_bytes(R), r.device)
+    check(lib().detbox_roi_locality_order(r.data_ptr(), R, _ptr(lv), ra.ctypes.data_as(_lib.P_float) if ra is not None else None,
+                                          L if (lv is not None or ra is not None) else 1, float(im_h), float(im_w), order.data_ptr(),
+                                          ws.data_ptr(), ws.numel(), _stream()), "roi_locality_order")
+    _count(2 if R <= 4096 else 14)
+    return order
+
+
+def _auto_order(order, nhwc, all_levels, r, spatial_scales, feat_shapes, levels, ref_areas):
+    """order: None / False -> RoI order (block i handles RoI i); "auto" -> roi_locality_order for NCHW inputs with enough
+    RoIs; a tensor -> used as is.  Off by default: measured on B200 at BASELINE configs[2] the order leaves the staged
+    forward where it is (0.243 ms; ~600 resident blocks x a 180 KB window over 256 channels already fill the 126 MB L2, so
+    overlapping RoIs rarely find each other's rows resident) and gains 3.5 % on the backward scatter — less than its
+    two launches cost a forward (profiles/r02_roi_staged_vs_generic.txt)."""
+    if order is None or order is False:
+        return None
+    if torch.is_tensor(order):
+        return _dev(order, torch.int32, "order").view(-1)
+    if order != "auto":
+        raise _lib.DetboxError("order must be None, False, 'auto' or an int32 permutation")
+    if nhwc or all_levels or r.shape[0] < ORDER_MIN_ROIS:
+        return None
+    return roi_locality_order(r, spatial_scales, feat_shapes, levels, ref_areas)
+
+
 def _out_tensor(R, C, ph, pw, nhwc, device):
     if nhwc:
         return torch.empty((R, ph, pw, C), dtype=torch.float32, device=device).permute(0, 3, 1, 2)
@@ -54,17 +93,22 @@ def _out_tensor(R, C, ph, pw, nhwc, device):
 
 
 def roi_align_forward(feats, rois, spatial_scales, ph, pw, mode=ROI_BIN_CENTRE, pool=None,
-                      levels=None, ref_areas=None, all_levels=False, extrapolation=0.0):
+                      levels=None, ref_areas=None, all_levels=False, extrapolation=0.0, order=None):
     """One launch over all pyramid levels.  feats: list of [B,C,H_l,W_l] (all NCHW-contiguous or all
     channels_last); rois [R,5] = (batch idx, x1, y1, x2, y2) in image coordinates.  Level of a RoI:
     `levels` (int32 [R]) if given, else computed in-kernel from ref_areas when there are several
-    levels (pyramid_roi_align.py:33-37).  Output [R, C (or L*C), ph, pw] in the input's memory format."""
+    levels (pyramid_roi_align.py:33-37).  Output [R, C (or L*C), ph, pw] in the input's memory format.
+    order: the block -> RoI assignment (results do not depend on it).  None / False: RoI order; "auto": for NCHW
+    inputs with at least ORDER_MIN_ROIS RoIs an L2-friendly order is computed (roi_locality_order: two small launches);
+    an int32 [R] permutation: used as is (share one between forward and backward)."""
     r = _dev(rois).view(-1, 5)
     cfg, keep, nhwc = _make_cfg(feats, spatial_scales, ref_areas, ph, pw, mode, pool, all_levels, extrapolation=extrapolation)
     if len(feats) > 1 and not all_levels and levels is None and ref_areas is None:
         raise _lib.DetboxError("several levels need `levels`, `ref_areas` or all_levels=True")
     lv = _dev(levels, torch.int32, "levels").view(-1) if levels is not None else None
     Ctot = cfg.channels * (len(feats) if all_levels else 1)
+    od = _auto_order(order, nhwc, all_levels, r, spatial_scales, [tuple(f.shape) for f in feats], lv, ref_areas)
+    cfg.roi_order = _ptr(od) or None
     out = _out_tensor(r.shape[0], Ctot, ph, pw, nhwc, r.device)
     check(lib().detbox_roi_align_forward(ctypes.byref(cfg), r.data_ptr(), r.shape[0], _ptr(lv), out.data_ptr(), _stream()),
           "roi_align_forward")
@@ -73,7 +117,7 @@ def roi_align_forward(feats, rois, spatial_scales, ph, pw, mode=ROI_BIN_CENTRE, 
 
 
 def roi_align_backward(grad_out, feat_shapes, rois, spatial_scales, mode=ROI_BIN_CENTRE, levels=None,
-                       ref_areas=None, all_levels=False, channels_last=False, grads=None, pool=None, feats=None):
+                       ref_areas=None, all_levels=False, channels_last=False, grads=None, pool=None, feats=None, order=None):
     """Gradient w.r.t. the feature maps (dense, zero-filled here unless `grads` is given, in which
     case it is accumulated into).  grad_out [R, C(or L*C), ph, pw] in the same memory format as the
     features.  pool='avg'|'max' differentiates the fused 2x2 pool of RoIAlignAvg/Max as well
@@ -113,6 +157,8 @@ def roi_align_backward(grad_out, feat_shapes, rois, spatial_scales, mode=ROI_BIN
         for l, f in enumerate(feats):
             c.feat[l] = f.data_ptr()
     lv = _dev(levels, torch.int32, "levels").view(-1) if levels is not None else None
+    od = _auto_order(order, channels_last, all_levels, r, spatial_scales, [tuple(t.shape) for t in grads], lv, ref_areas)
+    c.roi_order = _ptr(od) or None
     check(lib().detbox_roi_align_backward(ctypes.byref(c), r.data_ptr(), r.shape[0], _ptr(lv), g.data_ptr(), int(zero), _stream()),
           "roi_align_backward")
     _count(1 + (L if zero else 0))

@@ -301,6 +301,9 @@ typedef struct {
     int all_levels;
     float extrapolation;                    /* value of samples outside the map (crop modes; the
                                                RoIAlign wrapper passes 0, roi_align_tf.py:42)    */
+    const int32_t *roi_order;               /* device, int32 [R] permutation or NULL: block i processes RoI
+                                               roi_order[i] (results are written to the RoI's own slot, so they do
+                                               not depend on it); see detbox_roi_locality_order                  */
 } detbox_roi_cfg;
 
 int detbox_roi_align_forward(const detbox_roi_cfg *cfg, const float *rois_dev /*[R,5] b,x1,y1,x2,y2*/,
@@ -310,6 +313,13 @@ int detbox_roi_align_forward(const detbox_roi_cfg *cfg, const float *rois_dev /*
 int detbox_roi_align_backward(const detbox_roi_cfg *cfg, const float *rois_dev, long R,
                               const int32_t *levels_dev, const float *grad_out_dev, int zero_grad,
                               void *stream);
+/* A processing order for detbox_roi_cfg.roi_order that keeps overlapping RoIs close together in time: RoIs sorted by
+ * (level, image, row band, column band) of their centre on an im_h x im_w canvas, so that the feature rows neighbouring
+ * RoIs share are L2 hits instead of DRAM re-reads (the reference launches one thread per output element in RoI order,
+ * roi_align_kernel.cu:15-30 — no counterpart).  levels_dev / ref_areas as for the forward.  order_dev int32 [R]. */
+size_t detbox_roi_locality_order_workspace_bytes(long R);
+int detbox_roi_locality_order(const float *rois_dev, long R, const int32_t *levels_dev, const float *ref_areas_host, int n_levels,
+                              float im_h, float im_w, int32_t *order_dev, void *workspace_dev, size_t workspace_bytes, void *stream);
 /* level assignment alone (pyramid_roi_align.py:33-37) */
 int detbox_assign_levels(const float *boxes_dev /*[R,4]*/, long R, const float *ref_areas_host, int n_levels,
                          int32_t *levels_dev, void *stream);

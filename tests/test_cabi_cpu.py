@@ -33,10 +33,23 @@ def test_ctypes_prototypes_cover_the_header():
     detbox.lib()        # attaches every prototype; raises if one cannot be resolved
 
 
-def test_struct_layouts_match_header():
+def test_struct_layouts_match_header(tmp_path):
+    """Every ctypes mirror of a struct in include/detbox.h against what the C compiler makes of the header itself: sizes and
+    the offsets of the last fields (a field added to the header but not to the mirror, or the other way round, shows here)."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = tmp_path / "sizes.c"
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "detbox.h"\nint main(void) {\n'
+                   'printf("%zu %zu %zu %zu %zu %zu %zu\\n", sizeof(detbox_target_cfg), sizeof(detbox_roi_cfg), sizeof(detbox_match_cfg),\n'
+                   '       sizeof(detbox_pyramid_desc), offsetof(detbox_roi_cfg, extrapolation), offsetof(detbox_roi_cfg, roi_order),\n'
+                   '       offsetof(detbox_target_cfg, bbweights));\nreturn 0; }\n')
+    exe = tmp_path / "sizes"
+    subprocess.check_call(["gcc", "-I", os.path.join(root, "include"), str(src), "-o", str(exe)])
+    got = [int(x) for x in subprocess.check_output([str(exe)]).split()]
+    want = [ctypes.sizeof(_lib.TargetCfg), ctypes.sizeof(_lib.RoiCfg), ctypes.sizeof(_lib.MatchCfg), ctypes.sizeof(_lib.PyramidDesc),
+            _lib.RoiCfg.extrapolation.offset, _lib.RoiCfg.roi_order.offset, _lib.TargetCfg.bbweights.offset]
+    assert got == want, (got, want)
     assert ctypes.sizeof(_lib.TargetCfg) == 3 * 8 + 2 * 4 + 4 * 4
-    # n_levels(4)+pad(4) + 2*8 pointers*8 + 4*8*4 + 9*4 -> multiple of 8
-    assert ctypes.sizeof(_lib.RoiCfg) == 8 + 2 * 8 * 8 + 4 * 8 * 4 + 9 * 4 + 4
 
 
 def test_base_anchors_host(golden):

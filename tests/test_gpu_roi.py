@@ -340,3 +340,38 @@ def test_nchw_staged_backward_opt_in_subprocess():
         env = dict(os.environ, **{var: "1"})
         r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
         assert r.returncode == 0 and "staged backward ok" in r.stdout, var + "\n" + r.stdout + r.stderr
+
+
+def test_results_do_not_depend_on_the_roi_processing_order():
+    """detbox_roi_cfg.roi_order only changes which block handles which RoI (an L2-friendly order by (level, image, row
+    band, column band), detbox_roi_locality_order): the forward must be bit-identical for the RoI order, the automatic
+    order and a random permutation; the backward (float32 atomics: only the order of additions moves) stays inside the
+    summation bound.  The order itself must be a permutation sorted by the documented key."""
+    rng = np.random.RandomState(41)
+    B, C, ih, iw = 2, 24, 256, 384
+    feats = pyramid(rng, B, C, ih, iw)
+    cfg = O.Cfg(strides=tuple(STRIDES), anchor_scales=[[2, 2.52, 3.17], [4, 5.04, 6.35], [8, 10.08, 12.7], [16, 20.16, 25.4]])
+    ref_areas = O.pyramid_ref_areas(cfg)
+    rois = make_rois(rng, 700, B, ih, iw, 8, 300)                      # >= ORDER_MIN_ROIS: order="auto" computes one
+    scales = [np.float32(1.0 / s) for s in STRIDES]
+    fl = [cu(f) for f in feats]
+    shapes = [f.shape for f in feats]
+    od = detbox.ops_roi.roi_locality_order(cu(rois), scales, shapes, None, ref_areas)
+    o = od.cpu().numpy()
+    assert np.array_equal(np.sort(o), np.arange(700))
+    lv = O.assign_levels(rois[:, 1:], ref_areas)
+    key = ((lv[o].astype(np.int64) << 8 | rois[o, 0].astype(np.int64)) << 11)
+    assert (np.diff(key) <= 0).all()                                   # (level, image) major, descending
+    perm = cu(rng.permutation(700).astype(np.int32))
+    g = rng.normal(0, 1, (700, C, 7, 7)).astype(np.float32)
+    for mode, m in (("tf", detbox.ROI_BIN_CENTRE), ("grid", detbox.ROI_GRID_POINT)):
+        base = detbox.roi_align_forward(fl, cu(rois), scales, 7, 7, m, ref_areas=ref_areas, order=False)
+        for order in ("auto", od, perm):
+            assert torch.equal(detbox.roi_align_forward(fl, cu(rois), scales, 7, 7, m, ref_areas=ref_areas, order=order), base)
+        bwd = O.roi_align_tf_bwd if mode == "tf" else O.roi_align_grid_bwd
+        for order in (False, "auto", perm):
+            gi = detbox.roi_align_backward(cu(g), shapes, cu(rois), scales, m, ref_areas=ref_areas, order=order)
+            for l, f in enumerate(feats):
+                sel = lv == l
+                assert_bwd_within_bound(gi[l].cpu().numpy(), bwd(g[sel], rois[sel], scales[l], f.shape),
+                                        tap_stats(rois, float(scales[l]), 7, 7, f.shape, mode, g, sel), float(np.abs(g).max()))
