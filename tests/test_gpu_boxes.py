@@ -470,3 +470,27 @@ def test_anchor_target_decide_screen_adversarial(seed):
     got = run_target(anc, gts, cfg)
     for b, gt in enumerate(gts):
         check_target(got, b, gt, anc, cfg)
+
+
+def test_anchor_target_float32_anchor_contract(cpr_anchors, golden):
+    """ADVICE r1: the reference has two anchor dtypes on its own paths (float64 pyramid per sample, data_layer.py:99-102;
+    float32 per batch, :138-140).  This library implements the float32 one.  tests/golden/anchor_f64_delta.npz (from the
+    COMPILED reference, oracle/make_golden_f64_anchors.py) holds both paths' labels on the 12 densest real CityPersons images:
+    ours must equal the float32 path everywhere — including the 2 anchors (of 3.1 M) where the reference's own float64 path
+    labels differently."""
+    ref, _ = cpr_anchors
+    anc = ref.astype(np.float32)
+    g = golden("anchor_f64_delta")
+    ids = [int(i) for i in g["image_ids"]]
+    got = run_target(anc, [g["img%d_gt" % i] for i in ids], CPR)
+    n_diff = 0
+    for b, i in enumerate(ids):
+        k = "img%d_" % i
+        want = np.zeros(anc.shape[0], np.float32)
+        want[g[k + "labels32_nz_idx"]] = g[k + "labels32_nz_val"]
+        np.testing.assert_array_equal(got[0][b], want)
+        d = g[k + "diff_idx"]
+        if d.size:
+            assert (got[0][b][d] != g[k + "labels64_at_diff"]).all()       # the documented delta to the float64-anchor path
+        n_diff += d.size
+    assert n_diff == int(g["total_label_diffs"]) == 2
