@@ -9,13 +9,15 @@ gts = [bench.synth_gt(np.random.RandomState(i), 12) for i in range(B)]
 rng = np.random.RandomState(0)
 deltas, prob = bench.synth_head(rng, B * A, rng.choice(B * A, 20000, replace=False))
 hp, hb = torch.from_numpy(prob).pin_memory(), torch.from_numpy(deltas).pin_memory()
+kw = dict(format=sys.argv[1]) if len(sys.argv) > 1 else {}
+if len(sys.argv) > 2:
+    kw["chunk"] = int(sys.argv[2])
 for _ in range(3):
-    sess.run_host(gts, hp, hb)
+    sess.run_host(gts, hp, hb, **kw)
 sess.timeline = []
 t0 = time.perf_counter()
-sess.run_host(gts, hp, hb)
+sess.run_host(gts, hp, hb, **kw)
 wall = 1e3 * (time.perf_counter() - t0)
 ev0 = sess.timeline[0][0]
-print("wall ms", wall, "cpu issue done at ms", sess.issue_ms)
-for name, ev in sess.timeline[1:]:
-    print("%-10s %.3f" % (name, ev0[1].elapsed_time(ev)))
+print(kw, "wall ms %.3f" % wall, "cpu issue done at ms %.3f" % sess.issue_ms)
+print(" ".join("%s@%.2f" % (name, ev0[1].elapsed_time(ev)) for name, ev in sess.timeline[1:]))
