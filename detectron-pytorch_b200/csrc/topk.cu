@@ -384,8 +384,8 @@ partition_kernel(const uint32_t *__restrict__ keys, long seg_len, const SegState
     }
 }
 
-__global__ void __launch_bounds__(1024)
-cand_select_kernel(const uint32_t *__restrict__ cand_keys, const uint32_t *__restrict__ cand_idx, long seg_len,
+__device__ __forceinline__ void
+cand_select_body(const unsigned seg, const uint32_t *__restrict__ cand_keys, const uint32_t *__restrict__ cand_idx, long seg_len,
                    const SegState *__restrict__ state, const uint32_t *__restrict__ cnt, long K,
                    uint32_t *__restrict__ ckeys, uint32_t *__restrict__ cvals)
 {
@@ -394,9 +394,9 @@ cand_select_kernel(const uint32_t *__restrict__ cand_keys, const uint32_t *__res
     __shared__ uint32_t wsum[32];
     __shared__ uint32_t s_bin, s_before, s_out;
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    const SegState st = state[blockIdx.x];
-    const uint32_t c0 = cnt[2 * blockIdx.x + 1];
-    const uint32_t *ck = cand_keys + (size_t)blockIdx.x * seg_len, *ci = cand_idx + (size_t)blockIdx.x * seg_len;
+    const SegState st = state[seg];
+    const uint32_t c0 = cnt[2 * seg + 1];
+    const uint32_t *ck = cand_keys + (size_t)seg * seg_len, *ci = cand_idx + (size_t)seg * seg_len;
     uint32_t need = st.k_rem;                    // 1 <= need <= c0
     // composite = (key & 0x1fffff) << 32 | idx, 53 bits, digits MSB first: 11, 10 (key), 11, 11, 10 (index)
     const int shifts[5] = {42, 32, 21, 10, 0};
@@ -447,7 +447,7 @@ cand_select_kernel(const uint32_t *__restrict__ cand_keys, const uint32_t *__res
     // emit: every candidate with composite <= T (exactly k_rem of them), after the segment's outright winners
     if (tid == 0) s_out = 0;
     __syncthreads();
-    const size_t out0 = (size_t)blockIdx.x * K + st.n_better;
+    const size_t out0 = (size_t)seg * K + st.n_better;
     for (uint32_t i0 = 0; i0 < c0; i0 += 1024) {
         const uint32_t i = i0 + tid;
         bool take = false; uint32_t key = 0, idx = 0;
@@ -460,6 +460,14 @@ cand_select_kernel(const uint32_t *__restrict__ cand_keys, const uint32_t *__res
             if (take) { const size_t pos = out0 + base + __popc(m & ((1u << lane) - 1u)); ckeys[pos] = key; cvals[pos] = idx; }
         }
     }
+}
+
+__global__ void __launch_bounds__(1024)
+cand_select_kernel(const uint32_t *__restrict__ cand_keys, const uint32_t *__restrict__ cand_idx, long seg_len,
+                   const SegState *__restrict__ state, const uint32_t *__restrict__ cnt, long K,
+                   uint32_t *__restrict__ ckeys, uint32_t *__restrict__ cvals)
+{
+    cand_select_body(blockIdx.x, cand_keys, cand_idx, seg_len, state, cnt, K, ckeys, cvals);
 }
 
 // ---- 4'. sort of small segments (K <= 2048 winners each): one block per segment, bitonic network in
@@ -518,6 +526,63 @@ gather_decode_kernel(const uint32_t *__restrict__ ckeys, const uint32_t *__restr
         if (flat_idx) flat_idx[i] = (int64_t)idx;
         if (scores) scores[i] = ordered_to_float(~ckeys[i]);
         if (probs_out) for (int c = 0; c < C; ++c) probs_out[(size_t)i * C + c] = prob[(size_t)idx * C + c];
+    }
+}
+
+// Tail of the one-block route for K <= TAIL_MAX winners per segment, as ONE launch instead of three: select among the
+// threshold-bin candidates (cand_select_body), sort the segment's K winners in shared memory (the network of
+// seg_sort_kernel), then gather + decode straight from the sorted list (the body of gather_decode_kernel).  One block per
+// segment; the winners never travel back to HBM between the three steps.  Same results by construction; the separate
+// kernels stay for TAIL_MAX < K <= seg_sort_limit() and behind DETBOX_TOPK_UNFUSED_TAIL (A/B timing).
+constexpr int TAIL_MAX = 2048;
+__global__ void __launch_bounds__(1024)
+topk_tail_kernel(const uint32_t *__restrict__ cand_keys, const uint32_t *__restrict__ cand_idx, long seg_len,
+                 const SegState *__restrict__ state, const uint32_t *__restrict__ cnt, int K, int N /*pow2 >= K*/,
+                 uint32_t *ckeys, uint32_t *cvals,
+                 const float *__restrict__ prob, int C, const float4 *__restrict__ deltas,
+                 const float4 *__restrict__ anchors, long A, int enc,
+                 float4 *__restrict__ boxes, float *__restrict__ probs_out, int64_t *__restrict__ img_ids,
+                 float4 *__restrict__ sel_anchors, int64_t *__restrict__ flat_idx, float *__restrict__ scores)
+{
+    __shared__ unsigned long long v[TAIL_MAX];
+    const int tid = threadIdx.x;
+    cand_select_body(blockIdx.x, cand_keys, cand_idx, seg_len, state, cnt, (long)K, ckeys, cvals);
+    __syncthreads();                                  // this block's own winners are now visible to all of its threads
+    const uint32_t *k = ckeys + (size_t)blockIdx.x * K, *x = cvals + (size_t)blockIdx.x * K;
+    for (int i = tid; i < N; i += 1024)
+        v[i] = i < K ? ((unsigned long long)k[i] << 32) | x[i] : ~0ull;
+    __syncthreads();
+    for (int size = 2; size <= N; size <<= 1) {
+        for (int j = size >> 1; j > 0; j >>= 1) {
+            for (int t = tid; t < (N >> 1); t += 1024) {
+                const int i = 2 * t - (t & (j - 1)), q = i + j;
+                const unsigned long long a = v[i], b = v[q];
+                const bool up = (i & size) == 0;
+                if ((a > b) == up) { v[i] = b; v[q] = a; }
+            }
+            __syncthreads();
+        }
+    }
+    for (int t = tid; t < K; t += 1024) {
+        const uint32_t key = (uint32_t)(v[t] >> 32), idx = (uint32_t)v[t];
+        const size_t i = (size_t)blockIdx.x * K + t;
+        const long a = idx % A;
+        const float4 anc = anchors[a];
+        boxes[i] = decode_box(anc, deltas[idx], enc);
+        if (img_ids) img_ids[i] = (int64_t)(idx / A);
+        if (sel_anchors) sel_anchors[i] = anc;
+        if (flat_idx) flat_idx[i] = (int64_t)idx;
+        if (scores) scores[i] = ordered_to_float(~key);
+        if (probs_out && C <= 4) for (int c = 0; c < C; ++c) probs_out[i * C + c] = prob[(size_t)idx * C + c];
+    }
+    if (probs_out && C > 4) {                         // wide rows (81 COCO classes): one warp per row, lanes across the classes
+        const int lane = tid & 31;
+        for (int t = tid >> 5; t < K; t += 32) {
+            const uint32_t idx = (uint32_t)v[t];
+            const float *src = prob + (size_t)idx * C;
+            float *dst = probs_out + ((size_t)blockIdx.x * K + t) * C;
+            for (int c = lane; c < C; c += 32) dst[c] = src[c];
+        }
     }
 }
 
@@ -624,6 +689,15 @@ extern "C" int detbox_topk_decode(const float *prob, int C, const float *deltas,
         if (!scalar_part) partition_kernel<true><<<pgrid, TK_THREADS, 0, st>>>(keys, p.seg_len, state, p.K, cka, cva, cand_keys, cand_idx, part_cnt);
         else partition_kernel<false><<<pgrid, TK_THREADS, 0, st>>>(keys, p.seg_len, state, p.K, cka, cva, cand_keys, cand_idx, part_cnt);
         DETBOX_LAUNCH_CHECK();
+        static const bool unfused_tail = getenv("DETBOX_TOPK_UNFUSED_TAIL") != nullptr;
+        if (p.K <= TAIL_MAX && !unfused_tail) {
+            int N = 2; while (N < p.K) N <<= 1;
+            topk_tail_kernel<<<p.n_seg, 1024, 0, st>>>(cand_keys, cand_idx, p.seg_len, state, part_cnt, (int)p.K, N, cka, cva,
+                                                      prob, C, (const float4 *)deltas, (const float4 *)anchors, A, enc,
+                                                      (float4 *)boxes, probs_out, img_ids, (float4 *)sel_anchors, flat_idx, scores);
+            DETBOX_LAUNCH_CHECK();
+            return DETBOX_OK;
+        }
         cand_select_kernel<<<p.n_seg, 1024, 0, st>>>(cand_keys, cand_idx, p.seg_len, state, part_cnt, p.K, cka, cva);
         DETBOX_LAUNCH_CHECK();
     } else {

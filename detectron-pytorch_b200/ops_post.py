@@ -73,10 +73,13 @@ def topk_decode(rpn_box, rpn_prob, anchors, top_n, activation="softmax", box_enc
                                    _ptr(out.get("img_ids")), _ptr(out.get("anchors")), _ptr(out.get("flat_idx")),
                                    _ptr(out.get("scores")), ws.data_ptr(), ws.numel(), _stream()), "topk_decode")
     # kernels launched (memsets not counted): init, objectness, select, then
+    #   k <= 2048: partition, then ONE tail kernel (candidate select + per-segment sort + gather/decode) -> 5
     #   k <= the one-block sort's limit (4096 by default): partition, candidate select, per-segment sort -> 7 with the gather
     #   else     : 2 x (refine, select), count / scan / write, 13-launch radix sort (+3 per image-id pass)
     k_seg = min(int(top_n), A if per_image else B * A)
-    _count(7 if k_seg <= int(os.environ.get('DETBOX_SEG_SORT_LIMIT', 4096)) else 24 + (3 if per_image and B > 1 else 0))
+    limit = int(os.environ.get('DETBOX_SEG_SORT_LIMIT', 4096))
+    fused_tail = k_seg <= min(2048, limit) and 'DETBOX_TOPK_UNFUSED_TAIL' not in os.environ
+    _count(5 if fused_tail else 7 if k_seg <= limit else 24 + (3 if per_image and B > 1 else 0))
     return out
 
 
