@@ -375,7 +375,8 @@ colmax_kernel(const TargetParams p, int n_slices, int total_gt)
 }
 
 // label and regression flag of one anchor from its row summary — anchor.py:49-62,86-87
-__device__ __forceinline__ void label_of(const TargetParams &p, float gcls, double mo, bool promoted, double isum,
+template <class P>                                  // P: anything with bg / fg / ign / clobber (TargetParams, LabelRule)
+__device__ __forceinline__ void label_of(const P &p, float gcls, double mo, bool promoted, double isum,
                                          float &l_out, bool &flag_out)
 {
     float l = gcls;                                                         // anchor.py:49
@@ -436,6 +437,120 @@ __device__ __forceinline__ bool tab_targets(const PyrDev &y, const float2 *__res
     const float2 Y = __ldg(tb + y.eoff[l] + y.rowlen[l] + row * y.ncell[l] + cell);
     t = make_float4(X.x, Y.x, X.y, Y.y);
     return (__float_as_int(X.y) != TAB_SENT) & (__float_as_int(Y.y) != TAB_SENT);
+}
+
+// ---- decide phase for 33 .. GCH GT per image (one staged chunk, several 32-GT mask words per slice) -------------------
+// anchor_target_kernel's common path (at most 32 GT: one mask word per slice, everything in registers) sits exactly at 64
+// registers and ~2,900 instructions, and both are load-bearing (four blocks per SM; the kernel is sensitive to its code
+// size): folding a loop over mask words into it cost 10-13 % at G = 12 (profiles/r02_anchor_target_experiments.txt).
+// Images with more GT therefore take this FUNCTION — not inlined, so it has a register allocation of its own and the
+// common path is unchanged to the instruction: the same cull-up-front + float32 screen + exact fallback, over
+// nw = ceil(G / 32) words.  Before, such images went through the chunked loop: no up-front cull, no screen, exact
+// float64 for every (slice, GT) hit.  Writes s_res for the touched slices and the OR of a slice's words into s_any
+// (the emit phase's "skipped" test); returns the thread's (fg, bg) counts.
+struct LabelRule { double bg, fg, ign; int clobber; };
+constexpr int AT_MW = GCH / 32;
+template <bool SCREEN>
+__device__ __noinline__ int2 decide_multi(const LabelRule rule, const float4 *__restrict__ anchors, const long A, const long tile0,
+                                          const float *__restrict__ gt_img /* the image's first GT row */, const int G,
+                                          const GtChunk *__restrict__ smp, const float4 *__restrict__ s_wbb,
+                                          int2 (*__restrict__ s_res)[AT_THREADS], unsigned (*__restrict__ s_any)[AT_WARPS],
+                                          const int zero_any, const float l_zero, const int flag_zero)
+{
+    __shared__ unsigned s_mw[AT_MW][AT_ITEMS][AT_WARPS];
+    const GtChunk &sm = *smp;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const int nw = (G + 31) >> 5;
+    const float INF = __int_as_float(0x7f800000);
+#pragma unroll 1
+    for (int i = 0; i < AT_ITEMS; ++i) {
+        const float4 wbb = s_wbb[i * AT_WARPS + w];
+        unsigned any = 0;
+#pragma unroll 1
+        for (int wd = 0; wd < nw; ++wd) {
+            const int j = wd * 32 + lane;
+            const unsigned m = __ballot_sync(0xffffffffu, j < G && may_touch32(wbb, sm.fbox[min(j, GCH - 1)]));
+            if (lane == 0) s_mw[wd][i][w] = m;
+            any |= m;
+        }
+        if (lane == 0) s_any[i][w] = any;
+    }
+    __syncwarp();
+    int nfg = 0, nbg = 0;
+#pragma unroll 1
+    for (int i = 0; i < AT_ITEMS; ++i) {
+        if (s_any[i][w] == 0) continue;
+        const long a = tile0 + i * AT_THREADS + tid;
+        const bool valid = a < A;
+        const float4 anc = valid ? anchors[a] : make_float4(INF, INF, -INF, -INF);
+        double best = 0.0, isum = 0.0;
+        int best_g = 0;
+        bool promoted = zero_any != 0;
+        bool amb = !SCREEN;
+        float best32 = 0.0f, second32 = 0.0f, isum32 = 0.0f; int bj = 0;
+        if (SCREEN) {                                            // the float32 screen of the kernel, word after word
+            const float aw = anc.z - anc.x + 1.0f, ah = anc.w - anc.y + 1.0f, aarea32 = aw * ah;
+            if (valid && !(aw >= SCR_T && ah >= SCR_T)) amb = true;
+#pragma unroll 1
+            for (int wd = 0; wd < nw; ++wd) {
+                unsigned mm = s_mw[wd][i][w];
+                while (mm) {                                     // ascending GT index, like the exact loop
+                    const int j = wd * 32 + __ffs(mm) - 1;
+                    mm &= mm - 1;
+                    const float4 g = sm.fbox[j];
+                    const float iw = fminf(anc.z, g.z) - fmaxf(anc.x, g.x) + 1.0f, ih = fminf(anc.w, g.w) - fmaxf(anc.y, g.y) + 1.0f;
+                    if (iw <= -SCR_T || ih <= -SCR_T) continue;
+                    if (!(iw >= SCR_T && ih >= SCR_T)) { amb = true; continue; }
+                    const float inter = iw * ih, ua = aarea32 + sm.area32[j] - inter;
+                    const float ov = __fdividef(inter, ua);
+                    if (!(ua > 0.0f && ov < 2.0f && ov < sm.cmlo[j])) amb = true;
+                    if (ov > best32) { second32 = best32; best32 = ov; bj = j; } else second32 = fmaxf(second32, ov);
+                    if (sm.cls[j] < 0.0f) isum32 += __fdividef(inter, aarea32);
+                }
+            }
+            if (best32 > 0.0f) {
+                amb |= !(second32 < best32 * (1.0f - SCR_M));
+                amb |= scr_near(best32, (float)rule.bg) | scr_near(best32, (float)rule.fg) | scr_near(best32, 0.5f);
+                amb |= isum32 > 0.0f ? scr_near(isum32, (float)rule.ign) : !(isum32 == 0.0f);
+            }
+        }
+        if (__any_sync(0xffffffffu, amb)) {                      // exact, the whole slice (bbox.pyx:33-54, anchor.py:42-46,81-85)
+            const double ax1 = anc.x, ay1 = anc.y, ax2 = anc.z, ay2 = anc.w;
+            const double aarea = (ax2 - ax1 + 1) * (ay2 - ay1 + 1);
+#pragma unroll 1
+            for (int wd = 0; wd < nw; ++wd) {
+                unsigned m = s_mw[wd][i][w];
+                while (m) {
+                    const int j = wd * 32 + __ffs(m) - 1;
+                    m &= m - 1;
+                    double ov = 0.0;
+                    const double iw = fmin(ax2, sm.x2[j]) - fmax(ax1, sm.x1[j]) + 1;
+                    if (iw > 0) {
+                        const double ih = fmin(ay2, sm.y2[j]) - fmax(ay1, sm.y1[j]) + 1;
+                        if (ih > 0) {
+                            const double inter = iw * ih;
+                            const double ua = aarea + sm.area[j] - inter;
+                            ov = inter / ua;
+                            if (sm.cls[j] < 0.0f) isum = isum + inter / aarea;
+                        }
+                    }
+                    if (ov > 0.0) {
+                        if (ov > best) { best = ov; best_g = j; }
+                        if (valid && iou_bits(ov) == sm.colmax[j]) promoted = true;
+                    }
+                }
+            }
+        } else { best = (double)best32; best_g = bj; isum = (double)isum32; }
+        float l = l_zero; bool flag = flag_zero != 0;
+        int g = 0;
+        if (best > 0.0) {
+            g = best_g;
+            label_of(rule, gt_img[(size_t)g * 5 + 4], best, promoted, isum, l, flag);
+        }
+        s_res[i][tid] = make_int2(__float_as_int(l), g | (flag ? (int)0x80000000 : 0));
+        if (valid) { nfg += (l >= 1.0f); nbg += (l == 0.0f); }
+    }
+    return make_int2(nfg, nbg);
 }
 
 // EMIT_ILP: anchors encoded side by side in the emit loops; MINB: blocks per SM; TABLE: GT-0 targets come from the
@@ -606,6 +721,14 @@ anchor_target_kernel(const TargetParams p)
     // independent bounding-box loads and ballots — instead of one dependent load per slice inside the loop.
     __shared__ unsigned smask[AT_ITEMS][AT_WARPS];
     const bool use_masks = G <= 32;
+    const bool multi = single && !use_masks;         // 33 .. GCH GT: decide_multi() (its own register allocation)
+    const bool have_masks = single;                  // smask[i][w] == 0 <=> no GT near the slice (both routes)
+    if (multi) {
+        LabelRule rule; rule.bg = p.bg; rule.fg = p.fg; rule.ign = p.ign; rule.clobber = p.clobber;
+        const int2 c = decide_multi<SCREEN>(rule, p.anchors, p.A, tile0, p.gt + (size_t)g0 * 5, G, &sm, s_wbb, s_res, smask,
+                                            zero_any, l_zero, flag_zero ? 1 : 0);
+        nfg = c.x; nbg = c.y;
+    }
     if (use_masks) {
 #pragma unroll
         for (int i = 0; i < AT_ITEMS; ++i) {
@@ -624,7 +747,7 @@ anchor_target_kernel(const TargetParams p)
     //  the common path (17 % of the kernel's instructions) but only 1 % of its time at G = 12 (7 % at G = 32): the
     //  arithmetic of this loop is hidden, its per-slice latency chain is not.  profiles/r02_anchor_target_experiments.txt)
 #pragma unroll 1
-    for (int i = 0; i < AT_ITEMS; ++i) {
+    for (int i = 0; i < (multi ? 0 : AT_ITEMS); ++i) {
         if (use_masks && smask[i][w] == 0) continue;             // no GT near this slice: the emit phase uses (l_zero, GT 0)
         const long a = tile0 + i * AT_THREADS + tid;
         const bool valid = a < p.A;
@@ -728,7 +851,7 @@ anchor_target_kernel(const TargetParams p)
 #pragma unroll 1
         for (int h = 0; h < AT_ITEMS; ++h) {
             const int off = h * AT_THREADS + tid;
-            const bool skipped = use_masks && smask[h][w] == 0;
+            const bool skipped = have_masks && smask[h][w] == 0;
             const int2 r = skipped ? r_zero : s_res[h][tid];
             nskip += (skipped && off < rem);
             const int g = r.y & 0x7fffffff;
@@ -755,7 +878,7 @@ anchor_target_kernel(const TargetParams p)
                 anc[i] = nxt[i];
                 const int noff = off + EMIT_ILP * AT_THREADS;
                 if (MINB < 4) nxt[i] = (h + EMIT_ILP < AT_ITEMS && noff < rem) ? anc_t[noff] : make_float4(0, 0, 0, 0);
-                const bool skipped = use_masks && smask[h + i][w] == 0;
+                const bool skipped = have_masks && smask[h + i][w] == 0;
                 r[i] = skipped ? r_zero : s_res[h + i][tid];
                 nskip += (skipped && off < rem);
                 const int g = r[i].y & 0x7fffffff;

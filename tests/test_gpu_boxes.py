@@ -439,14 +439,16 @@ def test_anchor_target_64_real_citypersons_images(cpr_anchors, golden):
     assert np.array_equal(labels.numpy(), lab) and np.array_equal(lw.numpy(), got[1]) and np.array_equal(bw.numpy(), got[3])
 
 
+@pytest.mark.parametrize("fill", [0, 30, 110])
 @pytest.mark.parametrize("seed", range(3))
-def test_anchor_target_decide_screen_adversarial(seed):
+def test_anchor_target_decide_screen_adversarial(seed, fill):
     """The float32 screen of the decide phase must hand every undecidable case to the exact float64 path.  GT sets built
     FROM anchors so that the cases sit exactly on the screen's boundaries: a GT equal to an anchor (IoU 1 = its column
     maximum: promotion), the same GT twice (argmax tie: first maximum wins), GT that touch an anchor exactly (iw = 0),
     overlap it by exactly one pixel column (iw = 1), by 1e-4 (inside the undecided band) and by -1e-4, GT scaled so that
     the IoU with an anchor lands on the thresholds 0.5 / 0.6 up to rounding, ignore regions whose intersection fraction
-    lands on 0.3.  Labels / weights bit-exact against the oracle, as everywhere."""
+    lands on 0.3.  Labels / weights bit-exact against the oracle, as everywhere.  fill > 0 appends random GT rows so that
+    the image has 33 .. 128 GT and takes the several-mask-words route (decide_multi) with the same boundary cases."""
     rng = np.random.RandomState(900 + seed)
     scales = [[2, 2.52, 3.175], [4, 5.04, 6.349], [8, 10.079, 12.7]]
     anc = O.anchor_pyramid([8, 16, 32], 160, 256, scales, [1, 2.5], 16).astype(np.float32)
@@ -466,6 +468,8 @@ def test_anchor_target_decide_screen_adversarial(seed):
         gt = np.concatenate([np.asarray(rows, np.float64), np.ones((len(rows), 1))], 1)
         ign = [a[5, 0], a[5, 1], a[5, 0] + w[5] * 0.3 - 1, a[5, 3], -1]           # covers 0.3 of anchor 5
         gt = np.concatenate([gt, np.asarray([ign])], 0).astype(np.float32)
+        if fill:
+            gt = np.concatenate([gt, synth_gt(rng, fill, 160, 256, 0.2, ncls=2)], 0).astype(np.float32)
         gts.append(gt[rng.permutation(gt.shape[0])] if seed else gt)
     got = run_target(anc, gts, cfg)
     for b, gt in enumerate(gts):
