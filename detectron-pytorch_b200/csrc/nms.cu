@@ -19,7 +19,6 @@
 //      mask rows and bitsets in shared memory; one segment: a cooperative grid with grid.sync
 //      between rounds.  The fixed point is unique, so the result is the exact greedy set.
 //   5. ordered compaction of the kept bits into original indices + per-segment counts.
-#include <cstdlib>
 #include <mutex>
 #include <cooperative_groups.h>
 #include "sort.cuh"
@@ -67,7 +66,11 @@ __device__ __forceinline__ bool pair_suppresses(const NmsCmp &c, const float4 &a
         return suppresses(c, inter / uni) || (double)(inter / barea) > 0.95 || (double)(inter / aarea) > 0.95;
     }
     if (c.fast && uni > 1e-30f && uni < 1e30f) {
-        const float q = __fdividef(inter, uni);
+        // (uni is a normal number here: the bare MUFU.RCP, without __fdividef's rescaling of huge divisors — six
+        //  instructions of the ~50 of a candidate pair; the same <= 2 ulp the band below allows for)
+        float y;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(uni));
+        const float q = inter * y;
         if (q > c.q_hi) return true;
         if (q < c.q_lo) return false;
     }
@@ -123,19 +126,11 @@ __global__ void nms_seg_scan_kernel(int32_t *seg_off, int n_seg)
 constexpr int MASK_CT = 4;     // column tiles staged per iteration (one per 64-thread group)
 constexpr int MASK_RT = 2;     // row tiles per block: every staged column box is tested against 2 rows per
                                // thread, so the shared-memory read (the limiter at 1 row) is amortised
-// Narrow phase, warp-cooperative: the broad phase leaves every lane a different number of candidate pairs (a handful
-// per 64 columns on detection-shaped input), and a per-lane loop runs max-over-lanes trips with most lanes idle
-// (ncu, round 1: 20 of 32 lanes active over the kernel).  Instead the warp's candidates — (row of the block, column
-// of the tile) in 13 bits — are appended to a per-warp queue in shared memory at offsets from a warp scan, the lanes
-// then take queue entries round-robin (row box from the block's staged rows, column box from the staged tile) and
-// OR the outcome into the row's result word with a shared-memory atomic.  More than MASK_QCAP candidates in one
-// warp trip (near-duplicate boxes, thr <= 0, the multi-anchor variant) keep the per-lane loop, which is dense then.
-constexpr int MASK_QCAP = 512;
 
 template <int VARIANT>
 __global__ void __launch_bounds__(64 * MASK_CT)
 nms_mask_kernel(const float4 *__restrict__ boxes, const int32_t *__restrict__ seg, const int32_t *__restrict__ seg_off,
-                int n, int ncol, int cg, NmsCmp cmp, u64 *__restrict__ mask, const bool coop_off)
+                int n, int ncol, int cg, NmsCmp cmp, u64 *__restrict__ mask)
 {
     const int rt0 = blockIdx.y * MASK_RT;
     const int rt_last = min(rt0 + MASK_RT, ncol) - 1;
@@ -147,11 +142,7 @@ nms_mask_kernel(const float4 *__restrict__ boxes, const int32_t *__restrict__ se
     __shared__ float4 cb[64 * MASK_CT];
     __shared__ float4 ccull[64 * MASK_CT];      // (-(x1 - 1 rounded down), -(y1 - 1 down), x2 + 1 up, y2 + 1 up)
     __shared__ float carea[64 * MASK_CT];
-    __shared__ float4 s_row[64 * MASK_RT];      // the block's row boxes and areas, for the cooperative narrow phase
-    __shared__ float s_rarea[64 * MASK_RT];
-    __shared__ unsigned s_out[MASK_CT][64 * MASK_RT][2];
-    __shared__ unsigned short s_queue[2 * MASK_CT][MASK_QCAP];
-    const int tid = threadIdx.x, sub = tid >> 6, rl = tid & 63, lane = tid & 31;
+    const int tid = threadIdx.x, sub = tid >> 6, rl = tid & 63;
     float4 a[MASK_RT]; float aarea[MASK_RT]; int astart[MASK_RT];
 #pragma unroll
     for (int k = 0; k < MASK_RT; ++k) {
@@ -162,7 +153,6 @@ nms_mask_kernel(const float4 *__restrict__ boxes, const int32_t *__restrict__ se
             a[k] = boxes[r]; aarea[k] = (a[k].z - a[k].x + 1) * (a[k].w - a[k].y + 1);
             if (seg) astart[k] = seg_off[seg[r]];
         }
-        if (sub == 0) { s_row[k * 64 + rl] = a[k]; s_rarea[k * 64 + rl] = aarea[k]; }    // (published by the first __syncthreads below)
     }
     for (int ct_lo = ct_base + (int)blockIdx.x * cg; ct_lo <= rt_last; ct_lo += (int)gridDim.x * cg) {
     const int ct_hi = min(rt_last, ct_lo + cg - 1);
@@ -212,65 +202,27 @@ nms_mask_kernel(const float4 *__restrict__ boxes, const int32_t *__restrict__ se
                 }
             }
         }
-        // candidate words of this lane's rows: [k][half]; act: the row has a word to write in this column tile
-        unsigned cw[MASK_RT][2]; bool act[MASK_RT];
-        int cnt = 0;
 #pragma unroll
         for (int k = 0; k < MASK_RT; ++k) {
             const int rt = rt0 + k, r = rt * 64 + rl;
             const int lb = astart[k] - ct * 64;                    // columns below bit lb belong to earlier segments
-            act[k] = !(r >= n || ct > rt || lb >= 64);
+            if (r >= n || ct > rt || lb >= 64) continue;
             u64 cand = ((u64)hi[k] << 32) | lo[k];
             if (cmp.nonpos || VARIANT == DETBOX_NMS_VARIANT_MULTIANCHOR) cand = ~0ull;   // empty intersections matter too
             if (ct == rt) cand &= (1ull << rl) - 1ull;             // diagonal tile: only j < i
-            if (lb > 0) cand &= ~0ull << (lb & 63);
-            if (!act[k]) cand = 0ull;
-            cw[k][0] = (unsigned)cand; cw[k][1] = (unsigned)(cand >> 32);
-            cnt += __popc(cw[k][0]) + __popc(cw[k][1]);
-        }
-        int incl = cnt;                                            // inclusive warp scan of the candidate counts
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += y; }
-        const int total = __shfl_sync(0xffffffffu, incl, 31);
-        unsigned res[MASK_RT][2];
-        if (total <= MASK_QCAP && !coop_off) {
-            unsigned short *q = s_queue[tid >> 5];
-            int pos = incl - cnt;
-#pragma unroll
-            for (int k = 0; k < MASK_RT; ++k)
-#pragma unroll
-                for (int hf = 0; hf < 2; ++hf) {
-                    s_out[sub][k * 64 + rl][hf] = 0u;
-                    for (unsigned c32 = cw[k][hf]; c32; c32 &= c32 - 1)
-                        q[pos++] = (unsigned short)((k * 64 + rl) | ((hf * 32 + __ffs((int)c32) - 1) << 7));
-                }
-            __syncwarp();
-            for (int t = lane; t < total; t += 32) {
-                const unsigned e = q[t];
-                const int ri = e & 127, col = e >> 7;
-                if (pair_suppresses<VARIANT>(cmp, s_row[ri], s_rarea[ri], cb[cbase + col], carea[cbase + col]))
-                    atomicOr(&s_out[sub][ri][col >> 5], 1u << (col & 31));
+            if (lb > 0) cand &= ~0ull << lb;
+            // narrow phase, one 32-bit half at a time (32-bit find-first-set / clear-lowest are 1/3 of the 64-bit cost)
+            unsigned wlo = 0, whi = 0;
+            for (unsigned c32 = (unsigned)cand; c32; c32 &= c32 - 1) {
+                const int i = __ffs((int)c32) - 1;
+                if (pair_suppresses<VARIANT>(cmp, a[k], aarea[k], cb[cbase + i], carea[cbase + i])) wlo |= 1u << i;
             }
-            __syncwarp();
-#pragma unroll
-            for (int k = 0; k < MASK_RT; ++k) { res[k][0] = s_out[sub][k * 64 + rl][0]; res[k][1] = s_out[sub][k * 64 + rl][1]; }
-        } else {
-            // per-lane loop, one 32-bit half at a time (32-bit find-first-set / clear-lowest are 1/3 of the 64-bit cost)
-#pragma unroll
-            for (int k = 0; k < MASK_RT; ++k)
-#pragma unroll
-                for (int hf = 0; hf < 2; ++hf) {
-                    unsigned wv = 0;
-                    for (unsigned c32 = cw[k][hf]; c32; c32 &= c32 - 1) {
-                        const int i = __ffs((int)c32) - 1;
-                        if (pair_suppresses<VARIANT>(cmp, a[k], aarea[k], cb[cbase + hf * 32 + i], carea[cbase + hf * 32 + i])) wv |= 1u << i;
-                    }
-                    res[k][hf] = wv;
-                }
+            for (unsigned c32 = (unsigned)(cand >> 32); c32; c32 &= c32 - 1) {
+                const int i = __ffs((int)c32) - 1;
+                if (pair_suppresses<VARIANT>(cmp, a[k], aarea[k], cb[cbase + 32 + i], carea[cbase + 32 + i])) whi |= 1u << i;
+            }
+            mask[(size_t)r * ncol + ct] = ((u64)whi << 32) | wlo;
         }
-#pragma unroll
-        for (int k = 0; k < MASK_RT; ++k)
-            if (act[k]) mask[(size_t)(row0 + k * 64 + rl) * ncol + ct] = ((u64)res[k][1] << 32) | res[k][0];
     }
     }
 }
@@ -518,16 +470,18 @@ int nms_sorted(const NmsBuffers &b, const uint32_t *order, long n, int n_seg,
     const bool small_segs = seg_sorted && n / n_seg <= 4096;
     const int cg = small_segs ? MASK_CT : 32;
     unsigned gx = (unsigned)((ncol + cg - 1) / cg);
-    if (small_segs) { const unsigned want = 2u * (unsigned)((n / n_seg + 255) / 256) + 2u; if (gx > want) gx = want; }
+    // (any gx is correct — a block strides over its row tiles' column chunks — but every block right of the diagonal
+    //  costs two dependent loads before it can exit: ceil(L / 256) chunks + 2 for the alignment of the first chunk and
+    //  a row-tile pair that straddles two segments; the grid used to be twice that, 3,400 of 4,500 blocks idle at 64 x 900)
+    if (small_segs) { const unsigned want = (unsigned)((n / n_seg + 255) / 256) + 2u; if (gx > want) gx = want; }
     dim3 grid(gx, (unsigned)((ncol + MASK_RT - 1) / MASK_RT));
-    static const bool coop_off = getenv("DETBOX_NMS_NOCOOP") != nullptr;    // per-lane narrow phase, for A/B timing and its own test
     DETBOX_TRACE_BEGIN(DETBOX_K_NMS_MASK, st);
     if (cmp.variant == DETBOX_NMS_VARIANT_PLAIN)
-        nms_mask_kernel<0><<<grid, 64 * MASK_CT, 0, st>>>(b.sorted, seg_sorted, seg_sorted ? seg_off : nullptr, (int)n, ncol, cg, cmp, b.mask, coop_off);
+        nms_mask_kernel<0><<<grid, 64 * MASK_CT, 0, st>>>(b.sorted, seg_sorted, seg_sorted ? seg_off : nullptr, (int)n, ncol, cg, cmp, b.mask);
     else if (cmp.variant == DETBOX_NMS_VARIANT_NEW)
-        nms_mask_kernel<1><<<grid, 64 * MASK_CT, 0, st>>>(b.sorted, seg_sorted, seg_sorted ? seg_off : nullptr, (int)n, ncol, cg, cmp, b.mask, coop_off);
+        nms_mask_kernel<1><<<grid, 64 * MASK_CT, 0, st>>>(b.sorted, seg_sorted, seg_sorted ? seg_off : nullptr, (int)n, ncol, cg, cmp, b.mask);
     else
-        nms_mask_kernel<2><<<grid, 64 * MASK_CT, 0, st>>>(b.sorted, seg_sorted, seg_sorted ? seg_off : nullptr, (int)n, ncol, cg, cmp, b.mask, coop_off);
+        nms_mask_kernel<2><<<grid, 64 * MASK_CT, 0, st>>>(b.sorted, seg_sorted, seg_sorted ? seg_off : nullptr, (int)n, ncol, cg, cmp, b.mask);
     DETBOX_TRACE_END(DETBOX_K_NMS_MASK, st);
     DETBOX_LAUNCH_CHECK();
     int dev = 0;
