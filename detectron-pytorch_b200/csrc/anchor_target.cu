@@ -798,13 +798,19 @@ anchor_target_kernel(const TargetParams p)
                     mm &= mm - 1;
                     const float4 g = sm.fbox[j];
                     const float iw = fminf(anc.z, g.z) - fmaxf(anc.x, g.x) + 1.0f, ih = fminf(anc.w, g.w) - fmaxf(anc.y, g.y) + 1.0f;
-                    if (iw <= -SCR_T || ih <= -SCR_T) continue;                       // certainly disjoint (padding lanes: -inf)
-                    if (!(iw >= SCR_T && ih >= SCR_T)) { amb = true; continue; }       // within rounding of touching, or NaN
+                    // no per-lane early exits (they diverge and cost convergence barriers): one warp-uniform skip, then
+                    // predicates.  dis: certainly disjoint (padding lanes: -inf); ok: certainly overlapping (false for NaN);
+                    // neither: within rounding of touching -> exact path.  A lane that is not `ok` contributes ov = 0,
+                    // which changes neither the maximum nor the runner-up.
+                    const bool dis = iw <= -SCR_T || ih <= -SCR_T;
+                    if (__all_sync(0xffffffffu, dis)) continue;
+                    const bool ok = iw >= SCR_T && ih >= SCR_T;
                     const float inter = iw * ih, ua = aarea32 + sm.area32[j] - inter;
-                    const float ov = __fdividef(inter, ua);
-                    if (!(ua > 0.0f && ov < 2.0f && ov < sm.cmlo[j])) amb = true;     // odd union / may equal the column maximum
+                    const float ovr = __fdividef(inter, ua);
+                    amb |= !dis & !(ok && ua > 0.0f && ovr < 2.0f && ovr < sm.cmlo[j]);   // touching / odd union / may equal the column maximum
+                    const float ov = ok ? ovr : 0.0f;
                     if (ov > best32) { second32 = best32; best32 = ov; bj = j; } else second32 = fmaxf(second32, ov);
-                    if (sm.cls[j] < 0.0f) isum32 += __fdividef(inter, aarea32);
+                    if (sm.cls[j] < 0.0f) isum32 += ok ? __fdividef(inter, aarea32) : 0.0f;
                 }
                 if (best32 > 0.0f) {
                     amb |= !(second32 < best32 * (1.0f - SCR_M));

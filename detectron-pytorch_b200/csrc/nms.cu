@@ -211,15 +211,44 @@ nms_mask_kernel(const float4 *__restrict__ boxes, const int32_t *__restrict__ se
             if (cmp.nonpos || VARIANT == DETBOX_NMS_VARIANT_MULTIANCHOR) cand = ~0ull;   // empty intersections matter too
             if (ct == rt) cand &= (1ull << rl) - 1ull;             // diagonal tile: only j < i
             if (lb > 0) cand &= ~0ull << lb;
-            // narrow phase, one 32-bit half at a time (32-bit find-first-set / clear-lowest are 1/3 of the 64-bit cost)
+            // narrow phase, one 32-bit half at a time (32-bit find-first-set / clear-lowest are 1/3 of the 64-bit cost).
+            // Plain variant: a branch-free first pass decides every candidate whose approximate quotient is outside the
+            // band around the threshold (pair_suppresses' own rule, same arithmetic) and collects the others in `und`;
+            // the full routine then runs for those only.  On clustered detections a third of all pairs reach this loop
+            // (profiles/r02_nms_mask_experiments.txt), so its length is the kernel's: boxes by value, no early returns.
+            const bool fast = VARIANT == DETBOX_NMS_VARIANT_PLAIN && cmp.fast && !cmp.nonpos;
             unsigned wlo = 0, whi = 0;
-            for (unsigned c32 = (unsigned)cand; c32; c32 &= c32 - 1) {
-                const int i = __ffs((int)c32) - 1;
-                if (pair_suppresses<VARIANT>(cmp, a[k], aarea[k], cb[cbase + i], carea[cbase + i])) wlo |= 1u << i;
-            }
-            for (unsigned c32 = (unsigned)(cand >> 32); c32; c32 &= c32 - 1) {
-                const int i = __ffs((int)c32) - 1;
-                if (pair_suppresses<VARIANT>(cmp, a[k], aarea[k], cb[cbase + 32 + i], carea[cbase + 32 + i])) whi |= 1u << i;
+#pragma unroll
+            for (int hf = 0; hf < 2; ++hf) {
+                const unsigned cw = hf ? (unsigned)(cand >> 32) : (unsigned)cand;
+                const int col0 = cbase + hf * 32;
+                unsigned res = 0, und = cw;
+                if (fast) {
+                    und = 0;
+                    const float4 ar = a[k]; const float aa = aarea[k];
+                    const float qhi = cmp.q_hi, qlo = cmp.q_lo;
+                    for (unsigned c32 = cw; c32; c32 &= c32 - 1) {
+                        const int i = __ffs((int)c32) - 1;
+                        const float4 b = cb[col0 + i];
+                        const float ba = carea[col0 + i];
+                        const float w = fmaxf(0.0f, fminf(ar.z, b.z) - fmaxf(ar.x, b.x) + 1), h = fmaxf(0.0f, fminf(ar.w, b.w) - fmaxf(ar.y, b.y) + 1);
+                        const float inter = w * h;
+                        const float uni = ba + aa - inter;                  // (area_i + area_j) - inter, b is `i`
+                        float y;
+                        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(uni));
+                        const float q = inter * y;
+                        const bool rng = uni > 1e-30f && uni < 1e30f;
+                        const bool yes = q > qhi, no = q < qlo;      // (yes implies inter > 0: q_hi > 0)
+                        const unsigned bit = 1u << i;
+                        if (rng & yes) res |= bit;
+                        if (!(rng & (yes | no)) & (inter > 0.0f)) und |= bit;
+                    }
+                }
+                for (; und; und &= und - 1) {
+                    const int i = __ffs((int)und) - 1;
+                    if (pair_suppresses<VARIANT>(cmp, a[k], aarea[k], cb[col0 + i], carea[col0 + i])) res |= 1u << i;
+                }
+                if (hf) whi = res; else wlo = res;
             }
             mask[(size_t)r * ncol + ct] = ((u64)whi << 32) | wlo;
         }
