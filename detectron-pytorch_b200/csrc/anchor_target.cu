@@ -1061,7 +1061,15 @@ extern "C" int detbox_anchor_target_ex(const float *anchors, long A, const detbo
         DETBOX_LAUNCH_CHECK();
         DETBOX_TRACE_BEGIN(DETBOX_K_TARGET_COLMAX, st);
         const int n_slices = (int)n_tiles * AT_ITEMS * AT_WARPS;
-        colmax_kernel<<<dim3((unsigned)((n_slices + CM_SLICES - 1) / CM_SLICES), (unsigned)((total_gt + CM_GT - 1) / CM_GT)), CM_THREADS, 0, st>>>(p, n_slices, (int)total_gt);
+        // slices per block: at most CM_SLICES, fewer when three blocks per SM allow it (CP-R, 64 x 12 GT: 18 x 24 = 432 blocks
+        // instead of 16 x 24 = 384 = 2.6 per SM, an uneven single wave).  Measured 0.051 -> 0.047 ms; 4 / 6 / 8 blocks per SM
+        // 0.055 / 0.049 / 0.050 ms: more blocks also means more copies of the cull and a weaker running-maximum screen.
+        const long cm_gy = (total_gt + CM_GT - 1) / CM_GT;
+        long cm_gx = (n_slices + CM_SLICES - 1) / CM_SLICES;
+        static const int cm_wave = getenv("DETBOX_CM_WAVE") ? atoi(getenv("DETBOX_CM_WAVE")) : 3;     // blocks per SM aimed at (0: off)
+        if (cm_wave > 0 && (long)kNumSMs * cm_wave / cm_gy > cm_gx) cm_gx = (long)kNumSMs * cm_wave / cm_gy;
+        if (cm_gx > n_slices) cm_gx = n_slices;
+        colmax_kernel<<<dim3((unsigned)cm_gx, (unsigned)cm_gy), CM_THREADS, 0, st>>>(p, n_slices, (int)total_gt);
         DETBOX_TRACE_END(DETBOX_K_TARGET_COLMAX, st);
         DETBOX_LAUNCH_CHECK();
     }
