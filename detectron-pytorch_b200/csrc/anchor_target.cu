@@ -730,13 +730,17 @@ anchor_target_kernel(const TargetParams p)
         nfg = c.x; nbg = c.y;
     }
     if (use_masks) {
-#pragma unroll
-        for (int i = 0; i < AT_ITEMS; ++i) {
-            const float4 wbb = wbb_base[i * AT_WARPS];
-            const unsigned m = __ballot_sync(0xffffffffu, lane < G && may_touch32(wbb, sm.fbox[lane]));
-            if (lane == 0) smask[i][w] = m;
-        }
-        __syncwarp();
+        // four threads per slice (64 slices = 256 threads), each testing every fourth GT against the slice's box, the
+        // partial masks combined by two shuffles: G / 4 short trips per thread instead of eight 32-lane ballots per
+        // warp with at most G useful lanes each (6.5 M of the kernel's 105 M warp instructions at G = 12)
+        static_assert(AT_THREADS == 4 * AT_ITEMS * AT_WARPS, "one thread per (slice, GT quarter)");
+        const float4 wbb = s_wbb[tid >> 2];
+        unsigned m = 0;
+        for (int j = tid & 3; j < G; j += 4) m |= may_touch32(wbb, sm.fbox[j]) ? 1u << j : 0u;
+        m |= __shfl_xor_sync(0xffffffffu, m, 1);
+        m |= __shfl_xor_sync(0xffffffffu, m, 2);
+        if ((tid & 3) == 0) (&smask[0][0])[tid >> 2] = m;
+        __syncthreads();
     }
     // Decide phase.  One slice at a time keeps the float64 row state (argmax, ignore sum, area) of a single
     // anchor in registers; only slices some GT may touch load their anchors here.  With more than GCH GT the
