@@ -85,6 +85,8 @@ SIGNATURES = {
                                    c_void, c_void, c_size, c_void]),
     "detbox_roi_align_forward": (c_int, [ctypes.POINTER(RoiCfg), c_void, c_long, c_void, c_void, c_void]),
     "detbox_roi_align_backward": (c_int, [ctypes.POINTER(RoiCfg), c_void, c_long, c_void, c_void, c_int, c_void]),
+    "detbox_roi_align_backward_tiled_workspace_bytes": (c_size, [ctypes.POINTER(RoiCfg), c_long]),
+    "detbox_roi_align_backward_tiled": (c_int, [ctypes.POINTER(RoiCfg), c_void, c_long, c_void, c_void, c_void, c_size, c_void]),
     "detbox_roi_locality_order_workspace_bytes": (c_size, [c_long]),
     "detbox_roi_locality_order": (c_int, [c_void, c_long, c_void, P_float, c_int, c_float, c_float, c_void, c_void, c_size, c_void]),
     "detbox_assign_levels": (c_int, [c_void, c_long, P_float, c_int, c_void, c_void]),

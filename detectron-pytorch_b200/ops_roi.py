@@ -9,6 +9,13 @@ import torch
 from . import _lib
 from ._lib import check, lib
 from .ops import _ws, POOL, ROI_BIN_CENTRE, ROI_CROP_NORM, ROI_GRID_POINT, _count, _dev, _ptr, _stream  # noqa: F401
+import os
+
+# The tile-centric dense backward (detbox_roi_align_backward_tiled: every gradient map written once, deterministic summation
+# order, 1.6 GB of DRAM traffic instead of 2.9 GB at BASELINE configs[2]) runs at the scatter kernels' speed on B200 (0.76 ms
+# both), so the scatter path stays the default; roi_align_backward(..., deterministic=True) or DETBOX_ROI_BWD_TILED=1 selects it.
+_TILED_BWD = os.environ.get("DETBOX_ROI_BWD_TILED") is not None
+tiled_backward_calls = 0          # how often the tiled entry point ran (tests check that it really took a configuration)
 
 
 def _is_channels_last(t: torch.Tensor) -> bool:
@@ -117,12 +124,15 @@ def roi_align_forward(feats, rois, spatial_scales, ph, pw, mode=ROI_BIN_CENTRE, 
 
 
 def roi_align_backward(grad_out, feat_shapes, rois, spatial_scales, mode=ROI_BIN_CENTRE, levels=None,
-                       ref_areas=None, all_levels=False, channels_last=False, grads=None, pool=None, feats=None, order=None):
+                       ref_areas=None, all_levels=False, channels_last=False, grads=None, pool=None, feats=None, order=None,
+                       deterministic=None):
     """Gradient w.r.t. the feature maps (dense, zero-filled here unless `grads` is given, in which
     case it is accumulated into).  grad_out [R, C(or L*C), ph, pw] in the same memory format as the
     features.  pool='avg'|'max' differentiates the fused 2x2 pool of RoIAlignAvg/Max as well
     ('max' needs `feats`, the forward's feature maps, to recompute the arg-max).  Returns the list
-    of gradient maps."""
+    of gradient maps.  deterministic=True: the tile-centric dense kernel where it applies (NCHW, bin-centre / crop mode, no
+    pool, pooled size <= 8 x 8, `grads` not given) — bit-identical results from run to run, unlike the atomics of the
+    reference and of the default path."""
     r = _dev(rois).view(-1, 5)
     dev = r.device
     g = grad_out
@@ -157,6 +167,19 @@ def roi_align_backward(grad_out, feat_shapes, rois, spatial_scales, mode=ROI_BIN
         for l, f in enumerate(feats):
             c.feat[l] = f.data_ptr()
     lv = _dev(levels, torch.int32, "levels").view(-1) if levels is not None else None
+    if zero and not channels_last and POOL[pool] == 0 and not all_levels and int(mode) != ROI_GRID_POINT and \
+            (_TILED_BWD if deterministic is None else deterministic):
+        # the dense gradient written once, tile by tile (no memset, no atomics); configurations it does not cover fall through
+        nbytes = lib().detbox_roi_align_backward_tiled_workspace_bytes(ctypes.byref(c), r.shape[0])
+        ws = _ws.get(nbytes, dev)
+        rc = lib().detbox_roi_align_backward_tiled(ctypes.byref(c), r.data_ptr(), r.shape[0], _ptr(lv), g.data_ptr(),
+                                                   ws.data_ptr(), ws.numel(), _stream())
+        if rc != -4:                                  # DETBOX_ERR_UNSUPPORTED: not covered, use the scatter path
+            check(rc, "roi_align_backward_tiled")
+            global tiled_backward_calls
+            tiled_backward_calls += 1
+            _count(2 if r.shape[0] else 1)
+            return grads
     od = _auto_order(order, channels_last, all_levels, r, spatial_scales, [tuple(t.shape) for t in grads], lv, ref_areas)
     c.roi_order = _ptr(od) or None
     check(lib().detbox_roi_align_backward(ctypes.byref(c), r.data_ptr(), r.shape[0], _ptr(lv), g.data_ptr(), int(zero), _stream()),

@@ -313,6 +313,14 @@ int detbox_roi_align_forward(const detbox_roi_cfg *cfg, const float *rois_dev /*
 int detbox_roi_align_backward(const detbox_roi_cfg *cfg, const float *rois_dev, long R,
                               const int32_t *levels_dev, const float *grad_out_dev, int zero_grad,
                               void *stream);
+/* The same gradient as detbox_roi_align_backward(..., zero_grad = 1) — crop_and_resize.c:207-268 (CropAndResizeBackprop),
+ * crop_and_resize_kernel.cu:119-165, functions/crop_and_resize.py:34-47 — computed tile by tile of the OUTPUT: every grad_feat
+ * buffer is written exactly once, zeros included (no memset, no atomics, no read of the gradient; deterministic summation order:
+ * RoI index, bin row, bin column).  NCHW, bin-centre or normalised-crop mode, no pool, one level per RoI, pooled_h * pooled_w <= 320;
+ * anything else returns DETBOX_ERR_UNSUPPORTED and the caller uses detbox_roi_align_backward.  Workspace: 16 + 8 * (ph + pw) bytes per RoI. */
+size_t detbox_roi_align_backward_tiled_workspace_bytes(const detbox_roi_cfg *cfg, long R);
+int detbox_roi_align_backward_tiled(const detbox_roi_cfg *cfg, const float *rois_dev, long R, const int32_t *levels_dev,
+                                    const float *grad_out_dev, void *workspace_dev, size_t workspace_bytes, void *stream);
 /* A processing order for detbox_roi_cfg.roi_order that keeps overlapping RoIs close together in time: RoIs sorted by
  * (level, image, row band, column band) of their centre on an im_h x im_w canvas, so that the feature rows neighbouring
  * RoIs share are L2 hits instead of DRAM re-reads (the reference launches one thread per output element in RoI order,

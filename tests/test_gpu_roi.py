@@ -336,10 +336,86 @@ def test_nchw_staged_backward_opt_in_subprocess():
         "    gi = detbox.roi_align_backward(T.cu(g), [feat_shape], T.cu(rois), [0.25], m)[0].cpu().numpy()\n"
         "    T.assert_bwd_within_bound(gi, bwd(g, rois, np.float32(0.25), feat_shape), T.tap_stats(rois, 0.25, 7, 7, feat_shape, mode, g), float(np.abs(g).max()))\n"
         "print('staged backward ok')\n" % (root, os.path.join(root, "tests")))
-    for var in ("DETBOX_ROI_BWD_STAGED", "DETBOX_ROI_BWD_DIRECT", "DETBOX_ROI_BWD_GATHER"):
+    # (DETBOX_ROI_BWD_TILED=1 makes the tile-centric dense backward the default where it applies — it has a test of its own below)
+    for var in ("DETBOX_ROI_BWD_STAGED", "DETBOX_ROI_BWD_DIRECT", "DETBOX_ROI_BWD_GATHER", "DETBOX_ROI_BWD_TILED"):
         env = dict(os.environ, **{var: "1"})
         r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
         assert r.returncode == 0 and "staged backward ok" in r.stdout, var + "\n" + r.stdout + r.stderr
+
+
+def _bwd_both(g, shapes, rois, scales, mode, **kw):
+    """roi_align_backward through the tile-centric dense kernel and through the RoI-centric scatter kernels."""
+    import sys
+    mod = sys.modules[detbox.roi_align_backward.__module__]
+    before = mod.tiled_backward_calls
+    tiled = [t.cpu().numpy() for t in detbox.roi_align_backward(cu(g), shapes, cu(rois), scales, mode, deterministic=True, **kw)]
+    assert mod.tiled_backward_calls == before + 1, "the tiled entry point did not take this configuration"
+    tiled2 = [t.cpu().numpy() for t in detbox.roi_align_backward(cu(g), shapes, cu(rois), scales, mode, deterministic=True, **kw)]
+    scat = [t.cpu().numpy() for t in detbox.roi_align_backward(cu(g), shapes, cu(rois), scales, mode, deterministic=False, **kw)]
+    for a, b in zip(tiled, tiled2):
+        np.testing.assert_array_equal(a, b)                  # fixed summation order: bit-identical from run to run
+    return tiled, scat
+
+
+@pytest.mark.parametrize("case", ["pyramid_odd", "tiny_rois", "crowded_tile", "crop_norm", "no_rois", "partial_chunk"])
+def test_tiled_backward(case):
+    """detbox_roi_align_backward_tiled (roi_align_backward(deterministic=True): NCHW / bin-centre or normalised crop / no pool):
+    every gradient map written once, tile by tile.  Against the float64-derived bound of the oracle (crop_and_resize.c:207-268) and against the
+    scatter kernels; map sizes that are not multiples of the 8 x 32 tile, RoIs smaller than their 7 x 7 bins (more than two
+    bin columns per pixel: the generic column loop), more RoIs on one tile than one list round holds (accumulating rounds),
+    channel counts that are not a multiple of the 32-channel chunk, and R = 0 (all zeros)."""
+    rng = np.random.RandomState(sum(map(ord, case)))
+    mode, name = detbox.ROI_BIN_CENTRE, "tf"
+    B, C = 2, 40
+    if case == "pyramid_odd":
+        shapes = [(B, C, 61, 93), (B, C, 31, 47), (B, C, 16, 24), (B, C, 8, 12)]
+        scales = [np.float32(1.0 / s) for s in STRIDES]
+        rois = make_rois(rng, 300, B, 244, 372, 8, 300)
+        kw = dict(levels=cu(rng.randint(0, 4, 300).astype(np.int32)))
+    elif case == "tiny_rois":
+        shapes, scales = [(B, C, 40, 64)], [np.float32(0.25)]
+        rois = make_rois(rng, 200, B, 160, 256, 1.5, 14)          # 0.4 .. 3.5 feature pixels for 7 bins
+        kw = {}
+    elif case == "crowded_tile":
+        shapes, scales = [(1, 8, 24, 64)], [np.float32(0.25)]
+        rois = make_rois(rng, 700, 1, 40, 60, 20, 60)              # all 700 on the first tiles: 256-entry list rounds
+        kw = {}
+    elif case == "crop_norm":
+        mode, name = detbox.ROI_CROP_NORM, "crop"
+        shapes, scales = [(B, C, 50, 70)], [np.float32(1.0)]
+        y1, x1 = rng.uniform(-0.2, 0.8, 120), rng.uniform(-0.2, 0.8, 120)
+        rois = np.stack([rng.randint(0, B, 120), y1, x1, y1 + rng.uniform(0.05, 0.6, 120), x1 + rng.uniform(0.05, 0.6, 120)], 1).astype(np.float32)
+        kw = {}
+    elif case == "no_rois":
+        shapes, scales = [(B, C, 20, 40)], [np.float32(0.25)]
+        rois = np.zeros((0, 5), np.float32)
+        kw = {}
+    else:
+        shapes, scales = [(B, 37, 33, 65)], [np.float32(0.125)]
+        rois = make_rois(rng, 150, B, 264, 520, 16, 300)
+        kw = {}
+    Cc = shapes[0][1]
+    g = rng.normal(0, 1, (rois.shape[0], Cc, 7, 7)).astype(np.float32)
+    tiled, scat = _bwd_both(g, shapes, rois, scales, mode, **kw)
+    if case == "no_rois":
+        assert not tiled[0].any() and not scat[0].any()
+        return
+    lv = kw["levels"].cpu().numpy() if "levels" in kw else np.zeros(rois.shape[0], np.int64)
+    gmax = float(np.abs(g).max())
+    for l, shp in enumerate(shapes):
+        sel = lv == l
+        if name == "crop":
+            want = O.crop_and_resize_bwd(g[sel], rois[sel, 1:], rois[sel, 0].astype(np.int32), shp)
+            close(tiled[l], want, gmax * 8)
+            close(tiled[l], scat[l], gmax * 8)
+            continue
+        want = O.roi_align_tf_bwd(g[sel], rois[sel], scales[l], shp)
+        stats = tap_stats(rois, float(scales[l]), 7, 7, shp, name, g, sel)
+        assert_bwd_within_bound(tiled[l], want, stats, gmax)
+        assert_bwd_within_bound(scat[l], want, stats, gmax)
+        # untouched pixels are exact zeros in both (the tiled kernel writes them, the scatter path memsets them)
+        odd = (tiled[l] == 0) != (scat[l] == 0)
+        assert not odd.any() or max(np.abs(tiled[l][odd]).max(), np.abs(scat[l][odd]).max()) < 1e-6 * gmax
 
 
 def test_results_do_not_depend_on_the_roi_processing_order():
