@@ -841,6 +841,7 @@ roi_bwd_nchw_sep_kernel(const RoiArgs a)
 // warp-uniform (a warp is one tile row), the at most two bin columns landing on a pixel are found once per RoI.
 constexpr int RT_TH = 8, RT_TW = 32, RT_THREADS = RT_TH * RT_TW, RT_CH = 32, RT_CAP = 256, RT_NBMAX = 4, RT_J = 16;
 constexpr int RT_NC = 4;                         // listed RoIs whose weight tables are kept for the whole round
+constexpr int RT_NOTAP = -30000;
 constexpr int RT_PMAX = 8;                       // pooled size covered (7 x 7, 8 x 8); larger outputs keep the scatter kernels
 constexpr int RT_APITCH = RT_CH + 1;             // accumulator pitch: [pixel][33]
 struct RtTap { short i0, i1; float w; };          // i0 < 0: the bin samples nothing inside the map
@@ -884,15 +885,17 @@ roi_bwd_nchw_tile_kernel(const RoiArgs a, const int4 *__restrict__ hdr, const Rt
 {
     extern __shared__ __align__(16) float s_dynf[];               // accumulators [256 pixels][33], then grad_out [nb][RT_CH][bins]
     float *s_acc = s_dynf, *s_g = s_dynf + RT_THREADS * RT_APITCH;
-    // weight tables of a listed RoI against this tile: s_rw[slot][row][bin row], s_cw[slot][column][bin column] and, per row /
-    // column, the bit mask of the bins with a non-zero weight (the loops below walk set bits, not table entries).  Slots
+    // weight table of a listed RoI against this tile: s_rw[slot][row][bin row] and, per row, the bit mask of the bin rows with a
+    // non-zero weight (the loops below walk set bits, not table entries); the bin columns are walked tap by tap (s_ct).  Slots
     // 0 .. RT_NC-1 hold the first RT_NC RoIs of the list for the whole round (built once, used by every channel chunk);
     // later RoIs are rebuilt per chunk in slots RT_NC .. RT_NC+RT_NBMAX-1.
-    __shared__ float s_rw[RT_NC + RT_NBMAX][RT_TH][RT_PMAX], s_cw[RT_NC + RT_NBMAX][RT_TW][RT_PMAX];
-    __shared__ unsigned char s_rm[RT_NC + RT_NBMAX][RT_TH], s_cm[RT_NC + RT_NBMAX][RT_TW];
-    __shared__ int2 s_xr[RT_NC + RT_NBMAX];
+    __shared__ float s_rw[RT_NC + RT_NBMAX][RT_TH][RT_PMAX];
+    __shared__ unsigned char s_rm[RT_NC + RT_NBMAX][RT_TH];
+    __shared__ RtTap s_ct[RT_NC + RT_NBMAX][RT_PMAX];           // the bin columns' taps, pixel indices relative to the tile (i0 = RT_NOTAP: none)
+    __shared__ __align__(8) unsigned long long s_bar;            // completion of the bulk copies that stage grad_out
     __shared__ int s_list[RT_CAP];
     __shared__ __align__(16) unsigned short s_wc[RT_J][RT_THREADS / 32];
+    __shared__ __align__(16) unsigned short s_wany[RT_THREADS / 32];
     const detbox_roi_cfg &c = a.cfg;
     const int PH = c.pooled_h, PW = c.pooled_w, C = c.channels, bins = PH * PW;
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -911,6 +914,11 @@ roi_bwd_nchw_tile_kernel(const RoiArgs a, const int4 *__restrict__ hdr, const Rt
     // grad_out rows of a (RoI, chunk) are contiguous; 16-byte copies need every such block aligned and a whole number of pieces
     const bool vec16 = (((size_t)a.grad_out & 15) == 0) && (((size_t)C * bins) & 3) == 0 && ((bins * RT_CH) & 3) == 0 && (C % RT_CH == 0 || ((bins * (C % RT_CH)) & 3) == 0);
     const bool vecst = (W & 3) == 0 && (plane & 3) == 0 && (((size_t)c.grad_feat[l]) & 15) == 0;    // whole 16-byte quads
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"((unsigned)__cvta_generic_to_shared(&s_bar)) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    unsigned phase = 0;                                           // (the init is published by the barrier at the top of the first round)
     long base = 0;
     int round = 0;
     do {
@@ -918,7 +926,7 @@ roi_bwd_nchw_tile_kernel(const RoiArgs a, const int4 *__restrict__ hdr, const Rt
         //      would overflow the list, so rounds after the first — thousands of RoIs on one tile — accumulate into the stored tile)
         // RT_J records per thread are tested with their loads in flight together (one L2 latency, one barrier), then compacted in
         // index order: record i = base + j * 256 + tid, so the order is j, then warp, then lane.
-        unsigned hitmask = 0;
+        unsigned hitmask = 0, wany = 0;
 #pragma unroll
         for (int j0 = 0; j0 < RT_J; j0 += 8) {
             int4 h[8];
@@ -933,17 +941,23 @@ roi_bwd_nchw_tile_kernel(const RoiArgs a, const int4 *__restrict__ hdr, const Rt
                 const unsigned ball = __ballot_sync(0xffffffffu, hit);
                 if (lane == 0) s_wc[j0 + j][w] = (unsigned short)__popc(ball);
                 hitmask |= hit ? 1u << (j0 + j) : 0u;
+                wany |= ball ? 1u << (j0 + j) : 0u;
             }
         }
+        if (lane == 0) s_wany[w] = (unsigned short)wany;
         __syncthreads();
+        // the record groups j in which ANY warp had a hit (typically one to three of the 16): only those are compacted
+        const uint4 wa = *reinterpret_cast<const uint4 *>(s_wany);
+        unsigned jmask = wa.x | wa.y | wa.z | wa.w;
+        jmask = (jmask | (jmask >> 16)) & 0xffffu;
         int n = 0, J = RT_J;
-        for (int j = 0; j < RT_J; ++j) {
+        for (; jmask; jmask &= jmask - 1) {
+            const int j = __ffs((int)jmask) - 1;
             const uint4 wc = *reinterpret_cast<const uint4 *>(&s_wc[j][0]);      // eight 16-bit counts
             const unsigned cnt8[8] = {wc.x & 0xffffu, wc.x >> 16, wc.y & 0xffffu, wc.y >> 16, wc.z & 0xffffu, wc.z >> 16, wc.w & 0xffffu, wc.w >> 16};
             int tot = 0, off = 0;
 #pragma unroll
             for (int ww = 0; ww < RT_THREADS / 32; ++ww) { off += ww < w ? (int)cnt8[ww] : 0; tot += (int)cnt8[ww]; }
-            if (tot == 0) continue;
             if (n + tot > RT_CAP) { J = j; break; }               // block-uniform; tot <= 256 = RT_CAP, so J >= 1
             const bool hit = (hitmask >> j) & 1u;
             const unsigned ball = __ballot_sync(0xffffffffu, hit);
@@ -954,7 +968,7 @@ roi_bwd_nchw_tile_kernel(const RoiArgs a, const int4 *__restrict__ hdr, const Rt
         __syncthreads();
         // weight tables of list entries [e_lo, e_hi) into slots slot0 ..  (all threads; followed by a barrier at the caller)
         auto build_tables = [&](const int e_lo, const int e_hi, const int slot0) {
-            const int per = RT_TH * PH + RT_TW * PW;
+            const int per = RT_TH * PH + PW;
             for (int idx = tid; idx < (e_hi - e_lo) * per; idx += RT_THREADS) {
                 const int k = idx / per, q = idx - k * per;
                 const RtTap *tp = taps + (size_t)s_list[e_lo + k] * (PH + PW);
@@ -964,22 +978,18 @@ roi_bwd_nchw_tile_kernel(const RoiArgs a, const int4 *__restrict__ hdr, const Rt
                     const int yg = ty0 + yy;
                     s_rw[slot0 + k][yy][py] = t.i0 < 0 ? 0.0f : (t.i0 == yg ? 1 - t.w : 0.0f) + ((t.i1 == yg && t.i1 != t.i0) ? t.w : 0.0f);
                 } else {
-                    const int q2 = q - RT_TH * PH, xx = q2 / PW, px = q2 - xx * PW;
-                    const RtTap t = tp[PH + px];
-                    const int xg = tx0 + xx;
-                    s_cw[slot0 + k][xx][px] = t.i0 < 0 ? 0.0f : (t.i0 == xg ? 1 - t.w : 0.0f) + ((t.i1 == xg && t.i1 != t.i0) ? t.w : 0.0f);
+                    const int px = q - RT_TH * PH;
+                    RtTap t = tp[PH + px];
+                    if (t.i0 < 0) t.i0 = (short)RT_NOTAP; else { t.i0 = (short)(t.i0 - tx0); t.i1 = (short)(t.i1 - tx0); }
+                    s_ct[slot0 + k][px] = t;
                 }
             }
-            if (tid < e_hi - e_lo) {                              // the RoI's pixel columns inside this tile
-                const int4 h = __ldg(&hdr[s_list[e_lo + tid]]);
-                s_xr[slot0 + tid] = make_int2(max((h.z & 0xffff) - tx0, 0), min((h.z >> 16) - tx0, RT_TW - 1));
-            }
             __syncthreads();
-            for (int idx = tid; idx < (e_hi - e_lo) * (RT_TH + RT_TW); idx += RT_THREADS) {
-                const int k = idx / (RT_TH + RT_TW), q = idx - k * (RT_TH + RT_TW);
+            for (int idx = tid; idx < (e_hi - e_lo) * RT_TH; idx += RT_THREADS) {
+                const int k = idx / RT_TH, q = idx - k * RT_TH;
                 unsigned m = 0;
-                if (q < RT_TH) { for (int py = 0; py < PH; ++py) m |= s_rw[slot0 + k][q][py] != 0.0f ? 1u << py : 0u; s_rm[slot0 + k][q] = (unsigned char)m; }
-                else { for (int px = 0; px < PW; ++px) m |= s_cw[slot0 + k][q - RT_TH][px] != 0.0f ? 1u << px : 0u; s_cm[slot0 + k][q - RT_TH] = (unsigned char)m; }
+                for (int py = 0; py < PH; ++py) m |= s_rw[slot0 + k][q][py] != 0.0f ? 1u << py : 0u;
+                s_rm[slot0 + k][q] = (unsigned char)m;
             }
         };
         if (n == 0 && round == 0 && next >= a.R) {
@@ -1011,14 +1021,17 @@ roi_bwd_nchw_tile_kernel(const RoiArgs a, const int4 *__restrict__ hdr, const Rt
                 const int slot0 = e0 < RT_NC ? e0 : RT_NC;        // (RT_NC is a multiple of the batch size)
                 __syncthreads();                                  // the previous batch has been consumed (and s_acc is zero)
                 const int per_roi = nch * bins;
-                if (vec16) {                                      // 16-byte asynchronous copies, all in flight before the wait
-                    const int pieces = per_roi >> 2;
-                    for (int k = 0; k < nb; ++k) {
-                        const float *src = a.grad_out + ((size_t)s_list[e0 + k] * C + c0) * bins;
-                        float *dst = s_g + k * (RT_CH * bins);
-                        for (int q = tid; q < pieces; q += RT_THREADS) cp_async16(dst + 4 * q, src + 4 * q);
+                if (vec16) {                                      // one bulk copy (TMA, UBLKCP) per RoI: its chunk is contiguous
+                    if (tid == 0) {
+                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // earlier reads of s_g before the async writes
+                        const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_bar);
+                        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"((unsigned)(nb * per_roi * 4)) : "memory");
+                        for (int k = 0; k < nb; ++k) {
+                            const float *src = a.grad_out + ((size_t)s_list[e0 + k] * C + c0) * bins;
+                            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                                         :: "r"((unsigned)__cvta_generic_to_shared(s_g + k * (RT_CH * bins))), "l"(src), "r"((unsigned)(per_roi * 4)), "r"(bar) : "memory");
+                        }
                     }
-                    cp_async_commit();
                 } else {
                     for (int k = 0; k < nb; ++k) {
                         const float *src = a.grad_out + ((size_t)s_list[e0 + k] * C + c0) * bins;
@@ -1027,7 +1040,15 @@ roi_bwd_nchw_tile_kernel(const RoiArgs a, const int4 *__restrict__ hdr, const Rt
                     }
                 }
                 if (e0 >= RT_NC) build_tables(e0, e0 + nb, RT_NC);
-                if (vec16) cp_async_wait<0>();
+                if (vec16) {
+                    const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_bar);
+                    unsigned done;
+                    do {
+                        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                                     : "=r"(done) : "r"(bar), "r"(phase) : "memory");
+                    } while (!done);
+                    phase ^= 1u;
+                }
                 __syncthreads();
                 for (int k = 0; k < nb; ++k) {
                     const int sl = slot0 + k;
@@ -1035,7 +1056,6 @@ roi_bwd_nchw_tile_kernel(const RoiArgs a, const int4 *__restrict__ hdr, const Rt
                     if (rm == 0u || lane >= nch) continue;        // (the first test is warp-uniform)
                     const float *rwp = s_rw[sl][w];
                     const float *gk = s_g + k * (RT_CH * bins) + lane * bins;
-                    const int2 xr = s_xr[sl];
                     // separable, like roi_bwd_nchw_sep_kernel: T[bx] = sum over the bin rows landing on this feature row of
                     // roww * g[by][bx] once per (row, RoI, channel), then colw * T per pixel — the same weights, one rounding apart
                     // from the exact-term sum (inside the bound the tests derive)
@@ -1049,14 +1069,28 @@ roi_bwd_nchw_tile_kernel(const RoiArgs a, const int4 *__restrict__ hdr, const Rt
 #pragma unroll
                         for (int px = 0; px < RT_PMAX; ++px) if (px < PW) T[px] += rw * gp[px];
                     }
-                    for (int xx = xr.x; xx <= xr.y; ++xx) {
-                        if (s_cm[sl][xx] == 0u) continue;
-                        const float *cwp = s_cw[sl][xx];
-                        float v = 0.0f;
+                    // bin columns left to right: a bin adds (1 - w) * T to pixel i0 and w * T to pixel i1 = i0 + 1; a0 / a1 collect the
+                    // sums of pixels pc and pc + 1 and go to the accumulator when the walk leaves them (all of it warp-uniform)
+                    float *arow = s_acc + (w * RT_TW) * RT_APITCH + lane;
+                    int pc = RT_NOTAP; float a0 = 0.0f, a1 = 0.0f;
+                    auto flush = [&](const int p, const float v) { if (p >= 0 && p < RT_TW) arow[p * RT_APITCH] += v; };
 #pragma unroll
-                        for (int px = 0; px < RT_PMAX; ++px) if (px < PW) v += cwp[px] * T[px];
-                        s_acc[(w * RT_TW + xx) * RT_APITCH + lane] += v;
+                    for (int px = 0; px < RT_PMAX; ++px) {
+                        if (px >= PW) continue;
+                        const RtTap t = s_ct[sl][px];
+                        if (t.i0 == RT_NOTAP) continue;
+                        if (t.i0 != pc) {
+                            flush(pc, a0);
+                            if (t.i0 == pc + 1) { a0 = a1; }
+                            else { flush(pc + 1, a1); a0 = 0.0f; }
+                            a1 = 0.0f;
+                            pc = t.i0;
+                        }
+                        a0 += (1 - t.w) * T[px];
+                        if (t.i1 != t.i0) a1 += t.w * T[px];
                     }
+                    flush(pc, a0);
+                    flush(pc + 1, a1);
                 }
             }
             __syncthreads();

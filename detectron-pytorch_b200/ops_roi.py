@@ -12,9 +12,9 @@ from .ops import _ws, POOL, ROI_BIN_CENTRE, ROI_CROP_NORM, ROI_GRID_POINT, _coun
 import os
 
 # The tile-centric dense backward (detbox_roi_align_backward_tiled: every gradient map written once, deterministic summation
-# order, 1.6 GB of DRAM traffic instead of 2.9 GB at BASELINE configs[2]) runs at the scatter kernels' speed on B200 (0.76 ms
-# both), so the scatter path stays the default; roi_align_backward(..., deterministic=True) or DETBOX_ROI_BWD_TILED=1 selects it.
-_TILED_BWD = os.environ.get("DETBOX_ROI_BWD_TILED") is not None
+# order, 1.6 GB of DRAM traffic instead of 2.9 GB at BASELINE configs[2], 0.61 ms against 0.77 ms for memset + scatter on B200) is
+# the default where it applies; roi_align_backward(..., deterministic=False) or DETBOX_ROI_BWD_NOTILED=1 selects the scatter kernels.
+_TILED_BWD = os.environ.get("DETBOX_ROI_BWD_NOTILED") is None
 tiled_backward_calls = 0          # how often the tiled entry point ran (tests check that it really took a configuration)
 
 
@@ -130,9 +130,9 @@ def roi_align_backward(grad_out, feat_shapes, rois, spatial_scales, mode=ROI_BIN
     case it is accumulated into).  grad_out [R, C(or L*C), ph, pw] in the same memory format as the
     features.  pool='avg'|'max' differentiates the fused 2x2 pool of RoIAlignAvg/Max as well
     ('max' needs `feats`, the forward's feature maps, to recompute the arg-max).  Returns the list
-    of gradient maps.  deterministic=True: the tile-centric dense kernel where it applies (NCHW, bin-centre / crop mode, no
-    pool, pooled size <= 8 x 8, `grads` not given) — bit-identical results from run to run, unlike the atomics of the
-    reference and of the default path."""
+    of gradient maps.  The tile-centric dense kernel runs where it applies (NCHW, bin-centre / crop mode, no pool, pooled
+    size <= 8 x 8, `grads` not given) — bit-identical results from run to run, unlike the atomics of the reference and of
+    the scatter kernels; deterministic=False forces the scatter path, deterministic=True requires nothing more than the default."""
     r = _dev(rois).view(-1, 5)
     dev = r.device
     g = grad_out

@@ -336,9 +336,10 @@ def test_nchw_staged_backward_opt_in_subprocess():
         "    gi = detbox.roi_align_backward(T.cu(g), [feat_shape], T.cu(rois), [0.25], m)[0].cpu().numpy()\n"
         "    T.assert_bwd_within_bound(gi, bwd(g, rois, np.float32(0.25), feat_shape), T.tap_stats(rois, 0.25, 7, 7, feat_shape, mode, g), float(np.abs(g).max()))\n"
         "print('staged backward ok')\n" % (root, os.path.join(root, "tests")))
-    # (DETBOX_ROI_BWD_TILED=1 makes the tile-centric dense backward the default where it applies — it has a test of its own below)
-    for var in ("DETBOX_ROI_BWD_STAGED", "DETBOX_ROI_BWD_DIRECT", "DETBOX_ROI_BWD_GATHER", "DETBOX_ROI_BWD_TILED"):
-        env = dict(os.environ, **{var: "1"})
+    # (DETBOX_ROI_BWD_NOTILED=1: without it the bin-centre case takes the tile-centric dense backward, which has a test of
+    #  its own below; alone it selects the separable scatter kernel)
+    for var in ("DETBOX_ROI_BWD_STAGED", "DETBOX_ROI_BWD_DIRECT", "DETBOX_ROI_BWD_GATHER", "DETBOX_ROI_BWD_NOTILED"):
+        env = dict(os.environ, **{var: "1", "DETBOX_ROI_BWD_NOTILED": "1"})
         r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
         assert r.returncode == 0 and "staged backward ok" in r.stdout, var + "\n" + r.stdout + r.stderr
 
@@ -359,7 +360,7 @@ def _bwd_both(g, shapes, rois, scales, mode, **kw):
 
 @pytest.mark.parametrize("case", ["pyramid_odd", "tiny_rois", "crowded_tile", "crop_norm", "no_rois", "partial_chunk"])
 def test_tiled_backward(case):
-    """detbox_roi_align_backward_tiled (roi_align_backward(deterministic=True): NCHW / bin-centre or normalised crop / no pool):
+    """detbox_roi_align_backward_tiled (the default for NCHW / bin-centre or normalised crop / no pool / pooled size <= 8 x 8):
     every gradient map written once, tile by tile.  Against the float64-derived bound of the oracle (crop_and_resize.c:207-268) and against the
     scatter kernels; map sizes that are not multiples of the 8 x 32 tile, RoIs smaller than their 7 x 7 bins (more than two
     bin columns per pixel: the generic column loop), more RoIs on one tile than one list round holds (accumulating rounds),
