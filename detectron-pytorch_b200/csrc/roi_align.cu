@@ -1012,6 +1012,20 @@ roi_bwd_nchw_tile_kernel(const RoiArgs a, const int4 *__restrict__ hdr, const Rt
         //      shared memory ([pixel][33]: conflict-free for lane = channel here and for lane = pixel in the store below).
         //      (First version: lanes = pixels, accumulators in registers — 12.7 of 32 lanes active on pedestrian-shaped RoIs
         //      4-5 pixels wide, 2.0 G warp instructions, 4.1 ms; second: dense weight tables scanned per pixel, 0.85 G, 1.7 ms.)
+        // grad_out of list entries [e0, e0 + nb) for the chunk at c0 -> s_g: one bulk copy (TMA, UBLKCP) per RoI, its chunk is contiguous
+        auto issue = [&](const int c0x, const int e0x) {
+            if (tid != 0) return;
+            const int bytes = min(RT_CH, C - c0x) * bins * 4, nbx = min(nb_max, n - e0x);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");         // earlier reads of s_g before the async writes
+            const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_bar);
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"((unsigned)(nbx * bytes)) : "memory");
+            for (int k = 0; k < nbx; ++k) {
+                const float *src = a.grad_out + ((size_t)s_list[e0x + k] * C + c0x) * bins;
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                             :: "r"((unsigned)__cvta_generic_to_shared(s_g + k * (RT_CH * bins))), "l"(src), "r"((unsigned)bytes), "r"(bar) : "memory");
+            }
+        };
+        bool pre = false;                                         // the first batch of the coming chunk is already in flight
         for (int c0 = 0; c0 < C; c0 += RT_CH) {
             const int nch = min(RT_CH, C - c0);
             __syncthreads();                                      // s_acc of the previous chunk has been stored; tables are built
@@ -1021,17 +1035,9 @@ roi_bwd_nchw_tile_kernel(const RoiArgs a, const int4 *__restrict__ hdr, const Rt
                 const int slot0 = e0 < RT_NC ? e0 : RT_NC;        // (RT_NC is a multiple of the batch size)
                 __syncthreads();                                  // the previous batch has been consumed (and s_acc is zero)
                 const int per_roi = nch * bins;
-                if (vec16) {                                      // one bulk copy (TMA, UBLKCP) per RoI: its chunk is contiguous
-                    if (tid == 0) {
-                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // earlier reads of s_g before the async writes
-                        const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_bar);
-                        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"((unsigned)(nb * per_roi * 4)) : "memory");
-                        for (int k = 0; k < nb; ++k) {
-                            const float *src = a.grad_out + ((size_t)s_list[e0 + k] * C + c0) * bins;
-                            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                                         :: "r"((unsigned)__cvta_generic_to_shared(s_g + k * (RT_CH * bins))), "l"(src), "r"((unsigned)(per_roi * 4)), "r"(bar) : "memory");
-                        }
-                    }
+                if (vec16) {
+                    if (!(pre && e0 == 0)) issue(c0, e0);
+                    pre = false;
                 } else {
                     for (int k = 0; k < nb; ++k) {
                         const float *src = a.grad_out + ((size_t)s_list[e0 + k] * C + c0) * bins;
@@ -1094,6 +1100,8 @@ roi_bwd_nchw_tile_kernel(const RoiArgs a, const int4 *__restrict__ hdr, const Rt
                 }
             }
             __syncthreads();
+            // the next chunk's first batch is requested now: its L2 latency passes behind this chunk's store and the zeroing
+            if (vec16 && n > 0 && c0 + RT_CH < C) { issue(c0 + RT_CH, 0); pre = true; }
             if (round == 0 && vecst) {
                 // four pixels x one channel per store: lane = (channel offset 0..3, pixel quad 0..7); the four shared-memory reads
                 // of a quad hit banks (x + ch) % 32, distinct across the warp
