@@ -78,3 +78,30 @@ def test_ops_refuse_cpu_tensors():
         detbox.nms(torch.zeros(3, 4), torch.zeros(3), 0.5)
     with pytest.raises(detbox.DetboxError):
         detbox.bbox_overlaps(torch.zeros(3, 4, dtype=torch.float64), torch.zeros(2, 4, dtype=torch.float64))
+
+
+def test_tiled_roi_backward_rejects_what_it_does_not_cover():
+    """detbox_roi_align_backward_tiled decides from the configuration alone (before any CUDA call) whether it takes a case;
+    DETBOX_ERR_UNSUPPORTED (-4) tells the caller to use detbox_roi_align_backward.  Workspace: 16 + 8 * (ph + pw) bytes per RoI,
+    each array rounded up to 256 bytes."""
+    L = detbox.lib()
+
+    def cfg(**kw):
+        c = _lib.RoiCfg()
+        c.n_levels, c.batch, c.channels, c.pooled_h, c.pooled_w = 1, 2, 8, 7, 7
+        c.grad_feat[0], c.height[0], c.width[0], c.spatial_scale[0] = 0x1000, 16, 32, 0.25      # never dereferenced here
+        c.mode = detbox.ROI_BIN_CENTRE
+        for k, v in kw.items():
+            setattr(c, k, v)
+        return c
+
+    def call(c, R=4):
+        return L.detbox_roi_align_backward_tiled(ctypes.byref(c), 0x2000, R, None, 0x3000, None, 0, None)
+
+    for bad in (dict(layout=1, out_layout=1), dict(mode=detbox.ROI_GRID_POINT), dict(all_levels=1), dict(pooled_h=14, pooled_w=14),
+                dict(mode=detbox.ROI_GRID_POINT, pool=1)):
+        assert call(cfg(**bad)) == -4, bad
+    assert call(cfg()) == -2                     # covered, but no workspace was given: DETBOX_ERR_WORKSPACE, still before any launch
+    assert call(cfg(), R=-1) == -1               # DETBOX_ERR_INVALID
+    up = lambda v: (v + 255) // 256 * 256
+    assert L.detbox_roi_align_backward_tiled_workspace_bytes(ctypes.byref(cfg()), 1000) == up(1000 * 16) + up(1000 * 14 * 8)
